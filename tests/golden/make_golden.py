@@ -1,0 +1,124 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (imported from /root/reference).
+
+Run in the build container only:   python tests/golden/make_golden.py
+The reference cannot travel to the GPU box, so its outputs are committed as small fixtures.
+Inputs are regenerated at test time from oracle.synth (seeded numpy RNG); the fixtures hold the
+reference's OUTPUTS: per-step losses, final parameters (small cases) or per-tensor checksums
+(real-dimension cases), sampled indices, LR sequences.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import refimport, synth  # noqa: E402
+from oracle.buffer import slice_row  # noqa: E402
+from oracle.steps import dims  # noqa: E402
+
+torch.set_num_threads(1)  # fixtures must not depend on the thread count of the build box
+
+
+def checksum(sd):
+    out = {}
+    for k, v in sd.items():
+        v = v.detach().double().flatten()
+        out[k] = np.array([v.sum().item(), v.abs().sum().item(), *v[:6].tolist()])
+    return out
+
+
+def flat(prefix, d):
+    return {f"{prefix}/{k}": (v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in d.items()}
+
+
+def run_agent(kind, S, H, B, steps, max_steps, seed, A=2, tau=0.9, alpha=10.0, full=True):
+    args = dims(S, H, 2, False, 256, A)
+    cls = refimport.por_cls() if kind == "por" else refimport.sorl_cls()
+    agent = cls(args, max_steps=max_steps, tau=tau, alpha=alpha)
+    agent.load_state_dict(synth.det_state_dict(agent, seed))
+    rows = torch.from_numpy(synth.laser_rows(B * steps, S, seed + 1, A))
+    losses = []
+    for i in range(steps):
+        b = slice_row(rows[i * B:(i + 1) * B], S, A)
+        if kind == "por":
+            losses.append(agent.por_residual_update(b["observations"], b["next_observations"], b["rewards"], b["terminals"]))
+        else:
+            losses.append(agent.update(b["observations"], b["actions"], b["rewards"], b["next_observations"], b["terminals"]))
+    sched = agent.goal_lr_schedule if kind == "por" else agent.lr_schedule
+    out = dict(meta=np.array([S, H, B, steps, max_steps, seed, A]), hyper=np.array([tau, alpha]),
+               losses=np.array(losses, np.float64), last_lr=np.array(sched.get_last_lr(), np.float64))
+    out.update(flat("final", agent.state_dict()) if full else flat("sum", checksum(agent.state_dict())))
+    return out
+
+
+def run_cql(S, A, B, n_rows, iters, freq, seed):
+    t = refimport.make_cql_trainer(S, A, update_target_freq=freq)
+    t.q_network.load_state_dict(synth.det_state_dict(t.q_network, seed))
+    t.target_network.load_state_dict(t.q_network.state_dict())
+    t.batch_size = B
+    rows = synth.laser_rows(n_rows, S, seed + 1)
+    acts = synth.discrete_actions(n_rows, A, seed + 2)
+    b = slice_row(rows, S)
+    for i in range(n_rows):
+        t.replay_buffer.push(b["observations"][i], acts[i], b["rewards"][i], b["next_observations"][i], bool(b["terminals"][i]))
+    np.random.seed(seed + 3)
+    state = np.random.get_state()
+    idx = [np.random.choice(n_rows, B, replace=False) for _ in range(iters)]
+    np.random.set_state(state)
+    losses = t.train_offline(num_iterations=iters)
+    out = dict(meta=np.array([S, A, B, n_rows, iters, freq, seed]), losses=np.array(losses, np.float64), indices=np.stack(idx))
+    out.update(flat("q", t.q_network.state_dict()))
+    out.update(flat("target", t.target_network.state_dict()))
+    return out
+
+
+def run_buffer(seed):
+    RB = refimport.replay_buffer_cls()
+    rb = RB(50, (7,), torch.device("cpu"))
+    rng = np.random.RandomState(seed)
+    for i in range(70):  # wraps the ring
+        rb.push(rng.rand(7).astype(np.float32), int(rng.randint(5)), float(rng.randn()), rng.rand(7).astype(np.float32), bool(rng.rand() < 0.2))
+    np.random.seed(seed)
+    s, a, r, s2, d = rb.sample(16)
+    return dict(seed=np.array(seed), states=s.numpy(), actions=a.numpy(), rewards=r.numpy(), next_states=s2.numpy(), dones=d.numpy(),
+                size=np.array(len(rb)), position=np.array(rb.position))
+
+
+def run_cosine(base, t_max, n):
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.Adam([p], lr=base)
+    sch = torch.optim.lr_scheduler.CosineAnnealingLR(opt, t_max)
+    lrs = []
+    for _ in range(n):
+        lrs.append(opt.param_groups[0]["lr"])
+        opt.step()
+        sch.step()
+    return dict(base=np.array(base), t_max=np.array(t_max), lrs=np.array(lrs, np.float64))
+
+
+def main():
+    assert refimport.available(), "needs /root/reference"
+    cases = {
+        "por_small": run_agent("por", 22, 32, 16, 5, 3, 11),
+        "sorl_small": run_agent("sorl", 22, 32, 16, 5, 3, 12),
+        "sorl_small_tau5": run_agent("sorl", 22, 32, 16, 3, 1000, 13, tau=0.5, alpha=3.0),
+        "por_real": run_agent("por", 365, 1024, 64, 2, 1000, 21, full=False),
+        "sorl_real": run_agent("sorl", 362, 512, 64, 2, 1000, 22, full=False),
+        "cql_small": run_cql(22, 5, 16, 200, 5, 2, 31),
+        "cql_real": run_cql(362, 5, 64, 500, 3, 10, 32),
+        "replay_buffer": run_buffer(41),
+        "cosine_lr": run_cosine(1e-4, 4, 14),
+    }
+    for name, d in cases.items():
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, **d)
+        print(f"{name}: {os.path.getsize(path) / 1024:.1f} KiB")
+
+
+if __name__ == "__main__":
+    main()
