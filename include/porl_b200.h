@@ -1,0 +1,223 @@
+/* porl_b200.h -- C ABI of libporl_b200.so: the B200 (sm_100a) offline-RL update step of porl.
+ *
+ * The reference (hadleyhzy34/porl) has no FFI for this path: it is eager PyTorch called from
+ * Python agents.  This header is therefore the boundary a maintainer binds with ctypes from the
+ * reference's own classes.  Each entry point cites the reference code it
+ * replaces, paths relative to the reference root.
+ *
+ * Conventions
+ *   - every function returns an int status (PORL_OK or a negative PORL_ERR_*), never throws;
+ *     porl_last_error() gives the thread-local message of the last failure;
+ *   - all tensors are caller-owned DEVICE pointers (fp32 unless stated), row-major; `ld*` are
+ *     leading dimensions in elements; pointers handed to the GEMM paths must be 16-byte aligned
+ *     and their leading dimensions multiples of 4 (the host side pads widths to PORL_PAD);
+ *   - work is enqueued on the caller's stream (a cudaStream_t passed as void*) and is
+ *     asynchronous: no call synchronises the device;
+ *   - there is NO CPU fallback: every call fails with PORL_ERR_CUDA when no sm_100 device exists.
+ */
+#ifndef PORL_B200_H
+#define PORL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PORL_VERSION 100          /* 0.1.0 */
+#define PORL_PAD 32               /* feature widths are padded to this many floats in HBM */
+#define PORL_MAX_LAYERS 6         /* linear layers per MLP */
+#define PORL_MAX_CALLS 4          /* MLP evaluations merged into one grouped launch sequence */
+
+enum {
+  PORL_OK = 0,
+  PORL_ERR_INVALID = -1,          /* bad argument (shape, alignment, null pointer) */
+  PORL_ERR_CUDA = -2,             /* CUDA runtime / driver error, message in porl_last_error() */
+  PORL_ERR_UNSUPPORTED = -3,      /* valid request this build cannot serve */
+  PORL_ERR_WORKSPACE = -4         /* internal workspace too small for the request */
+};
+
+/* bits of the device status word (porl_ctx_status_ptr): set by kernels, read by the host when it
+ * reads the losses back.  Replaces the reference's pdb traps (agent/por.py:104-105). */
+enum {
+  PORL_FLAG_NONFINITE_LOSS = 1,   /* a loss became NaN/Inf */
+  PORL_FLAG_NONPOSITIVE_NLL = 2,  /* some per-sample NLL <= 0: where agent/por.py:104 drops into pdb */
+  PORL_FLAG_BAD_INDEX = 4,        /* gather index outside [0, n_rows) (clamped) */
+  PORL_FLAG_BAD_ACTION = 8        /* discrete action outside [0, A) (clamped) */
+};
+
+typedef struct porl_ctx porl_ctx_t;
+typedef struct porl_mlp porl_mlp_t;
+typedef void* porl_stream_t;      /* cudaStream_t */
+
+/* ---- context ------------------------------------------------------------------------------- */
+int porl_version(void);
+const char* porl_last_error(void);
+int porl_ctx_create(porl_ctx_t** out, int device);
+int porl_ctx_destroy(porl_ctx_t* ctx);
+/* kernels launched through this context so far (bench.py's gpu_launches) */
+int64_t porl_launch_count(const porl_ctx_t* ctx);
+/* device address of the 32-bit status word (PORL_FLAG_*), for an async read-back with the losses */
+int porl_ctx_status_ptr(porl_ctx_t* ctx, uint32_t** out);
+/* 0 = fp32 FFMA contractions ("exact" mode); 1 = tcgen05 3xTF32 split contractions where shapes allow */
+int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
+int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
+
+/* ---- per-kernel timing (bench.py's roofline leg) --------------------------------------------- */
+/* While enabled, every launch is bracketed by CUDA events on its own stream and attributed to a
+ * category together with its ALGORITHMIC work (flops for contractions, bytes for the HBM-bound
+ * kernels).  porl_profile_read synchronises the recorded events and returns per-category sums. */
+enum { PORL_CAT_CONTRACTION = 0, PORL_CAT_GATHER = 1, PORL_CAT_LOSS = 2, PORL_CAT_OPTIMIZER = 3,
+       PORL_CAT_NORM = 4, PORL_CAT_COUNT = 5 };
+typedef struct {
+  int64_t launches[PORL_CAT_COUNT];
+  double ms[PORL_CAT_COUNT];       /* sum of per-launch device durations */
+  double work[PORL_CAT_COUNT];     /* flops (contraction) or bytes (others) */
+} porl_profile_t;
+int porl_profile_enable(porl_ctx_t* ctx, int enable);   /* enabling clears earlier records */
+int porl_profile_read(porl_ctx_t* ctx, porl_profile_t* out);
+
+/* ---- K1: minibatch gather from the HBM-resident dataset ----------------------------------- */
+/* out[b, 0:row_len] = table[idx[b], 0:row_len]; bit-exact.
+ * Replaces DataLoader collate over CustomDataset.__getitem__ (dataloader/dataloader.py:34-52,
+ * por_train.py:59-63,71-72). */
+int porl_gather_rows_f32(porl_ctx_t* ctx, const float* table, int64_t n_rows, int64_t row_stride,
+                         int64_t row_len, const int64_t* idx, int64_t B, float* out,
+                         int64_t out_stride, porl_stream_t stream);
+/* Gather AoS rows [obs(S) | r | next_obs(S) | done | action(A)] straight into the padded SoA
+ * minibatch the update consumes: obs/next_obs (B, ld_obs) with columns S..ld_obs-1 zeroed,
+ * rewards (B), dones (B), actions (B, ld_act).  Fuses the gather with the column slicing of
+ * por_train.py:74-78 / sorl_train.py:54-58; payload bit-exact. */
+int porl_gather_transitions(porl_ctx_t* ctx, const float* table, int64_t n_rows, int64_t row_stride,
+                            int32_t S, int32_t A, const int64_t* idx, int64_t B, float* obs,
+                            float* next_obs, int64_t ld_obs, float* rewards, float* dones,
+                            float* actions, int64_t ld_act, porl_stream_t stream);
+/* SoA replay-buffer gather: the five fancy-index gathers of ReplayBuffer.sample
+ * (src/porl/buffer/replaybuffer.py:64-70).  states/next_states (cap, ld_state) -> (B, ld_out)
+ * with columns S..ld_out-1 zeroed; actions int64; bit-exact. */
+int porl_gather_soa(porl_ctx_t* ctx, const float* states, const float* next_states,
+                    const int64_t* actions, const float* rewards, const float* dones, int64_t cap,
+                    int32_t S, int64_t ld_state, const int64_t* idx, int64_t B, float* out_states,
+                    float* out_next_states, int64_t ld_out, int64_t* out_actions,
+                    float* out_rewards, float* out_dones, porl_stream_t stream);
+/* (B, n) strided rows -> (B, ld_out) padded rows, pad columns zeroed (packs tensors a caller
+ * passes to agent.update() into the layout the contractions need). */
+int porl_pack_rows(porl_ctx_t* ctx, const float* src, int64_t ld_src, int64_t B, int32_t n,
+                   float* dst, int64_t ld_dst, porl_stream_t stream);
+
+/* ---- K2/K3: fused MLP forward / backward --------------------------------------------------- */
+/* util/util.py:29-47 mlp(): Linear[+LayerNorm]+ReLU per hidden layer, Linear[+Tanh] head.
+ * n_nets > 1 evaluates structurally identical nets side by side on one input (TwinV.both,
+ * agent/value_functions.py:31-39). */
+typedef struct {
+  int32_t n_nets;
+  int32_t n_layers;                       /* linear layers */
+  int32_t dims[PORL_MAX_LAYERS + 1];      /* dims[0] = input width ... dims[n_layers] = output width */
+  int32_t layer_norm;                     /* LayerNorm after every hidden Linear (eps 1e-5) */
+  int32_t out_act;                        /* 0 none, 1 tanh (BoundedGaussianPolicy, agent/policy.py:38-39) */
+} porl_mlp_desc_t;
+
+enum { PORL_PARAM_WEIGHT = 0, PORL_PARAM_BIAS = 1, PORL_PARAM_LN_WEIGHT = 2, PORL_PARAM_LN_BIAS = 3 };
+
+int porl_mlp_create(porl_ctx_t* ctx, const porl_mlp_desc_t* desc, porl_mlp_t** out);
+int porl_mlp_destroy(porl_mlp_t* mlp);
+/* floats of the flat parameter (and gradient, and Adam moment) buffer of all n_nets nets */
+int64_t porl_mlp_param_floats(const porl_mlp_t* mlp);
+/* where tensor (net, layer, kind) lives in the flat buffer: offset in floats and, for weights,
+ * the leading dimension (input width padded to PORL_PAD; pad columns stay zero). */
+int porl_mlp_param_layout(const porl_mlp_t* mlp, int32_t net, int32_t layer, int32_t kind,
+                          int64_t* offset, int64_t* ld);
+/* floats of the saved-activation buffer a training forward at batch B needs */
+int64_t porl_mlp_saved_floats(const porl_mlp_t* mlp, int64_t B);
+/* padded leading dimension of the output rows, per net: out is (n_nets, B, ld_out) */
+int64_t porl_mlp_out_ld(const porl_mlp_t* mlp);
+
+typedef struct {
+  porl_mlp_t* mlp;
+  const float* params;    /* flat parameters */
+  const float* x;         /* (B, ldx) input, pad columns zero */
+  int64_t ldx;
+  float* saved;           /* porl_mlp_saved_floats(B) floats; a training forward keeps the activations
+                             here for porl_mlp_backward, an inference forward uses it as scratch */
+  float* out;             /* (n_nets, B, ld_out) */
+} porl_mlp_call_t;
+
+/* Forward of up to PORL_MAX_CALLS MLPs on the same batch size; layer l of every call runs in one
+ * grouped launch.  Replaces TwinV.both/forward, GaussianPolicy.net, QNetwork.forward. */
+int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp_call_t* calls, int64_t B,
+                     porl_stream_t stream);
+/* Backward of one MLP: dout (n_nets, B, ld_out) is the loss gradient w.r.t. the PRE-activation head
+ * output (the loss kernels fold tanh'), grads gets dW/db in the flat layout (every element
+ * written, no accumulation).  dout and `saved` are consumed (overwritten).  Replaces autograd of
+ * the nets (agent/por.py:89,108; agent/sorl.py:94,111; src/porl/train/cql_trainer.py:112). */
+int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, int64_t B, float* dout,
+                      float* grads, porl_stream_t stream);
+
+/* ---- K4: TD target + twin expectile loss (agent/por.py:15-17,85-87; agent/sorl.py:90-92) --- */
+/* target = r + (1-done)*gamma*min(nv1,nv2); loss = sum_k sum_i |tau-1[u<0]|u^2 / (2*B_norm),
+ * u = target - v_k; dv_k = -|tau-1[u<0]| u / B_norm.  B_norm is the GLOBAL batch (B * world).
+ * loss_out[0] is overwritten. */
+int porl_expectile_twin_loss(porl_ctx_t* ctx, const float* v1, const float* v2, const float* nv1,
+                             const float* nv2, int64_t ldv, const float* rewards, const float* dones,
+                             float gamma, float tau, int64_t B, int64_t B_norm, float* target_v,
+                             float* dv1, float* dv2, float* loss_out, porl_stream_t stream);
+
+/* ---- K5: advantage-weighted diagonal-Gaussian NLL (agent/por.py:97-106; agent/sorl.py:102-109;
+ *          agent/policy.py:18-23,42-49) ------------------------------------------------------- */
+enum { PORL_AWR_POR = 0 /* w = exp(adv/alpha) */, PORL_AWR_SORL = 1 /* w = exp(alpha*adv) */ };
+/* v = min(v1n, v2n); w = min(exp(..), 100); nll_i = 1/2 sum_j z_ij^2 + sum_j ls_j + D/2 log 2pi,
+ * z = (x-mean)/exp(ls), ls = clamp(log_std,-5,2); loss = sum_i w_i nll_i / B_norm.
+ * dz_out (B, ld_mean): gradient w.r.t. the pre-activation mean (times 1-mean^2 when tanh_out);
+ * dlog_std (D) overwritten; loss_out[0] overwritten. */
+int porl_awr_gauss_nll(porl_ctx_t* ctx, const float* mean, int64_t ld_mean, const float* log_std,
+                       const float* x, int64_t ld_x, const float* target_v, const float* v1n,
+                       const float* v2n, int64_t ldv, float alpha, int32_t mode, int32_t tanh_out,
+                       int64_t B, int32_t D, int64_t B_norm, float* dz_out, float* dlog_std,
+                       float* loss_out, porl_stream_t stream);
+
+/* ---- K6: discrete CQL head (src/porl/train/cql_trainer.py:72-86,94-108) -------------------- */
+/* t = r + gamma*max_a qn*(1-done); td = mean (q[a]-t)^2; pen = mean(logsumexp(q) - log A - q[a]);
+ * loss = td + alpha*pen; dq = (2/Bn)(q[a]-t)1[a] + (alpha/Bn)(softmax(q) - 1[a]).
+ * losses_out[0..2] = loss, td, penalty (overwritten). */
+int porl_cql_head(porl_ctx_t* ctx, const float* q, const float* q_next_tgt, int64_t ldq,
+                  const int64_t* actions, const float* rewards, const float* dones, float gamma,
+                  float alpha, int64_t B, int32_t A, int64_t B_norm, float* dq, float* losses_out,
+                  porl_stream_t stream);
+
+/* ---- K7: fused Adam (+ Polyak / hard target update) ---------------------------------------- */
+/* Device-resident optimizer state so that a captured CUDA graph can be replayed: the step
+ * counter and the (optionally cosine-annealed) learning rate advance on the device. */
+typedef struct {
+  int64_t step;          /* updates applied so far (t of the next step is step+1) */
+  double lr;             /* learning rate the NEXT step uses */
+  double base_lr;
+  int64_t t_max;         /* > 0: torch CosineAnnealingLR(T_max=t_max, eta_min=0), recursive form */
+  uint32_t blocks_done;  /* internal */
+  uint32_t pad_;
+} porl_opt_state_t;
+
+/* torch.optim.Adam.step (beta1 .9, beta2 .999, eps 1e-8 defaults passed explicitly; single-tensor
+ * formula of torch/optim/adam.py) over a flat buffer of n floats, then optionally
+ *   ema_beta > 0 : target = (1-ema_beta)*target + ema_beta*p   (util/util.py:54-56), or
+ *   hard_every > 0 : target = p when (step % hard_every == 0) after the step
+ *                    (src/porl/train/dqn_trainer.py:195-196),
+ * then advances *state (step += 1, cosine LR recursion: agent/por.py:65,110). */
+int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* m, float* v, int64_t n,
+                   porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
+                   float ema_beta, int32_t hard_every, porl_stream_t stream);
+
+/* ---- low-level contraction (exposed for tests and profiling) ------------------------------- */
+/* C[M,N] = opA(A)[M,K] * opB(B)[K,N] (+ bias[n]) with epilogue; trans flags:
+ *   a_kmajor: A(m,k) = A[m*lda+k] else A[k*lda+m];  b_kmajor: B(k,n) = B[n*ldb+k] else B[k*ldb+n].
+ * epilogue: 0 none, 1 relu, 2 tanh; relu_src (M, ld_relu): zero C where relu_src <= 0.
+ * n_store >= N: columns N..n_store-1 of C are written as zeros.  colsum (M): sum_k A(m,k), or NULL. */
+int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, int64_t M, int64_t N, int64_t K,
+              const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+              const float* bias, int32_t epilogue, const float* relu_src, int64_t ld_relu,
+              int64_t n_store, float* colsum, porl_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PORL_B200_H */

@@ -1,0 +1,185 @@
+"""ctypes binding of libporl_b200.so (the C ABI declared in include/porl_b200.h).
+
+No CPU fallback: importing this module without the built library raises, and creating a
+context without an sm_100 device raises PorlError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libporl_b200.so")
+
+PAD = 32
+MAX_LAYERS = 6
+MAX_CALLS = 4
+
+FLAG_NONFINITE_LOSS = 1
+FLAG_NONPOSITIVE_NLL = 2
+FLAG_BAD_INDEX = 4
+FLAG_BAD_ACTION = 8
+
+AWR_POR, AWR_SORL = 0, 1
+PARAM_WEIGHT, PARAM_BIAS, PARAM_LN_WEIGHT, PARAM_LN_BIAS = 0, 1, 2, 3
+
+
+class PorlError(RuntimeError):
+    pass
+
+
+class MlpDesc(C.Structure):
+    _fields_ = [("n_nets", C.c_int32), ("n_layers", C.c_int32), ("dims", C.c_int32 * (MAX_LAYERS + 1)),
+                ("layer_norm", C.c_int32), ("out_act", C.c_int32)]
+
+
+class MlpCall(C.Structure):
+    _fields_ = [("mlp", C.c_void_p), ("params", C.c_void_p), ("x", C.c_void_p), ("ldx", C.c_int64),
+                ("saved", C.c_void_p), ("out", C.c_void_p)]
+
+
+class OptState(C.Structure):
+    _fields_ = [("step", C.c_int64), ("lr", C.c_double), ("base_lr", C.c_double), ("t_max", C.c_int64),
+                ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
+
+
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm")
+
+
+class Profile(C.Structure):
+    _fields_ = [("launches", C.c_int64 * 5), ("ms", C.c_double * 5), ("work", C.c_double * 5)]
+
+
+_p, _i32, _i64, _f = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+_SIGNATURES = {
+    "porl_version": (C.c_int, []),
+    "porl_last_error": (C.c_char_p, []),
+    "porl_ctx_create": (C.c_int, [C.POINTER(_p), C.c_int]),
+    "porl_ctx_destroy": (C.c_int, [_p]),
+    "porl_launch_count": (_i64, [_p]),
+    "porl_ctx_status_ptr": (C.c_int, [_p, C.POINTER(_p)]),
+    "porl_ctx_set_gemm_mode": (C.c_int, [_p, C.c_int]),
+    "porl_ctx_get_gemm_mode": (C.c_int, [_p]),
+    "porl_profile_enable": (C.c_int, [_p, C.c_int]),
+    "porl_profile_read": (C.c_int, [_p, C.POINTER(Profile)]),
+    "porl_gather_rows_f32": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p, _i64, _p]),
+    "porl_gather_transitions": (C.c_int, [_p, _p, _i64, _i64, _i32, _i32, _p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _p]),
+    "porl_gather_soa": (C.c_int, [_p, _p, _p, _p, _p, _p, _i64, _i32, _i64, _p, _i64, _p, _p, _i64, _p, _p, _p, _p]),
+    "porl_pack_rows": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p]),
+    "porl_mlp_create": (C.c_int, [_p, C.POINTER(MlpDesc), C.POINTER(_p)]),
+    "porl_mlp_destroy": (C.c_int, [_p]),
+    "porl_mlp_param_floats": (_i64, [_p]),
+    "porl_mlp_param_layout": (C.c_int, [_p, _i32, _i32, _i32, C.POINTER(_i64), C.POINTER(_i64)]),
+    "porl_mlp_saved_floats": (_i64, [_p, _i64]),
+    "porl_mlp_out_ld": (_i64, [_p]),
+    "porl_mlp_forward": (C.c_int, [_p, _i32, C.POINTER(MlpCall), _i64, _p]),
+    "porl_mlp_backward": (C.c_int, [_p, C.POINTER(MlpCall), _i64, _p, _p, _p]),
+    "porl_expectile_twin_loss": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _p, _f, _f, _i64, _i64, _p, _p, _p, _p, _p]),
+    "porl_awr_gauss_nll": (C.c_int, [_p, _p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _f, _i32, _i32, _i64, _i32, _i64,
+                                     _p, _p, _p, _p]),
+    "porl_cql_head": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _f, _f, _i64, _i32, _i64, _p, _p, _p]),
+    "porl_adam_step": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
+    "porl_gemm": (C.c_int, [_p, _i32, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p, _i64,
+                            _i64, _p, _p]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m porl_b200.build` "
+            "(porl_b200 has no CPU or PyTorch fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype, fn.argtypes = res, args
+    return lib
+
+
+lib = _load()
+
+
+def check(status: int) -> None:
+    if status != 0:
+        raise PorlError(f"libporl_b200 error {status}: {lib.porl_last_error().decode(errors='replace')}")
+
+
+_CONTEXTS: dict[int, "Context"] = {}
+
+
+class Context:
+    """One per device; owns the library's internal workspaces."""
+
+    def __init__(self, device_index: int):
+        h = _p()
+        check(lib.porl_ctx_create(C.byref(h), device_index))
+        self.handle = h
+        self.device_index = device_index
+        sp = _p()
+        check(lib.porl_ctx_status_ptr(self.handle, C.byref(sp)))
+        self.status_ptr = sp.value
+
+    def status_tensor(self):
+        """Zero-copy int32 torch view of the device status word (PORL_FLAG_* bits)."""
+        import torch
+
+        class _Word:
+            __cuda_array_interface__ = {"shape": (1,), "typestr": "<i4", "data": (self.status_ptr, False),
+                                        "version": 3}
+
+        return torch.as_tensor(_Word(), device=torch.device("cuda", self.device_index))
+
+    @property
+    def launches(self) -> int:
+        return int(lib.porl_launch_count(self.handle))
+
+    def profile(self, enable: bool) -> None:
+        check(lib.porl_profile_enable(self.handle, int(enable)))
+
+    def profile_read(self) -> dict:
+        """{category: {"launches", "ms", "work"}} of the launches recorded since profile(True)."""
+        out = Profile()
+        check(lib.porl_profile_read(self.handle, C.byref(out)))
+        return {c: {"launches": int(out.launches[i]), "ms": float(out.ms[i]), "work": float(out.work[i])}
+                for i, c in enumerate(CATEGORIES)}
+
+    def set_gemm_mode(self, mode: int) -> None:
+        check(lib.porl_ctx_set_gemm_mode(self.handle, mode))
+
+    @property
+    def gemm_mode(self) -> int:
+        return int(lib.porl_ctx_get_gemm_mode(self.handle))
+
+
+def context(device) -> Context:
+    """Context for a torch.device / index (created on first use)."""
+    import torch
+
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise PorlError(f"porl_b200 runs on CUDA (sm_100a) devices only, got device '{dev}'; there is no CPU fallback")
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    if idx not in _CONTEXTS:
+        _CONTEXTS[idx] = Context(idx)
+    return _CONTEXTS[idx]
+
+
+def stream_ptr() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream
+
+
+def sync_stream() -> None:
+    import torch
+
+    torch.cuda.current_stream().synchronize()
+
+
+def pinned(n: int, dtype):
+    import torch
+
+    return torch.zeros(n, dtype=dtype).pin_memory()

@@ -1,0 +1,188 @@
+"""Shared update step of POR and SORL: twin expectile value step, Polyak target update, then an
+advantage-weighted Gaussian log-likelihood policy step (agent/por.py:73-112 == agent/sorl.py:78-128
+up to the weight formula, the regression target and the tanh head).
+
+Kernel sequence of one update (all on the caller's current CUDA stream, no host sync inside):
+   1  grouped MLP forward : target TwinV(next_obs) + online TwinV(obs)          [K2, 3 launches]
+   2  expectile loss      : TD target, twin loss, dL/dv                          [K4]
+   3  MLP backward        : dW/db of both value nets into the group's bucket     [K3, 5 launches]
+      (DP: all-reduce of the bucket -- gradients + loss scalar)
+   4  Adam + Polyak       : value params, moments, target net in one pass       [K7]
+   5  grouped MLP forward : online TwinV(obs) with the NEW weights + policy(obs) [K2]
+   6  AWR Gaussian NLL    : weight, NLL, dL/dmean (tanh' folded), dL/dlog_std    [K5]
+   7  MLP backward        : policy dW/db                                         [K3]
+      (DP: all-reduce)
+   8  Adam                : policy params (+ device-side cosine LR recursion)    [K7]
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from .. import _C, dist as pdist
+from .._C import check, lib
+from ..dataloader.dataset import PackedBatch
+from ..nets import (CosineSchedule, ParamGroup, Workspace, mlp_backward, mlp_call, mlp_forward, pack_rows, pad_to)
+from .policy import BoundedGaussianPolicy, GaussianPolicy
+from .value_functions import TwinV
+
+
+class ExpectileAgent(nn.Module):
+    # subclasses set these
+    _value_name = _target_name = _policy_name = ""
+    _awr_mode = _C.AWR_POR
+    _bounded = False
+
+    def _build(self, args, max_steps, tau, alpha, backbone, device, value_lr, policy_lr, discount, beta,
+               policy_out: int):
+        if backbone is not None:
+            raise NotImplementedError(
+                "the FasterNet scan encoder (agent/fasternet.py) is not built yet in porl_b200; "
+                "construct the agent with backbone=None (MLP-only heads, as sorl_train_v0.py)")
+        self.device = torch.device(device)
+        self.ctx = _C.context(self.device)
+        self.backbone = None
+        S, H, n_hidden = int(args.state_size), int(args.hidden_dim), int(args.n_hidden)
+        self.state_size, self.policy_out = S, int(policy_out)
+        dev = self.device
+
+        # --- value group: online TwinV parameters in the group's flat buffer; private target buffer
+        probe = TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, init=False)  # geometry only
+        self.v_group = ParamGroup(self.ctx, probe.plan.n_floats, dev, lr=value_lr)
+        policy_cls = BoundedGaussianPolicy if self._bounded else GaussianPolicy
+        # construction order follows the reference so that the global torch RNG is consumed alike:
+        # POR builds goal_policy then vf (por.py:35-45); SORL builds v_net then policy (sorl.py:36-45)
+        def make_value():
+            return TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, flat=self.v_group.params,
+                         grads=self.v_group.grads)
+
+        def make_policy():
+            pol_probe = policy_cls(S, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, init=False)
+            n = policy_cls.group_floats(pol_probe.plan, self.policy_out)
+            self.p_group = ParamGroup(self.ctx, n, dev, lr=policy_lr, t_max=int(max_steps))
+            return policy_cls(S, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, flat=self.p_group.params,
+                              grads=self.p_group.grads)
+
+        if self._policy_first:
+            policy, value = make_policy(), make_value()
+        else:
+            value, policy = make_value(), make_policy()
+        target = TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, trainable=False, init=False)
+        target.flat.copy_(self.v_group.params[:target.flat.numel()])       # deepcopy(vf).requires_grad_(False)
+        # registration order = the reference's attribute order, so state_dict() key order matches
+        first, second = ((self._policy_name, policy), (self._value_name, value))
+        if not self._policy_first:
+            first, second = second, first
+        setattr(self, first[0], first[1])
+        setattr(self, second[0], second[1])
+        setattr(self, self._target_name, target)
+        # aliases that bypass nn.Module registration (state_dict must hold the reference's keys only)
+        self.__dict__.update(_value=value, _policy=policy, _target=target)
+
+        self.v_optimizer = self.v_group
+        self._policy_optimizer = self.p_group
+        self._schedule = CosineSchedule(self.p_group)
+        self.tau, self.alpha, self.discount, self.beta = float(tau), float(alpha), float(discount), float(beta)
+        self._ws = Workspace(dev)
+        self._host = _C.pinned(4, torch.float32)
+        self._host_status = _C.pinned(1, torch.int32)
+        self._status = self.ctx.status_tensor()
+        self._packed: dict[int, PackedBatch] = {}
+
+    # ------------------------------------------------------------------ batch packing
+    def pack(self, observations, next_observations, rewards, terminals, actions=None) -> PackedBatch:
+        """Copy caller tensors (any strides, e.g. column views of a collated row batch) into the
+        padded device minibatch.  Inputs are not modified."""
+        B = int(observations.shape[0])
+        pb = self._packed.get(B)
+        if pb is None:
+            pb = PackedBatch(B, self.state_size, 2 if actions is None else int(actions.shape[-1]), self.device)
+            self._packed[B] = pb
+        dev = self.device
+        pack_rows(self.ctx, observations.to(dev), self.state_size, pb.obs, pb.ld_obs)
+        pack_rows(self.ctx, next_observations.to(dev), self.state_size, pb.next_obs, pb.ld_obs)
+        pack_rows(self.ctx, rewards.to(dev).reshape(B), 1, pb.rewards, 1)
+        pack_rows(self.ctx, terminals.to(dev).reshape(B), 1, pb.dones, 1)
+        if actions is not None:
+            pack_rows(self.ctx, actions.to(dev), pb.A, pb.actions, pb.ld_act)
+        return pb
+
+    # ------------------------------------------------------------------ the update
+    def _value_step(self, pb: PackedBatch) -> None:
+        ctx, B = self.ctx, pb.B
+        plan = self._value.plan
+        ws = self._ws
+        scratch_t = ws.get(("scratch_t", B), plan.saved_floats(B))
+        saved_v = ws.get(("saved_v", B), plan.saved_floats(B))
+        out_t = ws.get(("out_t", B), 2 * B * plan.out_ld)
+        out_v = ws.get(("out_v", B), 2 * B * plan.out_ld)
+        dv = ws.get(("dv", B), 2 * B * plan.out_ld)
+        target_v = ws.get(("target_v", B), B)
+        call_t = mlp_call(plan, self._target.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t)
+        call_v = mlp_call(plan, self.v_group.params, pb.obs, pb.ld_obs, saved_v, out_v)
+        mlp_forward(ctx, [call_t, call_v], B)
+        ld, net = plan.out_ld, B * plan.out_ld * 4
+        b_norm = B * pdist.world_size()
+        check(lib.porl_expectile_twin_loss(
+            ctx.handle, out_v.data_ptr(), out_v.data_ptr() + net, out_t.data_ptr(), out_t.data_ptr() + net, ld,
+            pb.rewards.data_ptr(), pb.dones.data_ptr(), self.discount, self.tau, B, b_norm, target_v.data_ptr(),
+            dv.data_ptr(), dv.data_ptr() + net, self.v_group.loss_ptr, _C.stream_ptr()))
+        mlp_backward(ctx, call_v, B, dv, self.v_group.grads)
+        pdist.allreduce_sum_(self.v_group.bucket)
+        self.v_group.step(target=self._target.flat, ema_beta=self.beta)
+
+    def _policy_step(self, pb: PackedBatch, x: torch.Tensor, ld_x: int) -> None:
+        ctx, B = self.ctx, pb.B
+        vplan, pplan = self._value.plan, self._policy.plan
+        ws = self._ws
+        scratch_v = ws.get(("scratch_v2", B), vplan.saved_floats(B))
+        out_v2 = ws.get(("out_v2", B), 2 * B * vplan.out_ld)
+        saved_p = ws.get(("saved_p", B), pplan.saved_floats(B))
+        out_p = ws.get(("out_p", B), B * pplan.out_ld)
+        dz_p = ws.get(("dz_p", B), B * pplan.out_ld)
+        target_v = ws.get(("target_v", B), B)
+        call_v = mlp_call(vplan, self.v_group.params, pb.obs, pb.ld_obs, scratch_v, out_v2)
+        call_p = mlp_call(pplan, self.p_group.params, pb.obs, pb.ld_obs, saved_p, out_p)
+        mlp_forward(ctx, [call_v, call_p], B)
+        off = self._policy.log_std_offset * 4
+        net = B * vplan.out_ld * 4
+        b_norm = B * pdist.world_size()
+        check(lib.porl_awr_gauss_nll(
+            ctx.handle, out_p.data_ptr(), pplan.out_ld, self.p_group.params.data_ptr() + off, x.data_ptr(), ld_x,
+            target_v.data_ptr(), out_v2.data_ptr(), out_v2.data_ptr() + net, vplan.out_ld, self.alpha,
+            self._awr_mode, int(self._bounded), B, self.policy_out, b_norm, dz_p.data_ptr(),
+            self.p_group.grads.data_ptr() + off, self.p_group.loss_ptr, _C.stream_ptr()))
+        mlp_backward(ctx, call_p, B, dz_p, self.p_group.grads)
+        pdist.allreduce_sum_(self.p_group.bucket)
+        self.p_group.step()
+
+    def _policy_target(self, pb: PackedBatch):
+        raise NotImplementedError
+
+    def update_packed(self, pb: PackedBatch) -> None:
+        """One gradient update on a packed device minibatch; asynchronous, returns nothing."""
+        self._value_step(pb)
+        x, ld_x = self._policy_target(pb)
+        self._policy_step(pb, x, ld_x)
+
+    def value_update_packed(self, pb: PackedBatch) -> None:
+        self._value_step(pb)
+
+    def read_losses(self) -> tuple[float, float]:
+        """Synchronising read of (v_loss, policy_loss) of the last update; raises on device flags."""
+        self._host[0:1].copy_(self.v_group.tail[0:1], non_blocking=True)
+        self._host[1:2].copy_(self.p_group.tail[0:1], non_blocking=True)
+        self._host_status.copy_(self._status, non_blocking=True)
+        _C.sync_stream()
+        flags = int(self._host_status[0])
+        if flags:
+            self._status.zero_()
+            msgs = []
+            if flags & _C.FLAG_NONFINITE_LOSS:
+                msgs.append("a loss is NaN/Inf")
+            if flags & _C.FLAG_NONPOSITIVE_NLL:
+                msgs.append("non-positive per-sample NLL (the reference drops into pdb here, agent/por.py:104)")
+            if flags & _C.FLAG_BAD_INDEX:
+                msgs.append("gather index out of range")
+            raise FloatingPointError("; ".join(msgs) or f"device status {flags}")
+        return float(self._host[0]), float(self._host[1])

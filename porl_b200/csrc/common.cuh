@@ -1,0 +1,137 @@
+// Shared device/host helpers for libporl_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <vector>
+
+#include "../../include/porl_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libporl_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace porl {
+
+constexpr int kMaxGroups = 8;       // problems per grouped contraction launch
+constexpr int kSemInts = 1 << 16;   // split-K turnstile words
+constexpr int kPartialFloats = 1 << 18;  // block partials of the loss reductions
+
+void set_error(const char* fmt, ...);
+
+}  // namespace porl
+
+struct porl_prof_rec {
+  int cat;
+  double work;
+  cudaEvent_t e0, e1;
+};
+
+struct porl_ctx {
+  bool profiling;
+  std::vector<porl_prof_rec> prof;
+  int device;
+  int sm_count;
+  int gemm_mode;            // 0 = fp32 FFMA, 1 = tcgen05 3xTF32 where supported
+  int64_t launches;
+  int* sem;                 // zero-initialised turnstile words (self-resetting)
+  float* partials;          // loss reduction partials
+  uint32_t* counters;       // [0] status word, [1..] last-block-done counters
+  float* split_ws;          // 3xTF32 operand split scratch
+  size_t split_ws_floats;
+};
+
+#define PORL_CHECK_ARG(cond, ...)                \
+  do {                                           \
+    if (!(cond)) {                               \
+      porl::set_error(__VA_ARGS__);              \
+      return PORL_ERR_INVALID;                   \
+    }                                            \
+  } while (0)
+
+#define PORL_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t e_ = (call);                                                         \
+    if (e_ != cudaSuccess) {                                                         \
+      porl::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return PORL_ERR_CUDA;                                                          \
+    }                                                                                \
+  } while (0)
+
+// after a kernel launch: count it and surface launch-configuration errors
+#define PORL_LAUNCHED(ctx)                                                           \
+  do {                                                                               \
+    (ctx)->launches++;                                                               \
+    cudaError_t e_ = cudaPeekAtLastError();                                          \
+    if (e_ != cudaSuccess) {                                                         \
+      porl::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return PORL_ERR_CUDA;                                                          \
+    }                                                                                \
+  } while (0)
+
+// Brackets the launches issued during its lifetime with CUDA events when profiling is enabled.
+struct ProfScope {
+  porl_ctx* ctx;
+  cudaStream_t st;
+  size_t idx;
+  bool on;
+  ProfScope(porl_ctx* c, int cat, double work, cudaStream_t s) : ctx(c), st(s), idx(0), on(c->profiling) {
+    if (!on) return;
+    porl_prof_rec r;
+    r.cat = cat;
+    r.work = work;
+    if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) {
+      on = false;
+      return;
+    }
+    cudaEventRecord(r.e0, st);
+    ctx->prof.push_back(r);
+    idx = ctx->prof.size() - 1;
+  }
+  ~ProfScope() {
+    if (on) cudaEventRecord(ctx->prof[idx].e1, st);
+  }
+};
+
+static inline cudaStream_t as_stream(porl_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+#ifdef __CUDACC__
+namespace porl {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Deterministic block sum for blockDim.x <= 1024 (multiple of 32); result valid in thread 0.
+__device__ __forceinline__ float block_sum(float v, float* smem32) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) smem32[warp] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float r = 0.f;
+  if (warp == 0) {
+    r = lane < nw ? smem32[lane] : 0.f;
+    r = warp_sum(r);
+  }
+  return r;
+}
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+}  // namespace porl
+#endif

@@ -1,0 +1,372 @@
+// K2 / K3: MLP forward and backward as sequences of grouped contractions with fused epilogues
+// (bias + ReLU / tanh forward; ReLU mask, bias gradient and zero padding backward), plus the
+// optional LayerNorm rows of util/util.py:34-39.
+//
+// Layout (all fp32, row-major):
+//   flat parameters, per net, in the reference's parameters() order:
+//       W_l (dims[l+1], pad32(dims[l]))   b_l (pad4(dims[l+1]))   [ln_w_l, ln_b_l (pad4 each)]
+//   saved activations, per net, per hidden layer l = 1..L-1:
+//       h_l (B, pad32(dims[l]))           [xhat_l (B, pad32(dims[l])), rstd_l (pad4(B))]
+//   head output: (n_nets, B, pad4(dims[L]))
+// Pad columns of weights, activations and gradients are zero, so contractions may run over the
+// padded extents (the tcgen05 path does) without changing results.
+#include <math.h>
+
+#include "gemm.cuh"
+
+struct porl_mlp {
+  porl_ctx* ctx;
+  porl_mlp_desc_t d;
+  int64_t w_off[PORL_MAX_LAYERS], b_off[PORL_MAX_LAYERS], lnw_off[PORL_MAX_LAYERS], lnb_off[PORL_MAX_LAYERS];
+  int64_t net_stride;     // floats per net in the flat buffer
+  int pad[PORL_MAX_LAYERS + 1];  // pad32(dims[l])
+  int ld_out;
+};
+
+namespace porl {
+
+static inline int pad32(int x) { return (int)round_up(x, PORL_PAD); }
+static inline int pad4(int64_t x) { return (int)round_up(x, 4); }
+
+// per-net saved layout helpers
+static int64_t saved_layer_floats(const porl_mlp* m, int l /*hidden layer 1..L-1*/, int64_t B) {
+  int64_t f = B * m->pad[l];
+  if (m->d.layer_norm) f += B * m->pad[l] + pad4(B);
+  return f;
+}
+static int64_t saved_net_floats(const porl_mlp* m, int64_t B) {
+  int64_t f = 0;
+  for (int l = 1; l < m->d.n_layers; ++l) f += saved_layer_floats(m, l, B);
+  return f;
+}
+static float* saved_h(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+  float* p = saved + net * saved_net_floats(m, B);
+  for (int i = 1; i < l; ++i) p += saved_layer_floats(m, i, B);
+  return p;
+}
+static float* saved_xhat(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+  return saved_h(m, saved, net, l, B) + B * m->pad[l];
+}
+static float* saved_rstd(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+  return saved_h(m, saved, net, l, B) + 2 * B * m->pad[l];
+}
+
+// ---------------------------------------------------------------- LayerNorm rows
+// z (B, ld) in place -> h = relu(xhat * gamma + beta); xhat and rstd saved.  One warp per row.
+__global__ void __launch_bounds__(256)
+ln_relu_forward_kernel(float* __restrict__ z, float* __restrict__ xhat, float* __restrict__ rstd,
+                       const float* __restrict__ gamma, const float* __restrict__ beta, int64_t B, int d,
+                       int ld) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= B) return;
+  float* zr = z + row * ld;
+  float* xr = xhat + row * ld;
+  float s = 0.f;
+  for (int j = lane; j < d; j += 32) s += zr[j];
+  const float mean = warp_sum(s) / (float)d;
+  float q = 0.f;
+  for (int j = lane; j < d; j += 32) {
+    const float c = zr[j] - mean;
+    q = fmaf(c, c, q);
+  }
+  const float var = warp_sum(q) / (float)d;     // biased, as torch.nn.LayerNorm
+  const float rs = rsqrtf(var + 1e-5f);
+  for (int j = lane; j < d; j += 32) {
+    const float xh = (zr[j] - mean) * rs;
+    xr[j] = xh;
+    zr[j] = fmaxf(fmaf(xh, gamma[j], beta[j]), 0.f);
+  }
+  for (int j = d + lane; j < ld; j += 32) {
+    xr[j] = 0.f;
+    zr[j] = 0.f;
+  }
+  if (lane == 0) rstd[row] = rs;
+}
+
+// dy (B, ld) in place -> dz = rstd * (g - mean_j(g) - xhat * mean_j(g * xhat)),  g = dy * gamma
+__global__ void __launch_bounds__(256)
+ln_backward_kernel(float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ rstd,
+                   const float* __restrict__ gamma, int64_t B, int d, int ld) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= B) return;
+  float* dr = dy + row * ld;
+  const float* xr = xhat + row * ld;
+  float s1 = 0.f, s2 = 0.f;
+  for (int j = lane; j < d; j += 32) {
+    const float g = dr[j] * gamma[j];
+    s1 += g;
+    s2 = fmaf(g, xr[j], s2);
+  }
+  s1 = warp_sum(s1) / (float)d;
+  s2 = warp_sum(s2) / (float)d;
+  const float rs = rstd[row];
+  for (int j = lane; j < d; j += 32) {
+    const float g = dr[j] * gamma[j];
+    dr[j] = rs * (g - s1 - xr[j] * s2);
+  }
+}
+
+// dgamma[j] = sum_m dy[m,j] * xhat[m,j];  dbeta[j] = sum_m dy[m,j].  One block per 32 columns,
+// 8 warps stride the rows, fixed-order shared-memory reduction -> deterministic.
+__global__ void __launch_bounds__(256)
+ln_param_grad_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, int64_t B, int d,
+                     int ld, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float sg[8][33], sb[8][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
+  float ag = 0.f, ab = 0.f;
+  if (j < d) {
+    for (int64_t m = warp; m < B; m += 8) {
+      const float g = dy[m * ld + j];
+      ab += g;
+      ag = fmaf(g, xhat[m * ld + j], ag);
+    }
+  }
+  sg[warp][lane] = ag;
+  sb[warp][lane] = ab;
+  __syncthreads();
+  if (warp == 0 && j < d) {
+    float tg = 0.f, tb = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      tg += sg[w][lane];
+      tb += sb[w][lane];
+    }
+    dgamma[j] = tg;
+    dbeta[j] = tb;
+  }
+}
+
+}  // namespace porl
+
+using namespace porl;
+
+extern "C" int porl_mlp_create(porl_ctx_t* ctx, const porl_mlp_desc_t* desc, porl_mlp_t** out) {
+  PORL_CHECK_ARG(ctx && desc && out, "porl_mlp_create: null argument");
+  PORL_CHECK_ARG(desc->n_nets >= 1 && desc->n_nets <= kMaxGroups, "porl_mlp_create: n_nets=%d", desc->n_nets);
+  PORL_CHECK_ARG(desc->n_layers >= 1 && desc->n_layers <= PORL_MAX_LAYERS, "porl_mlp_create: n_layers=%d",
+                 desc->n_layers);
+  PORL_CHECK_ARG(desc->out_act == 0 || desc->out_act == 1, "porl_mlp_create: out_act=%d", desc->out_act);
+  for (int l = 0; l <= desc->n_layers; ++l)
+    PORL_CHECK_ARG(desc->dims[l] >= 1 && desc->dims[l] <= 65536, "porl_mlp_create: dims[%d]=%d", l, desc->dims[l]);
+  porl_mlp* m = new porl_mlp();
+  m->ctx = ctx;
+  m->d = *desc;
+  int64_t off = 0;
+  for (int l = 0; l <= desc->n_layers; ++l) m->pad[l] = pad32(desc->dims[l]);
+  for (int l = 0; l < desc->n_layers; ++l) {
+    m->w_off[l] = off;
+    off += (int64_t)desc->dims[l + 1] * m->pad[l];
+    m->b_off[l] = off;
+    off += pad4(desc->dims[l + 1]);
+    m->lnw_off[l] = m->lnb_off[l] = -1;
+    if (desc->layer_norm && l < desc->n_layers - 1) {
+      m->lnw_off[l] = off;
+      off += pad4(desc->dims[l + 1]);
+      m->lnb_off[l] = off;
+      off += pad4(desc->dims[l + 1]);
+    }
+  }
+  m->net_stride = off;
+  m->ld_out = pad4(desc->dims[desc->n_layers]);
+  *out = m;
+  return PORL_OK;
+}
+
+extern "C" int porl_mlp_destroy(porl_mlp_t* mlp) {
+  delete mlp;
+  return PORL_OK;
+}
+
+extern "C" int64_t porl_mlp_param_floats(const porl_mlp_t* mlp) {
+  return mlp ? mlp->net_stride * mlp->d.n_nets : -1;
+}
+
+extern "C" int porl_mlp_param_layout(const porl_mlp_t* mlp, int32_t net, int32_t layer, int32_t kind,
+                                     int64_t* offset, int64_t* ld) {
+  PORL_CHECK_ARG(mlp && offset && ld, "porl_mlp_param_layout: null argument");
+  PORL_CHECK_ARG(net >= 0 && net < mlp->d.n_nets && layer >= 0 && layer < mlp->d.n_layers,
+                 "porl_mlp_param_layout: net=%d layer=%d", net, layer);
+  int64_t o = -1;
+  switch (kind) {
+    case PORL_PARAM_WEIGHT: o = mlp->w_off[layer]; *ld = mlp->pad[layer]; break;
+    case PORL_PARAM_BIAS: o = mlp->b_off[layer]; *ld = 1; break;
+    case PORL_PARAM_LN_WEIGHT: o = mlp->lnw_off[layer]; *ld = 1; break;
+    case PORL_PARAM_LN_BIAS: o = mlp->lnb_off[layer]; *ld = 1; break;
+    default: break;
+  }
+  PORL_CHECK_ARG(o >= 0, "porl_mlp_param_layout: tensor kind %d absent at layer %d", kind, layer);
+  *offset = net * mlp->net_stride + o;
+  return PORL_OK;
+}
+
+extern "C" int64_t porl_mlp_saved_floats(const porl_mlp_t* mlp, int64_t B) {
+  if (!mlp || B < 0) return -1;
+  int64_t f = saved_net_floats(mlp, B) * mlp->d.n_nets;
+  return f > 0 ? f : 4;
+}
+
+extern "C" int64_t porl_mlp_out_ld(const porl_mlp_t* mlp) { return mlp ? mlp->ld_out : -1; }
+
+extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp_call_t* calls, int64_t B,
+                                porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && calls && n_calls >= 1 && n_calls <= PORL_MAX_CALLS, "porl_mlp_forward: n_calls=%d", n_calls);
+  PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_forward: B=%lld", (long long)B);
+  int max_layers = 0, total_nets = 0;
+  for (int c = 0; c < n_calls; ++c) {
+    const porl_mlp_call_t& k = calls[c];
+    PORL_CHECK_ARG(k.mlp && k.params && k.x && k.saved && k.out, "porl_mlp_forward: null pointer in call %d", c);
+    PORL_CHECK_ARG(k.ldx >= k.mlp->d.dims[0] && (k.ldx & 3) == 0 && aligned16(k.x) && aligned16(k.params) &&
+                       aligned16(k.saved) && aligned16(k.out),
+                   "porl_mlp_forward: call %d needs 16-byte aligned buffers and ldx %% 4 == 0 (ldx=%lld)", c,
+                   (long long)k.ldx);
+    max_layers = k.mlp->d.n_layers > max_layers ? k.mlp->d.n_layers : max_layers;
+    total_nets += k.mlp->d.n_nets;
+  }
+  PORL_CHECK_ARG(total_nets <= kMaxGroups, "porl_mlp_forward: %d nets exceed the %d-problem group limit", total_nets,
+                 kMaxGroups);
+  cudaStream_t st = as_stream(stream);
+  for (int l = 0; l < max_layers; ++l) {
+    GemmBatch batch;
+    batch.n_groups = 0;
+    for (int c = 0; c < n_calls; ++c) {
+      const porl_mlp_call_t& k = calls[c];
+      const porl_mlp* m = k.mlp;
+      if (l >= m->d.n_layers) continue;
+      const bool last = (l == m->d.n_layers - 1);
+      for (int net = 0; net < m->d.n_nets; ++net) {
+        GemmGroup& g = batch.g[batch.n_groups++];
+        const float* P = k.params + net * m->net_stride;
+        g.A = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
+        g.lda = (l == 0) ? (int)k.ldx : m->pad[l];
+        g.B = P + m->w_off[l];
+        g.ldb = m->pad[l];
+        g.bias = P + m->b_off[l];
+        g.relu_src = nullptr;
+        g.ld_relu = 0;
+        g.colsum = nullptr;
+        g.M = (int)B;
+        g.N = m->d.dims[l + 1];
+        g.K = m->d.dims[l];
+        if (last) {
+          g.C = k.out + (int64_t)net * B * m->ld_out;
+          g.ldc = m->ld_out;
+          g.n_store = m->ld_out;
+          g.epilogue = m->d.out_act == 1 ? 2 : 0;
+        } else {
+          g.C = saved_h(m, k.saved, net, l + 1, B);
+          g.ldc = m->pad[l + 1];
+          g.n_store = m->pad[l + 1];
+          g.epilogue = m->d.layer_norm ? 0 : 1;
+        }
+      }
+    }
+    int rc = launch_gemm(ctx, true, true, batch, st);
+    if (rc != PORL_OK) return rc;
+    // LayerNorm + ReLU rows
+    for (int c = 0; c < n_calls; ++c) {
+      const porl_mlp_call_t& k = calls[c];
+      const porl_mlp* m = k.mlp;
+      if (!m->d.layer_norm || l >= m->d.n_layers - 1) continue;
+      for (int net = 0; net < m->d.n_nets; ++net) {
+        const float* P = k.params + net * m->net_stride;
+        ProfScope prof(ctx, PORL_CAT_NORM, (double)B * m->d.dims[l + 1] * 12.0, st);
+        ln_relu_forward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(
+            saved_h(m, k.saved, net, l + 1, B), saved_xhat(m, k.saved, net, l + 1, B),
+            saved_rstd(m, k.saved, net, l + 1, B), P + m->lnw_off[l], P + m->lnb_off[l], B,
+            m->d.dims[l + 1], m->pad[l + 1]);
+        PORL_LAUNCHED(ctx);
+      }
+    }
+  }
+  return PORL_OK;
+}
+
+extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, int64_t B, float* dout,
+                                 float* grads, porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && call && call->mlp && dout && grads && call->params && call->x && call->saved,
+                 "porl_mlp_backward: null argument");
+  PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_backward: B=%lld", (long long)B);
+  PORL_CHECK_ARG(aligned16(dout) && aligned16(grads) && aligned16(call->x) && (call->ldx & 3) == 0,
+                 "porl_mlp_backward: buffers must be 16-byte aligned, ldx %% 4 == 0");
+  const porl_mlp* m = call->mlp;
+  const int L = m->d.n_layers;
+  cudaStream_t st = as_stream(stream);
+  for (int l = L - 1; l >= 0; --l) {
+    // gradient of this layer's pre-activation output: dout for the head, else the (in-place
+    // rewritten) hidden activation buffer of layer l+1
+    auto dz_ptr = [&](int net) -> float* {
+      return (l == L - 1) ? dout + (int64_t)net * B * m->ld_out : saved_h(m, call->saved, net, l + 1, B);
+    };
+    const int ld_dz = (l == L - 1) ? m->ld_out : m->pad[l + 1];
+    // dW_l = dz^T input, db_l = colsum(dz)
+    GemmBatch bw;
+    bw.n_groups = 0;
+    for (int net = 0; net < m->d.n_nets; ++net) {
+      GemmGroup& g = bw.g[bw.n_groups++];
+      float* G = grads + net * m->net_stride;
+      g.A = dz_ptr(net);
+      g.lda = ld_dz;
+      g.B = (l == 0) ? call->x : saved_h(m, call->saved, net, l, B);
+      g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
+      g.C = G + m->w_off[l];
+      g.ldc = m->pad[l];
+      g.n_store = m->pad[l];
+      g.bias = nullptr;
+      g.relu_src = nullptr;
+      g.ld_relu = 0;
+      g.colsum = G + m->b_off[l];
+      g.M = m->d.dims[l + 1];
+      g.N = m->d.dims[l];
+      g.K = (int)B;
+      g.epilogue = 0;
+    }
+    int rc = launch_gemm(ctx, false, false, bw, st);
+    if (rc != PORL_OK) return rc;
+    if (l == 0) break;
+    // dh_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l
+    GemmBatch bx;
+    bx.n_groups = 0;
+    for (int net = 0; net < m->d.n_nets; ++net) {
+      GemmGroup& g = bx.g[bx.n_groups++];
+      const float* P = call->params + net * m->net_stride;
+      float* h = saved_h(m, call->saved, net, l, B);
+      g.A = dz_ptr(net);
+      g.lda = ld_dz;
+      g.B = P + m->w_off[l];
+      g.ldb = m->pad[l];
+      g.C = h;
+      g.ldc = m->pad[l];
+      g.n_store = m->pad[l];
+      g.bias = nullptr;
+      g.relu_src = h;
+      g.ld_relu = m->pad[l];
+      g.colsum = nullptr;
+      g.M = (int)B;
+      g.N = m->d.dims[l];
+      g.K = m->d.dims[l + 1];
+      g.epilogue = 0;
+    }
+    rc = launch_gemm(ctx, true, false, bx, st);
+    if (rc != PORL_OK) return rc;
+    if (m->d.layer_norm) {
+      for (int net = 0; net < m->d.n_nets; ++net) {
+        const float* P = call->params + net * m->net_stride;
+        float* G = grads + net * m->net_stride;
+        float* dy = saved_h(m, call->saved, net, l, B);
+        const float* xh = saved_xhat(m, call->saved, net, l, B);
+        const int d = m->d.dims[l];
+        ProfScope prof(ctx, PORL_CAT_NORM, (double)B * d * 20.0, st);
+        ln_param_grad_kernel<<<(d + 31) / 32, 256, 0, st>>>(dy, xh, B, d, m->pad[l], G + m->lnw_off[l - 1],
+                                                            G + m->lnb_off[l - 1]);
+        PORL_LAUNCHED(ctx);
+        ln_backward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(dy, xh, saved_rstd(m, call->saved, net, l, B),
+                                                                    P + m->lnw_off[l - 1], B, d, m->pad[l]);
+        PORL_LAUNCHED(ctx);
+      }
+    }
+  }
+  return PORL_OK;
+}

@@ -1,0 +1,112 @@
+"""DQN base trainer: constructor + offline loop of src/porl/train/dqn_trainer.py:35-91,93-117,182-231."""
+from __future__ import annotations
+
+from typing import List, Type
+
+import numpy as np
+import torch
+
+from .. import _C, dist as pdist
+from .._C import check, lib
+from ..buffer.replaybuffer import ReplayBuffer
+from ..dataloader.dataset import PackedBatch
+from ..net.q_network import QNetwork
+from ..nets import ParamGroup, Workspace, mlp_backward, mlp_call, mlp_forward
+from ..utils.logger import Logger
+
+
+class DQNTrainer:
+    """Same constructor as the reference (dqn_trainer.py:35-51).  Hard-coded there and kept:
+    Adam lr 0.0005 (:71), ReplayBuffer(100000) (:76), batch_size 64 (:78)."""
+
+    cql_alpha = 0.0      # plain DQN: TD loss only (dqn_trainer.py:93-117)
+
+    def __init__(self, state_size: int, action_size: int, gamma: float, epsilon: float, epsilon_min: float,
+                 epsilon_decay: float, learning_rate: float, update_target_freq: int, device: torch.device,
+                 network: Type[QNetwork] | None = QNetwork, log_dir: str = "logs", replay_buffer=None,
+                 transition_learning_step=10000):
+        self.state_size, self.action_size = int(state_size), int(action_size)
+        self.device = torch.device(device)
+        self.ctx = _C.context(self.device)
+        self.gamma, self.epsilon, self.epsilon_min = float(gamma), epsilon, epsilon_min
+        self.epsilon_decay, self.learning_rate = epsilon_decay, learning_rate
+        self.update_target_freq = int(update_target_freq)
+        self.training_learning_step = transition_learning_step
+        if network is not None:
+            if not (isinstance(network, type) and issubclass(network, QNetwork)):
+                raise TypeError("porl_b200 trainers take porl_b200.QNetwork (or a subclass) as `network`")
+            probe = network(state_size, action_size, device=self.device, init=False)
+            self.q_group = ParamGroup(self.ctx, probe.plan.n_floats, self.device, lr=0.0005)   # dqn_trainer.py:71
+            self.q_network = network(state_size, action_size, device=self.device, flat=self.q_group.params,
+                                     grads=self.q_group.grads)
+            self.target_network = network(state_size, action_size, device=self.device, trainable=False)
+            self.target_network.load_state_dict(self.q_network.state_dict())
+            self.optimizer = self.q_group
+        self.replay_buffer = replay_buffer if replay_buffer is not None else ReplayBuffer(
+            100000, (self.state_size,), self.device)
+        self.batch_size = 64
+        self.logger = Logger(log_dir=log_dir)
+        self.logger.log_hyperparameters({"learning_rate": self.learning_rate, "gamma": self.gamma,
+                                         "batch_size": self.batch_size, "epsilon_decay": self.epsilon_decay,
+                                         "update_target_freq": self.update_target_freq})
+        self._ws = Workspace(self.device)
+        self._host = _C.pinned(4, torch.float32)
+        self.training_step = 0
+
+    # ------------------------------------------------------------------ one update on a device batch
+    def learn_packed(self, pb: PackedBatch, hard_every: int = 0) -> None:
+        """TD (+ CQL) update on a packed minibatch; asynchronous.  losses land in q_group.tail[0:3]."""
+        ctx, B, plan = self.ctx, pb.B, self.q_network.plan
+        ws = self._ws
+        scratch_t = ws.get(("scratch_t", B), plan.saved_floats(B))
+        saved_q = ws.get(("saved_q", B), plan.saved_floats(B))
+        out_t = ws.get(("out_t", B), B * plan.out_ld)
+        out_q = ws.get(("out_q", B), B * plan.out_ld)
+        dq = ws.get(("dq", B), B * plan.out_ld)
+        call_t = mlp_call(plan, self.target_network.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t)
+        call_q = mlp_call(plan, self.q_group.params, pb.obs, pb.ld_obs, saved_q, out_q)
+        mlp_forward(ctx, [call_t, call_q], B)
+        check(lib.porl_cql_head(ctx.handle, out_q.data_ptr(), out_t.data_ptr(), plan.out_ld, pb.actions.data_ptr(),
+                                pb.rewards.data_ptr(), pb.dones.data_ptr(), self.gamma, float(self.cql_alpha), B,
+                                self.action_size, B * pdist.world_size(), dq.data_ptr(), self.q_group.loss_ptr,
+                                _C.stream_ptr()))
+        mlp_backward(ctx, call_q, B, dq, self.q_group.grads)
+        pdist.allreduce_sum_(self.q_group.bucket)
+        self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)
+
+    def read_losses(self) -> tuple[float, float, float]:
+        """Synchronising read of (loss, td, penalty) of the last update."""
+        self._host[0:3].copy_(self.q_group.tail[0:3], non_blocking=True)
+        _C.sync_stream()
+        return float(self._host[0]), float(self._host[1]), float(self._host[2])
+
+    def learn(self) -> float:
+        """One gradient update on a batch drawn from the replay buffer (dqn_trainer.py:93-117)."""
+        idx = torch.as_tensor(self.replay_buffer.draw_indices(self.batch_size))
+        self._pb = self.replay_buffer.gather_packed(idx, getattr(self, "_pb", None))
+        self.learn_packed(self._pb)
+        return self.read_losses()[0]
+
+    def sync_target(self) -> None:
+        """target_network.load_state_dict(q_network.state_dict()) (dqn_trainer.py:196)."""
+        self.target_network.flat.copy_(self.q_group.params[:self.target_network.flat.numel()])
+
+    def train_offline(self, policy=None, num_iterations: int = 10000, verbose: bool = True) -> List[float]:
+        losses = []
+        for self.training_step in range(num_iterations):
+            loss = self.learn() if policy is None else policy()
+            self.logger.log_loss(self.training_step, loss)
+            if self.training_step % self.update_target_freq == 0:
+                self.sync_target()
+            losses.append(loss)
+            if verbose and self.training_step % 10 == 0:
+                print(f"step {self.training_step}, Loss: {loss}")
+        self.logger.close()
+        return losses
+
+    def select_action(self, state: np.ndarray) -> int:
+        """Epsilon-greedy action (dqn_trainer.py:206-231)."""
+        if np.random.rand() < self.epsilon:
+            return int(np.random.randint(self.action_size))
+        q = self.q_network(torch.as_tensor(np.asarray(state, dtype=np.float32))[None])
+        return int(q.argmax().item())
