@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""Headline benchmark: offline-RL gradient updates/sec of the porl update step on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): SORL, MLP-only heads (S=362, H=512, A=2; sorl_train_v0.py's
+variant of agent/sorl.py), synthetic 1M-transition LaserScan+goal dataset resident in HBM, batch
+4096 per GPU.  One "step" = one gradient update = minibatch gather (K1) + value step + Polyak +
+policy step (K2..K7).  N > 1: data-parallel, one process per GPU, per-GPU batch fixed (weak
+scaling), one NCCL all-reduce per optimizer group; `value` counts 4096-sample minibatches/s over
+all ranks.  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+S, H, A, N_HIDDEN = 362, 512, 2, 2
+METRIC = "offline-RL gradient updates/sec"
+UNIT = "updates/s"
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=10)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--batch", type=int, default=4096)
+    p.add_argument("--rows", type=int, default=1_000_000)
+    p.add_argument("--gemm-mode", type=int, default=int(os.environ.get("PORL_GEMM_MODE", "1")),
+                   help="0 fp32 FFMA contractions, 1 tcgen05 3xTF32 where shapes allow")
+    p.add_argument("--graph", type=int, default=1, help="replay the update as a CUDA graph")
+    p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
+    p.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
+    p.add_argument("--also-batch", type=int, default=256, help="second batch size reported under 'also'")
+    return p.parse_args()
+
+
+def workload_name(batch):
+    return f"sorl_mlp_S{S}_H{H}_rows1M_b{batch}"
+
+
+def hyper():
+    from oracle.steps import dims
+    return dims(S, H, N_HIDDEN, False, 256, A), dict(max_steps=1_000_000, tau=0.9, alpha=10.0)
+
+
+def synth_rows_torch(n, device, seed):
+    """Synthetic LaserScan+goal transitions generated with torch on `device`."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    r = lambda *s: torch.rand(*s, generator=g, device=device)
+    scan = 0.13 + (3.5 - 0.13) * r(n, 360)
+    u = r(n, 360)
+    scan = torch.where(u < 0.25, torch.full_like(scan, 3.5), scan)
+    scan = torch.where(u > 0.97, torch.full_like(scan, 10.0), scan)
+    rad, th = 0.2 + 3.3 * r(n), (2 * r(n) - 1) * 3.14159265
+    goal = torch.stack([rad * torch.cos(th), rad * torch.sin(th)], 1)
+    nscan = (scan + 0.05 * torch.randn(n, 360, generator=g, device=device)).clamp(0.13, 3.5)
+    nscan = torch.where(scan == 3.5, scan, nscan)
+    nscan = torch.where(scan == 10.0, scan, nscan)
+    ngoal = goal + 0.05 * torch.randn(n, 2, generator=g, device=device)
+    done = (r(n) < 0.01).float()
+    sign = torch.where(r(n) < 0.5, -5.0, 5.0)
+    rew = 0.1 * torch.randn(n, generator=g, device=device) + done * sign
+    act = 2 * r(n, A) - 1
+    return torch.cat([scan, goal, rew[:, None], nscan, ngoal, done[:, None], act], 1).float()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_burst": d["bf16_tflops"], "bf16_sustained": d["bf16_tflops_sustained"],
+                "source": "measured"}
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_reference_updates(batch, steps, warmup, seconds=None):
+    """The reference's CPU path for this workload: the oracle restatement of agent/sorl.py (eager
+    torch fp32, all host threads), on a bounded sample of the same synthetic data.  Returns
+    (updates/s, n_timed, threads)."""
+    from oracle.buffer import slice_row
+    from oracle.steps import OracleSORL
+    args, hp = hyper()
+    torch.manual_seed(1000)
+    agent = OracleSORL(args, **hp)
+    n_distinct = min(max(steps, 1), 8)
+    rows = synth_rows_torch(batch * n_distinct, torch.device("cpu"), 20260102)
+    def one(i):
+        b = slice_row(rows[(i % n_distinct) * batch:((i % n_distinct) + 1) * batch], S, A)
+        agent.update(b["observations"], b["actions"], b["rewards"], b["next_observations"], b["terminals"])
+    for i in range(warmup):
+        one(i)
+    t0 = time.perf_counter()
+    n = 0
+    while n < steps:
+        one(n)
+        n += 1
+        if seconds is not None and time.perf_counter() - t0 > seconds:
+            break
+    dt = time.perf_counter() - t0
+    return n / dt, n, torch.get_num_threads(), dt
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    ups, n, threads, dt = cpu_reference_updates(a.batch, a.steps, max(a.warmup, 1))
+    sample = f"{n} updates of batch {a.batch} (oracle restatement of agent/sorl.py, eager torch fp32 CPU)"
+    line = {"impl": "reference", "metric": METRIC, "value": ups, "unit": UNIT, "n_gpus": a.gpus, "steps": n,
+            "warmup": max(a.warmup, 1), "ms_per_step": 1e3 * dt / n, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a.batch), "algo": "SORL", "batch": a.batch, "state_size": S,
+                       "hidden_dim": H, "device": "cpu"},
+            "cpu_baseline": {"value": ups, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": ups, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ B200 arm
+class Runner:
+    """Dataset replica + agent + (optionally graph-captured) step for one batch size on this rank."""
+
+    def __init__(self, a, batch, device, rank, world, table):
+        from porl_b200 import SORL, TransitionDataset
+        args, hp = hyper()
+        self.a, self.B, self.device, self.rank, self.world = a, batch, device, rank, world
+        self.ds = table
+        torch.manual_seed(1000)                      # identical initial weights on every rank
+        self.agent = SORL(args, device=device, **hp)
+        self.agent.ctx.set_gemm_mode(a.gemm_mode)
+        self.pb = self.ds.new_batch(batch)
+        self.idx_static = torch.zeros(batch, dtype=torch.int64, device=device)
+        self.graph = None
+
+    def indices(self, n_steps, seed):
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        total = n_steps * self.B * self.world
+        chunks = []
+        while total > 0:                              # epoch permutations (without replacement)
+            perm = torch.randperm(len(self.ds), generator=g, device=self.device)
+            chunks.append(perm[:total])
+            total -= chunks[-1].numel()
+        flat = torch.cat(chunks).view(n_steps, self.world, self.B)
+        return flat[:, self.rank].contiguous()
+
+    def step(self, idx):
+        self.ds.gather_packed(idx, self.pb)
+        self.agent.update_packed(self.pb)
+
+    def capture(self):
+        """CUDA graph of gather + update on a static index buffer (single process only: the NCCL
+        all-reduce of the DP path stays outside graphs here)."""
+        self.step(self.idx_static)                    # allocate workspaces outside capture
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step(self.idx_static)
+        self.graph = g
+
+    def run(self, idx_all):
+        if self.graph is None:
+            for i in range(idx_all.shape[0]):
+                self.step(idx_all[i])
+        else:
+            for i in range(idx_all.shape[0]):
+                self.idx_static.copy_(idx_all[i])
+                self.graph.replay()
+
+
+def timed(runner, idx_warm, idx_timed, dist_on):
+    import torch.distributed as dist
+    runner.run(idx_warm)
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = runner.agent.ctx.launches
+    e0.record()
+    runner.run(idx_timed)
+    e1.record()
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = runner.agent.ctx.launches - l0
+    if dist_on:
+        t = torch.tensor([ms], device=runner.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    return ms, launches
+
+
+def run_b200(a):
+    from porl_b200 import TransitionDataset, _C, dist as pdist
+    rank, local, world = pdist.init_from_env()
+    if world != a.gpus and rank == 0 and world > 1:
+        print(f"warning: --gpus {a.gpus} but WORLD_SIZE {world}", file=sys.stderr)
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    dist_on = world > 1
+    pk = peaks()
+
+    rows = synth_rows_torch(a.rows, device, 20260102)          # same replica on every rank
+    table = TransitionDataset(rows, S, A, device)
+    del rows
+    runner = Runner(a, a.batch, device, rank, world, table)
+    K, W = a.steps, max(a.warmup, 3)
+    use_graph = bool(a.graph) and not dist_on
+    if use_graph:
+        runner.capture()
+    idx_warm, idx_timed = runner.indices(W, 2000), runner.indices(K, 2001)
+
+    with ClockSampler(local) as clk:
+        ms, launches = timed(runner, idx_warm, idx_timed, dist_on)
+    v_loss, g_loss = runner.agent.read_losses()
+    clocks = clk.summary()
+    value = world * K / (ms * 1e-3)
+
+    line = None
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(a.batch), "algo": "SORL (agent/sorl.py, MLP-only heads)",
+                           "batch_per_gpu": a.batch, "global_batch": a.batch * world, "rows": a.rows,
+                           "state_size": S, "hidden_dim": H, "parallelism": f"dp{world}" if dist_on else "single",
+                           "contraction": "tcgen05 3xTF32" if a.gemm_mode == 1 else "fp32 FFMA",
+                           "cuda_graph": use_graph, "inputs_larger_than_l2": True,
+                           "l2_note": "each step gathers fresh random rows of a 2.9 GB HBM table (>> 126 MB L2)"},
+                "clocks": clocks, "gpu_launches": launches * (1 if not use_graph else 1),
+                "final_losses": {"v_loss": v_loss, "g_loss": g_loss}}
+        if use_graph:
+            # graph replays re-issue the captured launches; count them from the capture
+            line["gpu_launches"] = runner.launches_per_step * K if hasattr(runner, "launches_per_step") else launches
+
+    # ---- single-process extras on rank 0: roofline, e2e, cpu baseline, second batch size
+    if not dist_on:
+        ctx = runner.agent.ctx
+        # launches per step (eager) for the gpu_launches claim under graph replay
+        l0 = ctx.launches
+        runner.step(idx_timed[0])
+        per_step = ctx.launches - l0
+        line["gpu_launches"] = per_step * K
+        # per-kernel timing with events around every launch (eager, after the timed region)
+        ctx.profile(True)
+        for i in range(min(10, K)):
+            runner.step(idx_timed[i])
+        torch.cuda.synchronize()
+        prof = ctx.profile_read()
+        ctx.profile(False)
+        c = prof["contraction"]
+        achieved = c["work"] / (c["ms"] * 1e-3) / 1e12 if c["ms"] > 0 else 0.0
+        peak = pk["bf16_sustained"]
+        line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                            "frac": achieved / peak, "traffic": None,
+                            "kernel": "gemm_tc_kernel (tcgen05 3xTF32)" if a.gemm_mode == 1 else "gemm_simt_kernel (fp32 FFMA)",
+                            "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({pk['source']})",
+                            "launches_per_step": c["launches"] / max(1, min(10, K)),
+                            "share_of_step_ms": c["ms"] / max(1e-9, sum(v["ms"] for v in prof.values()))}
+        kern = {}
+        for name, v in prof.items():
+            if v["launches"] == 0:
+                continue
+            rate = v["work"] / (v["ms"] * 1e-3) if v["ms"] > 0 else 0.0
+            kern[name] = {"launches": v["launches"], "ms_total": v["ms"],
+                          "achieved": rate / (1e12 if name == "contraction" else 1e9),
+                          "unit": "TFLOP/s" if name == "contraction" else "GB/s",
+                          "frac_of_peak": rate / (peak * 1e12 if name == "contraction" else pk["hbm_gbs"] * 1e9)}
+        line["kernels"] = kern
+
+        # e2e: the public API with HOST buffers: pinned rows -> H2D -> agent.update() -> losses D2H
+        Ke = a.e2e_steps or K
+        ring = 8
+        host = torch.empty(ring, a.batch, table.row_len, dtype=torch.float32).pin_memory()
+        src_idx = runner.indices(ring, 2002)
+        for r in range(ring):
+            host[r].copy_(table.gather(src_idx[r]).cpu())
+        dev_rows = torch.empty(a.batch, table.row_len, dtype=torch.float32, device=device)
+        def e2e_step(i):
+            dev_rows.copy_(host[i % ring], non_blocking=True)
+            obs, rew = dev_rows[:, :S], dev_rows[:, S]
+            nxt, done, act = dev_rows[:, S + 1:2 * S + 1], dev_rows[:, 2 * S + 1], dev_rows[:, 2 * S + 2:]
+            return runner.agent.update(obs, act, rew, nxt, done)
+        for i in range(3):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(Ke):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        line["e2e"] = {"value": Ke / dt, "unit": UNIT, "h2d_bytes_per_step": a.batch * table.row_len * 4,
+                       "d2h_bytes_per_step": 12, "steps": Ke,
+                       "api": "SORL.update(observations, actions, rewards, next_observations, terminals) -> (float, float)"}
+
+        # second batch size of the metric (batch 256)
+        if a.also_batch and a.also_batch != a.batch:
+            r2 = Runner(a, a.also_batch, device, rank, world, table)
+            if use_graph:
+                r2.capture()
+            ms2, _ = timed(r2, r2.indices(W, 2003), r2.indices(K * 4, 2004), False)
+            line["also"] = {"workload": workload_name(a.also_batch), "value": K * 4 / (ms2 * 1e-3), "unit": UNIT,
+                            "ms_per_step": ms2 / (K * 4)}
+
+        # CPU baseline beside it (bounded sample; reported, not the target)
+        if a.cpu_seconds > 0:
+            torch.set_num_threads(os.cpu_count() or 1)
+            ups, n, threads, _ = cpu_reference_updates(a.batch, 10_000, 1, seconds=a.cpu_seconds)
+            line["cpu_baseline"] = {"value": ups, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"{n} updates of batch {a.batch} in <= {a.cpu_seconds:.0f} s "
+                                              "(oracle restatement of agent/sorl.py, eager torch fp32)"}
+    else:
+        if rank == 0:
+            # DP e2e: same public API per rank is exercised in the single-GPU run; report device-timed value
+            line["e2e"] = {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                           "note": "multi-GPU run: device-resident inputs; host-buffer e2e is measured at N=1"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist_on:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -77,6 +77,8 @@ class TransitionDataset:
         B = idx.shape[0]
         if out is None:
             out = torch.empty(B, self.row_len, dtype=torch.float32, device=self.device)
+        if B == 0:
+            return out
         check(lib.porl_gather_rows_f32(self.ctx.handle, self.table.data_ptr(), self.n_rows, self.row_stride,
                                        self.row_len, idx.data_ptr(), B, out.data_ptr(), out.stride(0),
                                        _C.stream_ptr()))

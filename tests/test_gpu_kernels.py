@@ -55,8 +55,7 @@ def test_gather_empty_and_bad_index(env):
     assert ds.gather(torch.zeros(0, dtype=torch.int64)).shape == (0, 48)
     out = ds.gather(torch.tensor([3, 99, -1]))          # out of range: clamped + flagged, never a fault
     torch.cuda.synchronize()
-    status = torch.as_tensor(type("S", (), {"__cuda_array_interface__": {
-        "shape": (1,), "typestr": "<i4", "data": (ctx.status_ptr, False), "version": 3}})(), device=dev)
+    status = ctx.status_tensor()
     assert int(status[0]) & _C.FLAG_BAD_INDEX
     status.zero_()
     assert torch.equal(out[0].cpu(), torch.from_numpy(rows[3]))
