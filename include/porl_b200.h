@@ -58,6 +58,8 @@ int porl_ctx_create(porl_ctx_t** out, int device);
 int porl_ctx_destroy(porl_ctx_t* ctx);
 /* kernels launched through this context so far (bench.py's gpu_launches) */
 int64_t porl_launch_count(const porl_ctx_t* ctx);
+/* of those, launches of the tcgen05 3xTF32 contraction kernel (evidence that the tensor-core path ran) */
+int64_t porl_tc_launch_count(const porl_ctx_t* ctx);
 /* device address of the 32-bit status word (PORL_FLAG_*), for an async read-back with the losses */
 int porl_ctx_status_ptr(porl_ctx_t* ctx, uint32_t** out);
 /* 0 = fp32 FFMA contractions ("exact" mode); 1 = tcgen05 3xTF32 split contractions where shapes allow */
@@ -69,7 +71,7 @@ int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
  * category together with its ALGORITHMIC work (flops for contractions, bytes for the HBM-bound
  * kernels).  porl_profile_read synchronises the recorded events and returns per-category sums. */
 enum { PORL_CAT_CONTRACTION = 0, PORL_CAT_GATHER = 1, PORL_CAT_LOSS = 2, PORL_CAT_OPTIMIZER = 3,
-       PORL_CAT_NORM = 4, PORL_CAT_COUNT = 5 };
+       PORL_CAT_NORM = 4, PORL_CAT_SPLIT = 5, PORL_CAT_COUNT = 6 };
 typedef struct {
   int64_t launches[PORL_CAT_COUNT];
   double ms[PORL_CAT_COUNT];       /* sum of per-launch device durations */

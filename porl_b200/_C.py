@@ -43,11 +43,11 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
-CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm")
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "split")
 
 
 class Profile(C.Structure):
-    _fields_ = [("launches", C.c_int64 * 5), ("ms", C.c_double * 5), ("work", C.c_double * 5)]
+    _fields_ = [("launches", C.c_int64 * 6), ("ms", C.c_double * 6), ("work", C.c_double * 6)]
 
 
 _p, _i32, _i64, _f = C.c_void_p, C.c_int32, C.c_int64, C.c_float
@@ -58,6 +58,7 @@ _SIGNATURES = {
     "porl_ctx_create": (C.c_int, [C.POINTER(_p), C.c_int]),
     "porl_ctx_destroy": (C.c_int, [_p]),
     "porl_launch_count": (_i64, [_p]),
+    "porl_tc_launch_count": (_i64, [_p]),
     "porl_ctx_status_ptr": (C.c_int, [_p, C.POINTER(_p)]),
     "porl_ctx_set_gemm_mode": (C.c_int, [_p, C.c_int]),
     "porl_ctx_get_gemm_mode": (C.c_int, [_p]),
@@ -145,6 +146,10 @@ class Context:
         check(lib.porl_profile_read(self.handle, C.byref(out)))
         return {c: {"launches": int(out.launches[i]), "ms": float(out.ms[i]), "work": float(out.work[i])}
                 for i, c in enumerate(CATEGORIES)}
+
+    @property
+    def tc_launches(self) -> int:
+        return int(lib.porl_tc_launch_count(self.handle))
 
     def set_gemm_mode(self, mode: int) -> None:
         check(lib.porl_ctx_set_gemm_mode(self.handle, mode))

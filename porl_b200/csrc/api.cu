@@ -31,6 +31,8 @@ int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, c
                    g.lda, g.ldb);
     PORL_CHECK_ARG(g.epilogue >= 0 && g.epilogue <= 2, "contraction group %d: epilogue=%d", i, g.epilogue);
     PORL_CHECK_ARG(!g.relu_src || g.ld_relu >= g.N, "contraction group %d: ld_relu=%d", i, g.ld_relu);
+    PORL_CHECK_ARG((!g.A_lo || aligned16(g.A_lo)) && (!g.B_lo || aligned16(g.B_lo)) && (!g.C_lo || aligned16(g.C_lo)),
+                   "contraction group %d: lo planes must be 16-byte aligned", i);
   }
   double flops = 0.0;
   for (int i = 0; i < batch.n_groups; ++i)
@@ -81,6 +83,7 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   porl_ctx* ctx = new porl_ctx();
   ctx->profiling = false;
   ctx->launches = 0;
+  ctx->tc_launches = 0;
   ctx->sem = nullptr;
   ctx->partials = nullptr;
   ctx->counters = nullptr;
@@ -92,8 +95,8 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   cudaError_t rc = cudaMalloc(&ctx->sem, kSemInts * sizeof(int));
   if (rc == cudaSuccess) rc = cudaMemset(ctx->sem, 0, kSemInts * sizeof(int));
   if (rc == cudaSuccess) rc = cudaMalloc(&ctx->partials, kPartialFloats * sizeof(float));
-  if (rc == cudaSuccess) rc = cudaMalloc(&ctx->counters, 64 * sizeof(uint32_t));
-  if (rc == cudaSuccess) rc = cudaMemset(ctx->counters, 0, 64 * sizeof(uint32_t));
+  if (rc == cudaSuccess) rc = cudaMalloc(&ctx->counters, kCounterWords * sizeof(uint32_t));
+  if (rc == cudaSuccess) rc = cudaMemset(ctx->counters, 0, kCounterWords * sizeof(uint32_t));
   cudaSetDevice(prev);
   if (rc != cudaSuccess) {
     set_error("porl_ctx_create: workspace allocation failed: %s", cudaGetErrorString(rc));
@@ -140,6 +143,8 @@ extern "C" int porl_profile_read(porl_ctx_t* ctx, porl_profile_t* out) {
 
 extern "C" int64_t porl_launch_count(const porl_ctx_t* ctx) { return ctx ? ctx->launches : -1; }
 
+extern "C" int64_t porl_tc_launch_count(const porl_ctx_t* ctx) { return ctx ? ctx->tc_launches : -1; }
+
 extern "C" int porl_ctx_status_ptr(porl_ctx_t* ctx, uint32_t** out) {
   PORL_CHECK_ARG(ctx && out, "porl_ctx_status_ptr: null argument");
   *out = ctx->counters;
@@ -164,10 +169,31 @@ extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, in
   GemmBatch b;
   b.n_groups = 1;
   GemmGroup& g = b.g[0];
-  g.A = A; g.B = B; g.C = C; g.bias = bias; g.relu_src = relu_src; g.colsum = colsum;
+  g.A = A; g.B = B; g.C = C; g.A_lo = nullptr; g.B_lo = nullptr; g.C_lo = nullptr; g.bias = bias; g.relu_src = relu_src; g.colsum = colsum;
   g.M = (int)M; g.N = (int)N; g.K = (int)K;
   g.lda = (int)lda; g.ldb = (int)ldb; g.ldc = (int)ldc; g.ld_relu = (int)ld_relu;
   g.n_store = (int)(n_store > 0 ? n_store : N);
   g.epilogue = epilogue;
+  if (ctx->gemm_mode == 1 && A && B && (lda & 3) == 0 && (ldb & 3) == 0 && !colsum) {
+    // 3xTF32 mode: split both operands into (hi, lo) planes held in a context-owned scratch
+    const int64_t na = (a_kmajor ? M : K) * lda, nb = (b_kmajor ? N : K) * ldb;
+    const size_t need = (size_t)(2 * (na + nb));
+    if (ctx->split_ws_floats < need) {
+      if (ctx->split_ws) cudaFree(ctx->split_ws);
+      ctx->split_ws = nullptr;
+      ctx->split_ws_floats = 0;
+      PORL_CUDA(cudaMalloc(&ctx->split_ws, need * sizeof(float)));
+      ctx->split_ws_floats = need;
+    }
+    float* w = ctx->split_ws;
+    SplitBatch sb;
+    sb.n_seg = 2;
+    sb.seg[0] = SplitSeg{A, w, w + na, na};
+    sb.seg[1] = SplitSeg{B, w + 2 * na, w + 2 * na + nb, nb};
+    int rc = launch_split(ctx, sb, as_stream(stream));
+    if (rc != PORL_OK) return rc;
+    g.A = w; g.A_lo = w + na;
+    g.B = w + 2 * na; g.B_lo = w + 2 * na + nb;
+  }
   return launch_gemm(ctx, a_kmajor != 0, b_kmajor != 0, b, as_stream(stream));
 }

@@ -18,6 +18,9 @@ namespace porl {
 constexpr int kMaxGroups = 8;       // problems per grouped contraction launch
 constexpr int kSemInts = 1 << 16;   // split-K turnstile words
 constexpr int kPartialFloats = 1 << 18;  // block partials of the loss reductions
+constexpr int kTicketBase = 64;          // counters[0] status, [1..63] kernel tickets, then per-chunk tickets
+constexpr int kTickets = 4096;
+constexpr int kCounterWords = kTicketBase + kTickets;
 
 void set_error(const char* fmt, ...);
 
@@ -36,6 +39,7 @@ struct porl_ctx {
   int sm_count;
   int gemm_mode;            // 0 = fp32 FFMA, 1 = tcgen05 3xTF32 where supported
   int64_t launches;
+  int64_t tc_launches;
   int* sem;                 // zero-initialised turnstile words (self-resetting)
   float* partials;          // loss reduction partials
   uint32_t* counters;       // [0] status word, [1..] last-block-done counters

@@ -10,10 +10,18 @@ namespace porl {
 // Linear forward   y = x W^T      : A = x (kmajor),  B = W (kmajor)
 // Linear input grad dx = dy W     : A = dy (kmajor), B = W (not kmajor)
 // Linear weight grad dW = dy^T x  : A = dy (not kmajor), B = x (not kmajor), K = batch
+//
+// Split ("pair") operands: in the tcgen05 3xTF32 mode an fp32 matrix travels as two planes,
+// hi = round-to-tf32(x) and lo = x - hi (hi + lo == x exactly).  A_lo / B_lo / C_lo are the lo planes
+// (same geometry as the hi planes in A / B / C); null means a plain fp32 matrix.  The FFMA kernel
+// accepts pairs too (it adds the planes on load, splits on store), so both paths interoperate.
 struct GemmGroup {
   const float* A;
   const float* B;
   float* C;
+  const float* A_lo;
+  const float* B_lo;
+  float* C_lo;
   const float* bias;      // (N) added once, or null
   const float* relu_src;  // (M, ld_relu): C is zeroed where relu_src <= 0 (ReLU backward), or null
   float* colsum;          // (M): sum_k A(m,k) (bias gradient in the dW form), or null
@@ -34,6 +42,30 @@ struct GemmBatch {
 // Validates and launches one grouped contraction; all groups share the trans flags.
 int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream);
 int launch_gemm_simt(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream);
+// hi = x rounded to tf32 (10-bit mantissa, round half away), exactly representable in tf32
+__host__ __device__ inline float tf32_hi(float x) {
+#ifdef __CUDA_ARCH__
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+#else
+  union { float f; unsigned u; } v;
+  v.f = x;
+  v.u = (v.u + 0x1000u) & 0xffffe000u;
+  return v.f;
+#endif
+}
+
+// ---- helpers of the 3xTF32 mode (split.cu) ----
+constexpr int kMaxSegs = 16;
+struct SplitSeg { const float* src; float* hi; float* lo; int64_t n; };          // n floats, multiple of 4
+struct SplitBatch { SplitSeg seg[kMaxSegs]; int n_seg; };
+struct TransposeSeg { const float* src; float* hi; float* lo; int rows, cols, ld_src, ld_dst; };
+struct TransposeBatch { TransposeSeg seg[kMaxSegs]; int n_seg; };
+struct ColsumSeg { const float* hi; const float* lo; float* out; int64_t rows; int n, ld; };
+struct ColsumBatch { ColsumSeg seg[kMaxGroups]; int n_seg; int max_n; };
+int launch_split(porl_ctx* ctx, const SplitBatch& sb, cudaStream_t st);
+int launch_transpose_split(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st);
+int launch_colsum_pair(porl_ctx* ctx, ColsumBatch& cb, cudaStream_t st);
+
 // tcgen05 3xTF32 path; returns PORL_ERR_UNSUPPORTED when the shapes do not fit it.
 int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream);
 

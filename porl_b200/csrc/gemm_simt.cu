@@ -19,8 +19,8 @@ struct TileLoader {
 
   // P: operand base; ld: leading dimension; o0: first outer index; outer_n: outer extent;
   // k0: first k; k_n: K extent.
-  __device__ __forceinline__ void load(const float* __restrict__ P, int ld, int o0, int outer_n,
-                                       int k0, int k_n, int tid) {
+  __device__ __forceinline__ void load(const float* __restrict__ P, const float* __restrict__ Plo, int ld,
+                                       int o0, int outer_n, int k0, int k_n, int tid) {
 #pragma unroll
     for (int i = 0; i < kVec; ++i) {
       const int f = tid + i * 256;
@@ -30,6 +30,10 @@ struct TileLoader {
         const int o = o0 + row, k = k0 + kq;
         if (o < outer_n && k < k_n) {
           r = *reinterpret_cast<const float4*>(P + (size_t)o * ld + k);
+          if (Plo) {
+            const float4 q = *reinterpret_cast<const float4*>(Plo + (size_t)o * ld + k);
+            r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
+          }
           if (k + 1 >= k_n) r.y = 0.f;
           if (k + 2 >= k_n) r.z = 0.f;
           if (k + 3 >= k_n) r.w = 0.f;
@@ -39,6 +43,10 @@ struct TileLoader {
         const int k = k0 + kr, o = o0 + c4;
         if (k < k_n && o < outer_n) {
           r = *reinterpret_cast<const float4*>(P + (size_t)k * ld + o);
+          if (Plo) {
+            const float4 q = *reinterpret_cast<const float4*>(Plo + (size_t)k * ld + o);
+            r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
+          }
           if (o + 1 >= outer_n) r.y = 0.f;
           if (o + 2 >= outer_n) r.z = 0.f;
           if (o + 3 >= outer_n) r.w = 0.f;
@@ -106,8 +114,8 @@ gemm_simt_kernel(const __grid_constant__ GemmBatch batch) {
   TileLoader<BN, BK> lb;
 
   if (kt_begin < kt_end) {
-    la.load(G.A, G.lda, m0, G.M, kt_begin * BKT, G.K, tid);
-    lb.load(G.B, G.ldb, n0, G.N, kt_begin * BKT, G.K, tid);
+    la.load(G.A, G.A_lo, G.lda, m0, G.M, kt_begin * BKT, G.K, tid);
+    lb.load(G.B, G.B_lo, G.ldb, n0, G.N, kt_begin * BKT, G.K, tid);
     la.store(As[0], tid);
     lb.store(Bs[0], tid);
   }
@@ -117,8 +125,8 @@ gemm_simt_kernel(const __grid_constant__ GemmBatch batch) {
     const int buf = (kt - kt_begin) & 1;
     const bool has_next = kt + 1 < kt_end;
     if (has_next) {
-      la.load(G.A, G.lda, m0, G.M, (kt + 1) * BKT, G.K, tid);
-      lb.load(G.B, G.ldb, n0, G.N, (kt + 1) * BKT, G.K, tid);
+      la.load(G.A, G.A_lo, G.lda, m0, G.M, (kt + 1) * BKT, G.K, tid);
+      lb.load(G.B, G.B_lo, G.ldb, n0, G.N, (kt + 1) * BKT, G.K, tid);
     }
 #pragma unroll
     for (int kk = 0; kk < BKT; ++kk) {
@@ -189,6 +197,23 @@ gemm_simt_kernel(const __grid_constant__ GemmBatch batch) {
         }
         o[j] = v;
       }
+      if (G.C_lo) {   // pair output: hi = tf32(v), lo = v - hi
+        float* lrow = G.C_lo + (size_t)row * G.ldc;
+        float l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float h = tf32_hi(o[j]);
+          l[j] = o[j] - h;
+          o[j] = h;
+        }
+        if (vec && col + 3 < G.n_store) {
+          *reinterpret_cast<float4*>(lrow + col) = make_float4(l[0], l[1], l[2], l[3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (col + j < G.n_store) lrow[col + j] = l[j];
+        }
+      }
       if (vec && col + 3 < G.n_store) {
         *reinterpret_cast<float4*>(crow + col) = make_float4(o[0], o[1], o[2], o[3]);
       } else {
@@ -231,7 +256,7 @@ int launch_gemm_simt(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& bat
     max_k = g.K > max_k ? g.K : max_k;
     tiles128 += (long long)((g.M + 127) / 128) * ((g.n_store + 127) / 128);
     tiles64 += (long long)((g.M + 63) / 64) * ((g.n_store + 63) / 64);
-    if (g.epilogue != 0 || g.relu_src != nullptr) can_split = false;
+    if (g.epilogue != 0 || g.relu_src != nullptr || g.C_lo != nullptr) can_split = false;
   }
   const int sms = ctx->sm_count;
   const bool big = tiles128 >= (long long)sms;   // enough 128x128 tiles for one CTA per SM

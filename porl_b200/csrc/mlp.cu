@@ -28,9 +28,16 @@ namespace porl {
 static inline int pad32(int x) { return (int)round_up(x, PORL_PAD); }
 static inline int pad4(int64_t x) { return (int)round_up(x, 4); }
 
-// per-net saved layout helpers
+// Layout of the caller's `saved` buffer (sized for both contraction modes, so the mode may be switched
+// between updates):
+//   [activations] per net, per hidden layer l = 1..L-1:  h hi plane, h lo plane (B x pad32(dims[l]) each)
+//                                                        [+ xhat (B x pad32), rstd (pad4(B)) with LayerNorm]
+//   [x split]     hi, lo planes of the input              (B x pad32(dims[0]) each)       -- 3xTF32 mode only
+//   [w split]     hi, lo planes of the flat parameters    (param floats each)
+//   [w^T split]   per net, per layer l = 1..L-1: W_l^T hi, lo   (dims[l] x pad32(dims[l+1]) each)
+//   [dout split]  hi, lo planes of the head gradient      (n_nets x B x ld_out each)
 static int64_t saved_layer_floats(const porl_mlp* m, int l /*hidden layer 1..L-1*/, int64_t B) {
-  int64_t f = B * m->pad[l];
+  int64_t f = 2 * B * m->pad[l];
   if (m->d.layer_norm) f += B * m->pad[l] + pad4(B);
   return f;
 }
@@ -44,12 +51,38 @@ static float* saved_h(const porl_mlp* m, float* saved, int net, int l, int64_t B
   for (int i = 1; i < l; ++i) p += saved_layer_floats(m, i, B);
   return p;
 }
-static float* saved_xhat(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+static float* saved_h_lo(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
   return saved_h(m, saved, net, l, B) + B * m->pad[l];
 }
-static float* saved_rstd(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+static float* saved_xhat(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
   return saved_h(m, saved, net, l, B) + 2 * B * m->pad[l];
 }
+static float* saved_rstd(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+  return saved_h(m, saved, net, l, B) + 3 * B * m->pad[l];
+}
+static int64_t wt_net_floats(const porl_mlp* m) {
+  int64_t f = 0;
+  for (int l = 1; l < m->d.n_layers; ++l) f += 2 * (int64_t)m->d.dims[l] * m->pad[l + 1];
+  return f;
+}
+static int64_t param_floats(const porl_mlp* m) { return m->net_stride * m->d.n_nets; }
+static float* xsplit_ptr(const porl_mlp* m, float* saved, int64_t B) {
+  return saved + saved_net_floats(m, B) * m->d.n_nets;
+}
+static float* wsplit_ptr(const porl_mlp* m, float* saved, int64_t B) { return xsplit_ptr(m, saved, B) + 2 * B * m->pad[0]; }
+static float* wt_ptr(const porl_mlp* m, float* saved, int64_t B, int net, int l) {
+  float* p = wsplit_ptr(m, saved, B) + 2 * param_floats(m) + net * wt_net_floats(m);
+  for (int i = 1; i < l; ++i) p += 2 * (int64_t)m->d.dims[i] * m->pad[i + 1];
+  return p;
+}
+static float* dsplit_ptr(const porl_mlp* m, float* saved, int64_t B) {
+  return wsplit_ptr(m, saved, B) + 2 * param_floats(m) + m->d.n_nets * wt_net_floats(m);
+}
+static int64_t saved_total_floats(const porl_mlp* m, int64_t B) {
+  return (dsplit_ptr(m, nullptr, B) - (float*)nullptr) + 2 * (int64_t)m->d.n_nets * B * m->ld_out;
+}
+// (hi, lo) planes travel only in the 3xTF32 mode; LayerNorm nets stay on the fp32 FFMA path
+static bool use_pairs(const porl_ctx* ctx, const porl_mlp* m) { return ctx->gemm_mode == 1 && !m->d.layer_norm; }
 
 // ---------------------------------------------------------------- LayerNorm rows
 // z (B, ld) in place -> h = relu(xhat * gamma + beta); xhat and rstd saved.  One warp per row.
@@ -204,11 +237,24 @@ extern "C" int porl_mlp_param_layout(const porl_mlp_t* mlp, int32_t net, int32_t
 
 extern "C" int64_t porl_mlp_saved_floats(const porl_mlp_t* mlp, int64_t B) {
   if (!mlp || B < 0) return -1;
-  int64_t f = saved_net_floats(mlp, B) * mlp->d.n_nets;
-  return f > 0 ? f : 4;
+  return saved_total_floats(mlp, B) + 4;
 }
 
 extern "C" int64_t porl_mlp_out_ld(const porl_mlp_t* mlp) { return mlp ? mlp->ld_out : -1; }
+
+
+static void clear_group(GemmGroup& g) {
+  g.A = g.B = nullptr;
+  g.C = nullptr;
+  g.A_lo = g.B_lo = nullptr;
+  g.C_lo = nullptr;
+  g.bias = g.relu_src = nullptr;
+  g.colsum = nullptr;
+  g.M = g.N = g.K = 0;
+  g.lda = g.ldb = g.ldc = g.ld_relu = 0;
+  g.n_store = 0;
+  g.epilogue = 0;
+}
 
 extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp_call_t* calls, int64_t B,
                                 porl_stream_t stream) {
@@ -222,12 +268,31 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
                        aligned16(k.saved) && aligned16(k.out),
                    "porl_mlp_forward: call %d needs 16-byte aligned buffers and ldx %% 4 == 0 (ldx=%lld)", c,
                    (long long)k.ldx);
+    PORL_CHECK_ARG(!use_pairs(ctx, k.mlp) || k.ldx == k.mlp->pad[0],
+                   "porl_mlp_forward: call %d: the 3xTF32 mode needs ldx == %d (input width padded to %d)", c,
+                   k.mlp->pad[0], PORL_PAD);
     max_layers = k.mlp->d.n_layers > max_layers ? k.mlp->d.n_layers : max_layers;
     total_nets += k.mlp->d.n_nets;
   }
   PORL_CHECK_ARG(total_nets <= kMaxGroups, "porl_mlp_forward: %d nets exceed the %d-problem group limit", total_nets,
                  kMaxGroups);
   cudaStream_t st = as_stream(stream);
+
+  // 3xTF32 mode: split the inputs and the parameters of every call into (hi, lo) planes, one launch
+  SplitBatch sb;
+  sb.n_seg = 0;
+  for (int c = 0; c < n_calls; ++c) {
+    const porl_mlp_call_t& k = calls[c];
+    const porl_mlp* m = k.mlp;
+    if (!use_pairs(ctx, m)) continue;
+    float* xs = xsplit_ptr(m, k.saved, B);
+    sb.seg[sb.n_seg++] = SplitSeg{k.x, xs, xs + B * m->pad[0], B * m->pad[0]};
+    float* ws = wsplit_ptr(m, k.saved, B);
+    sb.seg[sb.n_seg++] = SplitSeg{k.params, ws, ws + param_floats(m), param_floats(m)};
+  }
+  int rc = launch_split(ctx, sb, st);
+  if (rc != PORL_OK) return rc;
+
   for (int l = 0; l < max_layers; ++l) {
     GemmBatch batch;
     batch.n_groups = 0;
@@ -236,17 +301,26 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
       const porl_mlp* m = k.mlp;
       if (l >= m->d.n_layers) continue;
       const bool last = (l == m->d.n_layers - 1);
+      const bool pairs = use_pairs(ctx, m);
       for (int net = 0; net < m->d.n_nets; ++net) {
         GemmGroup& g = batch.g[batch.n_groups++];
+        clear_group(g);
         const float* P = k.params + net * m->net_stride;
-        g.A = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
-        g.lda = (l == 0) ? (int)k.ldx : m->pad[l];
-        g.B = P + m->w_off[l];
+        if (pairs) {
+          const float* ws = wsplit_ptr(m, k.saved, B);
+          const float* xs = xsplit_ptr(m, k.saved, B);
+          g.A = (l == 0) ? xs : saved_h(m, k.saved, net, l, B);
+          g.A_lo = (l == 0) ? xs + B * m->pad[0] : saved_h_lo(m, k.saved, net, l, B);
+          g.B = ws + net * m->net_stride + m->w_off[l];
+          g.B_lo = g.B + param_floats(m);
+          g.lda = m->pad[l];
+        } else {
+          g.A = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
+          g.lda = (l == 0) ? (int)k.ldx : m->pad[l];
+          g.B = P + m->w_off[l];
+        }
         g.ldb = m->pad[l];
         g.bias = P + m->b_off[l];
-        g.relu_src = nullptr;
-        g.ld_relu = 0;
-        g.colsum = nullptr;
         g.M = (int)B;
         g.N = m->d.dims[l + 1];
         g.K = m->d.dims[l];
@@ -257,13 +331,14 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
           g.epilogue = m->d.out_act == 1 ? 2 : 0;
         } else {
           g.C = saved_h(m, k.saved, net, l + 1, B);
+          if (pairs) g.C_lo = saved_h_lo(m, k.saved, net, l + 1, B);
           g.ldc = m->pad[l + 1];
           g.n_store = m->pad[l + 1];
           g.epilogue = m->d.layer_norm ? 0 : 1;
         }
       }
     }
-    int rc = launch_gemm(ctx, true, true, batch, st);
+    rc = launch_gemm(ctx, true, true, batch, st);
     if (rc != PORL_OK) return rc;
     // LayerNorm + ReLU rows
     for (int c = 0; c < n_calls; ++c) {
@@ -293,76 +368,139 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
                  "porl_mlp_backward: buffers must be 16-byte aligned, ldx %% 4 == 0");
   const porl_mlp* m = call->mlp;
   const int L = m->d.n_layers;
+  const int nn = m->d.n_nets;
+  const bool pairs = use_pairs(ctx, m);
   cudaStream_t st = as_stream(stream);
+  float* saved = call->saved;
+  int rc;
+
+  if (pairs) {
+    // head gradient -> (hi, lo); W_l^T (hi, lo) for the input-gradient contractions (K-major B operand)
+    SplitBatch sb;
+    sb.n_seg = 1;
+    float* ds = dsplit_ptr(m, saved, B);
+    const int64_t nd = (int64_t)nn * B * m->ld_out;
+    sb.seg[0] = SplitSeg{dout, ds, ds + nd, nd};
+    rc = launch_split(ctx, sb, st);
+    if (rc != PORL_OK) return rc;
+    TransposeBatch tb;
+    tb.n_seg = 0;
+    for (int net = 0; net < nn; ++net) {
+      for (int l = 1; l < L; ++l) {
+        float* wt = wt_ptr(m, saved, B, net, l);
+        TransposeSeg seg;
+        seg.src = call->params + net * m->net_stride + m->w_off[l];
+        seg.hi = wt;
+        seg.lo = wt + (int64_t)m->d.dims[l] * m->pad[l + 1];
+        seg.rows = m->d.dims[l + 1];
+        seg.cols = m->d.dims[l];
+        seg.ld_src = m->pad[l];
+        seg.ld_dst = m->pad[l + 1];
+        tb.seg[tb.n_seg++] = seg;
+        if (tb.n_seg == kMaxSegs) {
+          rc = launch_transpose_split(ctx, tb, st);
+          if (rc != PORL_OK) return rc;
+          tb.n_seg = 0;
+        }
+      }
+    }
+    rc = launch_transpose_split(ctx, tb, st);
+    if (rc != PORL_OK) return rc;
+  }
+
   for (int l = L - 1; l >= 0; --l) {
-    // gradient of this layer's pre-activation output: dout for the head, else the (in-place
-    // rewritten) hidden activation buffer of layer l+1
-    auto dz_ptr = [&](int net) -> float* {
-      return (l == L - 1) ? dout + (int64_t)net * B * m->ld_out : saved_h(m, call->saved, net, l + 1, B);
+    // gradient of this layer's pre-activation output: the head gradient, else the (in-place rewritten)
+    // hidden activation buffer of layer l+1
+    const bool head = (l == L - 1);
+    const int ld_dz = head ? m->ld_out : m->pad[l + 1];
+    auto dz_hi = [&](int net) -> float* {
+      if (!head) return saved_h(m, saved, net, l + 1, B);
+      return (pairs ? dsplit_ptr(m, saved, B) : dout) + (int64_t)net * B * m->ld_out;
     };
-    const int ld_dz = (l == L - 1) ? m->ld_out : m->pad[l + 1];
-    // dW_l = dz^T input, db_l = colsum(dz)
+    auto dz_lo = [&](int net) -> float* {
+      if (!pairs) return nullptr;
+      if (!head) return saved_h_lo(m, saved, net, l + 1, B);
+      return dsplit_ptr(m, saved, B) + (int64_t)nn * B * m->ld_out + (int64_t)net * B * m->ld_out;
+    };
+    // dW_l = dz^T input (contraction over the batch); db_l = sum_b dz
     GemmBatch bw;
     bw.n_groups = 0;
-    for (int net = 0; net < m->d.n_nets; ++net) {
+    ColsumBatch cb;
+    cb.n_seg = 0;
+    for (int net = 0; net < nn; ++net) {
       GemmGroup& g = bw.g[bw.n_groups++];
+      clear_group(g);
       float* G = grads + net * m->net_stride;
-      g.A = dz_ptr(net);
+      g.A = dz_hi(net);
+      g.A_lo = dz_lo(net);
       g.lda = ld_dz;
-      g.B = (l == 0) ? call->x : saved_h(m, call->saved, net, l, B);
-      g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
+      if (pairs) {
+        const float* xs = xsplit_ptr(m, saved, B);
+        g.B = (l == 0) ? xs : saved_h(m, saved, net, l, B);
+        g.B_lo = (l == 0) ? xs + B * m->pad[0] : saved_h_lo(m, saved, net, l, B);
+        g.ldb = m->pad[l];
+        cb.seg[cb.n_seg++] = ColsumSeg{dz_hi(net), dz_lo(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
+      } else {
+        g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);
+        g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
+        g.colsum = G + m->b_off[l];
+      }
       g.C = G + m->w_off[l];
       g.ldc = m->pad[l];
       g.n_store = m->pad[l];
-      g.bias = nullptr;
-      g.relu_src = nullptr;
-      g.ld_relu = 0;
-      g.colsum = G + m->b_off[l];
       g.M = m->d.dims[l + 1];
       g.N = m->d.dims[l];
       g.K = (int)B;
-      g.epilogue = 0;
     }
-    int rc = launch_gemm(ctx, false, false, bw, st);
+    rc = launch_gemm(ctx, false, false, bw, st);
+    if (rc != PORL_OK) return rc;
+    rc = launch_colsum_pair(ctx, cb, st);
     if (rc != PORL_OK) return rc;
     if (l == 0) break;
     // dh_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l
     GemmBatch bx;
     bx.n_groups = 0;
-    for (int net = 0; net < m->d.n_nets; ++net) {
+    for (int net = 0; net < nn; ++net) {
       GemmGroup& g = bx.g[bx.n_groups++];
+      clear_group(g);
       const float* P = call->params + net * m->net_stride;
-      float* h = saved_h(m, call->saved, net, l, B);
-      g.A = dz_ptr(net);
+      float* h = saved_h(m, saved, net, l, B);
+      g.A = dz_hi(net);
+      g.A_lo = dz_lo(net);
       g.lda = ld_dz;
-      g.B = P + m->w_off[l];
-      g.ldb = m->pad[l];
+      if (pairs) {
+        const float* wt = wt_ptr(m, saved, B, net, l);
+        g.B = wt;                                                  // W_l^T: (dims[l], dims[l+1]) K-major
+        g.B_lo = wt + (int64_t)m->d.dims[l] * m->pad[l + 1];
+        g.ldb = m->pad[l + 1];
+        g.C_lo = saved_h_lo(m, saved, net, l, B);
+      } else {
+        g.B = P + m->w_off[l];
+        g.ldb = m->pad[l];
+      }
       g.C = h;
       g.ldc = m->pad[l];
       g.n_store = m->pad[l];
-      g.bias = nullptr;
       g.relu_src = h;
       g.ld_relu = m->pad[l];
-      g.colsum = nullptr;
       g.M = (int)B;
       g.N = m->d.dims[l];
       g.K = m->d.dims[l + 1];
-      g.epilogue = 0;
     }
-    rc = launch_gemm(ctx, true, false, bx, st);
+    rc = launch_gemm(ctx, true, pairs, bx, st);
     if (rc != PORL_OK) return rc;
     if (m->d.layer_norm) {
-      for (int net = 0; net < m->d.n_nets; ++net) {
+      for (int net = 0; net < nn; ++net) {
         const float* P = call->params + net * m->net_stride;
         float* G = grads + net * m->net_stride;
-        float* dy = saved_h(m, call->saved, net, l, B);
-        const float* xh = saved_xhat(m, call->saved, net, l, B);
+        float* dy = saved_h(m, saved, net, l, B);
+        const float* xh = saved_xhat(m, saved, net, l, B);
         const int d = m->d.dims[l];
         ProfScope prof(ctx, PORL_CAT_NORM, (double)B * d * 20.0, st);
         ln_param_grad_kernel<<<(d + 31) / 32, 256, 0, st>>>(dy, xh, B, d, m->pad[l], G + m->lnw_off[l - 1],
                                                             G + m->lnb_off[l - 1]);
         PORL_LAUNCHED(ctx);
-        ln_backward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(dy, xh, saved_rstd(m, call->saved, net, l, B),
+        ln_backward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(dy, xh, saved_rstd(m, saved, net, l, B),
                                                                     P + m->lnw_off[l - 1], B, d, m->pad[l]);
         PORL_LAUNCHED(ctx);
       }

@@ -147,7 +147,11 @@ def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=Fal
 def test_gemm_forms(env, mode, a_k, b_k, M, N, K):
     env[1].set_gemm_mode(mode)
     try:
+        before = env[1].tc_launches
         _gemm(env, a_k, b_k, M, N, K, seed=M + N + K)
+        # the tcgen05 kernel must be the one that ran for tensor-core-sized problems (no silent FFMA fallback)
+        eligible = mode == 1 and a_k == b_k and N >= 64 and K >= 64 and M >= 32
+        assert (env[1].tc_launches - before) == (1 if eligible else 0)
     finally:
         env[1].set_gemm_mode(0)
 

@@ -62,7 +62,12 @@ def test_mlp_geometry_is_padded_and_aligned():
                 idx = v.long().flatten()
                 assert not seen[idx].any()                           # tensors do not overlap
                 seen[idx] = True
-    assert plan.saved_floats(256) == 2 * (2 * (2 * 256 * 512 + 256))
+    B = 256
+    acts = 2 * 2 * (2 * B * 512 + B * 512 + B)          # per net, per hidden layer: h hi/lo planes + xhat + rstd
+    xsplit, wsplit = 2 * B * 384, 2 * plan.n_floats       # 3xTF32 operand planes
+    wt = 2 * (2 * 512 * 512 + 2 * 512 * 32)               # W_2^T, W_3^T planes per net
+    dsplit = 2 * 2 * B * 4
+    assert plan.saved_floats(B) == acts + xsplit + wsplit + wt + dsplit + 4
     with pytest.raises(_C.PorlError):
         plan.layout(0, 2, _C.PARAM_LN_WEIGHT)                        # no LayerNorm after the head
 
