@@ -203,7 +203,7 @@ gemm_simt_kernel(const __grid_constant__ GemmBatch batch) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float h = tf32_hi(o[j]);
-          l[j] = o[j] - h;
+          l[j] = tf32_hi(o[j] - h);
           o[j] = h;
         }
         if (vec && col + 3 < G.n_store) {

@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           }
           if (G.C_lo) {
             const float h = tf32_hi(x);
-            G.C_lo[(size_t)row * G.ldc + col] = x - h;
+            G.C_lo[(size_t)row * G.ldc + col] = tf32_hi(x - h);
             x = h;
           }
           *cp = x;

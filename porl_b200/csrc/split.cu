@@ -1,11 +1,27 @@
 // Helpers of the 3xTF32 mode: fp32 -> (hi, lo) plane split, transposed weight split, and the
 // batch-sum of a pair (bias gradients).  All L2/HBM-bound elementwise or reduction kernels.
+#include <stdlib.h>
+
 #include "gemm.cuh"
 
 namespace porl {
 
 // ---------------------------------------------------------------- flat split
-__global__ void __launch_bounds__(256) split_kernel(const __grid_constant__ SplitBatch sb) {
+// variant 0: hi = RN_tf32(x), lo = x - hi (full fp32; the tensor core truncates it)
+// variant 1: hi = RN_tf32(x), lo = RN_tf32(x - hi)
+// variant 2: hi = x as is (the tensor core reads its top 19 bits), lo = RN_tf32(x - trunc_tf32(x))
+__device__ __forceinline__ void split1(float v, int variant, float& h, float& l) {
+  if (variant == 2) {
+    h = v;
+    l = tf32_hi(v - __uint_as_float(__float_as_uint(v) & 0xffffe000u));
+  } else {
+    h = tf32_hi(v);
+    l = v - h;
+    if (variant == 1) l = tf32_hi(l);
+  }
+}
+
+__global__ void __launch_bounds__(256) split_kernel(const __grid_constant__ SplitBatch sb, int variant) {
   const SplitSeg& s = sb.seg[blockIdx.y];
   const int64_t n4 = s.n >> 2;
   const float4* src = reinterpret_cast<const float4*>(s.src);
@@ -14,10 +30,10 @@ __global__ void __launch_bounds__(256) split_kernel(const __grid_constant__ Spli
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     const float4 v = src[i];
     float4 h, l;
-    h.x = tf32_hi(v.x); l.x = v.x - h.x;
-    h.y = tf32_hi(v.y); l.y = v.y - h.y;
-    h.z = tf32_hi(v.z); l.z = v.z - h.z;
-    h.w = tf32_hi(v.w); l.w = v.w - h.w;
+    split1(v.x, variant, h.x, l.x);
+    split1(v.y, variant, h.y, l.y);
+    split1(v.z, variant, h.z, l.z);
+    split1(v.w, variant, h.w, l.w);
     hi[i] = h;
     lo[i] = l;
   }
@@ -38,7 +54,12 @@ int launch_split(porl_ctx* ctx, const SplitBatch& sb, cudaStream_t st) {
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   ProfScope prof(ctx, PORL_CAT_SPLIT, (double)total * 12.0, st);
-  split_kernel<<<dim3((unsigned)bx, sb.n_seg), 256, 0, st>>>(sb);
+  static int variant = -1;
+  if (variant < 0) {
+    const char* e = getenv("PORL_SPLIT_VARIANT");
+    variant = e ? atoi(e) : 1;
+  }
+  split_kernel<<<dim3((unsigned)bx, sb.n_seg), 256, 0, st>>>(sb, variant);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }
@@ -64,7 +85,7 @@ __global__ void __launch_bounds__(256) transpose_split_kernel(const __grid_const
       const float v = tile[tx][ty + j];
       const float h = tf32_hi(v);
       s.hi[(size_t)c * s.ld_dst + r] = h;
-      s.lo[(size_t)c * s.ld_dst + r] = v - h;
+      s.lo[(size_t)c * s.ld_dst + r] = tf32_hi(v - h);
     }
   }
 }

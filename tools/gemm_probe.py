@@ -1,0 +1,85 @@
+"""Accuracy + timing probe of the contraction paths on a B200 (run under `timeout`).
+
+  python tools/gemm_probe.py acc      error statistics vs fp64 for the shapes of the SORL step
+  python tools/gemm_probe.py time     per-shape device time (CUDA events inside the library)
+"""
+import os, sys, math
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from porl_b200 import _C
+
+dev = torch.device("cuda:0")
+ctx = _C.context(dev)
+pad = lambda x: (x + 3) // 4 * 4
+SHAPES = [(1, 1, 4096, 512, 362), (1, 1, 4096, 512, 512), (0, 0, 512, 512, 4096), (0, 0, 512, 362, 4096),
+          (1, 0, 4096, 512, 512), (1, 1, 256, 512, 512), (0, 0, 512, 512, 256)]
+
+
+def operands(a_k, b_k, M, N, K, seed=1, relu_like=True):
+    g = torch.Generator().manual_seed(seed)
+    A = torch.randn((M, pad(K)) if a_k else (K, pad(M)), generator=g)
+    B = torch.randn((N, pad(K)) if b_k else (K, pad(N)), generator=g) * 0.05
+    if relu_like:
+        A = A.clamp_min(0)          # activations after ReLU: one-signed sums expose truncation bias
+    return A, B
+
+
+def run(a_k, b_k, M, N, K, Ad, Bd, Cd):
+    _C.check(_C.lib.porl_gemm(ctx.handle, a_k, b_k, M, N, K, Ad.data_ptr(), Ad.stride(0), Bd.data_ptr(), Bd.stride(0),
+                              Cd.data_ptr(), Cd.stride(0), None, 0, None, 0, N, None, _C.stream_ptr()))
+
+
+def acc():
+    for (a_k, b_k, M, N, K) in SHAPES[:4]:
+        A, B = operands(a_k, b_k, M, N, K)
+        Al = A[:, :K] if a_k else A[:, :M].t()
+        Bl = B[:, :K].t() if b_k else B[:, :N]
+        ref = Al.double() @ Bl.double()
+        Ad, Bd = A.to(dev), B.to(dev)
+        scale = float(ref.abs().mean())
+        rows = []
+        for mode in (0, 1):
+            ctx.set_gemm_mode(mode)
+            Cd = torch.zeros(M, pad(N), device=dev)
+            run(a_k, b_k, M, N, K, Ad, Bd, Cd)
+            torch.cuda.synchronize()
+            e = Cd.cpu()[:, :N].double() - ref
+            rows.append((f"mode{mode}", e))
+        ctx.set_gemm_mode(0)
+        torch.backends.cuda.matmul.allow_tf32 = False
+        e = (Al.to(dev) @ Bl.to(dev)).cpu().double() - ref
+        rows.append(("cublas_fp32", e))
+        e = (Al @ Bl).double() - ref
+        rows.append(("cpu_fp32", e))
+        for name, e in rows:
+            print(f"acc form=({a_k},{b_k}) M={M} N={N} K={K} {name:12s} rms_rel={float(e.pow(2).mean().sqrt())/scale:.3e} "
+                  f"max_rel={float(e.abs().max())/scale:.3e} bias_rel={float(e.mean())/scale:+.3e}", flush=True)
+
+
+def time_shapes():
+    for (a_k, b_k, M, N, K) in SHAPES:
+        A, B = operands(a_k, b_k, M, N, K)
+        Ad, Bd = A.to(dev), B.to(dev)
+        Cd = torch.zeros(M, pad(N), device=dev)
+        for mode in (0, 1):
+            if mode == 1 and a_k != b_k:
+                continue
+            ctx.set_gemm_mode(mode)
+            for _ in range(3):
+                run(a_k, b_k, M, N, K, Ad, Bd, Cd)
+            torch.cuda.synchronize()
+            ctx.profile(True)
+            for _ in range(20):
+                run(a_k, b_k, M, N, K, Ad, Bd, Cd)
+            torch.cuda.synchronize()
+            p = ctx.profile_read()
+            ctx.profile(False)
+            c = p["contraction"]
+            us = c["ms"] / c["launches"] * 1e3
+            print(f"time form=({a_k},{b_k}) M={M} N={N} K={K} mode={mode} {us:8.1f} us/launch "
+                  f"{2.0*M*N*K/us*1e-6:7.1f} TFLOP/s (split {p['split']['ms']/20*1e3:.1f} us)", flush=True)
+        ctx.set_gemm_mode(0)
+
+
+if __name__ == "__main__" and len(sys.argv) > 1:
+    {"acc": acc, "time": time_shapes}[sys.argv[1]]()
