@@ -62,16 +62,23 @@ int64_t porl_launch_count(const porl_ctx_t* ctx);
 int64_t porl_tc_launch_count(const porl_ctx_t* ctx);
 /* device address of the 32-bit status word (PORL_FLAG_*), for an async read-back with the losses */
 int porl_ctx_status_ptr(porl_ctx_t* ctx, uint32_t** out);
-/* 0 = fp32 FFMA contractions ("exact" mode); 1 = tcgen05 3xTF32 split contractions where shapes allow */
+/* 0 = fp32 FFMA contractions; 1 = tcgen05 3xTF32 contractions (operands split into tf32 hi/lo in shared
+ * memory, TMEM accumulator restarted every chunk and summed in fp32 registers) where shapes allow */
 int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
+/* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
+int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
+/* profiling aid: device buffer of 16 x 148 uint64 that receives per-CTA globaltimer stamps (kernel start,
+ * setup done, first/last TMA, first split, first/last MMA, chunk drain, epilogue, end; see gemm_tc.cu) of
+ * every tcgen05 contraction launch (NULL disables) */
+int porl_ctx_set_tc_debug(porl_ctx_t* ctx, uint64_t* stamps_dev);
 
 /* ---- per-kernel timing (bench.py's roofline leg) --------------------------------------------- */
 /* While enabled, every launch is bracketed by CUDA events on its own stream and attributed to a
  * category together with its ALGORITHMIC work (flops for contractions, bytes for the HBM-bound
  * kernels).  porl_profile_read synchronises the recorded events and returns per-category sums. */
 enum { PORL_CAT_CONTRACTION = 0, PORL_CAT_GATHER = 1, PORL_CAT_LOSS = 2, PORL_CAT_OPTIMIZER = 3,
-       PORL_CAT_NORM = 4, PORL_CAT_SPLIT = 5, PORL_CAT_COUNT = 6 };
+       PORL_CAT_NORM = 4, PORL_CAT_TRANSPOSE = 5, PORL_CAT_COUNT = 6 };
 typedef struct {
   int64_t launches[PORL_CAT_COUNT];
   double ms[PORL_CAT_COUNT];       /* sum of per-launch device durations */
@@ -143,6 +150,9 @@ typedef struct {
   float* saved;           /* porl_mlp_saved_floats(B) floats; a training forward keeps the activations
                              here for porl_mlp_backward, an inference forward uses it as scratch */
   float* out;             /* (n_nets, B, ld_out) */
+  int32_t inference;      /* 1: no backward follows (skip the transposed activation copies the tensor-core
+                             weight-gradient contractions read); 0: training forward */
+  int32_t pad_;
 } porl_mlp_call_t;
 
 /* Forward of up to PORL_MAX_CALLS MLPs on the same batch size; layer l of every call runs in one
@@ -214,10 +224,16 @@ int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* m, float* v
  *   a_kmajor: A(m,k) = A[m*lda+k] else A[k*lda+m];  b_kmajor: B(k,n) = B[n*ldb+k] else B[k*ldb+n].
  * epilogue: 0 none, 1 relu, 2 tanh; relu_src (M, ld_relu): zero C where relu_src <= 0.
  * n_store >= N: columns N..n_store-1 of C are written as zeros.  colsum (M): sum_k A(m,k), or NULL. */
+/* Ct (N, ldct): optional transposed copy of C (tcgen05 path only: mode 1, both operands K-major).
+ * On the tcgen05 path `bias` is read in 16-byte groups: it must be 16-byte aligned and readable (zero)
+ * through round_up(N, 4) floats. */
 int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, int64_t M, int64_t N, int64_t K,
               const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
               const float* bias, int32_t epilogue, const float* relu_src, int64_t ld_relu,
-              int64_t n_store, float* colsum, porl_stream_t stream);
+              int64_t n_store, float* colsum, float* Ct, int64_t ldct, porl_stream_t stream);
+/* dst (cols, ld_dst) = src (rows, ld_src)^T */
+int porl_transpose(porl_ctx_t* ctx, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* dst,
+                   int64_t ld_dst, porl_stream_t stream);
 
 #ifdef __cplusplus
 }

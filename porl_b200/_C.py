@@ -35,7 +35,7 @@ class MlpDesc(C.Structure):
 
 class MlpCall(C.Structure):
     _fields_ = [("mlp", C.c_void_p), ("params", C.c_void_p), ("x", C.c_void_p), ("ldx", C.c_int64),
-                ("saved", C.c_void_p), ("out", C.c_void_p)]
+                ("saved", C.c_void_p), ("out", C.c_void_p), ("inference", C.c_int32), ("pad_", C.c_int32)]
 
 
 class OptState(C.Structure):
@@ -43,7 +43,7 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
-CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "split")
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose")
 
 
 class Profile(C.Structure):
@@ -82,7 +82,10 @@ _SIGNATURES = {
     "porl_cql_head": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _f, _f, _i64, _i32, _i64, _p, _p, _p]),
     "porl_adam_step": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
     "porl_gemm": (C.c_int, [_p, _i32, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p, _i64,
-                            _i64, _p, _p]),
+                            _i64, _p, _p, _i64, _p]),
+    "porl_transpose": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p]),
+    "porl_ctx_set_tc_chunk": (C.c_int, [_p, C.c_int]),
+    "porl_ctx_set_tc_debug": (C.c_int, [_p, _p]),
 }
 
 EXPORTS = tuple(_SIGNATURES)
@@ -153,6 +156,12 @@ class Context:
 
     def set_gemm_mode(self, mode: int) -> None:
         check(lib.porl_ctx_set_gemm_mode(self.handle, mode))
+
+    def set_tc_chunk(self, k_blocks: int) -> None:
+        check(lib.porl_ctx_set_tc_chunk(self.handle, k_blocks))
+
+    def set_tc_debug(self, ptr) -> None:
+        check(lib.porl_ctx_set_tc_debug(self.handle, ptr))
 
     @property
     def gemm_mode(self) -> int:

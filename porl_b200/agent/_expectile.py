@@ -118,7 +118,7 @@ class ExpectileAgent(nn.Module):
         out_v = ws.get(("out_v", B), 2 * B * plan.out_ld)
         dv = ws.get(("dv", B), 2 * B * plan.out_ld)
         target_v = ws.get(("target_v", B), B)
-        call_t = mlp_call(plan, self._target.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t)
+        call_t = mlp_call(plan, self._target.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t, inference=True)
         call_v = mlp_call(plan, self.v_group.params, pb.obs, pb.ld_obs, saved_v, out_v)
         mlp_forward(ctx, [call_t, call_v], B)
         ld, net = plan.out_ld, B * plan.out_ld * 4
@@ -141,7 +141,7 @@ class ExpectileAgent(nn.Module):
         out_p = ws.get(("out_p", B), B * pplan.out_ld)
         dz_p = ws.get(("dz_p", B), B * pplan.out_ld)
         target_v = ws.get(("target_v", B), B)
-        call_v = mlp_call(vplan, self.v_group.params, pb.obs, pb.ld_obs, scratch_v, out_v2)
+        call_v = mlp_call(vplan, self.v_group.params, pb.obs, pb.ld_obs, scratch_v, out_v2, inference=True)
         call_p = mlp_call(pplan, self.p_group.params, pb.obs, pb.ld_obs, saved_p, out_p)
         mlp_forward(ctx, [call_v, call_p], B)
         off = self._policy.log_std_offset * 4

@@ -42,6 +42,9 @@ int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, c
     int rc = launch_gemm_tc(ctx, a_kmajor, b_kmajor, batch, stream);
     if (rc != PORL_ERR_UNSUPPORTED) return rc;
   }
+  for (int i = 0; i < batch.n_groups; ++i)
+    PORL_CHECK_ARG(!batch.g[i].Ct, "contraction group %d: a transposed output needs the tcgen05 path "
+                   "(gemm mode 1, K-major operands, M, N, K >= 32)", i);
   return launch_gemm_simt(ctx, a_kmajor, b_kmajor, batch, stream);
 }
 
@@ -87,14 +90,16 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->sem = nullptr;
   ctx->partials = nullptr;
   ctx->counters = nullptr;
-  ctx->split_ws = nullptr;
-  ctx->split_ws_floats = 0;
+  ctx->tc_chunk_kb = 1;
+  ctx->tc_ws = nullptr;
+  ctx->tc_dbg = nullptr;
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
   ctx->gemm_mode = 0;
   cudaError_t rc = cudaMalloc(&ctx->sem, kSemInts * sizeof(int));
   if (rc == cudaSuccess) rc = cudaMemset(ctx->sem, 0, kSemInts * sizeof(int));
   if (rc == cudaSuccess) rc = cudaMalloc(&ctx->partials, kPartialFloats * sizeof(float));
+  if (rc == cudaSuccess) rc = cudaMalloc(&ctx->tc_ws, kTcWsFloats * sizeof(float));
   if (rc == cudaSuccess) rc = cudaMalloc(&ctx->counters, kCounterWords * sizeof(uint32_t));
   if (rc == cudaSuccess) rc = cudaMemset(ctx->counters, 0, kCounterWords * sizeof(uint32_t));
   cudaSetDevice(prev);
@@ -111,8 +116,8 @@ extern "C" int porl_ctx_destroy(porl_ctx_t* ctx) {
   if (!ctx) return PORL_OK;
   if (ctx->sem) cudaFree(ctx->sem);
   if (ctx->partials) cudaFree(ctx->partials);
+  if (ctx->tc_ws) cudaFree(ctx->tc_ws);
   if (ctx->counters) cudaFree(ctx->counters);
-  if (ctx->split_ws) cudaFree(ctx->split_ws);
   prof_clear(ctx);
   delete ctx;
   return PORL_OK;
@@ -159,10 +164,22 @@ extern "C" int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode) {
 
 extern "C" int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx) { return ctx ? ctx->gemm_mode : -1; }
 
+extern "C" int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks) {
+  PORL_CHECK_ARG(ctx && k_blocks >= 1 && k_blocks <= 64, "porl_ctx_set_tc_chunk: k_blocks=%d", k_blocks);
+  ctx->tc_chunk_kb = k_blocks;
+  return PORL_OK;
+}
+
+extern "C" int porl_ctx_set_tc_debug(porl_ctx_t* ctx, uint64_t* stamps_dev) {
+  PORL_CHECK_ARG(ctx, "porl_ctx_set_tc_debug: null ctx");
+  ctx->tc_dbg = reinterpret_cast<unsigned long long*>(stamps_dev);
+  return PORL_OK;
+}
+
 extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, int64_t M, int64_t N, int64_t K,
                          const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                          const float* bias, int32_t epilogue, const float* relu_src, int64_t ld_relu,
-                         int64_t n_store, float* colsum, porl_stream_t stream) {
+                         int64_t n_store, float* colsum, float* Ct, int64_t ldct, porl_stream_t stream) {
   PORL_CHECK_ARG(ctx, "porl_gemm: null ctx");
   PORL_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1 << 24) && N < (1 << 24) && K < (1 << 24),
                  "porl_gemm: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
@@ -170,30 +187,10 @@ extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, in
   b.n_groups = 1;
   GemmGroup& g = b.g[0];
   g.A = A; g.B = B; g.C = C; g.A_lo = nullptr; g.B_lo = nullptr; g.C_lo = nullptr; g.bias = bias; g.relu_src = relu_src; g.colsum = colsum;
+  g.Ct = Ct; g.ldct = (int)ldct;
   g.M = (int)M; g.N = (int)N; g.K = (int)K;
   g.lda = (int)lda; g.ldb = (int)ldb; g.ldc = (int)ldc; g.ld_relu = (int)ld_relu;
   g.n_store = (int)(n_store > 0 ? n_store : N);
   g.epilogue = epilogue;
-  if (ctx->gemm_mode == 1 && A && B && (lda & 3) == 0 && (ldb & 3) == 0 && !colsum) {
-    // 3xTF32 mode: split both operands into (hi, lo) planes held in a context-owned scratch
-    const int64_t na = (a_kmajor ? M : K) * lda, nb = (b_kmajor ? N : K) * ldb;
-    const size_t need = (size_t)(2 * (na + nb));
-    if (ctx->split_ws_floats < need) {
-      if (ctx->split_ws) cudaFree(ctx->split_ws);
-      ctx->split_ws = nullptr;
-      ctx->split_ws_floats = 0;
-      PORL_CUDA(cudaMalloc(&ctx->split_ws, need * sizeof(float)));
-      ctx->split_ws_floats = need;
-    }
-    float* w = ctx->split_ws;
-    SplitBatch sb;
-    sb.n_seg = 2;
-    sb.seg[0] = SplitSeg{A, w, w + na, na};
-    sb.seg[1] = SplitSeg{B, w + 2 * na, w + 2 * na + nb, nb};
-    int rc = launch_split(ctx, sb, as_stream(stream));
-    if (rc != PORL_OK) return rc;
-    g.A = w; g.A_lo = w + na;
-    g.B = w + 2 * na; g.B_lo = w + 2 * na + nb;
-  }
   return launch_gemm(ctx, a_kmajor != 0, b_kmajor != 0, b, as_stream(stream));
 }

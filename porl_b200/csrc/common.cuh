@@ -17,6 +17,7 @@ namespace porl {
 
 constexpr int kMaxGroups = 8;       // problems per grouped contraction launch
 constexpr int kSemInts = 1 << 16;   // split-K turnstile words
+constexpr size_t kTcWsFloats = (size_t)1 << 24;   // 64 MB of split-K partial tiles for the tcgen05 kernel
 constexpr int kPartialFloats = 1 << 18;  // block partials of the loss reductions
 constexpr int kTicketBase = 64;          // counters[0] status, [1..63] kernel tickets, then per-chunk tickets
 constexpr int kTickets = 4096;
@@ -43,8 +44,9 @@ struct porl_ctx {
   int* sem;                 // zero-initialised turnstile words (self-resetting)
   float* partials;          // loss reduction partials
   uint32_t* counters;       // [0] status word, [1..] last-block-done counters
-  float* split_ws;          // 3xTF32 operand split scratch
-  size_t split_ws_floats;
+  float* tc_ws;             // split-K partial tiles of the tcgen05 kernel (kTcWsFloats)
+  int tc_chunk_kb;          // k-blocks per TMEM accumulation chunk of the tcgen05 kernel (1 or 2)
+  unsigned long long* tc_dbg;  // optional per-CTA timestamps of the tcgen05 kernel (device memory), or null
 };
 
 #define PORL_CHECK_ARG(cond, ...)                \

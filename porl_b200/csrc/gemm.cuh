@@ -11,10 +11,9 @@ namespace porl {
 // Linear input grad dx = dy W     : A = dy (kmajor), B = W (not kmajor)
 // Linear weight grad dW = dy^T x  : A = dy (not kmajor), B = x (not kmajor), K = batch
 //
-// Split ("pair") operands: in the tcgen05 3xTF32 mode an fp32 matrix travels as two planes,
-// hi = round-to-tf32(x) and lo = x - hi (hi + lo == x exactly).  A_lo / B_lo / C_lo are the lo planes
-// (same geometry as the hi planes in A / B / C); null means a plain fp32 matrix.  The FFMA kernel
-// accepts pairs too (it adds the planes on load, splits on store), so both paths interoperate.
+// A_lo / B_lo / C_lo: optional second planes the FFMA kernel adds on load / splits on store
+// (legacy of the first 3xTF32 design, which kept (hi, lo) planes in HBM; the tcgen05 kernel now
+// splits in shared memory and takes plain fp32 operands, so these stay null on the product path).
 struct GemmGroup {
   const float* A;
   const float* B;
@@ -24,9 +23,10 @@ struct GemmGroup {
   float* C_lo;
   const float* bias;      // (N) added once, or null
   const float* relu_src;  // (M, ld_relu): C is zeroed where relu_src <= 0 (ReLU backward), or null
-  float* colsum;          // (M): sum_k A(m,k) (bias gradient in the dW form), or null
+  float* colsum;          // (M): sum_k A(m,k) (bias gradient in the dW form), or null (FFMA path only)
+  float* Ct;              // optional transposed copy of the result: Ct[n * ldct + m] (tcgen05 path only), or null
   int M, N, K;
-  int lda, ldb, ldc, ld_relu;
+  int lda, ldb, ldc, ld_relu, ldct;
   int n_store;            // >= N; columns N..n_store-1 are written as zeros
   int epilogue;           // 0 none, 1 relu, 2 tanh
 };
@@ -54,19 +54,18 @@ __host__ __device__ inline float tf32_hi(float x) {
 #endif
 }
 
-// ---- helpers of the 3xTF32 mode (split.cu) ----
+// ---- helpers of the tensor-core mode (transpose.cu) ----
 constexpr int kMaxSegs = 16;
-struct SplitSeg { const float* src; float* hi; float* lo; int64_t n; };          // n floats, multiple of 4
-struct SplitBatch { SplitSeg seg[kMaxSegs]; int n_seg; };
-struct TransposeSeg { const float* src; float* hi; float* lo; int rows, cols, ld_src, ld_dst; };
+// dst (cols, ld_dst) = src (rows, ld_src)^T, plain fp32
+struct TransposeSeg { const float* src; float* dst; int rows, cols, ld_src, ld_dst; };
 struct TransposeBatch { TransposeSeg seg[kMaxSegs]; int n_seg; };
-struct ColsumSeg { const float* hi; const float* lo; float* out; int64_t rows; int n, ld; };
+struct ColsumSeg { const float* src; float* out; int64_t rows; int n, ld; };   // out[j] = sum_r src[r, j]
 struct ColsumBatch { ColsumSeg seg[kMaxGroups]; int n_seg; int max_n; };
-int launch_split(porl_ctx* ctx, const SplitBatch& sb, cudaStream_t st);
-int launch_transpose_split(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st);
-int launch_colsum_pair(porl_ctx* ctx, ColsumBatch& cb, cudaStream_t st);
+int launch_transpose(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st);
+int launch_colsum(porl_ctx* ctx, ColsumBatch& cb, cudaStream_t st);
 
-// tcgen05 3xTF32 path; returns PORL_ERR_UNSUPPORTED when the shapes do not fit it.
+// tcgen05 3xTF32 path (K-major operands only); returns PORL_ERR_UNSUPPORTED when the shapes do not fit it.
+bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor);
 int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream);
 
 }  // namespace porl

@@ -1,18 +1,27 @@
-// tcgen05 3xTF32 grouped contraction: fp32-grade accuracy on the 5th-gen tensor cores.
+// tcgen05 3xTF32 grouped contraction with fp32-grade accuracy: C[M,N] = A[M,K] * B[N,K]^T, both
+// operands plain fp32, K-major (K contiguous), optional transposed copy Ct[N,M] of the result.
 //
-// Every operand arrives as a (hi, lo) pair of tf32-exact planes (gemm.cuh).  One output tile
-// C[128 x 128] per CTA; per 32-wide k-block TMA stages four swizzled tiles (A_hi, A_lo, B_hi, B_lo,
-// 16 KB each) and one elected thread issues, per 8-wide k-step, three tcgen05.mma.kind::tf32 into a
-// single fp32 TMEM accumulator:   A_lo*B_hi + A_hi*B_lo + A_hi*B_hi   (the A_lo*B_lo term, 2^-22
-// relative, is dropped).  Warp roles: 0 = TMA producer, 1 = TMEM allocator + MMA issuer,
-// 2..5 = epilogue (tcgen05.ld -> smem transpose -> coalesced global stores with bias / ReLU / tanh /
-// ReLU-mask / pair split fused).  mbarrier ring: full[s] (TMA -> MMA), empty[s] (tcgen05.commit -> TMA),
-// tmem_full (last commit -> epilogue).  Split-K uses the same turnstile words as the FFMA kernel.
-//
-// Operand forms:
-//   K-major  (x W^T forward, dy W^T' input gradient): smem tile = 128 rows x 128 B, SWIZZLE_128B.
-//   MN-major (dy^T x weight gradient, contraction over the batch): four 32(mn) x 32(k) boxes,
-//            SWIZZLE_128B with 32-byte atoms -- the only MN-major layout tcgen05 accepts for tf32.
+// Persistent, warp-specialised kernel, one CTA per SM, 128x128 output tiles, 32-wide k-blocks:
+//   warp 0      TMA producer: raw fp32 A / B tiles (128 rows x 128 B, SWIZZLE_128B) -> stage ring
+//   warps 2..5  splitters: lo = RN_tf32(x - trunc_tf32(x)) written next to the raw tile (same
+//               swizzled layout, so the split is a flat elementwise pass over the stage).  The raw
+//               tile itself serves as the hi operand: kind::tf32 reads only the top 19 bits of
+//               each fp32 container, i.e. it truncates, and the split is built on that truncation.
+//   warp 1      TMEM allocator + MMA issuer: per k-block 8 "small" MMAs (A_lo*B_hi, A_hi*B_lo for
+//               the four 8-wide k-steps) then 4 "big" ones (A_hi*B_hi), all into one fp32 TMEM
+//               accumulator that is RESTARTED every chunk (chunk_kb k-blocks, default 1).
+//   warps 6..9  accumulators + epilogue: drain each chunk's TMEM accumulator (tcgen05.ld) and add it
+//               to a register accumulator with round-to-nearest fp32 adds, in fixed order.  The
+//               tensor core truncates (RZ) on every accumulate; restarting the TMEM accumulator
+//               every 32..64 k keeps that error at the fp32 rounding level (measured: DESIGN.md).
+//               After the last chunk: bias / ReLU / tanh / ReLU-mask epilogue straight from the
+//               registers (thread = row): 16-byte row-major stores, coalesced transposed stores.
+// TMEM holds two chunk accumulators (2 x 128 columns) so the MMAs of chunk c+1 overlap the drain
+// of chunk c.  mbarriers: raw_full[s] (TMA -> splitters), split_done[s] (splitters -> MMA),
+// empty[s] (tcgen05.commit -> TMA), tmem_full[b] (commit -> accumulators), tmem_empty[b].
+// Split-K (weight gradients, K = batch): every slice parks its partial tile in a workspace and the last
+// slice to arrive sums the partials in slice order, so results are bitwise reproducible and no slice
+// waits for another one.
 #include <cuda.h>
 
 #include <unordered_map>
@@ -23,17 +32,25 @@ namespace porl {
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;      // tile; BK floats = one 128-byte swizzle span
 constexpr int TC_STAGES = 3;
-constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB per plane tile
-constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES;         // A_hi, A_lo, B_hi, B_lo
-constexpr int TC_EPI_FLOATS = 4 * 32 * 33;                // per-warp 32x33 transpose scratch
+constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB
+constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES;         // A_raw, B_raw, A_lo, B_lo
+constexpr int TC_EPI_FLOATS = 0;                          // the epilogue stores straight from registers
+constexpr int TC_NUM_BARS = 3 * TC_STAGES + 4;
 constexpr int TC_SMEM_BYTES = 1024 /*align slack*/ + TC_STAGES * TC_STAGE_BYTES + TC_EPI_FLOATS * 4 + 256;
-constexpr int TC_THREADS = 192;
-constexpr int TC_TMEM_COLS = 128;
+constexpr int TC_THREADS = 320;
+constexpr int TC_TMEM_COLS = 256;
+constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 6;
 
 struct alignas(64) TcParams {
   CUtensorMap mapA[kMaxGroups];
   CUtensorMap mapB[kMaxGroups];
   GemmBatch batch;
+  int tile_begin[kMaxGroups + 1];   // prefix sum of tiles per group
+  int tiles_n[kMaxGroups];          // n-tiles per group
+  int total_tiles;
+  int chunk_kb;                     // k-blocks per TMEM accumulation chunk
+  float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
+  unsigned long long* dbg;          // optional per-CTA timestamps (tools/gemm_probe.py), or null
 };
 
 // ------------------------------------------------------------------------------------------ PTX
@@ -44,6 +61,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -57,11 +77,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "}" ::"r"(bar), "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
-                                            int c2) {
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
   asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -94,55 +113,83 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
-// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address, leading /
-// stride byte offsets in 16-byte units, version 1 (sm_100), layout type in bits [61,64).
-template <bool KMAJOR>
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout) of a K-major SWIZZLE_128B
+// tile: start address, SBO = 1024 B (8-row groups of 128-byte rows), version 1 (sm_100), layout type 2.
 __device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
-  // K-major SWIZZLE_128B (type 2): 8-row groups of 128-byte rows are 1024 B apart (SBO); LBO unused.
-  // MN-major SWIZZLE_128B_BASE32B (type 1): 4-row k-atoms 512 B apart (SBO); 32-wide mn blocks one
-  // 32x32 box = 4096 B apart (LBO).
-  constexpr uint64_t lbo = KMAJOR ? 1 : (4096 >> 4);
-  constexpr uint64_t sbo = KMAJOR ? (1024 >> 4) : (512 >> 4);
-  constexpr uint64_t type = KMAJOR ? 2 : 1;
-  return (uint64_t)((addr >> 4) & 0x3fffu) | (lbo << 16) | (sbo << 32) | (1ull << 46) | (type << 61);
+  return (uint64_t)((addr >> 4) & 0x3fffu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+
+// lo plane of the truncation split: x = trunc_tf32(x) + d exactly; lo = d rounded to tf32
+__device__ __forceinline__ float split_lo(float x) {
+  const float d = x - __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+  return __uint_as_float((__float_as_uint(d) + 0x1000u) & 0xffffe000u);
+}
+
+struct TcUnit {
+  int g, tile, m0, n0, kb0, kb1, split;
+};
+
+__device__ __forceinline__ bool tc_decode(const TcParams& P, int u, TcUnit& w) {
+  if (u >= P.total_tiles * P.batch.splits) return false;
+  w.split = u / P.total_tiles;
+  int t = u - w.split * P.total_tiles;
+  int g = 0;
+  while (g + 1 < P.batch.n_groups && t >= P.tile_begin[g + 1]) ++g;
+  t -= P.tile_begin[g];
+  w.g = g;
+  w.tile = t;
+  const int nt = P.tiles_n[g];
+  w.m0 = (t / nt) * TC_BM;
+  w.n0 = (t % nt) * TC_BN;
+  const int nkb = (P.batch.g[g].K + TC_BK - 1) / TC_BK;
+  w.kb0 = (int)((long long)w.split * nkb / P.batch.splits);
+  w.kb1 = (int)((long long)(w.split + 1) * nkb / P.batch.splits);
+  return true;
 }
 
 // ------------------------------------------------------------------------------------------ kernel
-template <bool AK, bool BK>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams P) {
-  const int gi = blockIdx.z % P.batch.n_groups;
-  const int split = blockIdx.z / P.batch.n_groups;
-  const GemmGroup& G = P.batch.g[gi];
-  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * TC_BN;
-  if (m0 >= G.M || n0 >= G.n_store) return;
-
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;                         // SWIZZLE_128B tiles: 1024-B aligned
   uint8_t* base_ptr = smem_raw + (base - raw);
-  float* epi = reinterpret_cast<float*>(base_ptr + TC_STAGES * TC_STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(base_ptr + TC_STAGES * TC_STAGE_BYTES + TC_EPI_FLOATS * 4);
-  // bars[0..S) full, bars[S..2S) empty, bars[2S] tmem_full; then the TMEM base address word
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
+  uint32_t* flag_slot = tmem_slot + 1;
   const uint32_t bar0 = smem_u32(bars);
-  auto full_bar = [&](int s) { return bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return bar0 + 8u * (TC_STAGES + s); };
-  const uint32_t tmem_full_bar = bar0 + 8u * (2 * TC_STAGES);
+  auto raw_full = [&](int s) { return bar0 + 8u * s; };
+  auto split_done = [&](int s) { return bar0 + 8u * (TC_STAGES + s); };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (2 * TC_STAGES + s); };
+  auto tmem_full = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + b); };
+  auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + 2 + b); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkb = (G.K + TC_BK - 1) / TC_BK;
-  const int kb0 = (int)((long long)split * nkb / P.batch.splits);
-  const int kb1 = (int)((long long)(split + 1) * nkb / P.batch.splits);
+  unsigned long long* const dbg = P.dbg ? P.dbg + 16 * blockIdx.x : nullptr;   // [0] start [1] setup done
+  // [2] first TMA issued [3] last TMA issued [4] first split done [5] first MMA issue [6] last MMA commit
+  // [7] first chunk full [8] last chunk drained [9] first tile epilogue done [10] all tiles done [15] end
+  if (dbg && threadIdx.x == 0) dbg[0] = gtime();
 
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapA[gi])) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapB[gi])) : "memory");
+    for (int g = 0; g < P.batch.n_groups; ++g) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapA[g])) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapB[g])) : "memory");
+    }
     for (int s = 0; s < TC_STAGES; ++s) {
-      mbar_init(full_bar(s), 1);
+      mbar_init(raw_full(s), 1);
+      mbar_init(split_done(s), 128);
       mbar_init(empty_bar(s), 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full(b), 1);
+      mbar_init(tmem_empty(b), 128);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -156,127 +203,234 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+  if (dbg && threadIdx.x == 0) dbg[1] = gtime();
+  const int chunk_kb = P.chunk_kb;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       int it = 0;
-      for (int kb = kb0; kb < kb1; ++kb, ++it) {
-        const int s = it % TC_STAGES;
-        const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
-        mbar_wait(empty_bar(s), ph ^ 1u);
-        mbar_expect_tx(full_bar(s), TC_STAGE_BYTES);
-        const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-        const int k = kb * TC_BK;
-#pragma unroll
-        for (int pl = 0; pl < 2; ++pl) {
-          const uint32_t a_dst = st + (uint32_t)pl * TC_TILE_BYTES;
-          const uint32_t b_dst = st + (uint32_t)(2 + pl) * TC_TILE_BYTES;
-          if (AK) {
-            tma_load_3d(a_dst, &P.mapA[gi], full_bar(s), k, m0, pl);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) tma_load_3d(a_dst + j * 4096u, &P.mapA[gi], full_bar(s), m0 + 32 * j, k, pl);
-          }
-          if (BK) {
-            tma_load_3d(b_dst, &P.mapB[gi], full_bar(s), k, n0, pl);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) tma_load_3d(b_dst + j * 4096u, &P.mapB[gi], full_bar(s), n0 + 32 * j, k, pl);
-          }
+      TcUnit w;
+      for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+        for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
+          const int s = it % TC_STAGES;
+          const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
+          mbar_wait(empty_bar(s), ph ^ 1u);
+          mbar_expect_tx(raw_full(s), 2 * TC_TILE_BYTES);
+          const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
+          tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0);
+          tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+          if (dbg && it == 0) dbg[2] = gtime();
         }
       }
+      if (dbg) dbg[3] = gtime();
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      // instruction descriptor: D fp32, A/B tf32, majors, N >> 3 at [17,23), M >> 4 at [24,29)
-      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((AK ? 0u : 1u) << 15) |
-                                 ((BK ? 0u : 1u) << 16) | ((uint32_t)(TC_BN >> 3) << 17) |
+      // instruction descriptor: D fp32, A/B tf32, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
                                  ((uint32_t)(TC_BM >> 4) << 24);
-      constexpr uint32_t a_step = AK ? (32 >> 4) : (1024 >> 4);   // descriptor advance per 8-wide k-step
-      constexpr uint32_t b_step = BK ? (32 >> 4) : (1024 >> 4);
-      int it = 0;
-      uint32_t acc = 0;
-      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+      int it = 0, chunk = 0;
+      TcUnit w;
+      for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+        int kb = w.kb0;
+        while (kb < w.kb1) {
+          const int buf = chunk & 1;
+          mbar_wait(tmem_empty(buf), (((uint32_t)chunk >> 1) & 1u) ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)(buf * TC_BN);
+          const int nk = (w.kb1 - kb) < chunk_kb ? (w.kb1 - kb) : chunk_kb;
+          uint32_t acc = 0;
+          for (int j = 0; j < nk; ++j, ++it) {
+            const int s = it % TC_STAGES;
+            const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
+            mbar_wait(split_done(s), ph);
+            tc_fence_after();
+            if (dbg && it == 0) dbg[5] = gtime();
+            const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
+            const uint64_t a_hi = smem_desc(st), b_hi = smem_desc(st + TC_TILE_BYTES);
+            const uint64_t a_lo = smem_desc(st + 2 * TC_TILE_BYTES), b_lo = smem_desc(st + 3 * TC_TILE_BYTES);
+            // small terms first (they meet the smallest accumulator), then the hi*hi terms
+#pragma unroll
+            for (int ks = 0; ks < TC_BK / 8; ++ks) {
+              const uint64_t o = (uint64_t)(2 * ks);        // 32 bytes per 8-wide k-step, in 16-byte units
+              tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+              acc = 1;
+              tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+            }
+#pragma unroll
+            for (int ks = 0; ks < TC_BK / 8; ++ks) {
+              const uint64_t o = (uint64_t)(2 * ks);
+              tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+            }
+            tc_commit(empty_bar(s));            // frees the stage once these MMAs have read it
+          }
+          tc_commit(tmem_full(buf));            // chunk accumulator complete
+          ++chunk;
+          kb += nk;
+        }
+      }
+      if (dbg) dbg[6] = gtime();
+    }
+  } else if (warp < TC_EPI_WARP0) {
+    // ===================== splitters: lo = RN_tf32(x - trunc_tf32(x)) =====================
+    const int t = threadIdx.x - TC_SPLIT_WARP0 * 32;     // 0..127
+    int it = 0;
+    TcUnit w;
+    for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+      for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
         const int s = it % TC_STAGES;
         const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
-        mbar_wait(full_bar(s), ph);
-        tc_fence_after();
-        const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-        const uint64_t a_hi = smem_desc<AK>(st), a_lo = smem_desc<AK>(st + TC_TILE_BYTES);
-        const uint64_t b_hi = smem_desc<BK>(st + 2 * TC_TILE_BYTES), b_lo = smem_desc<BK>(st + 3 * TC_TILE_BYTES);
+        mbar_wait(raw_full(s), ph);
+        const float4* src = reinterpret_cast<const float4*>(base_ptr + (size_t)s * TC_STAGE_BYTES);
+        float4* dst = reinterpret_cast<float4*>(base_ptr + (size_t)s * TC_STAGE_BYTES + 2 * TC_TILE_BYTES);
 #pragma unroll
-        for (int ks = 0; ks < TC_BK / 8; ++ks) {
-          const uint64_t ao = (uint64_t)(a_step * ks), bo = (uint64_t)(b_step * ks);
-          tc_mma_tf32(tmem_base, a_lo + ao, b_hi + bo, idesc, acc);   // small terms first
-          acc = 1;
-          tc_mma_tf32(tmem_base, a_hi + ao, b_lo + bo, idesc, 1u);
-          tc_mma_tf32(tmem_base, a_hi + ao, b_hi + bo, idesc, 1u);
+        for (int i = 0; i < (2 * TC_TILE_BYTES / 16) / 128; ++i) {
+          const float4 v = src[t + i * 128];
+          float4 l;
+          l.x = split_lo(v.x);
+          l.y = split_lo(v.y);
+          l.z = split_lo(v.z);
+          l.w = split_lo(v.w);
+          dst[t + i * 128] = l;
         }
-        tc_commit(empty_bar(s));            // frees the stage once these MMAs have read it
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> tensor-core reads
+        mbar_arrive(split_done(s));
+        if (dbg && it == 0 && t == 0) dbg[4] = gtime();
       }
-      tc_commit(tmem_full_bar);             // accumulator complete
     }
   } else {
-    // ===================== epilogue: TMEM -> registers -> smem transpose -> global =====================
+    // ===================== accumulators + epilogue =====================
     const int q = warp & 3;                 // TMEM lane quarter this warp may read
-    float* sc = epi + (warp - 2) * (32 * 33);
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    int* turn = nullptr;
-    if (P.batch.splits > 1) {
-      turn = P.batch.sem + gi * P.batch.sem_stride + blockIdx.y * gridDim.x + blockIdx.x;
-      if (lane == 0) {
-        while (ld_acquire(turn) != split) {
-        }
-      }
-      __syncwarp();
-    }
-    const bool first = (split == 0);
-    const int row_base = m0 + 32 * q;
-    for (int c0 = 0; c0 < TC_BN; c0 += 32) {
-      if (n0 + c0 >= G.n_store) break;
-      float v[32];
-      tc_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);   // lane = row, 32 columns
+    int chunk = 0;
+    TcUnit w;
+    for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+      // this tile's problem, by value: loads through a reference into the parameter block would be
+      // re-issued after every global store of the epilogue
+      const GemmGroup& Gp = P.batch.g[w.g];
+      float* const gC = Gp.C;
+      float* const gCt = Gp.Ct;
+      const float* const gBias = Gp.bias;
+      const float* const gRelu = Gp.relu_src;
+      const int gM = Gp.M, gN = Gp.N, gNs = Gp.n_store, gEpi = Gp.epilogue;
+      const size_t ldc = (size_t)Gp.ldc, ldr = (size_t)Gp.ld_relu, ldct = (size_t)Gp.ldct;
+
+      float acc[TC_BN];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) sc[lane * 33 + j] = v[j];
-      __syncwarp();
-      const int col = n0 + c0 + lane;                                       // lane = column from here on
-      const bool col_ok = col < G.n_store;
-      const bool col_real = col < G.N;
-      const float bias = (first && G.bias && col_real) ? G.bias[col] : 0.f;
-      for (int r = 0; r < 32; ++r) {
-        const int row = row_base + r;
-        if (row >= G.M) break;
-        float x = sc[r * 33 + lane];
-        if (col_ok) {
-          float* cp = G.C + (size_t)row * G.ldc + col;
-          if (col_real) {
-            if (!first) x += __ldcg(cp);
-            x += bias;
-            if (G.epilogue == 1) x = fmaxf(x, 0.f);
-            else if (G.epilogue == 2) x = tanhf(x);
-            if (G.relu_src && !(G.relu_src[(size_t)row * G.ld_relu + col] > 0.f)) x = 0.f;
-          } else {
-            x = 0.f;
+      for (int j = 0; j < TC_BN; ++j) acc[j] = 0.f;
+      const int nchunks = (w.kb1 - w.kb0 + chunk_kb - 1) / chunk_kb;
+      for (int c = 0; c < nchunks; ++c, ++chunk) {
+        const int buf = chunk & 1;
+        mbar_wait(tmem_full(buf), ((uint32_t)chunk >> 1) & 1u);
+        tc_fence_after();
+        if (dbg && chunk == 0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[7] = gtime();
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN);
+#pragma unroll
+        for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+          float v[32];
+          tc_ld32(taddr + (uint32_t)c0, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c0 + j] += v[j];
+        }
+        tc_fence_before();
+        mbar_arrive(tmem_empty(buf));
+      }
+
+      if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[8] = gtime();
+      // ---- split-K: every slice parks its partial tile in the workspace; the LAST slice to arrive (ticket)
+      // sums all partials in slice order -- a fixed order, so the result is bitwise reproducible whichever
+      // CTA happens to be last -- and runs the epilogue.  No slice ever waits for another one.
+      if (P.batch.splits > 1) {
+        const int S = P.batch.splits;
+        const int gt = P.tile_begin[w.g] + w.tile;
+        const int r_in_tile = 32 * q + lane;
+        float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * P.total_tiles + gt) * (32 * 128) + r_in_tile;
+#pragma unroll
+        for (int c4 = 0; c4 < TC_BN; c4 += 4)
+          wp[(c4 >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == TC_EPI_WARP0 && lane == 0) {
+          int* ticket = P.batch.sem + gt;
+          const int old = atomicAdd(ticket, 1);
+          const int last = (old == S - 1) ? 1 : 0;
+          if (last) *ticket = 0;                             // self-reset for the next launch (stream-ordered)
+          *flag_slot = (uint32_t)last;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const bool is_last = *reinterpret_cast<volatile uint32_t*>(flag_slot) != 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");      // flag consumed before the next unit rewrites it
+        if (!is_last) continue;
+        __threadfence();
+#pragma unroll
+        for (int j = 0; j < TC_BN; ++j) acc[j] = 0.f;
+        const float4* rp = reinterpret_cast<const float4*>(P.ws) + (size_t)gt * (32 * 128) + r_in_tile;
+        for (int sl = 0; sl < S; ++sl) {
+#pragma unroll
+          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
+            const float4 o = __ldcg(rp + (c4 >> 2) * 128);
+            acc[c4] += o.x; acc[c4 + 1] += o.y; acc[c4 + 2] += o.z; acc[c4 + 3] += o.w;
           }
-          if (G.C_lo) {
-            const float h = tf32_hi(x);
-            G.C_lo[(size_t)row * G.ldc + col] = tf32_hi(x - h);
-            x = h;
-          }
-          *cp = x;
+          rp += (size_t)P.total_tiles * (32 * 128);
         }
       }
-      __syncwarp();
+      // Straight from the register accumulator (thread = output row): row-major C as 16-byte stores
+      // (a warp store covers 32 rows x 16 B; two consecutive stores fill each 32-byte sector), the
+      // transposed copy as fully coalesced 128-byte stores (lanes = consecutive rows of one Ct row).
+      const int row = w.m0 + 32 * q + lane;
+      const bool row_ok = row < gM;
+      float* const crow = gC + (size_t)row * ldc;
+      const float* const rrow = gRelu ? gRelu + (size_t)row * ldr : nullptr;
+      // Pad columns (N <= col < n_store) need no special case: their B rows are out of bounds for TMA, so
+      // their accumulators are exact zeros, C and relu_src own those columns (ldc, ld_relu >= n_store), the
+      // bias is zero-padded to a multiple of 4 and relu maps 0 to 0; only the transposed store is guarded.
+      // One pass per epilogue feature keeps the dynamic instruction count of these single-warp-per-
+      // scheduler roles low (the first versions of this epilogue were instruction-issue bound).
+      if (row_ok) {
+        const int gN4 = (gN + 3) & ~3;
+        if (gBias) {
+#pragma unroll
+          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
+            if (w.n0 + c4 < gN4) {                            // same address in every lane: broadcast load
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(gBias + w.n0 + c4));
+              acc[c4] += b4.x; acc[c4 + 1] += b4.y; acc[c4 + 2] += b4.z; acc[c4 + 3] += b4.w;
+            }
+          }
+        }
+        if (gEpi == 1) {
+#pragma unroll
+          for (int j = 0; j < TC_BN; ++j) acc[j] = fmaxf(acc[j], 0.f);
+        }
+        if (rrow) {
+#pragma unroll
+          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
+            if (w.n0 + c4 < gNs) {
+              const float4 g4 = *reinterpret_cast<const float4*>(rrow + w.n0 + c4);
+              if (!(g4.x > 0.f)) acc[c4] = 0.f;
+              if (!(g4.y > 0.f)) acc[c4 + 1] = 0.f;
+              if (!(g4.z > 0.f)) acc[c4 + 2] = 0.f;
+              if (!(g4.w > 0.f)) acc[c4 + 3] = 0.f;
+            }
+          }
+        }
+#pragma unroll
+        for (int c4 = 0; c4 < TC_BN; c4 += 4) {
+          if (w.n0 + c4 < gNs)
+            *reinterpret_cast<float4*>(crow + w.n0 + c4) = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
+        }
+        if (gCt) {
+          float* ct = gCt + (size_t)w.n0 * ldct + row;
+#pragma unroll
+          for (int j = 0; j < TC_BN; ++j) {
+            if (w.n0 + j < gN) *ct = acc[j];
+            ct += ldct;
+          }
+        }
+      }
+      if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
-    if (P.batch.splits > 1) {
-      __threadfence();
-      // the four epilogue warps of this CTA release the turnstile together
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (warp == 2 && lane == 0) st_release(turn, split + 1 == P.batch.splits ? 0 : split + 1);
-    }
+    if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) dbg[10] = gtime();
   }
 
   tc_fence_before();
@@ -286,6 +440,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS)
                  : "memory");
   }
+  if (dbg && threadIdx.x == 0) dbg[15] = gtime();
 }
 
 // ------------------------------------------------------------------------------------------ host
@@ -309,17 +464,16 @@ static EncodeTiledFn encode_fn() {
 
 struct MapKey {
   const void* ptr;
-  long long plane;   // lo - hi in floats
-  int outer, inner, ld, kmajor;
+  int outer, inner, ld;
   bool operator==(const MapKey& o) const {
-    return ptr == o.ptr && plane == o.plane && outer == o.outer && inner == o.inner && ld == o.ld && kmajor == o.kmajor;
+    return ptr == o.ptr && outer == o.outer && inner == o.inner && ld == o.ld;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.ptr);
     auto mix = [&](size_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix((size_t)k.plane); mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld); mix((size_t)k.kmajor);
+    mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld);
     return h;
   }
 };
@@ -328,12 +482,10 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash>& map_cache() {
   return c;
 }
 
-// 3-D tensor map over a (hi, lo) pair: dims {contiguous extent, strided extent, 2 planes}.
-//   K-major operand  (rows x K, K contiguous):      box {32 k, 128 rows, 1}, SWIZZLE_128B
-//   MN-major operand (K rows x MN, MN contiguous):  box {32 mn, 32 k, 1},    SWIZZLE_128B_ATOM_32B
-static int make_map(CUtensorMap* out, const float* hi, const float* lo, int contiguous, int strided, int ld,
-                    bool kmajor) {
-  MapKey key{hi, (long long)(lo - hi), strided, contiguous, ld, kmajor ? 1 : 0};
+// 2-D tensor map of a K-major fp32 operand (rows x K, K contiguous, row pitch ld floats):
+// box {32 k, 128 rows}, SWIZZLE_128B; out-of-bounds elements (k >= K, row >= rows) read as zero.
+static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, int ld) {
+  MapKey key{ptr, rows, k_extent, ld};
   auto& cache = map_cache();
   auto it = cache.find(key);
   if (it != cache.end()) {
@@ -345,18 +497,15 @@ static int make_map(CUtensorMap* out, const float* hi, const float* lo, int cont
     set_error("cuTensorMapEncodeTiled is not available from the driver");
     return PORL_ERR_CUDA;
   }
-  const long long plane = lo - hi;
-  if (plane <= 0 || (plane & 3)) return PORL_ERR_UNSUPPORTED;
-  cuuint64_t dims[3] = {(cuuint64_t)contiguous, (cuuint64_t)strided, 2};
-  cuuint64_t strides[2] = {(cuuint64_t)ld * 4ull, (cuuint64_t)plane * 4ull};
-  cuuint32_t box[3] = {32u, kmajor ? 128u : 32u, 1u};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(hi), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  kmajor ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  cuuint64_t dims[2] = {(cuuint64_t)k_extent, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4ull};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)TC_BM};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed (%d) for extent %d x %d, ld %d", (int)r, strided, contiguous, ld);
+    set_error("cuTensorMapEncodeTiled failed (%d) for extent %d x %d, ld %d", (int)r, rows, k_extent, ld);
     return PORL_ERR_CUDA;
   }
   if (cache.size() > 4096) cache.clear();
@@ -364,79 +513,76 @@ static int make_map(CUtensorMap* out, const float* hi, const float* lo, int cont
   return PORL_OK;
 }
 
-template <bool AK, bool BK>
-static int launch_cfg(const TcParams& P, dim3 grid, cudaStream_t st) {
+bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor) {
+  if (!a_kmajor || !b_kmajor) return false;
+  if (g.A_lo || g.B_lo || g.C_lo || g.colsum) return false;
+  if (g.N < 32 || g.K < 32 || g.M < 32) return false;
+  if ((double)g.M * g.N * g.K < (double)(1 << 20)) return false;       // tiny problems: FFMA kernel
+  if ((g.lda & 3) || (g.ldb & 3) || !aligned16(g.A) || !aligned16(g.B)) return false;
+  if ((g.ldc & 3) || (g.n_store & 3) || !aligned16(g.C)) return false;   // 16-byte row-major stores
+  if (g.epilogue == 2) return false;                                     // tanh heads are narrow: FFMA kernel
+  if (g.bias && !aligned16(g.bias)) return false;                        // read as float4 through pad4(N)
+  if (g.relu_src && ((g.ld_relu & 3) || g.ld_relu < g.n_store || !aligned16(g.relu_src))) return false;
+  if (g.Ct && g.ldct < g.M) return false;
+  return true;
+}
+
+int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
+  bool can_split = true;
+  int min_nkb = 1 << 30;
+  TcParams P;
+  int tiles = 0;
+  for (int i = 0; i < batch.n_groups; ++i) {
+    const GemmGroup& g = batch.g[i];
+    if (!gemm_tc_eligible(g, a_kmajor, b_kmajor)) return PORL_ERR_UNSUPPORTED;
+    const int nkb = (g.K + TC_BK - 1) / TC_BK;
+    min_nkb = nkb < min_nkb ? nkb : min_nkb;
+    if (g.epilogue != 0 || g.relu_src != nullptr) can_split = false;
+    P.tile_begin[i] = tiles;
+    P.tiles_n[i] = (g.n_store + TC_BN - 1) / TC_BN;
+    tiles += ((g.M + TC_BM - 1) / TC_BM) * P.tiles_n[i];
+  }
+  for (int i = batch.n_groups; i <= kMaxGroups; ++i) P.tile_begin[i] = tiles;
+  for (int i = batch.n_groups; i < kMaxGroups; ++i) P.tiles_n[i] = 1;
+  P.total_tiles = tiles;
+  for (int i = 0; i < batch.n_groups; ++i) {
+    const GemmGroup& g = batch.g[i];
+    int rc = make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
+    if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
+    if (rc != PORL_OK) return rc;
+  }
+  const int sms = ctx->sm_count;
+  int splits = 1;
+  if (can_split && 2 * tiles <= sms) {
+    int want = sms / tiles;
+    int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
+    splits = want < cap ? want : cap;
+    const long long ws_tiles = (long long)(kTcWsFloats / (TC_BM * TC_BN));
+    if ((long long)splits * tiles > ws_tiles) splits = (int)(ws_tiles / tiles);
+    if (splits > 32) splits = 32;
+    if (splits < 1) splits = 1;
+  }
+  if (tiles > kSemInts) splits = 1;
+  batch.splits = splits;
+  batch.sem = ctx->sem;
+  batch.sem_stride = 0;
+  P.ws = ctx->tc_ws;
+  P.batch = batch;
+  P.chunk_kb = ctx->tc_chunk_kb > 0 ? ctx->tc_chunk_kb : 1;
+  P.dbg = ctx->tc_dbg;
+  const long long units = (long long)tiles * splits;
+  const int grid = (int)(units < sms ? units : sms);
+
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<AK, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         TC_SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(max dynamic smem %d) failed: %s", TC_SMEM_BYTES, cudaGetErrorString(e));
       return PORL_ERR_CUDA;
     }
     configured = true;
   }
-  gemm_tc_kernel<AK, BK><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(P);
-  return PORL_OK;
-}
-
-int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
-  if (a_kmajor != b_kmajor) return PORL_ERR_UNSUPPORTED;     // forward / dx (both K-major) and dW (both MN-major)
-  int max_m = 0, max_ns = 0, max_k = 0;
-  long long tiles = 0;
-  bool can_split = true;
-  for (int i = 0; i < batch.n_groups; ++i) {
-    const GemmGroup& g = batch.g[i];
-    if (!g.A_lo || !g.B_lo) return PORL_ERR_UNSUPPORTED;      // operands must be (hi, lo) pairs
-    if (g.colsum) return PORL_ERR_UNSUPPORTED;                 // bias gradients come from colsum_kernel
-    if (g.N < 64 || g.K < 64 || g.M < 32) return PORL_ERR_UNSUPPORTED;
-    if ((g.ldc & 3) || !aligned16(g.C)) return PORL_ERR_UNSUPPORTED;
-    max_m = g.M > max_m ? g.M : max_m;
-    max_ns = g.n_store > max_ns ? g.n_store : max_ns;
-    max_k = g.K > max_k ? g.K : max_k;
-    tiles += (long long)((g.M + TC_BM - 1) / TC_BM) * ((g.n_store + TC_BN - 1) / TC_BN);
-    if (g.epilogue != 0 || g.relu_src != nullptr || g.C_lo != nullptr) can_split = false;
-  }
-  TcParams P;
-  for (int i = 0; i < batch.n_groups; ++i) {
-    const GemmGroup& g = batch.g[i];
-    int rc;
-    if (a_kmajor) {
-      rc = make_map(&P.mapA[i], g.A, g.A_lo, g.K, g.M, g.lda, true);
-      if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.B_lo, g.K, g.N, g.ldb, true);
-    } else {
-      rc = make_map(&P.mapA[i], g.A, g.A_lo, g.M, g.K, g.lda, false);
-      if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.B_lo, g.N, g.K, g.ldb, false);
-    }
-    if (rc != PORL_OK) return rc;
-  }
-  dim3 grid((max_ns + TC_BN - 1) / TC_BN, (max_m + TC_BM - 1) / TC_BM, 1);
-  int splits = 1;
-  const int sms = ctx->sm_count;
-  if (can_split && tiles < sms) {
-    const int nkb = (max_k + TC_BK - 1) / TC_BK;
-    int want = (int)((sms + tiles - 1) / tiles);
-    int cap = nkb / 8;                       // at least 8 k-blocks (256 k) per slice
-    splits = want < cap ? want : cap;
-    if (splits < 1) splits = 1;
-    if (splits > 16) splits = 16;
-    int min_nkb = nkb;
-    for (int i = 0; i < batch.n_groups; ++i) {
-      const int n = (batch.g[i].K + TC_BK - 1) / TC_BK;
-      min_nkb = n < min_nkb ? n : min_nkb;
-    }
-    if (splits > min_nkb) splits = min_nkb;  // never an empty k-slice (the accumulator would be undefined)
-  }
-  const int tiles_per_group = grid.x * grid.y;
-  if (splits > 1 && (long long)tiles_per_group * batch.n_groups > kSemInts) splits = 1;
-  batch.splits = splits;
-  batch.sem = ctx->sem;
-  batch.sem_stride = tiles_per_group;
-  grid.z = batch.n_groups * splits;
-  if (grid.y > 65535 || grid.z > 65535) return PORL_ERR_UNSUPPORTED;
-  P.batch = batch;
-  int rc = a_kmajor ? launch_cfg<true, true>(P, grid, stream) : launch_cfg<false, false>(P, grid, stream);
-  if (rc != PORL_OK) return rc;
+  gemm_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(P);
   ctx->tc_launches++;
   PORL_LAUNCHED(ctx);
   return PORL_OK;

@@ -30,14 +30,18 @@ static inline int pad4(int64_t x) { return (int)round_up(x, 4); }
 
 // Layout of the caller's `saved` buffer (sized for both contraction modes, so the mode may be switched
 // between updates):
-//   [activations] per net, per hidden layer l = 1..L-1:  h hi plane, h lo plane (B x pad32(dims[l]) each)
+//   [activations] per net, per hidden layer l = 1..L-1:  h_l (B x pad32(dims[l])), h_l^T (dims[l] x pad4(B))
 //                                                        [+ xhat (B x pad32), rstd (pad4(B)) with LayerNorm]
-//   [x split]     hi, lo planes of the input              (B x pad32(dims[0]) each)       -- 3xTF32 mode only
-//   [w split]     hi, lo planes of the flat parameters    (param floats each)
-//   [w^T split]   per net, per layer l = 1..L-1: W_l^T hi, lo   (dims[l] x pad32(dims[l+1]) each)
-//   [dout split]  hi, lo planes of the head gradient      (n_nets x B x ld_out each)
+//   [x^T]         (dims[0] x pad4(B))                                                      -- tensor-core mode
+//   [W^T]         per net, per layer l = 1..L-1: W_l^T (dims[l] x pad4(dims[l+1]))
+//   [dout^T]      per net: (dims[L] x pad4(B))
+// The tcgen05 kernel takes K-major operands only, so the backward contractions read transposed copies:
+//   dW_l = dz_{l+1}^T a_l   ->  A = dz_{l+1}^T (dims[l+1] x B),  B = a_l^T (dims[l] x B),   K = batch
+//   da_l = dz_{l+1} W_l     ->  A = dz_{l+1}   (B x dims[l+1]),  B = W_l^T (dims[l] x dims[l+1])
+// h_l^T is written by the forward epilogue, dz_l^T by the input-gradient epilogue (over h_l^T, like dz_l
+// over h_l); x^T, W_l^T and dout^T come from one batched transpose launch at the start of the backward.
 static int64_t saved_layer_floats(const porl_mlp* m, int l /*hidden layer 1..L-1*/, int64_t B) {
-  int64_t f = 2 * B * m->pad[l];
+  int64_t f = B * m->pad[l] + (int64_t)m->d.dims[l] * pad4(B);
   if (m->d.layer_norm) f += B * m->pad[l] + pad4(B);
   return f;
 }
@@ -51,38 +55,41 @@ static float* saved_h(const porl_mlp* m, float* saved, int net, int l, int64_t B
   for (int i = 1; i < l; ++i) p += saved_layer_floats(m, i, B);
   return p;
 }
-static float* saved_h_lo(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+static float* saved_ht(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
   return saved_h(m, saved, net, l, B) + B * m->pad[l];
 }
 static float* saved_xhat(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
-  return saved_h(m, saved, net, l, B) + 2 * B * m->pad[l];
+  return saved_ht(m, saved, net, l, B) + (int64_t)m->d.dims[l] * pad4(B);
 }
 static float* saved_rstd(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
-  return saved_h(m, saved, net, l, B) + 3 * B * m->pad[l];
+  return saved_xhat(m, saved, net, l, B) + B * m->pad[l];
 }
 static int64_t wt_net_floats(const porl_mlp* m) {
   int64_t f = 0;
-  for (int l = 1; l < m->d.n_layers; ++l) f += 2 * (int64_t)m->d.dims[l] * m->pad[l + 1];
+  for (int l = 1; l < m->d.n_layers; ++l) f += (int64_t)m->d.dims[l] * pad4(m->d.dims[l + 1]);
   return f;
 }
-static int64_t param_floats(const porl_mlp* m) { return m->net_stride * m->d.n_nets; }
-static float* xsplit_ptr(const porl_mlp* m, float* saved, int64_t B) {
+static float* xt_ptr(const porl_mlp* m, float* saved, int64_t B) {
   return saved + saved_net_floats(m, B) * m->d.n_nets;
 }
-static float* wsplit_ptr(const porl_mlp* m, float* saved, int64_t B) { return xsplit_ptr(m, saved, B) + 2 * B * m->pad[0]; }
 static float* wt_ptr(const porl_mlp* m, float* saved, int64_t B, int net, int l) {
-  float* p = wsplit_ptr(m, saved, B) + 2 * param_floats(m) + net * wt_net_floats(m);
-  for (int i = 1; i < l; ++i) p += 2 * (int64_t)m->d.dims[i] * m->pad[i + 1];
+  float* p = xt_ptr(m, saved, B) + (int64_t)m->d.dims[0] * pad4(B) + net * wt_net_floats(m);
+  for (int i = 1; i < l; ++i) p += (int64_t)m->d.dims[i] * pad4(m->d.dims[i + 1]);
   return p;
 }
-static float* dsplit_ptr(const porl_mlp* m, float* saved, int64_t B) {
-  return wsplit_ptr(m, saved, B) + 2 * param_floats(m) + m->d.n_nets * wt_net_floats(m);
+static float* doutt_ptr(const porl_mlp* m, float* saved, int64_t B, int net) {
+  return xt_ptr(m, saved, B) + (int64_t)m->d.dims[0] * pad4(B) + m->d.n_nets * wt_net_floats(m) +
+         (int64_t)net * m->d.dims[m->d.n_layers] * pad4(B);
 }
 static int64_t saved_total_floats(const porl_mlp* m, int64_t B) {
-  return (dsplit_ptr(m, nullptr, B) - (float*)nullptr) + 2 * (int64_t)m->d.n_nets * B * m->ld_out;
+  return (doutt_ptr(m, nullptr, B, m->d.n_nets) - (float*)nullptr);
 }
-// (hi, lo) planes travel only in the 3xTF32 mode; LayerNorm nets stay on the fp32 FFMA path
-static bool use_pairs(const porl_ctx* ctx, const porl_mlp* m) { return ctx->gemm_mode == 1 && !m->d.layer_norm; }
+// layer l (dims[l] -> dims[l+1]) runs its three contractions on the tcgen05 path
+static bool tc_layer(const porl_ctx* ctx, const porl_mlp* m, int l, int64_t B) {
+  if (ctx->gemm_mode != 1 || m->d.layer_norm || l < 0 || l >= m->d.n_layers) return false;
+  const int64_t di = m->d.dims[l], dn = m->d.dims[l + 1];
+  return di >= 32 && dn >= 32 && B >= 32 && (double)B * di * dn >= (double)(1 << 20);
+}
 
 // ---------------------------------------------------------------- LayerNorm rows
 // z (B, ld) in place -> h = relu(xhat * gamma + beta); xhat and rstd saved.  One warp per row.
@@ -250,8 +257,9 @@ static void clear_group(GemmGroup& g) {
   g.C_lo = nullptr;
   g.bias = g.relu_src = nullptr;
   g.colsum = nullptr;
+  g.Ct = nullptr;
   g.M = g.N = g.K = 0;
-  g.lda = g.ldb = g.ldc = g.ld_relu = 0;
+  g.lda = g.ldb = g.ldc = g.ld_relu = g.ldct = 0;
   g.n_store = 0;
   g.epilogue = 0;
 }
@@ -268,57 +276,31 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
                        aligned16(k.saved) && aligned16(k.out),
                    "porl_mlp_forward: call %d needs 16-byte aligned buffers and ldx %% 4 == 0 (ldx=%lld)", c,
                    (long long)k.ldx);
-    PORL_CHECK_ARG(!use_pairs(ctx, k.mlp) || k.ldx == k.mlp->pad[0],
-                   "porl_mlp_forward: call %d: the 3xTF32 mode needs ldx == %d (input width padded to %d)", c,
-                   k.mlp->pad[0], PORL_PAD);
     max_layers = k.mlp->d.n_layers > max_layers ? k.mlp->d.n_layers : max_layers;
     total_nets += k.mlp->d.n_nets;
   }
   PORL_CHECK_ARG(total_nets <= kMaxGroups, "porl_mlp_forward: %d nets exceed the %d-problem group limit", total_nets,
                  kMaxGroups);
   cudaStream_t st = as_stream(stream);
-
-  // 3xTF32 mode: split the inputs and the parameters of every call into (hi, lo) planes, one launch
-  SplitBatch sb;
-  sb.n_seg = 0;
-  for (int c = 0; c < n_calls; ++c) {
-    const porl_mlp_call_t& k = calls[c];
-    const porl_mlp* m = k.mlp;
-    if (!use_pairs(ctx, m)) continue;
-    float* xs = xsplit_ptr(m, k.saved, B);
-    sb.seg[sb.n_seg++] = SplitSeg{k.x, xs, xs + B * m->pad[0], B * m->pad[0]};
-    float* ws = wsplit_ptr(m, k.saved, B);
-    sb.seg[sb.n_seg++] = SplitSeg{k.params, ws, ws + param_floats(m), param_floats(m)};
-  }
-  int rc = launch_split(ctx, sb, st);
-  if (rc != PORL_OK) return rc;
+  int rc;
 
   for (int l = 0; l < max_layers; ++l) {
-    GemmBatch batch;
-    batch.n_groups = 0;
+    GemmBatch tc, ff;           // tensor-core problems and FFMA problems of this layer
+    tc.n_groups = ff.n_groups = 0;
     for (int c = 0; c < n_calls; ++c) {
       const porl_mlp_call_t& k = calls[c];
       const porl_mlp* m = k.mlp;
       if (l >= m->d.n_layers) continue;
       const bool last = (l == m->d.n_layers - 1);
-      const bool pairs = use_pairs(ctx, m);
+      const bool on_tc = tc_layer(ctx, m, l, B);
       for (int net = 0; net < m->d.n_nets; ++net) {
+        GemmBatch& batch = on_tc ? tc : ff;
         GemmGroup& g = batch.g[batch.n_groups++];
         clear_group(g);
         const float* P = k.params + net * m->net_stride;
-        if (pairs) {
-          const float* ws = wsplit_ptr(m, k.saved, B);
-          const float* xs = xsplit_ptr(m, k.saved, B);
-          g.A = (l == 0) ? xs : saved_h(m, k.saved, net, l, B);
-          g.A_lo = (l == 0) ? xs + B * m->pad[0] : saved_h_lo(m, k.saved, net, l, B);
-          g.B = ws + net * m->net_stride + m->w_off[l];
-          g.B_lo = g.B + param_floats(m);
-          g.lda = m->pad[l];
-        } else {
-          g.A = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
-          g.lda = (l == 0) ? (int)k.ldx : m->pad[l];
-          g.B = P + m->w_off[l];
-        }
+        g.A = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
+        g.lda = (l == 0) ? (int)k.ldx : m->pad[l];
+        g.B = P + m->w_off[l];
         g.ldb = m->pad[l];
         g.bias = P + m->b_off[l];
         g.M = (int)B;
@@ -331,15 +313,25 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
           g.epilogue = m->d.out_act == 1 ? 2 : 0;
         } else {
           g.C = saved_h(m, k.saved, net, l + 1, B);
-          if (pairs) g.C_lo = saved_h_lo(m, k.saved, net, l + 1, B);
           g.ldc = m->pad[l + 1];
           g.n_store = m->pad[l + 1];
           g.epilogue = m->d.layer_norm ? 0 : 1;
+          // the weight gradient of the next layer reads h^T when it runs on the tensor cores
+          if (on_tc && !k.inference && tc_layer(ctx, m, l + 1, B)) {
+            g.Ct = saved_ht(m, k.saved, net, l + 1, B);
+            g.ldct = pad4(B);
+          }
         }
       }
     }
-    rc = launch_gemm(ctx, true, true, batch, st);
-    if (rc != PORL_OK) return rc;
+    if (tc.n_groups) {
+      rc = launch_gemm(ctx, true, true, tc, st);
+      if (rc != PORL_OK) return rc;
+    }
+    if (ff.n_groups) {
+      rc = launch_gemm(ctx, true, true, ff, st);
+      if (rc != PORL_OK) return rc;
+    }
     // LayerNorm + ReLU rows
     for (int c = 0; c < n_calls; ++c) {
       const porl_mlp_call_t& k = calls[c];
@@ -366,63 +358,66 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
   PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_backward: B=%lld", (long long)B);
   PORL_CHECK_ARG(aligned16(dout) && aligned16(grads) && aligned16(call->x) && (call->ldx & 3) == 0,
                  "porl_mlp_backward: buffers must be 16-byte aligned, ldx %% 4 == 0");
+  PORL_CHECK_ARG(!call->inference, "porl_mlp_backward: the forward of this call ran with inference=1");
   const porl_mlp* m = call->mlp;
   const int L = m->d.n_layers;
   const int nn = m->d.n_nets;
-  const bool pairs = use_pairs(ctx, m);
+  const int ldB = pad4(B);
   cudaStream_t st = as_stream(stream);
   float* saved = call->saved;
   int rc;
 
-  if (pairs) {
-    // head gradient -> (hi, lo); W_l^T (hi, lo) for the input-gradient contractions (K-major B operand)
-    SplitBatch sb;
-    sb.n_seg = 1;
-    float* ds = dsplit_ptr(m, saved, B);
-    const int64_t nd = (int64_t)nn * B * m->ld_out;
-    sb.seg[0] = SplitSeg{dout, ds, ds + nd, nd};
-    rc = launch_split(ctx, sb, st);
-    if (rc != PORL_OK) return rc;
+  // transposed operands the tensor-core layers need and no epilogue has produced
+  {
     TransposeBatch tb;
     tb.n_seg = 0;
+    auto push = [&](const float* src, float* dst, int rows, int cols, int ld_src, int ld_dst) -> int {
+      tb.seg[tb.n_seg++] = TransposeSeg{src, dst, rows, cols, ld_src, ld_dst};
+      if (tb.n_seg == kMaxSegs) {
+        int r = launch_transpose(ctx, tb, st);
+        tb.n_seg = 0;
+        return r;
+      }
+      return PORL_OK;
+    };
+    if (tc_layer(ctx, m, 0, B)) {
+      rc = push(call->x, xt_ptr(m, saved, B), (int)B, m->d.dims[0], (int)call->ldx, ldB);
+      if (rc != PORL_OK) return rc;
+    }
     for (int net = 0; net < nn; ++net) {
       for (int l = 1; l < L; ++l) {
-        float* wt = wt_ptr(m, saved, B, net, l);
-        TransposeSeg seg;
-        seg.src = call->params + net * m->net_stride + m->w_off[l];
-        seg.hi = wt;
-        seg.lo = wt + (int64_t)m->d.dims[l] * m->pad[l + 1];
-        seg.rows = m->d.dims[l + 1];
-        seg.cols = m->d.dims[l];
-        seg.ld_src = m->pad[l];
-        seg.ld_dst = m->pad[l + 1];
-        tb.seg[tb.n_seg++] = seg;
-        if (tb.n_seg == kMaxSegs) {
-          rc = launch_transpose_split(ctx, tb, st);
+        if (!tc_layer(ctx, m, l, B)) continue;
+        rc = push(call->params + net * m->net_stride + m->w_off[l], wt_ptr(m, saved, B, net, l), m->d.dims[l + 1],
+                  m->d.dims[l], m->pad[l], pad4(m->d.dims[l + 1]));
+        if (rc != PORL_OK) return rc;
+        if (!tc_layer(ctx, m, l - 1, B)) {   // h_l came from the FFMA kernel: no transposed copy yet
+          rc = push(saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B, m->d.dims[l], m->pad[l], ldB);
           if (rc != PORL_OK) return rc;
-          tb.n_seg = 0;
         }
       }
+      if (tc_layer(ctx, m, L - 1, B)) {
+        rc = push(dout + (int64_t)net * B * m->ld_out, doutt_ptr(m, saved, B, net), (int)B, m->d.dims[L], m->ld_out,
+                  ldB);
+        if (rc != PORL_OK) return rc;
+      }
     }
-    rc = launch_transpose_split(ctx, tb, st);
+    rc = launch_transpose(ctx, tb, st);
     if (rc != PORL_OK) return rc;
   }
 
   for (int l = L - 1; l >= 0; --l) {
     // gradient of this layer's pre-activation output: the head gradient, else the (in-place rewritten)
-    // hidden activation buffer of layer l+1
+    // hidden activation buffer of layer l+1 (and its transposed twin)
     const bool head = (l == L - 1);
+    const bool on_tc = tc_layer(ctx, m, l, B);
     const int ld_dz = head ? m->ld_out : m->pad[l + 1];
-    auto dz_hi = [&](int net) -> float* {
-      if (!head) return saved_h(m, saved, net, l + 1, B);
-      return (pairs ? dsplit_ptr(m, saved, B) : dout) + (int64_t)net * B * m->ld_out;
+    auto dz = [&](int net) -> float* {
+      return head ? dout + (int64_t)net * B * m->ld_out : saved_h(m, saved, net, l + 1, B);
     };
-    auto dz_lo = [&](int net) -> float* {
-      if (!pairs) return nullptr;
-      if (!head) return saved_h_lo(m, saved, net, l + 1, B);
-      return dsplit_ptr(m, saved, B) + (int64_t)nn * B * m->ld_out + (int64_t)net * B * m->ld_out;
+    auto dzt = [&](int net) -> float* {
+      return head ? doutt_ptr(m, saved, B, net) : saved_ht(m, saved, net, l + 1, B);
     };
-    // dW_l = dz^T input (contraction over the batch); db_l = sum_b dz
+    // dW_l = dz^T a_l (contraction over the batch); db_l = sum_b dz
     GemmBatch bw;
     bw.n_groups = 0;
     ColsumBatch cb;
@@ -431,16 +426,15 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       GemmGroup& g = bw.g[bw.n_groups++];
       clear_group(g);
       float* G = grads + net * m->net_stride;
-      g.A = dz_hi(net);
-      g.A_lo = dz_lo(net);
-      g.lda = ld_dz;
-      if (pairs) {
-        const float* xs = xsplit_ptr(m, saved, B);
-        g.B = (l == 0) ? xs : saved_h(m, saved, net, l, B);
-        g.B_lo = (l == 0) ? xs + B * m->pad[0] : saved_h_lo(m, saved, net, l, B);
-        g.ldb = m->pad[l];
-        cb.seg[cb.n_seg++] = ColsumSeg{dz_hi(net), dz_lo(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
+      if (on_tc) {
+        g.A = dzt(net);
+        g.lda = ldB;
+        g.B = (l == 0) ? xt_ptr(m, saved, B) : saved_ht(m, saved, net, l, B);
+        g.ldb = ldB;
+        cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
       } else {
+        g.A = dz(net);
+        g.lda = ld_dz;
         g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);
         g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
         g.colsum = G + m->b_off[l];
@@ -452,12 +446,13 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       g.N = m->d.dims[l];
       g.K = (int)B;
     }
-    rc = launch_gemm(ctx, false, false, bw, st);
+    rc = launch_gemm(ctx, on_tc, on_tc, bw, st);
     if (rc != PORL_OK) return rc;
-    rc = launch_colsum_pair(ctx, cb, st);
+    rc = launch_colsum(ctx, cb, st);
     if (rc != PORL_OK) return rc;
     if (l == 0) break;
-    // dh_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l
+    // da_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l (and over h_l^T)
+    const bool prev_tc = tc_layer(ctx, m, l - 1, B);
     GemmBatch bx;
     bx.n_groups = 0;
     for (int net = 0; net < nn; ++net) {
@@ -465,15 +460,15 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       clear_group(g);
       const float* P = call->params + net * m->net_stride;
       float* h = saved_h(m, saved, net, l, B);
-      g.A = dz_hi(net);
-      g.A_lo = dz_lo(net);
+      g.A = dz(net);
       g.lda = ld_dz;
-      if (pairs) {
-        const float* wt = wt_ptr(m, saved, B, net, l);
-        g.B = wt;                                                  // W_l^T: (dims[l], dims[l+1]) K-major
-        g.B_lo = wt + (int64_t)m->d.dims[l] * m->pad[l + 1];
-        g.ldb = m->pad[l + 1];
-        g.C_lo = saved_h_lo(m, saved, net, l, B);
+      if (on_tc) {
+        g.B = wt_ptr(m, saved, B, net, l);                        // W_l^T: (dims[l], dims[l+1]) K-major
+        g.ldb = pad4(m->d.dims[l + 1]);
+        if (prev_tc) {
+          g.Ct = saved_ht(m, saved, net, l, B);
+          g.ldct = ldB;
+        }
       } else {
         g.B = P + m->w_off[l];
         g.ldb = m->pad[l];
@@ -487,8 +482,17 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       g.N = m->d.dims[l];
       g.K = m->d.dims[l + 1];
     }
-    rc = launch_gemm(ctx, true, pairs, bx, st);
+    rc = launch_gemm(ctx, true, on_tc, bx, st);
     if (rc != PORL_OK) return rc;
+    if (!on_tc && prev_tc) {   // dz_l came from the FFMA kernel: transpose it for the next weight gradient
+      TransposeBatch tb;
+      tb.n_seg = 0;
+      for (int net = 0; net < nn; ++net)
+        tb.seg[tb.n_seg++] = TransposeSeg{saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B,
+                                          m->d.dims[l], m->pad[l], ldB};
+      rc = launch_transpose(ctx, tb, st);
+      if (rc != PORL_OK) return rc;
+    }
     if (m->d.layer_norm) {
       for (int net = 0; net < nn; ++net) {
         const float* P = call->params + net * m->net_stride;

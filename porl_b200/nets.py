@@ -223,9 +223,9 @@ class Workspace:
 
 
 def mlp_call(plan: FlatMLP, params: torch.Tensor, x: torch.Tensor, ldx: int, saved: torch.Tensor,
-             out: torch.Tensor) -> _C.MlpCall:
+             out: torch.Tensor, inference: bool = False) -> _C.MlpCall:
     return _C.MlpCall(mlp=plan.handle.value, params=params.data_ptr(), x=x.data_ptr(), ldx=ldx,
-                      saved=saved.data_ptr(), out=out.data_ptr())
+                      saved=saved.data_ptr(), out=out.data_ptr(), inference=int(inference), pad_=0)
 
 
 def mlp_forward(ctx: _C.Context, calls: Sequence[_C.MlpCall], batch: int) -> None:
@@ -264,5 +264,5 @@ class InferenceMixin:
         pack_rows(ctx, x, plan.dims[0], xin, plan.in_ld)
         saved = torch.empty(plan.saved_floats(batch), dtype=torch.float32, device=flat.device)
         out = torch.empty(plan.n_nets, batch, plan.out_ld, dtype=torch.float32, device=flat.device)
-        mlp_forward(ctx, [mlp_call(plan, flat, xin, plan.in_ld, saved, out)], batch)
+        mlp_forward(ctx, [mlp_call(plan, flat, xin, plan.in_ld, saved, out, inference=True)], batch)
         return out[:, :, :plan.dims[-1]]

@@ -45,7 +45,7 @@ class CQLTrainer(DQNTrainer):
         dq = ws.get(("pen_dq", B), B * plan.out_ld)
         zeros = ws.get(("pen_z", B), B)
         res = ws.get(("pen_r", 0), 4)
-        mlp_forward(self.ctx, [mlp_call(plan, self.q_group.params, x, plan.in_ld, scratch, out)], B)
+        mlp_forward(self.ctx, [mlp_call(plan, self.q_group.params, x, plan.in_ld, scratch, out, inference=True)], B)
         acts = actions.to(self.device, torch.int64).contiguous()
         check(lib.porl_cql_head(self.ctx.handle, out.data_ptr(), out.data_ptr(), plan.out_ld, acts.data_ptr(),
                                 zeros.data_ptr(), zeros.data_ptr(), 0.0, 1.0, B, self.action_size, B,

@@ -63,7 +63,7 @@ class DQNTrainer:
         out_t = ws.get(("out_t", B), B * plan.out_ld)
         out_q = ws.get(("out_q", B), B * plan.out_ld)
         dq = ws.get(("dq", B), B * plan.out_ld)
-        call_t = mlp_call(plan, self.target_network.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t)
+        call_t = mlp_call(plan, self.target_network.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t, inference=True)
         call_q = mlp_call(plan, self.q_group.params, pb.obs, pb.ld_obs, saved_q, out_q)
         mlp_forward(ctx, [call_t, call_q], B)
         check(lib.porl_cql_head(ctx.handle, out_q.data_ptr(), out_t.data_ptr(), plan.out_ld, pb.actions.data_ptr(),

@@ -99,7 +99,8 @@ def test_replay_buffer_push_batch_equals_push(env):
 
 
 # ------------------------------------------------------------------------------------------ contraction
-def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=False, n_store=None, seed=0):
+def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=False, n_store=None, seed=0,
+          transposed=False):
     _C, ctx, dev = env
     g = torch.Generator().manual_seed(seed)
     pad = lambda x: (x + 3) // 4 * 4
@@ -126,10 +127,16 @@ def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=Fal
     rd = relu_src.to(dev) if relu else None
     cs = torch.zeros(M, device=dev) if colsum else None
     p = lambda t: t.data_ptr() if t is not None else None
+    ldct = pad(M)
+    Ct = torch.full((N, ldct), 7.0, device=dev) if transposed else None
     _C.check(_C.lib.porl_gemm(ctx.handle, int(a_k), int(b_k), M, N, K, p(Ad), Ad.stride(0), p(Bd), Bd.stride(0),
-                              p(Cd), ldc, p(bd), epilogue, p(rd), ldc, n_store, p(cs), _C.stream_ptr()))
+                              p(Cd), ldc, p(bd), epilogue, p(rd), ldc, n_store, p(cs), p(Ct), ldct, _C.stream_ptr()))
     torch.cuda.synchronize()
     got = Cd.cpu()
+    if transposed:
+        assert torch.equal(Ct.cpu()[:, :M].t(), got[:, :N])                # bitwise the same values, transposed
+        if ldct > M:
+            assert bool((Ct.cpu()[:, M:] == 7.0).all())
     scale = float(ref.abs().max())
     err = float((got[:, :N].double() - ref).abs().max())
     assert err <= 2e-6 * max(scale, 1.0) * math.sqrt(K), (err, scale)      # fp32 accumulation over K terms
@@ -150,7 +157,7 @@ def test_gemm_forms(env, mode, a_k, b_k, M, N, K):
         before = env[1].tc_launches
         _gemm(env, a_k, b_k, M, N, K, seed=M + N + K)
         # the tcgen05 kernel must be the one that ran for tensor-core-sized problems (no silent FFMA fallback)
-        eligible = mode == 1 and a_k == b_k and N >= 64 and K >= 64 and M >= 32
+        eligible = mode == 1 and a_k == 1 and b_k == 1 and min(M, N, K) >= 32 and M * N * K >= 2 ** 20
         assert (env[1].tc_launches - before) == (1 if eligible else 0)
     finally:
         env[1].set_gemm_mode(0)
@@ -166,6 +173,13 @@ def test_gemm_epilogues_and_split_k(env, mode):
         _gemm(env, 0, 0, 512, 362, 4096, colsum=True, n_store=384)               # weight grad, split-K + bias grad
         _gemm(env, 0, 0, 1, 512, 4096, colsum=True)                              # scalar-head weight grad
         _gemm(env, 0, 0, 64, 64, 100000, colsum=True)                            # deep split-K
+        _gemm(env, 1, 1, 512, 362, 4096, n_store=384)                            # weight grad, K-major form, split-K
+        _gemm(env, 1, 1, 64, 64, 100000)                                         # deep split-K, K-major
+        _gemm(env, 1, 1, 200, 100, 365, relu=True, n_store=128)                  # ReLU backward mask, K-major
+        if mode == 1:
+            _gemm(env, 1, 1, 300, 200, 365, epilogue=1, bias=True, n_store=224, transposed=True)
+            _gemm(env, 1, 1, 4096, 512, 512, relu=True, transposed=True)
+            _gemm(env, 1, 1, 37, 33, 1000, n_store=36, transposed=True)
     finally:
         env[1].set_gemm_mode(0)
 
@@ -179,7 +193,7 @@ def test_gemm_split_k_is_deterministic(env):
     for _ in range(3):
         Cd = torch.zeros(128, 256, device=dev)
         _C.check(_C.lib.porl_gemm(ctx.handle, 0, 0, 128, 256, 8192, A.data_ptr(), 128, Bm.data_ptr(), 256,
-                                  Cd.data_ptr(), 256, None, 0, None, 0, 256, None, _C.stream_ptr()))
+                                  Cd.data_ptr(), 256, None, 0, None, 0, 256, None, None, 0, _C.stream_ptr()))
         outs.append(Cd.cpu())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
 
@@ -188,7 +202,7 @@ def test_gemm_rejects_bad_arguments(env):
     _C, ctx, dev = env
     A = torch.zeros(8, 6, device=dev)
     rc = _C.lib.porl_gemm(ctx.handle, 1, 1, 8, 8, 6, A.data_ptr(), 6, A.data_ptr(), 6, A.data_ptr(), 8, None, 0,
-                          None, 0, 8, None, _C.stream_ptr())
+                          None, 0, 8, None, None, 0, _C.stream_ptr())
     assert rc == -1 and b"leading dimensions" in _C.lib.porl_last_error()
 
 
@@ -381,7 +395,10 @@ def test_mlp_forward_backward_matches_autograd(env, mode, dims, n_nets, ln, tanh
         for m, ref in zip(mods, refs):
             rp = dict(ref.named_parameters())
             for k, p in m.named_parameters():
-                assert rel_l2(p.grad, rp[k].grad) <= 1e-5, k                 # per-tensor gradient rel-L2 <= 1e-5
+                # per-tensor gradient rel-L2 <= 1e-5; a bias gradient is a cancelling fp32 sum over the batch, so
+                # its error is bounded against the summed magnitudes instead (3e-7 * sum_b |dout|)
+                d = float((p.grad.detach().cpu().double() - rp[k].grad).abs().max())
+                assert rel_l2(p.grad, rp[k].grad) <= 1e-5 or d <= 3e-7 * float(up.abs().sum()), k
         # padding of the gradient bucket is written as exact zeros
         w0 = plan.layout(0, 0, _C.PARAM_WEIGHT)
         g0 = grads[w0[0]:w0[0] + dims[1] * w0[1]].view(dims[1], w0[1])

@@ -11,8 +11,9 @@ from porl_b200 import _C
 dev = torch.device("cuda:0")
 ctx = _C.context(dev)
 pad = lambda x: (x + 3) // 4 * 4
-SHAPES = [(1, 1, 4096, 512, 362), (1, 1, 4096, 512, 512), (0, 0, 512, 512, 4096), (0, 0, 512, 362, 4096),
-          (1, 0, 4096, 512, 512), (1, 1, 256, 512, 512), (0, 0, 512, 512, 256)]
+SHAPES = [(1, 1, 4096, 512, 362), (1, 1, 4096, 512, 512), (1, 1, 512, 512, 4096), (1, 1, 512, 362, 4096),
+          (1, 1, 4096, 1024, 1024), (1, 1, 1024, 1024, 4096), (1, 1, 256, 512, 512), (1, 1, 512, 512, 256),
+          (1, 1, 16384, 512, 512)]
 
 
 def operands(a_k, b_k, M, N, K, seed=1, relu_like=True):
@@ -26,11 +27,11 @@ def operands(a_k, b_k, M, N, K, seed=1, relu_like=True):
 
 def run(a_k, b_k, M, N, K, Ad, Bd, Cd):
     _C.check(_C.lib.porl_gemm(ctx.handle, a_k, b_k, M, N, K, Ad.data_ptr(), Ad.stride(0), Bd.data_ptr(), Bd.stride(0),
-                              Cd.data_ptr(), Cd.stride(0), None, 0, None, 0, N, None, _C.stream_ptr()))
+                              Cd.data_ptr(), Cd.stride(0), None, 0, None, 0, N, None, None, 0, _C.stream_ptr()))
 
 
 def acc():
-    for (a_k, b_k, M, N, K) in SHAPES[:4]:
+    for (a_k, b_k, M, N, K) in SHAPES[:4] + [(1, 1, 100, 70, 133), (1, 1, 513, 129, 47)]:
         A, B = operands(a_k, b_k, M, N, K)
         Al = A[:, :K] if a_k else A[:, :M].t()
         Bl = B[:, :K].t() if b_k else B[:, :N]
@@ -38,13 +39,15 @@ def acc():
         Ad, Bd = A.to(dev), B.to(dev)
         scale = float(ref.abs().mean())
         rows = []
-        for mode in (0, 1):
+        for mode, chunk in ((0, 1), (1, 1), (1, 2), (1, 64)):
             ctx.set_gemm_mode(mode)
+            ctx.set_tc_chunk(chunk)
             Cd = torch.zeros(M, pad(N), device=dev)
             run(a_k, b_k, M, N, K, Ad, Bd, Cd)
             torch.cuda.synchronize()
             e = Cd.cpu()[:, :N].double() - ref
-            rows.append((f"mode{mode}", e))
+            rows.append((f"mode{mode}_chunk{chunk}", e))
+        ctx.set_tc_chunk(1)
         ctx.set_gemm_mode(0)
         torch.backends.cuda.matmul.allow_tf32 = False
         e = (Al.to(dev) @ Bl.to(dev)).cpu().double() - ref
@@ -61,10 +64,11 @@ def time_shapes():
         A, B = operands(a_k, b_k, M, N, K)
         Ad, Bd = A.to(dev), B.to(dev)
         Cd = torch.zeros(M, pad(N), device=dev)
-        for mode in (0, 1):
-            if mode == 1 and a_k != b_k:
-                continue
+        stamps = torch.zeros(16 * 148, dtype=torch.int64, device=dev)
+        for mode, chunk in ((0, 1), (1, 1), (1, 2)):
             ctx.set_gemm_mode(mode)
+            ctx.set_tc_chunk(chunk)
+            ctx.set_tc_debug(stamps.data_ptr() if mode == 1 else None)
             for _ in range(3):
                 run(a_k, b_k, M, N, K, Ad, Bd, Cd)
             torch.cuda.synchronize()
@@ -76,8 +80,21 @@ def time_shapes():
             ctx.profile(False)
             c = p["contraction"]
             us = c["ms"] / c["launches"] * 1e3
-            print(f"time form=({a_k},{b_k}) M={M} N={N} K={K} mode={mode} {us:8.1f} us/launch "
-                  f"{2.0*M*N*K/us*1e-6:7.1f} TFLOP/s (split {p['split']['ms']/20*1e3:.1f} us)", flush=True)
+            extra = ""
+            if mode == 1:
+                t = stamps.cpu().view(148, 16)
+                t = t[t[:, 15] > 0]
+                if len(t):
+                    d = t[:, 15] - t[:, 0]
+                    extra = (f" ctas={len(t)} cta_us min/mean/max={float(d.min())/1e3:.1f}/"
+                             f"{float(d.double().mean())/1e3:.1f}/{float(d.max())/1e3:.1f} "
+                             f"span={float(t[:,15].max()-t[:,0].min())/1e3:.1f}\n     cta0 stamps (us from start): "
+                             + " ".join(f"[{i}]{(int(t[0, i]) - int(t[0, 0]))/1e3:.1f}" for i in (1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 15)))
+                stamps.zero_()
+            print(f"time form=({a_k},{b_k}) M={M} N={N} K={K} mode={mode} chunk={chunk} {us:8.1f} us/launch "
+                  f"{2.0*M*N*K/us*1e-6:7.1f} TFLOP/s{extra}", flush=True)
+        ctx.set_tc_debug(None)
+        ctx.set_tc_chunk(1)
         ctx.set_gemm_mode(0)
 
 

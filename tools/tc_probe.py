@@ -23,7 +23,7 @@ def main():
     Ad, Bd = A.to(dev), B.to(dev)
     t0 = ctx.tc_launches
     _C.check(_C.lib.porl_gemm(ctx.handle, a_k, b_k, M, N, K, Ad.data_ptr(), Ad.stride(0), Bd.data_ptr(), Bd.stride(0),
-                              Cd.data_ptr(), ldc, None, 0, None, 0, N, None, _C.stream_ptr()))
+                              Cd.data_ptr(), ldc, None, 0, None, 0, N, None, None, 0, _C.stream_ptr()))
     torch.cuda.synchronize()
     got = Cd.cpu()[:, :N].double()
     err = (got - ref).abs()
