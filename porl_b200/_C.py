@@ -43,11 +43,11 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
-CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose")
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head")
 
 
 class Profile(C.Structure):
-    _fields_ = [("launches", C.c_int64 * 6), ("ms", C.c_double * 6), ("work", C.c_double * 6)]
+    _fields_ = [("launches", C.c_int64 * 7), ("ms", C.c_double * 7), ("work", C.c_double * 7)]
 
 
 _p, _i32, _i64, _f = C.c_void_p, C.c_int32, C.c_int64, C.c_float

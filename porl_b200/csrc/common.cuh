@@ -18,7 +18,7 @@ namespace porl {
 constexpr int kMaxGroups = 8;       // problems per grouped contraction launch
 constexpr int kSemInts = 1 << 16;   // split-K turnstile words
 constexpr size_t kTcWsFloats = (size_t)1 << 24;   // 64 MB of split-K partial tiles for the tcgen05 kernel
-constexpr int kPartialFloats = 1 << 18;  // block partials of the loss reductions
+constexpr int kPartialFloats = 1 << 20;  // block partials of the loss reductions
 constexpr int kTicketBase = 64;          // counters[0] status, [1..63] kernel tickets, then per-chunk tickets
 constexpr int kTickets = 4096;
 constexpr int kCounterWords = kTicketBase + kTickets;

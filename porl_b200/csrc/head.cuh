@@ -1,0 +1,43 @@
+// Narrow-head (n_out <= 8) forward / backward launch interface (head.cu).
+#pragma once
+#include "common.cuh"
+
+namespace porl {
+
+constexpr int kHeadMax = 8;        // widest output layer served by the head kernels
+constexpr int kHeadRowChunks = 32; // most row chunks (block partials) of the backward reduction
+
+struct HeadFwdSeg {
+  const float* h;      // (B, ldh) input activation, pad columns zero
+  const float* W;      // (n_out, ldw), pad columns zero
+  const float* bias;   // (n_out) or null
+  float* out;          // (B, ld_out); columns n_out..ld_out-1 written as zeros
+  int n_out, H, ldh, ldw, ld_out;
+  int act;             // 0 none, 1 relu, 2 tanh
+};
+struct HeadFwdBatch {
+  HeadFwdSeg seg[kMaxGroups];
+  int n_seg;
+  int64_t B;
+};
+
+struct HeadBwdSeg {
+  float* h;            // in: (B, ldh) activation feeding the head; out: dz = relu-masked input gradient
+  const float* dout;   // (B, ld_out) gradient w.r.t. the head's pre-activation output
+  const float* W;      // (n_out, ldw)
+  float* dW;           // (n_out, ldw) overwritten (pad columns zero)
+  float* db;           // (n_out) overwritten
+  float* db_prev;      // (H) = sum_b dz[b, :], or null
+};
+struct HeadBwdBatch {
+  HeadBwdSeg seg[kMaxGroups];
+  int n_seg;
+  int64_t B;
+  int n_out, H, ldh, ldw, ld_out;
+  int need_dz;         // 0: only dW / db (single-layer net)
+};
+
+int launch_head_forward(porl_ctx* ctx, const HeadFwdBatch& hb, cudaStream_t st);
+int launch_head_backward(porl_ctx* ctx, const HeadBwdBatch& hb, cudaStream_t st);
+
+}  // namespace porl

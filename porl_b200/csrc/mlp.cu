@@ -13,6 +13,7 @@
 #include <math.h>
 
 #include "gemm.cuh"
+#include "head.cuh"
 
 struct porl_mlp {
   porl_ctx* ctx;
@@ -83,6 +84,10 @@ static float* doutt_ptr(const porl_mlp* m, float* saved, int64_t B, int net) {
 }
 static int64_t saved_total_floats(const porl_mlp* m, int64_t B) {
   return (doutt_ptr(m, nullptr, B, m->d.n_nets) - (float*)nullptr);
+}
+// the output layer is served by the row-wise head kernels (head.cu) instead of a contraction
+static bool narrow_head(const porl_mlp* m) {
+  return m->d.dims[m->d.n_layers] <= kHeadMax && m->ld_out <= 32;
 }
 // layer l (dims[l] -> dims[l+1]) runs its three contractions on the tcgen05 path
 static bool tc_layer(const porl_ctx* ctx, const porl_mlp* m, int l, int64_t B) {
@@ -287,12 +292,32 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
   for (int l = 0; l < max_layers; ++l) {
     GemmBatch tc, ff;           // tensor-core problems and FFMA problems of this layer
     tc.n_groups = ff.n_groups = 0;
+    HeadFwdBatch hf;            // narrow output layers of this step
+    hf.n_seg = 0;
+    hf.B = B;
     for (int c = 0; c < n_calls; ++c) {
       const porl_mlp_call_t& k = calls[c];
       const porl_mlp* m = k.mlp;
       if (l >= m->d.n_layers) continue;
       const bool last = (l == m->d.n_layers - 1);
       const bool on_tc = tc_layer(ctx, m, l, B);
+      if (last && narrow_head(m)) {
+        for (int net = 0; net < m->d.n_nets; ++net) {
+          const float* P = k.params + net * m->net_stride;
+          HeadFwdSeg& h = hf.seg[hf.n_seg++];
+          h.h = (l == 0) ? k.x : saved_h(m, k.saved, net, l, B);
+          h.ldh = (l == 0) ? (int)k.ldx : m->pad[l];
+          h.W = P + m->w_off[l];
+          h.ldw = m->pad[l];
+          h.bias = P + m->b_off[l];
+          h.out = k.out + (int64_t)net * B * m->ld_out;
+          h.n_out = m->d.dims[l + 1];
+          h.H = m->d.dims[l];
+          h.ld_out = m->ld_out;
+          h.act = m->d.out_act == 1 ? 2 : 0;
+        }
+        continue;
+      }
       for (int net = 0; net < m->d.n_nets; ++net) {
         GemmBatch& batch = on_tc ? tc : ff;
         GemmGroup& g = batch.g[batch.n_groups++];
@@ -332,6 +357,8 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
       rc = launch_gemm(ctx, true, true, ff, st);
       if (rc != PORL_OK) return rc;
     }
+    rc = launch_head_forward(ctx, hf, st);
+    if (rc != PORL_OK) return rc;
     // LayerNorm + ReLU rows
     for (int c = 0; c < n_calls; ++c) {
       const porl_mlp_call_t& k = calls[c];
@@ -405,7 +432,73 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     if (rc != PORL_OK) return rc;
   }
 
-  for (int l = L - 1; l >= 0; --l) {
+  auto layer_norm_backward = [&](int l) -> int {   // h_l holds dL/d(LayerNorm output) -> dL/d(Linear output)
+    for (int net = 0; net < nn; ++net) {
+      const float* P = call->params + net * m->net_stride;
+      float* G = grads + net * m->net_stride;
+      float* dy = saved_h(m, saved, net, l, B);
+      const float* xh = saved_xhat(m, saved, net, l, B);
+      const int d = m->d.dims[l];
+      ProfScope prof(ctx, PORL_CAT_NORM, (double)B * d * 20.0, st);
+      ln_param_grad_kernel<<<(d + 31) / 32, 256, 0, st>>>(dy, xh, B, d, m->pad[l], G + m->lnw_off[l - 1],
+                                                          G + m->lnb_off[l - 1]);
+      PORL_LAUNCHED(ctx);
+      ln_backward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(dy, xh, saved_rstd(m, saved, net, l, B),
+                                                                  P + m->lnw_off[l - 1], B, d, m->pad[l]);
+      PORL_LAUNCHED(ctx);
+    }
+    return PORL_OK;
+  };
+  auto transpose_dz = [&](int l) -> int {          // dz_l (over h_l) -> dz_l^T (over h_l^T)
+    TransposeBatch tb;
+    tb.n_seg = 0;
+    for (int net = 0; net < nn; ++net)
+      tb.seg[tb.n_seg++] = TransposeSeg{saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B,
+                                        m->d.dims[l], m->pad[l], ldB};
+    return launch_transpose(ctx, tb, st);
+  };
+
+  int l_first = L - 1;
+  bool bias_done[PORL_MAX_LAYERS] = {false, false, false, false, false, false};
+  if (narrow_head(m)) {
+    // output layer: weight / bias gradient, ReLU-masked input gradient and (without LayerNorm) the bias
+    // gradient of the layer below in one pass over the last hidden activation
+    const int l = L - 1;
+    HeadBwdBatch hb;
+    hb.n_seg = 0;
+    hb.B = B;
+    hb.n_out = m->d.dims[L];
+    hb.H = m->d.dims[l];
+    hb.ldh = (l == 0) ? (int)call->ldx : m->pad[l];
+    hb.ldw = m->pad[l];
+    hb.ld_out = m->ld_out;
+    hb.need_dz = l > 0 ? 1 : 0;
+    const bool give_bias = l > 0 && !m->d.layer_norm;
+    for (int net = 0; net < nn; ++net) {
+      HeadBwdSeg& s = hb.seg[hb.n_seg++];
+      float* G = grads + net * m->net_stride;
+      s.h = (l == 0) ? const_cast<float*>(call->x) : saved_h(m, saved, net, l, B);
+      s.dout = dout + (int64_t)net * B * m->ld_out;
+      s.W = call->params + net * m->net_stride + m->w_off[l];
+      s.dW = G + m->w_off[l];
+      s.db = G + m->b_off[l];
+      s.db_prev = give_bias ? G + m->b_off[l - 1] : nullptr;
+    }
+    rc = launch_head_backward(ctx, hb, st);
+    if (rc != PORL_OK) return rc;
+    if (give_bias) bias_done[l - 1] = true;
+    if (l > 0 && tc_layer(ctx, m, l - 1, B)) {
+      rc = transpose_dz(l);
+      if (rc != PORL_OK) return rc;
+    }
+    if (l > 0 && m->d.layer_norm) {
+      rc = layer_norm_backward(l);
+      if (rc != PORL_OK) return rc;
+    }
+    l_first = L - 2;
+  }
+
+  for (int l = l_first; l >= 0; --l) {
     // gradient of this layer's pre-activation output: the head gradient, else the (in-place rewritten)
     // hidden activation buffer of layer l+1 (and its transposed twin)
     const bool head = (l == L - 1);
@@ -431,13 +524,13 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
         g.lda = ldB;
         g.B = (l == 0) ? xt_ptr(m, saved, B) : saved_ht(m, saved, net, l, B);
         g.ldb = ldB;
-        cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
+        if (!bias_done[l]) cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
       } else {
         g.A = dz(net);
         g.lda = ld_dz;
         g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);
         g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
-        g.colsum = G + m->b_off[l];
+        if (!bias_done[l]) g.colsum = G + m->b_off[l];
       }
       g.C = G + m->w_off[l];
       g.ldc = m->pad[l];
@@ -485,29 +578,12 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     rc = launch_gemm(ctx, true, on_tc, bx, st);
     if (rc != PORL_OK) return rc;
     if (!on_tc && prev_tc) {   // dz_l came from the FFMA kernel: transpose it for the next weight gradient
-      TransposeBatch tb;
-      tb.n_seg = 0;
-      for (int net = 0; net < nn; ++net)
-        tb.seg[tb.n_seg++] = TransposeSeg{saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B,
-                                          m->d.dims[l], m->pad[l], ldB};
-      rc = launch_transpose(ctx, tb, st);
+      rc = transpose_dz(l);
       if (rc != PORL_OK) return rc;
     }
     if (m->d.layer_norm) {
-      for (int net = 0; net < nn; ++net) {
-        const float* P = call->params + net * m->net_stride;
-        float* G = grads + net * m->net_stride;
-        float* dy = saved_h(m, saved, net, l, B);
-        const float* xh = saved_xhat(m, saved, net, l, B);
-        const int d = m->d.dims[l];
-        ProfScope prof(ctx, PORL_CAT_NORM, (double)B * d * 20.0, st);
-        ln_param_grad_kernel<<<(d + 31) / 32, 256, 0, st>>>(dy, xh, B, d, m->pad[l], G + m->lnw_off[l - 1],
-                                                            G + m->lnb_off[l - 1]);
-        PORL_LAUNCHED(ctx);
-        ln_backward_kernel<<<(unsigned)((B + 7) / 8), 256, 0, st>>>(dy, xh, saved_rstd(m, saved, net, l, B),
-                                                                    P + m->lnw_off[l - 1], B, d, m->pad[l]);
-        PORL_LAUNCHED(ctx);
-      }
+      rc = layer_norm_backward(l);
+      if (rc != PORL_OK) return rc;
     }
   }
   return PORL_OK;

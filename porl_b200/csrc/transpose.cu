@@ -61,7 +61,16 @@ __global__ void __launch_bounds__(256) colsum_kernel(const __grid_constant__ Col
   const int64_t r0 = (int64_t)blockIdx.y * s.rows / R, r1 = (int64_t)(blockIdx.y + 1) * s.rows / R;
   float acc = 0.f;
   if (col < s.n) {
-    for (int64_t r = r0 + warp; r < r1; r += 8) acc += s.src[r * s.ld + col];
+    // four independent loads in flight per lane (a dependent acc += load chain ran at DRAM latency)
+    int64_t r = r0 + warp;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (; r + 24 < r1; r += 32) {
+      const float v0 = s.src[r * s.ld + col], v1 = s.src[(r + 8) * s.ld + col];
+      const float v2 = s.src[(r + 16) * s.ld + col], v3 = s.src[(r + 24) * s.ld + col];
+      a0 += v0; a1 += v1; a2 += v2; a3 += v3;
+    }
+    for (; r < r1; r += 8) a0 += s.src[r * s.ld + col];
+    acc = (a0 + a1) + (a2 + a3);
   }
   sm[warp][lane] = acc;
   __syncthreads();

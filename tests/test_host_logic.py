@@ -63,11 +63,11 @@ def test_mlp_geometry_is_padded_and_aligned():
                 assert not seen[idx].any()                           # tensors do not overlap
                 seen[idx] = True
     B = 256
-    acts = 2 * 2 * (2 * B * 512 + B * 512 + B)          # per net, per hidden layer: h hi/lo planes + xhat + rstd
-    xsplit, wsplit = 2 * B * 384, 2 * plan.n_floats       # 3xTF32 operand planes
-    wt = 2 * (2 * 512 * 512 + 2 * 512 * 32)               # W_2^T, W_3^T planes per net
-    dsplit = 2 * 2 * B * 4
-    assert plan.saved_floats(B) == acts + xsplit + wsplit + wt + dsplit + 4
+    acts = 2 * 2 * (B * 512 + 512 * B + B * 512 + B)     # per net, per hidden layer: h, h^T, xhat, rstd
+    xt = 362 * B                                          # x^T for the layer-0 weight gradient
+    wt = 2 * (512 * 512 + 512 * 4)                        # per net: W_1^T (512 x 512), W_2^T (512 x pad4(1))
+    doutt = 2 * 1 * B                                     # per net: head gradient transposed
+    assert plan.saved_floats(B) == acts + xt + wt + doutt + 4
     with pytest.raises(_C.PorlError):
         plan.layout(0, 2, _C.PARAM_LN_WEIGHT)                        # no LayerNorm after the head
 
