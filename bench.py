@@ -320,8 +320,15 @@ def run_b200(a):
         c = prof["contraction"]
         achieved = c["work"] / (c["ms"] * 1e-3) / 1e12 if c["ms"] > 0 else 0.0
         peak = pk["bf16_sustained"]
+        traffic = None
+        try:   # dram__bytes_read+write per launch of this kernel from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "r01_gemm_tc_traffic.json")) as f:
+                traffic = json.load(f)["mean_bytes_per_launch"] if a.gemm_mode == 1 else None
+        except Exception:
+            pass
         line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                            "frac": achieved / peak, "traffic": None,
+                            "frac": achieved / peak, "traffic": traffic,
+                            "frac_of_3xtf32_ceiling": achieved / (peak / 6.0),
                             "kernel": "gemm_tc_kernel (tcgen05 3xTF32)" if a.gemm_mode == 1 else "gemm_simt_kernel (fp32 FFMA)",
                             "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({pk['source']})",
                             "launches_per_step": c["launches"] / max(1, min(10, K)),
