@@ -68,6 +68,9 @@ int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
 /* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
 int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
+/* tcgen05 kernel variant: 1 = the A operand's tf32 hi/lo planes are staged in tensor memory (tcgen05.st) and
+ * the MMAs read A from TMEM; 0 = all four operand planes in shared memory */
+int porl_ctx_set_tc_variant(porl_ctx_t* ctx, int a_in_tmem);
 /* profiling aid: device buffer of 16 x 148 uint64 that receives per-CTA globaltimer stamps (kernel start,
  * setup done, first/last TMA, first split, first/last MMA, chunk drain, epilogue, end; see gemm_tc.cu) of
  * every tcgen05 contraction launch (NULL disables) */

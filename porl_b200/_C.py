@@ -86,6 +86,7 @@ _SIGNATURES = {
     "porl_transpose": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p]),
     "porl_ctx_set_tc_chunk": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_tc_debug": (C.c_int, [_p, _p]),
+    "porl_ctx_set_tc_variant": (C.c_int, [_p, C.c_int]),
 }
 
 EXPORTS = tuple(_SIGNATURES)
@@ -159,6 +160,9 @@ class Context:
 
     def set_tc_chunk(self, k_blocks: int) -> None:
         check(lib.porl_ctx_set_tc_chunk(self.handle, k_blocks))
+
+    def set_tc_variant(self, a_in_tmem: int) -> None:
+        check(lib.porl_ctx_set_tc_variant(self.handle, a_in_tmem))
 
     def set_tc_debug(self, ptr) -> None:
         check(lib.porl_ctx_set_tc_debug(self.handle, ptr))

@@ -1,5 +1,6 @@
 // Context, error reporting and the contraction dispatcher of libporl_b200.so.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "gemm.cuh"
@@ -91,6 +92,10 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->partials = nullptr;
   ctx->counters = nullptr;
   ctx->tc_chunk_kb = 1;
+  {
+    const char* e = getenv("PORL_TC_A_IN_TMEM");
+    ctx->tc_a_in_tmem = e ? atoi(e) : 0;
+  }
   ctx->tc_ws = nullptr;
   ctx->tc_dbg = nullptr;
   ctx->device = device;
@@ -167,6 +172,12 @@ extern "C" int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx) { return ctx ? ctx-
 extern "C" int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks) {
   PORL_CHECK_ARG(ctx && k_blocks >= 1 && k_blocks <= 64, "porl_ctx_set_tc_chunk: k_blocks=%d", k_blocks);
   ctx->tc_chunk_kb = k_blocks;
+  return PORL_OK;
+}
+
+extern "C" int porl_ctx_set_tc_variant(porl_ctx_t* ctx, int a_in_tmem) {
+  PORL_CHECK_ARG(ctx && (a_in_tmem == 0 || a_in_tmem == 1), "porl_ctx_set_tc_variant: a_in_tmem=%d", a_in_tmem);
+  ctx->tc_a_in_tmem = a_in_tmem;
   return PORL_OK;
 }
 

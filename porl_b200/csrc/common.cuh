@@ -45,6 +45,7 @@ struct porl_ctx {
   float* partials;          // loss reduction partials
   uint32_t* counters;       // [0] status word, [1..] last-block-done counters
   float* tc_ws;             // split-K partial tiles of the tcgen05 kernel (kTcWsFloats)
+  int tc_a_in_tmem;         // tcgen05 kernel variant: A operand staged in tensor memory (default) or in shared memory
   int tc_chunk_kb;          // k-blocks per TMEM accumulation chunk of the tcgen05 kernel (1 or 2)
   unsigned long long* tc_dbg;  // optional per-CTA timestamps of the tcgen05 kernel (device memory), or null
 };

@@ -31,14 +31,22 @@
 namespace porl {
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;      // tile; BK floats = one 128-byte swizzle span
-constexpr int TC_STAGES = 3;
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB
-constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES;         // A_raw, B_raw, A_lo, B_lo
-constexpr int TC_EPI_FLOATS = 0;                          // the epilogue stores straight from registers
-constexpr int TC_NUM_BARS = 3 * TC_STAGES + 4;
-constexpr int TC_SMEM_BYTES = 1024 /*align slack*/ + TC_STAGES * TC_STAGE_BYTES + TC_EPI_FLOATS * 4 + 256;
 constexpr int TC_THREADS = 320;
-constexpr int TC_TMEM_COLS = 256;
+constexpr int TC_ACC_COLS = 2 * TC_BN;                    // two chunk accumulators
+// Two variants.  ATM = false: A_hi, A_lo, B_hi, B_lo all in shared memory (stage = 4 tiles, 3 stages).
+// ATM = true: the splitters put A_hi / A_lo into TENSOR MEMORY (tcgen05.st, 64 columns per stage) and the
+// MMAs take A from TMEM, which removes the A reads from the shared-memory port (the measured limiter)
+// and the A_lo tile from the stage (stage = A_raw, B_raw, B_lo: 3 tiles, 4 stages).
+template <bool ATM>
+struct TcCfg {
+  static constexpr int STAGES = ATM ? 4 : 3;
+  static constexpr int STAGE_BYTES = (ATM ? 3 : 4) * TC_TILE_BYTES;
+  static constexpr int B_LO_OFF = (ATM ? 2 : 3) * TC_TILE_BYTES;
+  static constexpr int NUM_BARS = 3 * STAGES + 4;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + 256;
+  static constexpr int TMEM_COLS = ATM ? 512 : 256;
+};
 constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 6;
 
 struct alignas(64) TcParams {
@@ -113,6 +121,27 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ unsigned long long gtime() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -155,12 +184,16 @@ __device__ __forceinline__ bool tc_decode(const TcParams& P, int u, TcUnit& w) {
 }
 
 // ------------------------------------------------------------------------------------------ kernel
+template <bool ATM>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams P) {
+  using C = TcCfg<ATM>;
+  constexpr int TC_STAGES = C::STAGES, TC_STAGE_BYTES = C::STAGE_BYTES, TC_NUM_BARS = C::NUM_BARS;
+  constexpr int TC_TMEM_COLS = C::TMEM_COLS;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;                         // SWIZZLE_128B tiles: 1024-B aligned
   uint8_t* base_ptr = smem_raw + (base - raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(base_ptr + TC_STAGES * TC_STAGE_BYTES + TC_EPI_FLOATS * 4);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(base_ptr + TC_STAGES * TC_STAGE_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
   uint32_t* flag_slot = tmem_slot + 1;
   const uint32_t bar0 = smem_u32(bars);
@@ -249,20 +282,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             tc_fence_after();
             if (dbg && it == 0) dbg[5] = gtime();
             const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-            const uint64_t a_hi = smem_desc(st), b_hi = smem_desc(st + TC_TILE_BYTES);
-            const uint64_t a_lo = smem_desc(st + 2 * TC_TILE_BYTES), b_lo = smem_desc(st + 3 * TC_TILE_BYTES);
+            const uint64_t b_hi = smem_desc(st + TC_TILE_BYTES), b_lo = smem_desc(st + C::B_LO_OFF);
             // small terms first (they meet the smallest accumulator), then the hi*hi terms
+            if (ATM) {
+              const uint32_t a_hi = tmem_base + (uint32_t)(TC_ACC_COLS + s * 64), a_lo = a_hi + 32u;
 #pragma unroll
-            for (int ks = 0; ks < TC_BK / 8; ++ks) {
-              const uint64_t o = (uint64_t)(2 * ks);        // 32 bytes per 8-wide k-step, in 16-byte units
-              tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
-              acc = 1;
-              tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
-            }
+              for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                const uint64_t o = (uint64_t)(2 * ks);      // 32 bytes per 8-wide k-step, in 16-byte units
+                tc_mma_tf32_ts(d_tmem, a_lo + 8u * ks, b_hi + o, idesc, acc);
+                acc = 1;
+                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_lo + o, idesc, 1u);
+              }
 #pragma unroll
-            for (int ks = 0; ks < TC_BK / 8; ++ks) {
-              const uint64_t o = (uint64_t)(2 * ks);
-              tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+              for (int ks = 0; ks < TC_BK / 8; ++ks)
+                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + (uint64_t)(2 * ks), idesc, 1u);
+            } else {
+              const uint64_t a_hi = smem_desc(st), a_lo = smem_desc(st + 2 * TC_TILE_BYTES);
+#pragma unroll
+              for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                const uint64_t o = (uint64_t)(2 * ks);
+                tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+                acc = 1;
+                tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+              }
+#pragma unroll
+              for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                const uint64_t o = (uint64_t)(2 * ks);
+                tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+              }
             }
             tc_commit(empty_bar(s));            // frees the stage once these MMAs have read it
           }
@@ -283,17 +330,42 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         const int s = it % TC_STAGES;
         const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
         mbar_wait(raw_full(s), ph);
-        const float4* src = reinterpret_cast<const float4*>(base_ptr + (size_t)s * TC_STAGE_BYTES);
-        float4* dst = reinterpret_cast<float4*>(base_ptr + (size_t)s * TC_STAGE_BYTES + 2 * TC_TILE_BYTES);
+        uint8_t* stage = base_ptr + (size_t)s * TC_STAGE_BYTES;
+        if (ATM) {
+          // B: flat elementwise pass raw -> lo (same swizzled layout)
+          const float4* src = reinterpret_cast<const float4*>(stage + TC_TILE_BYTES);
+          float4* dst = reinterpret_cast<float4*>(stage + C::B_LO_OFF);
 #pragma unroll
-        for (int i = 0; i < (2 * TC_TILE_BYTES / 16) / 128; ++i) {
-          const float4 v = src[t + i * 128];
-          float4 l;
-          l.x = split_lo(v.x);
-          l.y = split_lo(v.y);
-          l.z = split_lo(v.z);
-          l.w = split_lo(v.w);
-          dst[t + i * 128] = l;
+          for (int i = 0; i < (TC_TILE_BYTES / 16) / 128; ++i) {
+            const float4 v = src[t + i * 128];
+            dst[t + i * 128] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+          }
+          // A: this thread owns tile row r = its TMEM lane; un-swizzle the row (16-byte chunk j of row r sits at
+          // chunk j ^ (r & 7)) and store hi / lo as 32 + 32 TMEM columns (column = k index)
+          const int r = 32 * (warp & 3) + lane;
+          const uint8_t* arow = stage + r * 128;
+          uint32_t hi[32], lo[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
+            hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
+            hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
+            hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
+            hi[4 * j + 3] = __float_as_uint(v.w); lo[4 * j + 3] = __float_as_uint(split_lo(v.w));
+          }
+          const uint32_t ta = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(TC_ACC_COLS + s * 64);
+          tc_st32(ta, hi);
+          tc_st32(ta + 32u, lo);
+          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+          tc_fence_before();
+        } else {
+          const float4* src = reinterpret_cast<const float4*>(stage);
+          float4* dst = reinterpret_cast<float4*>(stage + 2 * TC_TILE_BYTES);
+#pragma unroll
+          for (int i = 0; i < (2 * TC_TILE_BYTES / 16) / 128; ++i) {
+            const float4 v = src[t + i * 128];
+            dst[t + i * 128] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+          }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> tensor-core reads
         mbar_arrive(split_done(s));
@@ -575,14 +647,21 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
 
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         TcCfg<false>::SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               TcCfg<true>::SMEM_BYTES);
     if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(max dynamic smem %d) failed: %s", TC_SMEM_BYTES, cudaGetErrorString(e));
+      set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
       return PORL_ERR_CUDA;
     }
     configured = true;
   }
-  gemm_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(P);
+  if (ctx->tc_a_in_tmem)
+    gemm_tc_kernel<true><<<grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream>>>(P);
+  else
+    gemm_tc_kernel<false><<<grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream>>>(P);
   ctx->tc_launches++;
   PORL_LAUNCHED(ctx);
   return PORL_OK;
