@@ -3,14 +3,14 @@
 //
 // Persistent, warp-specialised kernel, one CTA per SM, 128x128 output tiles, 32-wide k-blocks:
 //   warp 0      TMA producer: raw fp32 A / B tiles (128 rows x 128 B, SWIZZLE_128B) -> stage ring
-//   warps 2..5  splitters: lo = RN_tf32(x - trunc_tf32(x)) written next to the raw tile (same
+//   warps 2..7  splitters: lo = RN_tf32(x - trunc_tf32(x)) written next to the raw tile (same
 //               swizzled layout, so the split is a flat elementwise pass over the stage).  The raw
 //               tile itself serves as the hi operand: kind::tf32 reads only the top 19 bits of
 //               each fp32 container, i.e. it truncates, and the split is built on that truncation.
 //   warp 1      TMEM allocator + MMA issuer: per k-block 8 "small" MMAs (A_lo*B_hi, A_hi*B_lo for
 //               the four 8-wide k-steps) then 4 "big" ones (A_hi*B_hi), all into one fp32 TMEM
 //               accumulator that is RESTARTED every chunk (chunk_kb k-blocks, default 1).
-//   warps 6..9  accumulators + epilogue: drain each chunk's TMEM accumulator (tcgen05.ld) and add it
+//   warps 8..11 accumulators + epilogue: drain each chunk's TMEM accumulator (tcgen05.ld) and add it
 //               to a register accumulator with round-to-nearest fp32 adds, in fixed order.  The
 //               tensor core truncates (RZ) on every accumulate; restarting the TMEM accumulator
 //               every 32..64 k keeps that error at the fp32 rounding level (measured: DESIGN.md).
@@ -32,7 +32,8 @@ namespace porl {
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;      // tile; BK floats = one 128-byte swizzle span
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB
-constexpr int TC_THREADS = 320;
+constexpr int TC_THREADS = 384;                           // 12 warps: TMA, MMA, 6 splitters, 4 accumulators
+constexpr int TC_SPLIT_THREADS = 192;
 constexpr int TC_ACC_COLS = 2 * TC_BN;                    // two chunk accumulators
 // Two variants.  ATM = false: A_hi, A_lo, B_hi, B_lo all in shared memory (stage = 4 tiles, 3 stages).
 // ATM = true: the splitters put A_hi / A_lo into TENSOR MEMORY (tcgen05.st, 64 columns per stage) and the
@@ -47,7 +48,7 @@ struct TcCfg {
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + 256;
   static constexpr int TMEM_COLS = ATM ? 512 : 256;
 };
-constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 6;
+constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 8;
 
 struct alignas(64) TcParams {
   CUtensorMap mapA[kMaxGroups];
@@ -156,9 +157,11 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
 }
 
 // lo plane of the truncation split: x = trunc_tf32(x) + d exactly; lo = d rounded to tf32
+// (adding half a tf32 ulp to the bit pattern; the tensor core's own truncation of the container completes
+// the round-to-nearest, so no second mask is needed: 3 ALU instructions per element)
 __device__ __forceinline__ float split_lo(float x) {
   const float d = x - __uint_as_float(__float_as_uint(x) & 0xffffe000u);
-  return __uint_as_float((__float_as_uint(d) + 0x1000u) & 0xffffe000u);
+  return __uint_as_float(__float_as_uint(d) + 0x1000u);
 }
 
 struct TcUnit {
@@ -205,8 +208,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long* const dbg = P.dbg ? P.dbg + 16 * blockIdx.x : nullptr;   // [0] start [1] setup done
-  // [2] first TMA issued [3] last TMA issued [4] first split done [5] first MMA issue [6] last MMA commit
+  // [2] first TMA issued [3] last TMA issued [6] last MMA commit; wait totals in SM clocks: [11] producer on empty
+  // [12] splitters on raw_full [13] MMA on split_done [14] MMA on tmem_empty [4] accumulators on tmem_full [5] CTA clocks
   // [7] first chunk full [8] last chunk drained [9] first tile epilogue done [10] all tiles done [15] end
+  const long long clk0 = clock64();
   if (dbg && threadIdx.x == 0) dbg[0] = gtime();
 
   if (warp == 0 && lane == 0) {
@@ -216,7 +221,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     }
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(raw_full(s), 1);
-      mbar_init(split_done(s), 128);
+      mbar_init(split_done(s), TC_SPLIT_THREADS);
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -243,12 +248,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     // ===================== TMA producer =====================
     if (lane == 0) {
       int it = 0;
+      long long w_prod = 0;
       TcUnit w;
       for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
         for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
           const int s = it % TC_STAGES;
           const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
+          const long long tw = dbg ? clock64() : 0;
           mbar_wait(empty_bar(s), ph ^ 1u);
+          if (dbg) w_prod += clock64() - tw;
           mbar_expect_tx(raw_full(s), 2 * TC_TILE_BYTES);
           const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
           tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0);
@@ -256,7 +264,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           if (dbg && it == 0) dbg[2] = gtime();
         }
       }
-      if (dbg) dbg[3] = gtime();
+      if (dbg) { dbg[3] = gtime(); dbg[11] = (unsigned long long)w_prod; }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -265,12 +273,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
                                  ((uint32_t)(TC_BM >> 4) << 24);
       int it = 0, chunk = 0;
+      long long w_te = 0, w_sd = 0;
       TcUnit w;
       for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
         int kb = w.kb0;
         while (kb < w.kb1) {
           const int buf = chunk & 1;
+          const long long tw0 = dbg ? clock64() : 0;
           mbar_wait(tmem_empty(buf), (((uint32_t)chunk >> 1) & 1u) ^ 1u);
+          if (dbg) w_te += clock64() - tw0;
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(buf * TC_BN);
           const int nk = (w.kb1 - kb) < chunk_kb ? (w.kb1 - kb) : chunk_kb;
@@ -278,9 +289,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           for (int j = 0; j < nk; ++j, ++it) {
             const int s = it % TC_STAGES;
             const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
+            const long long tw1 = dbg ? clock64() : 0;
             mbar_wait(split_done(s), ph);
+            if (dbg) w_sd += clock64() - tw1;
             tc_fence_after();
-            if (dbg && it == 0) dbg[5] = gtime();
             const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
             const uint64_t b_hi = smem_desc(st + TC_TILE_BYTES), b_lo = smem_desc(st + C::B_LO_OFF);
             // small terms first (they meet the smallest accumulator), then the hi*hi terms
@@ -318,64 +330,77 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           kb += nk;
         }
       }
-      if (dbg) dbg[6] = gtime();
+      if (dbg) { dbg[6] = gtime(); dbg[13] = (unsigned long long)w_sd; dbg[14] = (unsigned long long)w_te; }
     }
   } else if (warp < TC_EPI_WARP0) {
     // ===================== splitters: lo = RN_tf32(x - trunc_tf32(x)) =====================
-    const int t = threadIdx.x - TC_SPLIT_WARP0 * 32;     // 0..127
+    const int t = threadIdx.x - TC_SPLIT_WARP0 * 32;     // 0..191
     int it = 0;
+    long long w_rf = 0;
     TcUnit w;
     for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
       for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
         const int s = it % TC_STAGES;
         const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
+        const long long tw = dbg ? clock64() : 0;
         mbar_wait(raw_full(s), ph);
+        if (dbg) w_rf += clock64() - tw;
         uint8_t* stage = base_ptr + (size_t)s * TC_STAGE_BYTES;
         if (ATM) {
-          // B: flat elementwise pass raw -> lo (same swizzled layout)
+          // B: flat elementwise pass raw -> lo (same swizzled layout), shared by all six splitter warps
           const float4* src = reinterpret_cast<const float4*>(stage + TC_TILE_BYTES);
           float4* dst = reinterpret_cast<float4*>(stage + C::B_LO_OFF);
 #pragma unroll
-          for (int i = 0; i < (TC_TILE_BYTES / 16) / 128; ++i) {
-            const float4 v = src[t + i * 128];
-            dst[t + i * 128] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+          for (int i = 0; i < (TC_TILE_BYTES / 16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
+            const int e = t + i * TC_SPLIT_THREADS;
+            if (e < TC_TILE_BYTES / 16) {
+              const float4 v = src[e];
+              dst[e] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+            }
           }
-          // A: this thread owns tile row r = its TMEM lane; un-swizzle the row (16-byte chunk j of row r sits at
-          // chunk j ^ (r & 7)) and store hi / lo as 32 + 32 TMEM columns (column = k index)
-          const int r = 32 * (warp & 3) + lane;
-          const uint8_t* arow = stage + r * 128;
-          uint32_t hi[32], lo[32];
+          if (warp < TC_SPLIT_WARP0 + 4) {
+            // A (first four splitter warps): this thread owns tile row r = its TMEM lane; un-swizzle the row
+            // (16-byte chunk j of row r sits at chunk j ^ (r & 7)) and store hi / lo as 32 + 32 TMEM columns
+            // (column = k index)
+            const int r = 32 * (warp & 3) + lane;
+            const uint8_t* arow = stage + r * 128;
+            uint32_t hi[32], lo[32];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
-            hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
-            hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
-            hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
-            hi[4 * j + 3] = __float_as_uint(v.w); lo[4 * j + 3] = __float_as_uint(split_lo(v.w));
+            for (int j = 0; j < 8; ++j) {
+              const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
+              hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
+              hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
+              hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
+              hi[4 * j + 3] = __float_as_uint(v.w); lo[4 * j + 3] = __float_as_uint(split_lo(v.w));
+            }
+            const uint32_t ta = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(TC_ACC_COLS + s * 64);
+            tc_st32(ta, hi);
+            tc_st32(ta + 32u, lo);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
           }
-          const uint32_t ta = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(TC_ACC_COLS + s * 64);
-          tc_st32(ta, hi);
-          tc_st32(ta + 32u, lo);
-          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-          tc_fence_before();
         } else {
           const float4* src = reinterpret_cast<const float4*>(stage);
           float4* dst = reinterpret_cast<float4*>(stage + 2 * TC_TILE_BYTES);
 #pragma unroll
-          for (int i = 0; i < (2 * TC_TILE_BYTES / 16) / 128; ++i) {
-            const float4 v = src[t + i * 128];
-            dst[t + i * 128] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+          for (int i = 0; i < (2 * TC_TILE_BYTES / 16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
+            const int e = t + i * TC_SPLIT_THREADS;
+            if (e < 2 * TC_TILE_BYTES / 16) {
+              const float4 v = src[e];
+              dst[e] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
+            }
           }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> tensor-core reads
         mbar_arrive(split_done(s));
-        if (dbg && it == 0 && t == 0) dbg[4] = gtime();
       }
     }
+    if (dbg && t == 0) dbg[12] = (unsigned long long)w_rf;
   } else {
     // ===================== accumulators + epilogue =====================
     const int q = warp & 3;                 // TMEM lane quarter this warp may read
     int chunk = 0;
+    long long w_tf = 0;
     TcUnit w;
     for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
       // this tile's problem, by value: loads through a reference into the parameter block would be
@@ -394,7 +419,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       const int nchunks = (w.kb1 - w.kb0 + chunk_kb - 1) / chunk_kb;
       for (int c = 0; c < nchunks; ++c, ++chunk) {
         const int buf = chunk & 1;
+        const long long tw = dbg ? clock64() : 0;
         mbar_wait(tmem_full(buf), ((uint32_t)chunk >> 1) & 1u);
+        if (dbg) w_tf += clock64() - tw;
         tc_fence_after();
         if (dbg && chunk == 0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[7] = gtime();
         const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN);
@@ -502,7 +529,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       }
       if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
-    if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) dbg[10] = gtime();
+    if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
   }
 
   tc_fence_before();
@@ -512,7 +539,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS)
                  : "memory");
   }
-  if (dbg && threadIdx.x == 0) dbg[15] = gtime();
+  if (dbg && threadIdx.x == 0) { dbg[15] = gtime(); dbg[5] = (unsigned long long)(clock64() - clk0); }
 }
 
 // ------------------------------------------------------------------------------------------ host

@@ -39,15 +39,17 @@ def acc():
         Ad, Bd = A.to(dev), B.to(dev)
         scale = float(ref.abs().mean())
         rows = []
-        for mode, chunk in ((0, 1), (1, 1), (1, 2), (1, 64)):
+        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 1, 1), (1, 2, 1), (1, 64, 0)):
             ctx.set_gemm_mode(mode)
             ctx.set_tc_chunk(chunk)
+            ctx.set_tc_variant(atm)
             Cd = torch.zeros(M, pad(N), device=dev)
             run(a_k, b_k, M, N, K, Ad, Bd, Cd)
             torch.cuda.synchronize()
             e = Cd.cpu()[:, :N].double() - ref
-            rows.append((f"mode{mode}_chunk{chunk}", e))
+            rows.append((f"mode{mode}_chunk{chunk}_atm{atm}", e))
         ctx.set_tc_chunk(1)
+        ctx.set_tc_variant(0)
         ctx.set_gemm_mode(0)
         torch.backends.cuda.matmul.allow_tf32 = False
         e = (Al.to(dev) @ Bl.to(dev)).cpu().double() - ref
@@ -65,9 +67,10 @@ def time_shapes():
         Ad, Bd = A.to(dev), B.to(dev)
         Cd = torch.zeros(M, pad(N), device=dev)
         stamps = torch.zeros(16 * 148, dtype=torch.int64, device=dev)
-        for mode, chunk in ((0, 1), (1, 1), (1, 2)):
+        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 2, 0), (1, 64, 0), (1, 1, 1), (1, 2, 1), (1, 64, 1)):
             ctx.set_gemm_mode(mode)
             ctx.set_tc_chunk(chunk)
+            ctx.set_tc_variant(atm)
             ctx.set_tc_debug(stamps.data_ptr() if mode == 1 else None)
             for _ in range(3):
                 run(a_k, b_k, M, N, K, Ad, Bd, Cd)
@@ -89,11 +92,16 @@ def time_shapes():
                     extra = (f" ctas={len(t)} cta_us min/mean/max={float(d.min())/1e3:.1f}/"
                              f"{float(d.double().mean())/1e3:.1f}/{float(d.max())/1e3:.1f} "
                              f"span={float(t[:,15].max()-t[:,0].min())/1e3:.1f}\n     cta0 stamps (us from start): "
-                             + " ".join(f"[{i}]{(int(t[0, i]) - int(t[0, 0]))/1e3:.1f}" for i in (1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 15)))
+                             + " ".join(f"[{i}]{(int(t[0, i]) - int(t[0, 0]))/1e3:.1f}" for i in (1, 2, 3, 6, 7, 8, 9, 10, 15))
+                             + "\n     cta0 wait share of CTA clocks: "
+                             + " ".join(f"{n}={int(t[0, i]) / max(int(t[0, 5]), 1):.2f}" for n, i in
+                                        (("producer/empty", 11), ("split/raw_full", 12), ("mma/split_done", 13),
+                                         ("mma/tmem_empty", 14), ("acc/tmem_full", 4))) + f" clocks={int(t[0, 5])}")
                 stamps.zero_()
-            print(f"time form=({a_k},{b_k}) M={M} N={N} K={K} mode={mode} chunk={chunk} {us:8.1f} us/launch "
+            print(f"time form=({a_k},{b_k}) M={M} N={N} K={K} mode={mode} chunk={chunk} atm={atm} {us:8.1f} us/launch "
                   f"{2.0*M*N*K/us*1e-6:7.1f} TFLOP/s{extra}", flush=True)
         ctx.set_tc_debug(None)
+        ctx.set_tc_variant(0)
         ctx.set_tc_chunk(1)
         ctx.set_gemm_mode(0)
 
