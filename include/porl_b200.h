@@ -44,7 +44,9 @@ enum {
   PORL_FLAG_NONFINITE_LOSS = 1,   /* a loss became NaN/Inf */
   PORL_FLAG_NONPOSITIVE_NLL = 2,  /* some per-sample NLL <= 0: where agent/por.py:104 drops into pdb */
   PORL_FLAG_BAD_INDEX = 4,        /* gather index outside [0, n_rows) (clamped) */
-  PORL_FLAG_BAD_ACTION = 8        /* discrete action outside [0, A) (clamped) */
+  PORL_FLAG_BAD_ACTION = 8,       /* discrete action outside [0, A) (clamped) */
+  PORL_FLAG_SCAN_RANGE = 16       /* scan value outside [0, 4.0001) u (8, inf): where state2costmap's scatter_ raises
+                                     (util/costmap.py:29); the beam is skipped */
 };
 
 typedef struct porl_ctx porl_ctx_t;
@@ -81,7 +83,7 @@ int porl_ctx_set_tc_debug(porl_ctx_t* ctx, uint64_t* stamps_dev);
  * category together with its ALGORITHMIC work (flops for contractions, bytes for the HBM-bound
  * kernels).  porl_profile_read synchronises the recorded events and returns per-category sums. */
 enum { PORL_CAT_CONTRACTION = 0, PORL_CAT_GATHER = 1, PORL_CAT_LOSS = 2, PORL_CAT_OPTIMIZER = 3,
-       PORL_CAT_NORM = 4, PORL_CAT_TRANSPOSE = 5, PORL_CAT_HEAD = 6, PORL_CAT_COUNT = 7 };
+       PORL_CAT_NORM = 4, PORL_CAT_TRANSPOSE = 5, PORL_CAT_HEAD = 6, PORL_CAT_ENCODER = 7, PORL_CAT_COUNT = 8 };
 typedef struct {
   int64_t launches[PORL_CAT_COUNT];
   double ms[PORL_CAT_COUNT];       /* sum of per-launch device durations */
@@ -237,6 +239,56 @@ int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, int64_t M, in
 /* dst (cols, ld_dst) = src (rows, ld_src)^T */
 int porl_transpose(porl_ctx_t* ctx, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* dst,
                    int64_t ld_dst, porl_stream_t stream);
+
+/* ---- K8/K9: scan encoder (util/costmap.py + agent/fasternet.py), forward only ------------------- */
+/* state2costmap (util/costmap.py:7-64): out (B, 360, 256, 3) fp32 NHWC -- the buffer the reference returns
+ * as the permuted (B, 3, 360, 256) view -- from state rows (B, >= 362 floats, stride ld_state).  Like the
+ * reference it clamps the caller's state IN PLACE (values > 8 become 0, costmap.py:17).  Beams whose bin
+ * falls outside [0, 256) set PORL_FLAG_SCAN_RANGE (the reference raises) and are skipped. */
+int porl_costmap(porl_ctx_t* ctx, float* state, int64_t ld_state, int64_t B, float* out, porl_stream_t stream);
+
+/* BatchNorm2d parameters and running statistics (device pointers, C floats each) */
+typedef struct {
+  const float* weight;
+  const float* bias;
+  float* running_mean;   /* updated: (1 - 0.1) r + 0.1 batch mean */
+  float* running_var;    /* updated with the UNBIASED batch variance */
+} porl_bn_t;
+
+/* MLPBlock (agent/fasternet.py:141-195) of width C: weights in the layouts the kernels read */
+typedef struct {
+  const float* pconv_w;  /* (9, C/4, C/4): partial_conv3.weight (co, ci, kh, kw) permuted to [kh*3+kw][ci][co] */
+  const float* w1;       /* (2C, C): mlp.0.weight */
+  porl_bn_t bn;          /* mlp.1 over 2C channels */
+  const float* w2;       /* (C, 2C): mlp.3.weight */
+  const float* keep;     /* (B) DropPath factors mask / keep_prob (fasternet.py:76-93), or NULL = keep all */
+} porl_fn_block_t;
+
+/* FasterNet(in_chans=3, num_classes=feature_dim, embed_dim=96, depths=(1, 2)) as the agents build it
+ * (sorl_train.py:29-32) */
+typedef struct {
+  const float* pe_w;          /* (48, 96): patch_embed.proj.weight (o, c, kh, kw) permuted to [(c, kh, kw)][o] */
+  porl_bn_t pe_bn;            /* 96 */
+  porl_fn_block_t block[3];   /* stages.0.blocks.0 (C = 96), stages.2.blocks.0/1 (C = 192) */
+  const float* merge_w;       /* (192, 384): stages.1.reduction.weight (o, c, kh, kw) permuted to [o][(kh, kw, c)] */
+  porl_bn_t merge_bn;         /* 192 */
+  const float* head_conv_w;   /* (1280, 192): avgpool_pre_head.1.weight */
+  const float* head_w;        /* (feature_dim, 1280): head.weight */
+  const float* head_b;        /* (round_up(feature_dim, 4)), 16-byte aligned: head.bias */
+  int32_t feature_dim;
+  int32_t pad_;
+} porl_fasternet_t;
+
+/* floats of scratch porl_fasternet_forward needs for a batch of B states */
+int64_t porl_fasternet_workspace_floats(int64_t B);
+/* FasterNet.forward_cls (agent/fasternet.py:428-438) in TRAIN mode: features (B, ld_feat >= feature_dim)
+ * from state rows (B, ld_state >= 362), which are clamped in place like porl_costmap does.  Every
+ * BatchNorm uses the statistics of THIS batch and updates its running statistics once (the caller
+ * counts num_batches_tracked).  No backward pass exists: no optimizer owns these parameters in the
+ * reference (agent/sorl.py:60,63), so its gradients are never applied. */
+int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* net, float* state, int64_t ld_state,
+                           int64_t B, float* features, int64_t ld_feat, float* workspace,
+                           int64_t workspace_floats, porl_stream_t stream);
 
 #ifdef __cplusplus
 }

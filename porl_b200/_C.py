@@ -19,6 +19,7 @@ FLAG_NONFINITE_LOSS = 1
 FLAG_NONPOSITIVE_NLL = 2
 FLAG_BAD_INDEX = 4
 FLAG_BAD_ACTION = 8
+FLAG_SCAN_RANGE = 16
 
 AWR_POR, AWR_SORL = 0, 1
 PARAM_WEIGHT, PARAM_BIAS, PARAM_LN_WEIGHT, PARAM_LN_BIAS = 0, 1, 2, 3
@@ -43,14 +44,28 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
-CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head")
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head", "encoder")
 
 
 class Profile(C.Structure):
-    _fields_ = [("launches", C.c_int64 * 7), ("ms", C.c_double * 7), ("work", C.c_double * 7)]
+    _fields_ = [("launches", C.c_int64 * len(CATEGORIES)), ("ms", C.c_double * len(CATEGORIES)), ("work", C.c_double * len(CATEGORIES))]
 
 
 _p, _i32, _i64, _f = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+
+class BnParams(C.Structure):                       # porl_bn_t
+    _fields_ = [("weight", _p), ("bias", _p), ("running_mean", _p), ("running_var", _p)]
+
+
+class FnBlock(C.Structure):                        # porl_fn_block_t
+    _fields_ = [("pconv_w", _p), ("w1", _p), ("bn", BnParams), ("w2", _p), ("keep", _p)]
+
+
+class FasterNetParams(C.Structure):                # porl_fasternet_t
+    _fields_ = [("pe_w", _p), ("pe_bn", BnParams), ("block", FnBlock * 3), ("merge_w", _p), ("merge_bn", BnParams),
+                ("head_conv_w", _p), ("head_w", _p), ("head_b", _p), ("feature_dim", _i32), ("pad_", _i32)]
+
 
 _SIGNATURES = {
     "porl_version": (C.c_int, []),
@@ -84,6 +99,9 @@ _SIGNATURES = {
     "porl_gemm": (C.c_int, [_p, _i32, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p, _i64,
                             _i64, _p, _p, _i64, _p]),
     "porl_transpose": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p]),
+    "porl_costmap": (C.c_int, [_p, _p, _i64, _i64, _p, _p]),
+    "porl_fasternet_workspace_floats": (_i64, [_i64]),
+    "porl_fasternet_forward": (C.c_int, [_p, C.POINTER(FasterNetParams), _p, _i64, _i64, _p, _i64, _p, _i64, _p]),
     "porl_ctx_set_tc_chunk": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_tc_debug": (C.c_int, [_p, _p]),
     "porl_ctx_set_tc_variant": (C.c_int, [_p, C.c_int]),

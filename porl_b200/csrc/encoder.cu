@@ -1,0 +1,539 @@
+// K8/K9: the frozen scan encoder of the POR/SORL agents -- util/costmap.py:7-64 (state2costmap) followed by
+// agent/fasternet.py:428-438 (FasterNet.forward_cls) in train mode (batch-statistic BatchNorm, DropPath).
+//
+// Layout: every activation is an NHWC matrix  X[(b, h, w), C]  (row-major, C contiguous), so a 1x1 convolution
+// is the K-major contraction  Z = X W^T  the tcgen05 kernel already provides (gemm_tc.cu), BatchNorm is a
+// per-column affine map, and the 3x3 partial convolution / 2x2 patch merging read neighbouring rows.
+// The 1.1 MB/sample costmap is never materialised on the training path: it holds ~365 ones, so the 4x4/s4
+// patch embedding is evaluated sparsely from the scan itself (porl_costmap writes the dense raster for the
+// state2costmap API and the tests).
+//
+// No backward: no optimizer owns the encoder's parameters in the reference (agent/sorl.py:60,63,
+// agent/por.py:61,64), so gradients that reach it are never applied.
+#include "encoder.cuh"
+
+#include <math.h>
+
+namespace porl {
+
+namespace {
+
+constexpr int kScan = 360, kBins = 256, kState = 362;
+constexpr int kPH = 90, kPW = 64;                 // patch-embedding output grid (360/4, 256/4)
+
+// Constants of util/costmap.py:19-20,34,44 in the precision torch uses them: python doubles cast to fp32
+// when they meet an fp32 tensor.
+__device__ __forceinline__ float dist_inc() { return (float)((4.0 + 1e-4) / 256.0); }
+__device__ __forceinline__ float angle_inc() { return (float)((2.0 * 3.141592653589793 + 1e-4) / 360.0); }
+
+__device__ __forceinline__ float clamp8(float v) { return v > 8.0f ? 0.0f : v; }   // costmap.py:17
+
+// Range bin of a scan beam (costmap.py:25): trunc(v / dist_inc); -1 when the reference's scatter_ would raise.
+__device__ __forceinline__ int scan_bin(float v) {
+  const float q = __fdiv_rn(clamp8(v), dist_inc());
+  if (!(q > -1.0f) || !(q < 256.0f)) return -1;
+  return (int)q;                                   // q in (-1, 256): trunc toward zero gives 0..255
+}
+
+// Goal cross centre (costmap.py:33-46): row deg in [1, 358], column dist in [0, 254].
+__device__ __forceinline__ void goal_cell(float gx, float gy, int& deg, int& dist) {
+  gx = clamp8(gx);
+  gy = clamp8(gy);
+  const float pi = 3.14159265358979323846f;
+  const float lim = (float)((2.0 * 3.141592653589793 + 2e-4) / 360.0);
+  const float lo = (float)(-3.141592653589793 + (2.0 * 3.141592653589793 + 2e-4) / 360.0);
+  const float hi = (float)(3.141592653589793 - (2.0 * 3.141592653589793 + 2e-4) / 360.0);
+  (void)lim;
+  float a = atan2f(gy, gx);
+  a = fminf(fmaxf(a, lo), hi);
+  deg = (int)__fdiv_rn(__fadd_rn(a, pi), angle_inc());
+  float d = sqrtf(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)));
+  d = fminf(d, (float)(4.0 - 4.0 / 256.0));
+  dist = (int)__fdiv_rn(d, dist_inc());
+}
+
+// ------------------------------------------------------------------------------------ dense costmap
+// grid (360 / 8, B), 256 threads: block = 8 raster rows of one sample (8 x 256 x 3 floats).
+__global__ void __launch_bounds__(256) costmap_kernel(float* __restrict__ state, int64_t ld_state, float* __restrict__ out,
+                                                      uint32_t* __restrict__ status) {
+  const int b = blockIdx.y, r0 = blockIdx.x * 8;
+  float* s = state + (size_t)b * ld_state;
+  float* o = out + ((size_t)b * kScan + r0) * (kBins * 3);
+  float4* o4 = reinterpret_cast<float4*>(o);
+  for (int i = threadIdx.x; i < 8 * kBins * 3 / 4; i += 256) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    const int r = r0 + threadIdx.x;
+    const int beam = (r + 180) % kScan;            // torch.roll(idx, 180, 1): row r shows beam r - 180
+    const int bin = scan_bin(s[beam]);
+    if (bin < 0) atomicOr(status, (uint32_t)PORL_FLAG_SCAN_RANGE);
+    else if (bin > 0) o[(threadIdx.x * kBins + bin) * 3] = 1.0f;       // bin 0 is cleared (costmap.py:30)
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int deg, dist;
+    goal_cell(s[kState - 2], s[kState - 1], deg, dist);
+    const int rr[5] = {deg, deg, deg, deg - 1, deg + 1};
+    const int cc[5] = {(dist + 255) % kBins, dist, (dist + 1) % kBins, dist, dist};
+    for (int i = 0; i < 5; ++i) {
+      const int r = (rr[i] + kScan) % kScan;
+      if (r >= r0 && r < r0 + 8) {
+        float* p = o + ((r - r0) * kBins + cc[i]) * 3;
+        p[0] = p[1] = p[2] = 1.0f;
+      }
+    }
+  }
+  // the in-place clamp of the caller's state (costmap.py:17); every reader above clamps on read
+  if (blockIdx.x == 0)
+    for (int i = threadIdx.x; i < kState; i += 256)
+      if (s[i] > 8.0f) s[i] = 0.0f;
+}
+
+// ------------------------------------------------------------------------------------ sparse patch embedding
+// Y[(b, ph, pw), o] = sum_{c,kh,kw} W[o, c, kh, kw] * costmap[b, c, 4 ph + kh, 4 pw + kw]   (Conv2d k4 s4, no bias)
+// grid (90, B), 192 threads: one block = one patch row (64 patches x 96 channels).  The 4 x 256 x 3 raster
+// window of the patch row is rebuilt as a byte map in shared memory; only patches that hold a one are summed,
+// in the fixed order (c, kh, kw).  wk: (48, 96) = W transposed to [(c, kh, kw), o].
+__global__ void __launch_bounds__(192) patch_embed_kernel(float* __restrict__ state, int64_t ld_state,
+                                                          const float* __restrict__ wk, float* __restrict__ out,
+                                                          uint32_t* __restrict__ status) {
+  __shared__ unsigned char pix[3][4][kBins];
+  __shared__ unsigned char hit[kPW];
+  const int ph = blockIdx.x, b = blockIdx.y, t = threadIdx.x;
+  float* s = state + (size_t)b * ld_state;
+  for (int i = t; i < 3 * 4 * kBins / 4; i += 192) reinterpret_cast<uint32_t*>(&pix[0][0][0])[i] = 0u;
+  if (t < kPW) hit[t] = 0;
+  __syncthreads();
+  if (t < 4) {
+    const int r = 4 * ph + t;
+    const int bin = scan_bin(s[(r + 180) % kScan]);
+    if (bin < 0) atomicOr(status, (uint32_t)PORL_FLAG_SCAN_RANGE);
+    else if (bin > 0) { pix[0][t][bin] = 1; hit[bin >> 2] = 1; }
+  }
+  __syncthreads();
+  if (t == 0) {
+    int deg, dist;
+    goal_cell(s[kState - 2], s[kState - 1], deg, dist);
+    const int rr[5] = {deg, deg, deg, deg - 1, deg + 1};
+    const int cc[5] = {(dist + 255) % kBins, dist, (dist + 1) % kBins, dist, dist};
+    for (int i = 0; i < 5; ++i) {
+      const int r = (rr[i] + kScan) % kScan;
+      if ((r >> 2) == ph) {
+        pix[0][r & 3][cc[i]] = pix[1][r & 3][cc[i]] = pix[2][r & 3][cc[i]] = 1;
+        hit[cc[i] >> 2] = 1;
+      }
+    }
+  }
+  __syncthreads();
+  const int o = t % 96;
+  float* orow = out + ((size_t)b * kPH + ph) * (size_t)(kPW * 96);
+  for (int pw = t / 96; pw < kPW; pw += 2) {
+    float acc = 0.f;
+    if (hit[pw]) {
+      for (int c = 0; c < 3; ++c)
+        for (int kh = 0; kh < 4; ++kh)
+          for (int kw = 0; kw < 4; ++kw)
+            if (pix[c][kh][4 * pw + kw]) acc += wk[(c * 16 + kh * 4 + kw) * 96 + o];
+    }
+    orow[pw * 96 + o] = acc;
+  }
+  if (ph == 0)
+    for (int i = t; i < kState; i += 192)
+      if (s[i] > 8.0f) s[i] = 0.0f;
+}
+
+// ------------------------------------------------------------------------------------ BatchNorm (train mode)
+// Column statistics of X[rows, C] in two levels: every block reduces a slab of rows (fp32 running sums flushed
+// into fp64 every 16 rows, fixed order), writes (sum, sum of squares) per column as fp64 partials, and the last
+// block to finish (ticket) adds the partials in block order and emits
+//     scale = gamma / sqrt(var_biased + eps),  shift = beta - mean * scale
+// plus the running-stat update  r = (1 - m) r + m stat  (unbiased variance), nn.BatchNorm2d training forward.
+// block = 192 threads = (192 / (C/4)) row lanes x (C/4) float4 column groups; C in {96, 192, 384}.
+constexpr int kBnThreads = 192;
+
+__global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __restrict__ x, int64_t rows, int C,
+                                                              int64_t rows_per_block, double* __restrict__ partial,
+                                                              uint32_t* __restrict__ ticket, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, float* __restrict__ run_mean,
+                                                              float* __restrict__ run_var, float eps, float momentum,
+                                                              float* __restrict__ scale_shift) {
+  extern __shared__ double sred[];                 // [lanes][C][2]
+  __shared__ bool last;
+  const int c4n = C >> 2, lanes = kBnThreads / c4n;
+  const int cg = threadIdx.x % c4n, lane = threadIdx.x / c4n;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+  float fs[4] = {0, 0, 0, 0}, fq[4] = {0, 0, 0, 0};
+  int n = 0;
+  for (int64_t r = r0 + lane; r < r1; r += lanes) {
+    const float4 v = *reinterpret_cast<const float4*>(x + r * C + 4 * cg);
+    fs[0] += v.x; fs[1] += v.y; fs[2] += v.z; fs[3] += v.w;
+    fq[0] = fmaf(v.x, v.x, fq[0]); fq[1] = fmaf(v.y, v.y, fq[1]);
+    fq[2] = fmaf(v.z, v.z, fq[2]); fq[3] = fmaf(v.w, v.w, fq[3]);
+    if (++n == 16) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { s[j] += fs[j]; q[j] += fq[j]; fs[j] = 0.f; fq[j] = 0.f; }
+      n = 0;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { s[j] += fs[j]; q[j] += fq[j]; }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    sred[((size_t)lane * C + 4 * cg + j) * 2 + 0] = s[j];
+    sred[((size_t)lane * C + 4 * cg + j) * 2 + 1] = q[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    double a = 0, b = 0;
+    for (int l = 0; l < lanes; ++l) { a += sred[((size_t)l * C + c) * 2]; b += sred[((size_t)l * C + c) * 2 + 1]; }
+    partial[((size_t)blockIdx.x * C + c) * 2] = a;
+    partial[((size_t)blockIdx.x * C + c) * 2 + 1] = b;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    double a = 0, b = 0;
+    for (unsigned g = 0; g < gridDim.x; ++g) {
+      a += __ldcg(&partial[((size_t)g * C + c) * 2]);
+      b += __ldcg(&partial[((size_t)g * C + c) * 2 + 1]);
+    }
+    const double mean = a / (double)rows;
+    double var = b / (double)rows - mean * mean;
+    if (var < 0) var = 0;
+    const float sc = (float)((double)gamma[c] / sqrt(var + (double)eps));
+    scale_shift[c] = sc;
+    scale_shift[C + c] = (float)((double)beta[c] - mean * (double)sc);
+    const double unbiased = rows > 1 ? var * (double)rows / (double)(rows - 1) : var;
+    run_mean[c] = (float)((1.0 - (double)momentum) * (double)run_mean[c] + (double)momentum * mean);
+    run_var[c] = (float)((1.0 - (double)momentum) * (double)run_var[c] + (double)momentum * unbiased);
+  }
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+
+// y = x * scale[c] + shift[c] (+ ReLU), in place; float4 over an (rows x C) matrix
+__global__ void __launch_bounds__(256) bn_apply_kernel(float* __restrict__ x, int64_t n4, int c4n,
+                                                       const float* __restrict__ scale_shift, int C, int relu) {
+  const float4* sc4 = reinterpret_cast<const float4*>(scale_shift);
+  const float4* sh4 = reinterpret_cast<const float4*>(scale_shift + C);
+  float4* x4 = reinterpret_cast<float4*>(x);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    const int cg = (int)(i % c4n);
+    const float4 sc = __ldg(sc4 + cg), sh = __ldg(sh4 + cg);
+    float4 v = x4[i];
+    v.x = fmaf(v.x, sc.x, sh.x); v.y = fmaf(v.y, sc.y, sh.y); v.z = fmaf(v.z, sc.z, sh.z); v.w = fmaf(v.w, sc.w, sh.w);
+    if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    x4[i] = v;
+  }
+}
+
+// x[(b, p), :] += keep[b] * t[(b, p), :]    (residual + DropPath, fasternet.py:183-187); keep may be null (all 1)
+__global__ void __launch_bounds__(256) residual_kernel(float* __restrict__ x, const float* __restrict__ t, int64_t n4,
+                                                       int64_t per_sample4, const float* __restrict__ keep) {
+  float4* x4 = reinterpret_cast<float4*>(x);
+  const float4* t4 = reinterpret_cast<const float4*>(t);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    const float k = keep ? __ldg(keep + i / per_sample4) : 1.0f;
+    float4 v = x4[i];
+    const float4 u = t4[i];
+    // the reference multiplies the branch by the mask first, then adds the shortcut (two roundings)
+    v.x = __fadd_rn(v.x, __fmul_rn(u.x, k)); v.y = __fadd_rn(v.y, __fmul_rn(u.y, k));
+    v.z = __fadd_rn(v.z, __fmul_rn(u.z, k)); v.w = __fadd_rn(v.w, __fmul_rn(u.w, k));
+    x4[i] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------ partial 3x3 convolution
+// Partial_conv3.forward_split_cat (fasternet.py:131-138) on an NHWC matrix: channels [0, c) of the output are
+// the zero-padded 3x3 convolution of channels [0, c) of the input, channels [c, C) are copied.
+// grid (tiles_w, tiles_h, B), 128 threads; one block = 16 x 16 pixels, one thread = pixels (ty, tx) and
+// (ty + 8, tx) with all c output channels in registers.  Input channels go through shared memory 8 at a
+// time (18 x 18 halo tile, pixel stride 9 floats: conflict-free) together with the matching weight slab.
+// wk: (9, c, c) = [tap = kh * 3 + kw][ci][co].
+template <int CC>
+__global__ void __launch_bounds__(128) pconv3_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                     const float* __restrict__ wk, int H, int W, int C) {
+  constexpr int CI = 8, XS = CI + 1;
+  __shared__ float xs[18 * 18 * XS];
+  __shared__ __align__(16) float ws[9 * CI * CC];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;       // ty 0..7
+  const int w0 = blockIdx.x * 16, h0 = blockIdx.y * 16, b = blockIdx.z;
+  const float* xb = x + (size_t)b * H * W * C;
+  float* yb = y + (size_t)b * H * W * C;
+  float acc0[CC], acc1[CC];
+#pragma unroll
+  for (int j = 0; j < CC; ++j) acc0[j] = acc1[j] = 0.f;
+
+  for (int ci0 = 0; ci0 < CC; ci0 += CI) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 18 * 18 * 2; i += 128) {       // halo pixels x two float4 halves
+      const int pix = i >> 1, half = i & 1;
+      const int hh = h0 - 1 + pix / 18, ww = w0 - 1 + pix % 18;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (hh >= 0 && hh < H && ww >= 0 && ww < W)
+        v = *reinterpret_cast<const float4*>(xb + ((size_t)hh * W + ww) * C + ci0 + 4 * half);
+      float* d = xs + pix * XS + 4 * half;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+    for (int i = threadIdx.x; i < 9 * CI * CC / 4; i += 128) {
+      const int tap = i / (CI * CC / 4), rem = i % (CI * CC / 4);
+      reinterpret_cast<float4*>(ws)[i] =
+          *reinterpret_cast<const float4*>(wk + ((size_t)tap * CC + ci0) * CC + 4 * rem);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int tap = 0; tap < 9; ++tap) {
+      const int dy = tap / 3, dx = tap % 3;
+      const float* p0 = xs + ((ty + dy) * 18 + tx + dx) * XS;
+      const float* p1 = p0 + 8 * 18 * XS;
+      const float* wt = ws + tap * CI * CC;
+#pragma unroll
+      for (int ci = 0; ci < CI; ++ci) {
+        const float a0 = p0[ci], a1 = p1[ci];
+#pragma unroll
+        for (int co = 0; co < CC; co += 4) {
+          const float4 wv = *reinterpret_cast<const float4*>(wt + ci * CC + co);
+          acc0[co] = fmaf(a0, wv.x, acc0[co]); acc0[co + 1] = fmaf(a0, wv.y, acc0[co + 1]);
+          acc0[co + 2] = fmaf(a0, wv.z, acc0[co + 2]); acc0[co + 3] = fmaf(a0, wv.w, acc0[co + 3]);
+          acc1[co] = fmaf(a1, wv.x, acc1[co]); acc1[co + 1] = fmaf(a1, wv.y, acc1[co + 1]);
+          acc1[co + 2] = fmaf(a1, wv.z, acc1[co + 2]); acc1[co + 3] = fmaf(a1, wv.w, acc1[co + 3]);
+        }
+      }
+    }
+  }
+  const int w = w0 + tx;
+  if (w < W) {
+    const int ha = h0 + ty, hb = h0 + ty + 8;
+    if (ha < H) {
+      float4* o = reinterpret_cast<float4*>(yb + ((size_t)ha * W + w) * C);
+#pragma unroll
+      for (int co = 0; co < CC; co += 4) o[co >> 2] = make_float4(acc0[co], acc0[co + 1], acc0[co + 2], acc0[co + 3]);
+    }
+    if (hb < H) {
+      float4* o = reinterpret_cast<float4*>(yb + ((size_t)hb * W + w) * C);
+#pragma unroll
+      for (int co = 0; co < CC; co += 4) o[co >> 2] = make_float4(acc1[co], acc1[co + 1], acc1[co + 2], acc1[co + 3]);
+    }
+  }
+  // untouched channels [CC, C): straight copy of the tile
+  const int rest4 = (C - CC) >> 2;
+  for (int i = threadIdx.x; i < 256 * rest4; i += 128) {
+    const int pix = i / rest4, j = i % rest4;
+    const int hh = h0 + (pix >> 4), ww = w0 + (pix & 15);
+    if (hh < H && ww < W) {
+      const size_t off = ((size_t)hh * W + ww) * C + CC + 4 * j;
+      *reinterpret_cast<float4*>(yb + off) = *reinterpret_cast<const float4*>(xb + off);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ 2x2 space-to-depth
+// out[(b, h2, w2), (kh * 2 + kw) * C + c] = in[(b, 2 h2 + kh, 2 w2 + kw), c]: the im2col of the k2 s2 patch-merging
+// convolution (fasternet.py:264-277), so that it becomes one K = 4C contraction.
+__global__ void __launch_bounds__(256) space_to_depth_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                             int64_t n4, int H2, int W2, int c4n) {
+  const float4* in4 = reinterpret_cast<const float4*>(in);
+  float4* out4 = reinterpret_cast<float4*>(out);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    const int cg = (int)(i % c4n);
+    int64_t r = i / c4n;
+    const int tap = (int)(r & 3);
+    r >>= 2;
+    const int w2 = (int)(r % W2);
+    r /= W2;
+    const int h2 = (int)(r % H2);
+    const int64_t b = r / H2;
+    const int64_t src = ((b * (2 * H2) + 2 * h2 + (tap >> 1)) * (2 * W2) + 2 * w2 + (tap & 1)) * c4n + cg;
+    out4[i] = in4[src];
+  }
+}
+
+// ------------------------------------------------------------------------------------ global average pool
+// out[b, c] = mean_p x[(b, p), c]   (AdaptiveAvgPool2d(1), fasternet.py:372); grid B, block (C, 4): four row
+// lanes per column, combined in lane order.
+__global__ void avgpool_kernel(const float* __restrict__ x, float* __restrict__ out, int P, int C, int64_t ld_out) {
+  extern __shared__ float spool[];                 // [4][C]
+  const int c = threadIdx.x, lane = threadIdx.y;
+  const float* xb = x + (size_t)blockIdx.x * P * C;
+  float a0 = 0.f, a1 = 0.f;
+  int p = lane;
+  for (; p + 4 < P; p += 8) { a0 += xb[(size_t)p * C + c]; a1 += xb[(size_t)(p + 4) * C + c]; }
+  if (p < P) a0 += xb[(size_t)p * C + c];
+  spool[lane * C + c] = a0 + a1;
+  __syncthreads();
+  if (lane == 0)
+    out[(size_t)blockIdx.x * ld_out + c] = __fdiv_rn((spool[c] + spool[C + c]) + (spool[2 * C + c] + spool[3 * C + c]), (float)P);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------ host side
+namespace {
+
+constexpr int kBnMaxBlocks = 592;                 // 4 x 148 slabs at most
+constexpr int kBnTicket = 8;                      // ctx->counters word of the BatchNorm reduction
+constexpr int64_t kHdrFloats = (int64_t)kBnMaxBlocks * 384 * 2 * 2 + 1024;   // fp64 partials + scale/shift
+constexpr int64_t kPerSample = (int64_t)kPH * kPW * 384;                       // R0 + R1 + R2 floats per sample
+
+struct EncWs {
+  double* partial;
+  float* scale_shift;
+  float *r0, *r1, *r2;
+};
+
+int conv1x1(porl_ctx* ctx, const float* A, int64_t rows, int K, const float* W, int N, float* C, int64_t ldc,
+            const float* bias, int epilogue, cudaStream_t st) {
+  GemmBatch gb;
+  gb.n_groups = 1;
+  gb.splits = 1;
+  GemmGroup& g = gb.g[0];
+  g = GemmGroup{};
+  g.A = A; g.B = W; g.C = C; g.bias = bias;
+  g.M = (int)rows; g.N = N; g.K = K;
+  g.lda = K; g.ldb = K; g.ldc = (int)ldc; g.n_store = N; g.epilogue = epilogue;
+  return launch_gemm(ctx, true, true, gb, st);
+}
+
+int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, const porl_bn_t& bn, int relu, cudaStream_t st) {
+  PORL_CHECK_ARG(bn.weight && bn.bias && bn.running_mean && bn.running_var, "fasternet: null BatchNorm tensor");
+  int64_t G = (rows + 255) / 256;
+  if (G > kBnMaxBlocks) G = kBnMaxBlocks;
+  const int64_t rpb = (rows + G - 1) / G;
+  G = (rows + rpb - 1) / rpb;
+  const size_t smem = (size_t)(kBnThreads / (C / 4)) * C * 2 * sizeof(double);
+  {
+    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 4.0, st);
+    bn_stats_kernel<<<(unsigned)G, kBnThreads, smem, st>>>(x, rows, C, rpb, w.partial, ctx->counters + kBnTicket, bn.weight,
+                                                           bn.bias, bn.running_mean, bn.running_var, 1e-5f, 0.1f,
+                                                           w.scale_shift);
+    PORL_LAUNCHED(ctx);
+  }
+  const int64_t n4 = rows * C / 4;
+  int64_t grid = (n4 + 255) / 256;
+  if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
+  ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 8.0, st);
+  bn_apply_kernel<<<(unsigned)grid, 256, 0, st>>>(x, n4, C / 4, w.scale_shift, C, relu);
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+// MLPBlock.forward: x (rows, C) is updated in place; xm (rows, C) and z (rows, 2C) are scratch
+int mlp_block(porl_ctx* ctx, const EncWs& w, const porl_fn_block_t& blk, float* x, float* xm, float* z, int64_t B, int H,
+              int W, int C, cudaStream_t st) {
+  PORL_CHECK_ARG(blk.pconv_w && blk.w1 && blk.w2, "fasternet: null block weight");
+  const int64_t rows = B * H * W;
+  {
+    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 8.0, st);
+    const dim3 grid((W + 15) / 16, (H + 15) / 16, (unsigned)B);
+    if (C == 96) pconv3_kernel<24><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);
+    else pconv3_kernel<48><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);
+    PORL_LAUNCHED(ctx);
+  }
+  int rc = conv1x1(ctx, xm, rows, C, blk.w1, 2 * C, z, 2 * C, nullptr, 0, st);
+  if (rc != PORL_OK) return rc;
+  rc = batch_norm(ctx, w, z, rows, 2 * C, blk.bn, 1, st);
+  if (rc != PORL_OK) return rc;
+  rc = conv1x1(ctx, z, rows, 2 * C, blk.w2, C, xm, C, nullptr, 0, st);      // branch output reuses xm
+  if (rc != PORL_OK) return rc;
+  const int64_t n4 = rows * C / 4;
+  int64_t grid = (n4 + 255) / 256;
+  if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
+  ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 12.0, st);
+  residual_kernel<<<(unsigned)grid, 256, 0, st>>>(x, xm, n4, (int64_t)H * W * C / 4, blk.keep);
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+}  // namespace
+}  // namespace porl
+
+using namespace porl;
+
+extern "C" int porl_costmap(porl_ctx_t* ctx, float* state, int64_t ld_state, int64_t B, float* out, porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && state && out, "porl_costmap: null argument");
+  PORL_CHECK_ARG(B >= 0 && B <= 65535 && ld_state >= kState, "porl_costmap: B=%lld ld_state=%lld", (long long)B,
+                 (long long)ld_state);
+  PORL_CHECK_ARG(aligned16(out), "porl_costmap: out must be 16-byte aligned");
+  if (B == 0) return PORL_OK;
+  cudaStream_t st = as_stream(stream);
+  ProfScope prof(ctx, PORL_CAT_ENCODER, (double)B * kScan * kBins * 3 * 4.0, st);
+  costmap_kernel<<<dim3(kScan / 8, (unsigned)B), 256, 0, st>>>(state, ld_state, out, ctx->counters);
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+extern "C" int64_t porl_fasternet_workspace_floats(int64_t B) { return B < 0 ? -1 : kHdrFloats + B * kPerSample; }
+
+extern "C" int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* net, float* state, int64_t ld_state,
+                                      int64_t B, float* features, int64_t ld_feat, float* workspace,
+                                      int64_t workspace_floats, porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && net && state && features && workspace, "porl_fasternet_forward: null argument");
+  // rows * 2C must stay below 2^31 for the contraction's 32-bit extents: 1024 x 5760 x 192 = 1.13e9
+  PORL_CHECK_ARG(B >= 1 && B <= 1024, "porl_fasternet_forward: B=%lld outside [1, 1024]", (long long)B);
+  PORL_CHECK_ARG(ld_state >= kState, "porl_fasternet_forward: ld_state=%lld", (long long)ld_state);
+  const int F = net->feature_dim;
+  PORL_CHECK_ARG(F >= 1 && ld_feat >= F, "porl_fasternet_forward: feature_dim=%d ld_feat=%lld", F, (long long)ld_feat);
+  PORL_CHECK_ARG(workspace_floats >= porl_fasternet_workspace_floats(B) && aligned16(workspace),
+                 "porl_fasternet_forward: workspace of %lld floats, %lld needed (16-byte aligned)",
+                 (long long)workspace_floats, (long long)porl_fasternet_workspace_floats(B));
+  PORL_CHECK_ARG(net->pe_w && net->merge_w && net->head_conv_w && net->head_w && net->head_b,
+                 "porl_fasternet_forward: null weight");
+  cudaStream_t st = as_stream(stream);
+  const int64_t rows0 = B * kPH * kPW, rows1 = rows0 / 4;
+  EncWs w;
+  w.partial = reinterpret_cast<double*>(workspace);
+  w.scale_shift = workspace + (int64_t)kBnMaxBlocks * 384 * 2 * 2;
+  w.r0 = workspace + kHdrFloats;
+  w.r1 = w.r0 + rows0 * 96;
+  w.r2 = w.r1 + rows0 * 96;
+
+  // patch embedding straight from the scan (costmap never materialised) + BatchNorm
+  {
+    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows0 * 96 * 4.0, st);
+    patch_embed_kernel<<<dim3(kPH, (unsigned)B), 192, 0, st>>>(state, ld_state, net->pe_w, w.r0, ctx->counters);
+    PORL_LAUNCHED(ctx);
+  }
+  int rc = batch_norm(ctx, w, w.r0, rows0, 96, net->pe_bn, 0, st);
+  if (rc != PORL_OK) return rc;
+  // stage 0: one MLPBlock of width 96 on the 90 x 64 grid
+  rc = mlp_block(ctx, w, net->block[0], w.r0, w.r1, w.r2, B, kPH, kPW, 96, st);
+  if (rc != PORL_OK) return rc;
+  // patch merging: k2 s2 convolution as space-to-depth + one K = 384 contraction, then BatchNorm
+  float* a1 = w.r2;
+  float* x1 = w.r1;
+  {
+    const int64_t n4 = rows1 * 384 / 4;
+    int64_t grid = (n4 + 255) / 256;
+    if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
+    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows1 * 384 * 8.0, st);
+    space_to_depth_kernel<<<(unsigned)grid, 256, 0, st>>>(w.r0, a1, n4, kPH / 2, kPW / 2, 96 / 4);
+    PORL_LAUNCHED(ctx);
+  }
+  rc = conv1x1(ctx, a1, rows1, 384, net->merge_w, 192, x1, 192, nullptr, 0, st);
+  if (rc != PORL_OK) return rc;
+  rc = batch_norm(ctx, w, x1, rows1, 192, net->merge_bn, 0, st);
+  if (rc != PORL_OK) return rc;
+  // stage 1: two MLPBlocks of width 192 on the 45 x 32 grid
+  float* xm1 = w.r1 + rows1 * 192;
+  float* z1 = w.r2 + rows1 * 384;
+  for (int i = 1; i <= 2; ++i) {
+    rc = mlp_block(ctx, w, net->block[i], x1, xm1, z1, B, kPH / 2, kPW / 2, 192, st);
+    if (rc != PORL_OK) return rc;
+  }
+  // head: global average pool, 1x1 conv 192 -> 1280 + ReLU, Linear 1280 -> feature_dim
+  float* pooled = w.r0;
+  float* hidden = w.r0 + B * 192;
+  {
+    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows1 * 192 * 4.0, st);
+    avgpool_kernel<<<(unsigned)B, dim3(192, 4), 4 * 192 * sizeof(float), st>>>(x1, pooled, (kPH / 2) * (kPW / 2), 192, 192);
+    PORL_LAUNCHED(ctx);
+  }
+  rc = conv1x1(ctx, pooled, B, 192, net->head_conv_w, 1280, hidden, 1280, nullptr, 1, st);
+  if (rc != PORL_OK) return rc;
+  return conv1x1(ctx, hidden, B, 1280, net->head_w, F, features, ld_feat, net->head_b, 0, st);
+}

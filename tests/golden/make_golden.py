@@ -101,8 +101,50 @@ def run_cosine(base, t_max, n):
     return dict(base=np.array(base), t_max=np.array(t_max), lrs=np.array(lrs, np.float64))
 
 
+def run_encoder(seed, B):
+    """The unmodified reference FasterNet(3, 256) on deterministic weights; DropPath masks injected by replacing
+    the module-level drop_path function (agent/fasternet.py:76-93) with one that replays recorded factors."""
+    from oracle import encoder
+    FN = refimport.fasternet_cls()
+    import agent.fasternet as rf
+    st, keeps = encoder.encoder_inputs(seed, B)
+    cm = refimport.costmap_fn()(st.clone())
+    m = FN(3, 256)
+    keys = list(m.state_dict().keys())
+    m.load_state_dict(encoder.det_encoder_state_dict(seed + 1))
+    queue = [k for k in keeps if k is not None]
+    orig = rf.drop_path
+
+    def replay(x, drop_prob=0., training=False, scale_by_keep=True):
+        if drop_prob == 0. or not training:
+            return x
+        return x * queue.pop(0).view(-1, 1, 1, 1).to(x.dtype)
+
+    rf.drop_path = replay
+    try:
+        x = st.clone()
+        feats = [m(x).detach().numpy()]
+    finally:
+        rf.drop_path = orig
+    sd = m.state_dict()
+    out = dict(meta=np.array([seed, B]), keys=np.array(keys), features=feats[0], clamped_state=x.numpy(),
+               costmap_nonzero=np.argwhere(cm.numpy() != 0).astype(np.int32))
+    out.update(flat("stats", {k: v for k, v in sd.items() if "running" in k or "tracked" in k}))
+    torch.manual_seed(seed)
+    init = FN(3, 256).state_dict()
+    out.update(flat("init", {k: np.array([v.double().sum().item(), v.double().abs().sum().item()])
+                             for k, v in init.items() if v.is_floating_point()}))
+    return out
+
+
 def main():
     assert refimport.available(), "needs /root/reference"
+    if len(sys.argv) > 1 and sys.argv[1] == "encoder":
+        d = run_encoder(51, 6)
+        path = os.path.join(HERE, "encoder_small.npz")
+        np.savez_compressed(path, **d)
+        print(f"encoder_small: {os.path.getsize(path) / 1024:.1f} KiB")
+        return
     cases = {
         "por_small": run_agent("por", 22, 32, 16, 5, 3, 11),
         "sorl_small": run_agent("sorl", 22, 32, 16, 5, 3, 12),
@@ -113,6 +155,7 @@ def main():
         "cql_real": run_cql(362, 5, 64, 500, 3, 10, 32),
         "replay_buffer": run_buffer(41),
         "cosine_lr": run_cosine(1e-4, 4, 14),
+        "encoder_small": run_encoder(51, 6),
     }
     for name, d in cases.items():
         path = os.path.join(HERE, name + ".npz")
