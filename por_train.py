@@ -14,11 +14,13 @@ def train(args):
     device = torch.device(args.device)
     if device.type != "cuda":
         raise SystemExit("porl_b200 runs on CUDA (sm_100a) only; use the reference for --device cpu")
-    if args.backbone != "none":
-        raise NotImplementedError("the FasterNet scan encoder is not built yet (DESIGN.md section 8)")
     torch.manual_seed(1000 + args.seed)
+    backbone = None
+    if args.backbone == "fasternet":                    # BASELINE config 4: POR with the FasterNet scan encoder
+        from porl_b200.agent.fasternet import FasterNet
+        backbone = FasterNet(3, args.feature_dim)
     agent = POR(args, max_steps=args.train_steps, tau=args.tau, alpha=args.alpha, discount=args.discount,
-                value_lr=args.value_lr, policy_lr=args.policy_lr, device=device)          # por_train.py:48-57
+                value_lr=args.value_lr, policy_lr=args.policy_lr, device=device, backbone=backbone)  # por_train.py:48-57
     out = run(args, agent, lambda a, pb: a.update_packed(pb), save_every=25, name="por")   # :96-97 every 25 episodes
     print(out)
     return out

@@ -35,39 +35,46 @@ class ExpectileAgent(nn.Module):
 
     def _build(self, args, max_steps, tau, alpha, backbone, device, value_lr, policy_lr, discount, beta,
                policy_out: int):
-        if backbone is not None:
-            raise NotImplementedError(
-                "the FasterNet scan encoder (agent/fasternet.py) is not built yet in porl_b200; "
-                "construct the agent with backbone=None (MLP-only heads, as sorl_train_v0.py)")
         self.device = torch.device(device)
         self.ctx = _C.context(self.device)
-        self.backbone = None
         S, H, n_hidden = int(args.state_size), int(args.hidden_dim), int(args.n_hidden)
         self.state_size, self.policy_out = S, int(policy_out)
         dev = self.device
+        # agent/por.py:34,46 / agent/sorl.py:34,47: with a backbone the heads read its (B, feature_dim) output.
+        # Registered first, like the reference, so its keys lead the state_dict.
+        self.backbone = None
+        if backbone is not None:
+            if not hasattr(backbone, "forward_features"):
+                raise TypeError("backbone must be a porl_b200.agent.fasternet.FasterNet (kernel-backed encoder)")
+            if S != 362:
+                raise ValueError(f"the scan encoder reads 362-float states (util/costmap.py:11), got state_size={S}")
+            self.backbone = backbone.to(dev)
+        F_in = int(args.feature_dim) if backbone is not None else S
+        self.in_features = F_in
+        S_heads = F_in
 
         # --- value group: online TwinV parameters in the group's flat buffer; private target buffer
-        probe = TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, init=False)  # geometry only
+        probe = TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, init=False)  # geometry only
         self.v_group = ParamGroup(self.ctx, probe.plan.n_floats, dev, lr=value_lr)
         policy_cls = BoundedGaussianPolicy if self._bounded else GaussianPolicy
         # construction order follows the reference so that the global torch RNG is consumed alike:
         # POR builds goal_policy then vf (por.py:35-45); SORL builds v_net then policy (sorl.py:36-45)
         def make_value():
-            return TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, flat=self.v_group.params,
+            return TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, flat=self.v_group.params,
                          grads=self.v_group.grads)
 
         def make_policy():
-            pol_probe = policy_cls(S, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, init=False)
+            pol_probe = policy_cls(S_heads, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, init=False)
             n = policy_cls.group_floats(pol_probe.plan, self.policy_out)
             self.p_group = ParamGroup(self.ctx, n, dev, lr=policy_lr, t_max=int(max_steps))
-            return policy_cls(S, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, flat=self.p_group.params,
+            return policy_cls(S_heads, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, flat=self.p_group.params,
                               grads=self.p_group.grads)
 
         if self._policy_first:
             policy, value = make_policy(), make_value()
         else:
             value, policy = make_value(), make_policy()
-        target = TwinV(S, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, trainable=False, init=False)
+        target = TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, trainable=False, init=False)
         target.flat.copy_(self.v_group.params[:target.flat.numel()])       # deepcopy(vf).requires_grad_(False)
         # registration order = the reference's attribute order, so state_dict() key order matches
         first, second = ((self._policy_name, policy), (self._value_name, value))
@@ -88,6 +95,7 @@ class ExpectileAgent(nn.Module):
         self._host_status = _C.pinned(1, torch.int32)
         self._status = self.ctx.status_tensor()
         self._packed: dict[int, PackedBatch] = {}
+        self._features: dict[int, tuple[torch.Tensor, torch.Tensor]] = {}
 
     # ------------------------------------------------------------------ batch packing
     def pack(self, observations, next_observations, rewards, terminals, actions=None) -> PackedBatch:
@@ -108,7 +116,22 @@ class ExpectileAgent(nn.Module):
         return pb
 
     # ------------------------------------------------------------------ the update
-    def _value_step(self, pb: PackedBatch) -> None:
+    def _head_inputs(self, pb: PackedBatch):
+        """(x_obs, x_next, ld): what the value / policy heads read.  With a backbone: its features of obs, then of
+        next_obs (that order: agent/sorl.py:81-83, agent/por.py:75-77), each call a train-mode forward that also
+        clamps the packed states in place (util/costmap.py:17)."""
+        if self.backbone is None:
+            return pb.obs, pb.next_obs, pb.ld_obs
+        ld = pad_to(self.in_features)
+        f = self._features.get(pb.B)
+        if f is None:
+            f = tuple(torch.zeros(pb.B, ld, dtype=torch.float32, device=self.device) for _ in range(2))
+            self._features[pb.B] = f
+        self.backbone.forward_features(pb.obs, pb.ld_obs, pb.B, f[0])
+        self.backbone.forward_features(pb.next_obs, pb.ld_obs, pb.B, f[1])
+        return f[0], f[1], ld
+
+    def _value_step(self, pb: PackedBatch, x_obs, x_next, ld_x) -> None:
         ctx, B = self.ctx, pb.B
         plan = self._value.plan
         ws = self._ws
@@ -118,8 +141,8 @@ class ExpectileAgent(nn.Module):
         out_v = ws.get(("out_v", B), 2 * B * plan.out_ld)
         dv = ws.get(("dv", B), 2 * B * plan.out_ld)
         target_v = ws.get(("target_v", B), B)
-        call_t = mlp_call(plan, self._target.flat, pb.next_obs, pb.ld_obs, scratch_t, out_t, inference=True)
-        call_v = mlp_call(plan, self.v_group.params, pb.obs, pb.ld_obs, saved_v, out_v)
+        call_t = mlp_call(plan, self._target.flat, x_next, ld_x, scratch_t, out_t, inference=True)
+        call_v = mlp_call(plan, self.v_group.params, x_obs, ld_x, saved_v, out_v)
         mlp_forward(ctx, [call_t, call_v], B)
         ld, net = plan.out_ld, B * plan.out_ld * 4
         b_norm = B * pdist.world_size()
@@ -131,7 +154,7 @@ class ExpectileAgent(nn.Module):
         pdist.allreduce_sum_(self.v_group.bucket)
         self.v_group.step(target=self._target.flat, ema_beta=self.beta)
 
-    def _policy_step(self, pb: PackedBatch, x: torch.Tensor, ld_x: int) -> None:
+    def _policy_step(self, pb: PackedBatch, x_obs, ld_obs, x: torch.Tensor, ld_x: int) -> None:
         ctx, B = self.ctx, pb.B
         vplan, pplan = self._value.plan, self._policy.plan
         ws = self._ws
@@ -141,8 +164,8 @@ class ExpectileAgent(nn.Module):
         out_p = ws.get(("out_p", B), B * pplan.out_ld)
         dz_p = ws.get(("dz_p", B), B * pplan.out_ld)
         target_v = ws.get(("target_v", B), B)
-        call_v = mlp_call(vplan, self.v_group.params, pb.obs, pb.ld_obs, scratch_v, out_v2, inference=True)
-        call_p = mlp_call(pplan, self.p_group.params, pb.obs, pb.ld_obs, saved_p, out_p)
+        call_v = mlp_call(vplan, self.v_group.params, x_obs, ld_obs, scratch_v, out_v2, inference=True)
+        call_p = mlp_call(pplan, self.p_group.params, x_obs, ld_obs, saved_p, out_p)
         mlp_forward(ctx, [call_v, call_p], B)
         off = self._policy.log_std_offset * 4
         net = B * vplan.out_ld * 4
@@ -161,12 +184,13 @@ class ExpectileAgent(nn.Module):
 
     def update_packed(self, pb: PackedBatch) -> None:
         """One gradient update on a packed device minibatch; asynchronous, returns nothing."""
-        self._value_step(pb)
+        x_obs, x_next, ld = self._head_inputs(pb)
+        self._value_step(pb, x_obs, x_next, ld)
         x, ld_x = self._policy_target(pb)
-        self._policy_step(pb, x, ld_x)
+        self._policy_step(pb, x_obs, ld, x, ld_x)
 
     def value_update_packed(self, pb: PackedBatch) -> None:
-        self._value_step(pb)
+        self._value_step(pb, *self._head_inputs(pb))
 
     def read_losses(self) -> tuple[float, float]:
         """Synchronising read of (v_loss, policy_loss) of the last update; raises on device flags."""
@@ -184,5 +208,8 @@ class ExpectileAgent(nn.Module):
                 msgs.append("non-positive per-sample NLL (the reference drops into pdb here, agent/por.py:104)")
             if flags & _C.FLAG_BAD_INDEX:
                 msgs.append("gather index out of range")
+            if flags & _C.FLAG_SCAN_RANGE:
+                msgs.append("scan value outside [0, 4.0001) u (8, inf): state2costmap's scatter_ raises here "
+                            "(util/costmap.py:29)")
             raise FloatingPointError("; ".join(msgs) or f"device status {flags}")
         return float(self._host[0]), float(self._host[1])

@@ -193,6 +193,11 @@ class FasterNet(nn.Module):
             out.append(r.reshape(B))
         return out
 
+    def replay_keep_scales(self, per_forward: list) -> None:
+        """Parity hook: the next len(per_forward) forwards use these DropPath factors ([None, (B,), (B,)] each)
+        instead of drawing them (the tests feed the oracle and this module the same masks)."""
+        self._cache["keep_queue"] = list(per_forward)
+
     # ------------------------------------------------------------------ forward
     def forward_features(self, state: torch.Tensor, ld_state: int, B: int, out: torch.Tensor, keep_scales=None) -> None:
         """Kernel-level entry: `state` is a float32 CUDA buffer of B rows with stride ld_state (clamped in
@@ -202,6 +207,8 @@ class FasterNet(nn.Module):
         if not self.training:
             raise NotImplementedError("eval-mode BatchNorm is not built: the reference never leaves train mode")
         ctx = _C.context(state.device)
+        if keep_scales is None and self._cache.get("keep_queue"):
+            keep_scales = self._cache["keep_queue"].pop(0)
         keeps = keep_scales if keep_scales is not None else self._keep_scales(state, B)
         keeps = [None if k is None else k.to(state.device, torch.float32).contiguous() for k in keeps]
         n = int(lib.porl_fasternet_workspace_floats(B))

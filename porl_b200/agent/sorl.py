@@ -33,6 +33,8 @@ class SORL(ExpectileAgent):
 
     def select_action(agent, observations):
         """agent/sorl.py:71-76: policy mean as a numpy array (B, A)."""
+        if agent.backbone is not None:                  # sorl.py:73-74 (train-mode encoder, as the reference)
+            observations = agent.backbone(observations)
         return agent.policy(observations).mean.cpu().numpy()
 
     def update(agent, observations, actions, rewards, next_observations, terminals):

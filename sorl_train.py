@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """SORL offline training on B200: same flags and loop shape as the reference sorl_train.py:20-106
 (agent.update(obs, actions, rewards, next_obs, dones)).  The reference always wraps the heads in a FasterNet
-encoder (sorl_train.py:29-32); that encoder is not built yet, so this runs the MLP-only variant of
-sorl_train_v0.py (backbone=None).  New flags: see porl_b200/train/offline_loop.py."""
+encoder (sorl_train.py:29-32): pass --backbone fasternet for that; the default (--backbone none) is the
+MLP-only variant of sorl_train_v0.py.  New flags: see porl_b200/train/offline_loop.py."""
 import argparse
 
 import torch
@@ -15,11 +15,13 @@ def train(args):
     device = torch.device(args.device)
     if device.type != "cuda":
         raise SystemExit("porl_b200 runs on CUDA (sm_100a) only; use the reference for --device cpu")
-    if args.backbone != "none":
-        raise NotImplementedError("the FasterNet scan encoder is not built yet (DESIGN.md section 8)")
     torch.manual_seed(1000 + args.seed)
+    backbone = None
+    if args.backbone == "fasternet":
+        from porl_b200.agent.fasternet import FasterNet
+        backbone = FasterNet(3, args.feature_dim)                                          # sorl_train.py:29
     agent = SORL(args, max_steps=args.train_steps, tau=args.tau, alpha=args.alpha, discount=args.discount,
-                 value_lr=args.value_lr, policy_lr=args.policy_lr, device=device)         # sorl_train.py:31-40
+                 value_lr=args.value_lr, policy_lr=args.policy_lr, device=device, backbone=backbone)  # sorl_train.py:31-40
     out = run(args, agent, lambda a, pb: a.update_packed(pb), save_every=2 if args.evaluate else 0, name="sorl")
     print(out)
     return out

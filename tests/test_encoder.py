@@ -190,3 +190,71 @@ def test_cuda_fasternet_larger_batch_vs_oracle_and_determinism():
     sd64 = {k: (v.double() if v.is_floating_point() else v.clone()) for k, v in sd.items()}
     f64 = encoder.fasternet_forward(sd64, st.clone(), [None if k is None else k.cpu() for k in keeps])
     assert rel(outs[0].cpu(), f64) < FEAT_TOL, rel(outs[0].cpu(), f64)
+
+
+# ------------------------------------------------------------------------------------------ GPU: agents with a backbone
+class OracleBackbone:
+    """The oracle's encoder as the callable the oracle agents expect (mutates its input, consumes one set of
+    DropPath factors per call, updates the running statistics held in `sd`)."""
+
+    def __init__(self, sd, keeps_per_call):
+        self.sd, self.queue = sd, list(keeps_per_call)
+
+    def __call__(self, x):
+        return encoder.fasternet_forward(self.sd, x, self.queue.pop(0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,mode", [("sorl", 0), ("sorl", 1), ("por", 1)])
+def test_agent_with_backbone_vs_oracle(kind, mode):
+    """agent/sorl.py:81-83 / agent/por.py:75-77: both observation sets go through the train-mode encoder, the
+    heads read its 256 features; POR regresses the raw next state AFTER the encoder's in-place clamp."""
+    from porl_b200 import POR, SORL
+    from porl_b200.agent.fasternet import FasterNet
+    from oracle import synth
+    from oracle.buffer import slice_row
+    from oracle.compare import assert_params_close
+    from oracle.steps import OraclePOR, OracleSORL, dims
+    S, H, A, B, steps = 362, 64, 2, 40, 2
+    args = dims(S, H, 2, False, 256, A)
+    enc_sd = encoder.det_encoder_state_dict(21)
+    g = torch.Generator().manual_seed(8)
+    probs = encoder.drop_probs()
+    keeps = [[None] + [torch.bernoulli(torch.full((B,), 1 - p), generator=g) / (1 - p) for p in probs[1:]]
+             for _ in range(2 * steps)]
+    ocls, cls = (OraclePOR, POR) if kind == "por" else (OracleSORL, SORL)
+    hyper = dict(max_steps=1000, tau=0.8, alpha=10.0 if kind == "por" else 3.0)
+    oracle = ocls(args, backbone=OracleBackbone({k: v.clone() for k, v in enc_sd.items()}, keeps), **hyper)
+    head_sd = synth.det_state_dict(oracle, 5)
+    oracle.load_state_dict(head_sd)
+    net = FasterNet(3, 256)
+    agent = cls(args, backbone=net, device=torch.device("cuda:0"), **hyper)
+    full = {("backbone." + k): v for k, v in encoder.order_like(enc_sd, net.state_dict().keys()).items()}
+    full.update(head_sd)
+    assert list(agent.state_dict().keys())[:len(enc_sd)] == ["backbone." + k for k in net.state_dict().keys()]
+    agent.load_state_dict(full)
+    agent.backbone.replay_keep_scales(keeps)
+    agent.ctx.set_gemm_mode(mode)
+    try:
+        rows = torch.from_numpy(synth.laser_rows(B * steps, S, 19, A))
+        for i in range(steps):
+            chunk = rows[i * B:(i + 1) * B]
+            bo, bd = slice_row(chunk.clone(), S, A), slice_row(chunk.clone().cuda(), S, A)
+            if kind == "por":
+                want = oracle.por_residual_update(bo["observations"], bo["next_observations"], bo["rewards"], bo["terminals"])
+                got = agent.por_residual_update(bd["observations"], bd["next_observations"], bd["rewards"], bd["terminals"])
+            else:
+                want = oracle.update(bo["observations"], bo["actions"], bo["rewards"], bo["next_observations"], bo["terminals"])
+                got = agent.update(bd["observations"], bd["actions"], bd["rewards"], bd["next_observations"], bd["terminals"])
+            np.testing.assert_allclose(got, want, rtol=2e-5, atol=0)
+        sd, osd = agent.state_dict(), oracle.state_dict()
+        for k, v in osd.items():
+            assert_params_close(sd[k], v, lr=1e-4, n_steps=steps, name=k)
+        for k, v in oracle.backbone.sd.items():
+            if "running" in k:
+                scale = float(v.abs().max())
+                assert float((sd["backbone." + k].cpu() - v).abs().max()) <= 2e-6 * scale + 1e-6, k
+            elif "tracked" in k:
+                assert int(sd["backbone." + k]) == 2 * steps
+    finally:
+        agent.ctx.set_gemm_mode(0)
