@@ -46,6 +46,8 @@ def parse():
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     p.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     p.add_argument("--also-batch", type=int, default=256, help="second batch size reported under 'also'")
+    p.add_argument("--encoder-batch", type=int, default=256,
+                   help="batch of the SORL + FasterNet scan-encoder workload reported under 'also_encoder' (0: skip)")
     return p.parse_args()
 
 
@@ -54,8 +56,9 @@ def workload_name(batch):
 
 
 def hyper():
-    from oracle.steps import dims
-    return dims(S, H, N_HIDDEN, False, 256, A), dict(max_steps=1_000_000, tau=0.9, alpha=10.0)
+    from types import SimpleNamespace
+    args = SimpleNamespace(state_size=S, hidden_dim=H, n_hidden=N_HIDDEN, layer_norm=False, feature_dim=256, action_size=A)
+    return args, dict(max_steps=1_000_000, tau=0.9, alpha=10.0)
 
 
 def synth_rows_torch(n, device, seed):
@@ -167,6 +170,37 @@ def cpu_reference_updates(batch, steps, warmup, seconds=None):
     return n / dt, n, torch.get_num_threads(), dt
 
 
+def cpu_reference_encoder(batch, seconds):
+    """CPU path of the SORL + FasterNet agent (config 2b): oracle restatement (agent/sorl.py:78-128 over
+    oracle.encoder's fasternet_forward), eager torch fp32 on all host threads, a bounded number of updates at a
+    small batch (B=32 on the host).  Forward-only encoder, i.e. LESS work than the reference,
+    which also back-propagates through it.  Returns (updates/s, samples/s, n)."""
+    from oracle import encoder
+    from oracle.buffer import slice_row
+    from oracle.steps import OracleSORL
+    args, hp = hyper()
+    torch.manual_seed(1000)
+    sd = encoder.det_encoder_state_dict(1)
+
+    class Backbone:
+        def __call__(self, x):
+            with torch.no_grad():
+                return encoder.fasternet_forward(sd, x, None)
+
+    agent = OracleSORL(args, backbone=Backbone(), **hp)
+    rows = synth_rows_torch(batch * 2, torch.device("cpu"), 20260102)
+    def one(i):
+        b = slice_row(rows[(i % 2) * batch:((i % 2) + 1) * batch].clone(), S, A)
+        agent.update(b["observations"], b["actions"], b["rewards"], b["next_observations"], b["terminals"])
+    one(0)
+    t0, n = time.perf_counter(), 0
+    while n < 1 or time.perf_counter() - t0 < seconds:
+        one(n)
+        n += 1
+    dt = time.perf_counter() - t0
+    return n / dt, n * batch / dt, n
+
+
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -189,12 +223,15 @@ def run_reference(a):
 class Runner:
     """Dataset replica + agent + (optionally graph-captured) step for one batch size on this rank."""
 
-    def __init__(self, a, batch, device, rank, world, table):
+    def __init__(self, a, batch, device, rank, world, table, backbone=False):
         from porl_b200 import SORL, TransitionDataset
         args, hp = hyper()
         self.a, self.B, self.device, self.rank, self.world = a, batch, device, rank, world
         self.ds = table
         torch.manual_seed(1000)                      # identical initial weights on every rank
+        if backbone:                                 # the literal sorl_train.py:29-32 agent (BASELINE config 2b)
+            from porl_b200.agent.fasternet import FasterNet
+            hp = dict(hp, backbone=FasterNet(3, args.feature_dim))
         self.agent = SORL(args, device=device, **hp)
         self.agent.ctx.set_gemm_mode(a.gemm_mode)
         self.pb = self.ds.new_batch(batch)
@@ -378,6 +415,19 @@ def run_b200(a):
             line["also"] = {"workload": workload_name(a.also_batch), "value": K * 4 / (ms2 * 1e-3), "unit": UNIT,
                             "ms_per_step": ms2 / (K * 4)}
 
+        # the literal sorl_train.py agent: FasterNet scan encoder in front of the heads (config 2b); eager launches
+        # (DropPath draws from torch's device generator every forward)
+        if a.encoder_batch:
+            Be = a.encoder_batch
+            r3 = Runner(a, Be, device, rank, world, table, backbone=True)
+            ms3, l3 = timed(r3, r3.indices(3, 2005), r3.indices(10, 2006), False)
+            r3.agent.read_losses()                    # raises on device flags (scan range, NaN)
+            flop = 3.449e9 * Be                       # 2 encoder forwards + heads, algorithmic
+            line["also_encoder"] = {"workload": f"sorl_fasternet_S{S}_F256_H{H}_rows1M_b{Be}", "value": 10 / (ms3 * 1e-3),
+                                    "unit": UNIT, "ms_per_step": ms3 / 10, "gpu_launches": l3,
+                                    "achieved_tflops": flop / (ms3 / 10 * 1e-3) * 1e-12, "graph": False}
+            del r3
+
         # CPU baseline beside it (bounded sample; reported, not the target)
         if a.cpu_seconds > 0:
             torch.set_num_threads(os.cpu_count() or 1)
@@ -385,6 +435,13 @@ def run_b200(a):
             line["cpu_baseline"] = {"value": ups, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{n} updates of batch {a.batch} in <= {a.cpu_seconds:.0f} s "
                                               "(oracle restatement of agent/sorl.py, eager torch fp32)"}
+            if a.encoder_batch and "also_encoder" in line:
+                ups_e, sps_e, n_e = cpu_reference_encoder(32, a.cpu_seconds / 3)
+                line["also_encoder"]["cpu_baseline"] = {
+                    "value": ups_e, "unit": UNIT, "samples_per_s": sps_e, "batch": 32, "cores": threads, "kind": "port",
+                    "sample": f"{n_e} updates of batch 32 (oracle SORL + forward-only FasterNet; the reference also "
+                              "back-propagates through the encoder)"}
+                line["also_encoder"]["samples_per_s"] = line["also_encoder"]["value"] * a.encoder_batch
     else:
         if rank == 0:
             # DP e2e: same public API per rank is exercised in the single-GPU run; report device-timed value

@@ -166,17 +166,28 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __res
   double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
   float fs[4] = {0, 0, 0, 0}, fq[4] = {0, 0, 0, 0};
   int n = 0;
-  for (int64_t r = r0 + lane; r < r1; r += lanes) {
-    const float4 v = *reinterpret_cast<const float4*>(x + r * C + 4 * cg);
+  auto add = [&](const float4 v) {
     fs[0] += v.x; fs[1] += v.y; fs[2] += v.z; fs[3] += v.w;
     fq[0] = fmaf(v.x, v.x, fq[0]); fq[1] = fmaf(v.y, v.y, fq[1]);
     fq[2] = fmaf(v.z, v.z, fq[2]); fq[3] = fmaf(v.w, v.w, fq[3]);
-    if (++n == 16) {
+  };
+  const float* xc = x + 4 * cg;
+  int64_t r = r0 + lane;
+  // four rows in flight per thread (independent 16-byte loads), fp32 running sums flushed to fp64 every 16 rows
+  for (; r + 3 * (int64_t)lanes < r1; r += 4 * (int64_t)lanes) {
+    const float4 v0 = *reinterpret_cast<const float4*>(xc + r * C);
+    const float4 v1 = *reinterpret_cast<const float4*>(xc + (r + lanes) * C);
+    const float4 v2 = *reinterpret_cast<const float4*>(xc + (r + 2 * (int64_t)lanes) * C);
+    const float4 v3 = *reinterpret_cast<const float4*>(xc + (r + 3 * (int64_t)lanes) * C);
+    add(v0); add(v1); add(v2); add(v3);
+    n += 4;
+    if (n == 16) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) { s[j] += fs[j]; q[j] += fq[j]; fs[j] = 0.f; fq[j] = 0.f; }
       n = 0;
     }
   }
+  for (; r < r1; r += lanes) add(*reinterpret_cast<const float4*>(xc + r * C));
 #pragma unroll
   for (int j = 0; j < 4; ++j) { s[j] += fs[j]; q[j] += fq[j]; }
 #pragma unroll
@@ -386,16 +397,20 @@ struct EncWs {
   float *r0, *r1, *r2;
 };
 
+void conv1x1_group(GemmGroup& g, const float* A, int64_t rows, int K, const float* W, int N, float* C, int64_t ldc,
+                   const float* bias, int epilogue) {
+  g = GemmGroup{};
+  g.A = A; g.B = W; g.C = C; g.bias = bias;
+  g.M = (int)rows; g.N = N; g.K = K;
+  g.lda = K; g.ldb = K; g.ldc = (int)ldc; g.n_store = N; g.epilogue = epilogue;
+}
+
 int conv1x1(porl_ctx* ctx, const float* A, int64_t rows, int K, const float* W, int N, float* C, int64_t ldc,
             const float* bias, int epilogue, cudaStream_t st) {
   GemmBatch gb;
   gb.n_groups = 1;
   gb.splits = 1;
-  GemmGroup& g = gb.g[0];
-  g = GemmGroup{};
-  g.A = A; g.B = W; g.C = C; g.bias = bias;
-  g.M = (int)rows; g.N = N; g.K = K;
-  g.lda = K; g.ldb = K; g.ldc = (int)ldc; g.n_store = N; g.epilogue = epilogue;
+  conv1x1_group(gb.g[0], A, rows, K, W, N, C, ldc, bias, epilogue);
   return launch_gemm(ctx, true, true, gb, st);
 }
 

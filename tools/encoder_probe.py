@@ -8,19 +8,20 @@ from porl_b200.agent.fasternet import FasterNet
 from porl_b200.dataloader.dataset import synthetic_rows
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+QUICK = len(sys.argv) > 2 and sys.argv[2] == "quick"      # one warm-up + one forward in mode 1 (for ncu)
 dev = torch.device("cuda:0")
 ctx = _C.context(dev)
 torch.manual_seed(0)
 net = FasterNet(3, 256).to(dev)
 st = torch.from_numpy(synthetic_rows(B, 362, 1)[:, :362].copy()).to(dev)
 out = torch.empty(B, 256, device=dev)
-for mode in (0, 1):
+for mode in ((1,) if QUICK else (0, 1)):
     ctx.set_gemm_mode(mode)
-    for _ in range(3):
+    for _ in range(1 if QUICK else 3):
         net.forward_features(st, st.stride(0), B, out)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n = 10
+    n = 1 if QUICK else 10
     l0 = ctx.launches
     e0.record()
     for _ in range(n):
@@ -31,6 +32,8 @@ for mode in (0, 1):
     flops = 2 * 0.860e9 * B
     print(f"B={B} mode={mode}: {ms:.3f} ms/forward  {flops / ms * 1e-9:.1f} TFLOP/s (0.86 GMAC/sample)  "
           f"{(ctx.launches - l0) // n} launches/forward", flush=True)
+    if QUICK:
+        break
     ctx.profile(True)
     net.forward_features(st, st.stride(0), B, out)
     torch.cuda.synchronize()
