@@ -94,7 +94,7 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->tc_chunk_kb = 1;
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");
-    ctx->tc_a_in_tmem = e ? atoi(e) : 1;
+    ctx->tc_a_in_tmem = e ? atoi(e) : 0;
   }
   ctx->tc_ws = nullptr;
   ctx->tc_dbg = nullptr;

@@ -34,7 +34,6 @@ constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;      // tile; BK floats = on
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB
 constexpr int TC_THREADS = 384;                           // 12 warps: TMA, MMA, 6 splitters, 4 accumulators
 constexpr int TC_SPLIT_THREADS = 192;
-constexpr int TC_ACC_COLS = 2 * TC_BN;                    // two chunk accumulators
 // Two variants.  ATM = false: A_hi, A_lo, B_hi, B_lo all in shared memory (stage = 4 tiles, 3 stages).
 // ATM = true: the splitters put A_hi / A_lo into TENSOR MEMORY (tcgen05.st, 64 columns per stage) and the
 // MMAs take A from TMEM, which removes the A reads from the shared-memory port (the measured limiter)
@@ -44,15 +43,21 @@ struct TcCfg {
   static constexpr int STAGES = ATM ? 4 : 3;
   static constexpr int STAGE_BYTES = (ATM ? 3 : 4) * TC_TILE_BYTES;
   static constexpr int B_LO_OFF = (ATM ? 2 : 3) * TC_TILE_BYTES;
-  static constexpr int NUM_BARS = 3 * STAGES + 4;
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + 256;
-  static constexpr int TMEM_COLS = ATM ? 512 : 256;
+  // chunk accumulators in TMEM: the MMAs may run NBUF chunks ahead of the accumulator warps, which matters while
+  // those warps are busy with a tile's epilogue (short-K tiles: a whole next tile fits into four buffers)
+  static constexpr int NBUF = ATM ? 2 : 4;
+  static constexpr int ACC_COLS = NBUF * TC_BN;
+  static constexpr int NUM_BARS = 3 * STAGES + 2 * NBUF;
+  static constexpr int STAGING_BYTES = 2 * TC_TILE_BYTES;   // epilogue: two 128 x 32 fp32 slabs for the TMA stores of C
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + STAGING_BYTES + 256;
+  static constexpr int TMEM_COLS = 512;
 };
 constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 8;
 
 struct alignas(64) TcParams {
   CUtensorMap mapA[kMaxGroups];
   CUtensorMap mapB[kMaxGroups];
+  CUtensorMap mapC[kMaxGroups];     // row-major C (n_store x M), box {32, 128}: the epilogue's TMA stores
   GemmBatch batch;
   int tile_begin[kMaxGroups + 1];   // prefix sum of tiles per group
   int tiles_n[kMaxGroups];          // n-tiles per group
@@ -91,6 +96,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -191,12 +202,13 @@ template <bool ATM>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams P) {
   using C = TcCfg<ATM>;
   constexpr int TC_STAGES = C::STAGES, TC_STAGE_BYTES = C::STAGE_BYTES, TC_NUM_BARS = C::NUM_BARS;
-  constexpr int TC_TMEM_COLS = C::TMEM_COLS;
+  constexpr int TC_TMEM_COLS = C::TMEM_COLS, TC_NBUF = C::NBUF, TC_ACC_COLS = C::ACC_COLS;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;                         // SWIZZLE_128B tiles: 1024-B aligned
   uint8_t* base_ptr = smem_raw + (base - raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(base_ptr + TC_STAGES * TC_STAGE_BYTES);
+  uint8_t* const staging = base_ptr + TC_STAGES * TC_STAGE_BYTES;       // 1024-byte aligned like the stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
   uint32_t* flag_slot = tmem_slot + 1;
   const uint32_t bar0 = smem_u32(bars);
@@ -204,7 +216,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   auto split_done = [&](int s) { return bar0 + 8u * (TC_STAGES + s); };
   auto empty_bar = [&](int s) { return bar0 + 8u * (2 * TC_STAGES + s); };
   auto tmem_full = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + b); };
-  auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + 2 + b); };
+  auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + TC_NBUF + b); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long* const dbg = P.dbg ? P.dbg + 16 * blockIdx.x : nullptr;   // [0] start [1] setup done
@@ -218,13 +230,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     for (int g = 0; g < P.batch.n_groups; ++g) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapA[g])) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapB[g])) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapC[g])) : "memory");
     }
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(raw_full(s), 1);
       mbar_init(split_done(s), TC_SPLIT_THREADS);
       mbar_init(empty_bar(s), 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < TC_NBUF; ++b) {
       mbar_init(tmem_full(b), 1);
       mbar_init(tmem_empty(b), 128);
     }
@@ -278,9 +291,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
         int kb = w.kb0;
         while (kb < w.kb1) {
-          const int buf = chunk & 1;
+          const int buf = chunk % TC_NBUF;
           const long long tw0 = dbg ? clock64() : 0;
-          mbar_wait(tmem_empty(buf), (((uint32_t)chunk >> 1) & 1u) ^ 1u);
+          mbar_wait(tmem_empty(buf), ((uint32_t)(chunk / TC_NBUF) & 1u) ^ 1u);
           if (dbg) w_te += clock64() - tw0;
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(buf * TC_BN);
@@ -399,7 +412,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   } else {
     // ===================== accumulators + epilogue =====================
     const int q = warp & 3;                 // TMEM lane quarter this warp may read
-    int chunk = 0;
+    int chunk = 0, sbuf = 0;
     long long w_tf = 0;
     TcUnit w;
     for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
@@ -418,9 +431,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       for (int j = 0; j < TC_BN; ++j) acc[j] = 0.f;
       const int nchunks = (w.kb1 - w.kb0 + chunk_kb - 1) / chunk_kb;
       for (int c = 0; c < nchunks; ++c, ++chunk) {
-        const int buf = chunk & 1;
+        const int buf = chunk % TC_NBUF;
         const long long tw = dbg ? clock64() : 0;
-        mbar_wait(tmem_full(buf), ((uint32_t)chunk >> 1) & 1u);
+        mbar_wait(tmem_full(buf), (uint32_t)(chunk / TC_NBUF) & 1u);
         if (dbg) w_tf += clock64() - tw;
         tc_fence_after();
         if (dbg && chunk == 0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[7] = gtime();
@@ -479,7 +492,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // transposed copy as fully coalesced 128-byte stores (lanes = consecutive rows of one Ct row).
       const int row = w.m0 + 32 * q + lane;
       const bool row_ok = row < gM;
-      float* const crow = gC + (size_t)row * ldc;
       const float* const rrow = gRelu ? gRelu + (size_t)row * ldr : nullptr;
       // Pad columns (N <= col < n_store) need no special case: their B rows are out of bounds for TMA, so
       // their accumulators are exact zeros, C and relu_src own those columns (ldc, ld_relu >= n_store), the
@@ -513,11 +525,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             }
           }
         }
-#pragma unroll
-        for (int c4 = 0; c4 < TC_BN; c4 += 4) {
-          if (w.n0 + c4 < gNs)
-            *reinterpret_cast<float4*>(crow + w.n0 + c4) = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
-        }
         if (gCt) {
           float* ct = gCt + (size_t)w.n0 * ldct + row;
 #pragma unroll
@@ -527,8 +534,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           }
         }
       }
+      // Row-major C leaves through TMA: the tile goes to shared memory one 128 x 32 slab at a time (thread = row,
+      // eight 16-byte slots XOR-swizzled by row like every SWIZZLE_128B tile: conflict-free) and one thread hands
+      // each slab to the copy engine, which writes full 128-byte row segments and clips rows >= M and columns
+      // >= n_store.  The stores are asynchronous: these warps return to the next tile's chunks at once (a thread
+      // storing its own row with 16-byte STGs kept the LSU queues full for 2.4-4 us per tile).  Two slab buffers:
+      // before a buffer is rewritten, wait_group.read 1 guarantees every store but the latest one (which reads
+      // the other buffer) has finished reading.
+#pragma unroll
+      for (int sl = 0; sl < TC_BN / 32; ++sl) {
+        if (w.n0 + 32 * sl >= gNs) break;
+        uint8_t* const buf = staging + (size_t)sbuf * TC_TILE_BYTES;
+        if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        uint8_t* const srow = buf + (32 * q + lane) * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c4 = 32 * sl + 4 * j;
+          *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) =
+              make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> copy-engine reads
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(&P.mapC[w.g], smem_u32(buf), w.n0 + 32 * sl, w.m0);
+        sbuf ^= 1;
+      }
       if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
+    if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
   }
 
@@ -648,6 +681,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
     const GemmGroup& g = batch.g[i];
     int rc = make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
     if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
+    if (rc == PORL_OK) rc = make_map(&P.mapC[i], g.C, g.n_store, g.M, g.ldc);
     if (rc != PORL_OK) return rc;
   }
   const int sms = ctx->sm_count;

@@ -14,6 +14,7 @@ pad = lambda x: (x + 3) // 4 * 4
 SHAPES = [(1, 1, 4096, 512, 362), (1, 1, 4096, 512, 512), (1, 1, 512, 512, 4096), (1, 1, 512, 362, 4096),
           (1, 1, 4096, 1024, 1024), (1, 1, 1024, 1024, 4096), (1, 1, 256, 512, 512), (1, 1, 512, 512, 256),
           (1, 1, 16384, 512, 512)]
+ENC_SHAPES = [(1, 1, 147456, 192, 96), (1, 1, 147456, 96, 192), (1, 1, 36864, 192, 384), (1, 1, 36864, 384, 192)]
 
 
 def operands(a_k, b_k, M, N, K, seed=1, relu_like=True):
@@ -62,12 +63,12 @@ def acc():
 
 
 def time_shapes():
-    for (a_k, b_k, M, N, K) in SHAPES:
+    for (a_k, b_k, M, N, K) in (ENC_SHAPES if len(sys.argv) > 2 and sys.argv[2] == "enc" else SHAPES):
         A, B = operands(a_k, b_k, M, N, K)
         Ad, Bd = A.to(dev), B.to(dev)
         Cd = torch.zeros(M, pad(N), device=dev)
         stamps = torch.zeros(16 * 148, dtype=torch.int64, device=dev)
-        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 2, 0), (1, 64, 0), (1, 1, 1), (1, 2, 1), (1, 64, 1)):
+        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 64, 0), (1, 1, 1)):
             ctx.set_gemm_mode(mode)
             ctx.set_tc_chunk(chunk)
             ctx.set_tc_variant(atm)
@@ -106,5 +107,19 @@ def time_shapes():
         ctx.set_gemm_mode(0)
 
 
+def one():
+    """python tools/gemm_probe.py one M N K [atm]: three launches of one shape in tensor-core mode (for ncu)."""
+    M, N, K = (int(x) for x in sys.argv[2:5])
+    A, B = operands(1, 1, M, N, K)
+    Ad, Bd = A.to(dev), B.to(dev)
+    Cd = torch.zeros(M, pad(N), device=dev)
+    ctx.set_gemm_mode(1)
+    ctx.set_tc_variant(int(sys.argv[5]) if len(sys.argv) > 5 else 0)
+    for _ in range(3):
+        run(1, 1, M, N, K, Ad, Bd, Cd)
+    torch.cuda.synchronize()
+    ctx.set_gemm_mode(0)
+
+
 if __name__ == "__main__" and len(sys.argv) > 1:
-    {"acc": acc, "time": time_shapes}[sys.argv[1]]()
+    {"acc": acc, "time": time_shapes, "one": one}[sys.argv[1]]()
