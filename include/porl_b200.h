@@ -264,6 +264,12 @@ typedef struct {
   const float* keep;     /* (B) DropPath factors mask / keep_prob (fasternet.py:76-93), or NULL = keep all */
 } porl_fn_block_t;
 
+/* Data-parallel BatchNorm: called on the host between the statistics kernel and the normalisation of every
+ * BatchNorm layer with a device buffer of n doubles (per-channel sum, sum of squares of THIS rank's rows); it must
+ * enqueue, on `stream`, an in-place SUM over all ranks (e.g. ncclAllReduce / torch.distributed.all_reduce) and
+ * return 0.  The statistics then cover the global batch, as in a single-process run of the reference. */
+typedef int (*porl_allreduce_f64_fn)(void* user, double* buf_dev, int64_t n, porl_stream_t stream);
+
 /* FasterNet(in_chans=3, num_classes=feature_dim, embed_dim=96, depths=(1, 2)) as the agents build it
  * (sorl_train.py:29-32) */
 typedef struct {
@@ -276,7 +282,11 @@ typedef struct {
   const float* head_w;        /* (feature_dim, 1280): head.weight */
   const float* head_b;        /* (round_up(feature_dim, 4)), 16-byte aligned: head.bias */
   int32_t feature_dim;
-  int32_t pad_;
+  int32_t world;              /* ranks sharing the batch (every rank passes the same B); <= 1: statistics stay local */
+  porl_allreduce_f64_fn stats_allreduce;   /* required when world > 1, ignored otherwise */
+  void* stats_user;
+  double* stats_buf;          /* optional (768 doubles): where the per-layer sums are staged for stats_allreduce;
+                                 NULL = inside the workspace */
 } porl_fasternet_t;
 
 /* floats of scratch porl_fasternet_forward needs for a batch of B states */

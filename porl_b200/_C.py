@@ -64,7 +64,11 @@ class FnBlock(C.Structure):                        # porl_fn_block_t
 
 class FasterNetParams(C.Structure):                # porl_fasternet_t
     _fields_ = [("pe_w", _p), ("pe_bn", BnParams), ("block", FnBlock * 3), ("merge_w", _p), ("merge_bn", BnParams),
-                ("head_conv_w", _p), ("head_w", _p), ("head_b", _p), ("feature_dim", _i32), ("pad_", _i32)]
+                ("head_conv_w", _p), ("head_w", _p), ("head_b", _p), ("feature_dim", _i32), ("world", _i32),
+                ("stats_allreduce", _p), ("stats_user", _p), ("stats_buf", _p)]
+
+
+ALLREDUCE_F64_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p)   # porl_allreduce_f64_fn
 
 
 _SIGNATURES = {

@@ -175,7 +175,41 @@ class FasterNet(nn.Module):
         bn(p.merge_bn, bns[2])
         p.head_conv_w, p.head_w, p.head_b = ptr(c["head_conv_w"]), ptr(c["head_w"]), ptr(c["head_b"])
         p.feature_dim = self.num_classes
+        # data parallel: BatchNorm statistics cover the GLOBAL batch (sums all-reduced between the statistics
+        # and the normalisation of every layer), so N ranks x B/N rows reproduce the single-process forward
+        sync = self._cache.get("stats_sync")
+        if sync is None:
+            from .. import dist as pdist
+            sync = (pdist.world_size(), pdist.allreduce_sum_) if pdist.is_dp() else (1, None)
+        world, reduce_fn = sync
+        p.world = world
+        if world > 1:
+            dev = self.head.weight.device
+            buf = c.get("stats_buf")
+            if buf is None or buf.device != dev:
+                buf = c["stats_buf"] = torch.zeros(768, dtype=torch.float64, device=dev)
+
+                def _cb(user, ptr_, n, stream, _buf=buf, _self=self):
+                    try:                        # ptr_ is _buf's storage (p.stats_buf); torch needs the tensor
+                        from .. import dist as pdist
+                        fn = (_self._cache.get("stats_sync") or (0, None))[1] or pdist.allreduce_sum_
+                        fn(_buf[:n])
+                        return 0
+                    except Exception as e:      # never unwind through the C frame
+                        _self._cache["stats_error"] = e
+                        return 1
+
+                c["stats_cb"] = _C.ALLREDUCE_F64_FN(_cb)
+            p.stats_buf = buf.data_ptr()
+            p.stats_allreduce = C.cast(c["stats_cb"], C.c_void_p)
         return p
+
+    def sync_batch_stats(self, world: int, reduce_fn) -> None:
+        """Override how BatchNorm sums are combined across `world` ranks: reduce_fn(tensor_f64) must sum IN PLACE
+        over ranks on the current stream.  Default (not called): torch.distributed's default group when it is
+        initialised with more than one rank."""
+        self._cache["stats_sync"] = (int(world), reduce_fn)
+        self._cache.pop("stats_buf", None)
 
     def _keep_scales(self, x, B):
         """drop_path (agent/fasternet.py:76-93): one Bernoulli(keep)/keep factor per sample, drawn with the same

@@ -145,18 +145,16 @@ __global__ void __launch_bounds__(192) patch_embed_kernel(float* __restrict__ st
 // ------------------------------------------------------------------------------------ BatchNorm (train mode)
 // Column statistics of X[rows, C] in two levels: every block reduces a slab of rows (fp32 running sums flushed
 // into fp64 every 16 rows, fixed order), writes (sum, sum of squares) per column as fp64 partials, and the last
-// block to finish (ticket) adds the partials in block order and emits
+// block to finish (ticket) adds the partials in block order into totals[C][2].  bn_finalize_kernel then emits
 //     scale = gamma / sqrt(var_biased + eps),  shift = beta - mean * scale
-// plus the running-stat update  r = (1 - m) r + m stat  (unbiased variance), nn.BatchNorm2d training forward.
+// plus the running-stat update  r = (1 - m) r + m stat  (unbiased variance), nn.BatchNorm2d training forward;
+// between the two, a data-parallel run sums the totals over the ranks (porl_fasternet_t.stats_allreduce).
 // block = 192 threads = (192 / (C/4)) row lanes x (C/4) float4 column groups; C in {96, 192, 384}.
 constexpr int kBnThreads = 192;
 
 __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __restrict__ x, int64_t rows, int C,
                                                               int64_t rows_per_block, double* __restrict__ partial,
-                                                              uint32_t* __restrict__ ticket, const float* __restrict__ gamma,
-                                                              const float* __restrict__ beta, float* __restrict__ run_mean,
-                                                              float* __restrict__ run_var, float eps, float momentum,
-                                                              float* __restrict__ scale_shift) {
+                                                              uint32_t* __restrict__ ticket, double* __restrict__ totals) {
   extern __shared__ double sred[];                 // [lanes][C][2]
   __shared__ bool last;
   const int c4n = C >> 2, lanes = kBnThreads / c4n;
@@ -214,17 +212,28 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __res
       a += __ldcg(&partial[((size_t)g * C + c) * 2]);
       b += __ldcg(&partial[((size_t)g * C + c) * 2 + 1]);
     }
-    const double mean = a / (double)rows;
-    double var = b / (double)rows - mean * mean;
+    totals[2 * c] = a;
+    totals[2 * c + 1] = b;
+  }
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+
+// totals (sum, sum of squares per channel over `rows` rows, possibly summed over ranks) -> scale / shift and the
+// running-statistic update of nn.BatchNorm2d's training forward
+__global__ void bn_finalize_kernel(const double* __restrict__ totals, double rows, int C, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* __restrict__ run_mean, float* __restrict__ run_var,
+                                   float eps, float momentum, float* __restrict__ scale_shift) {
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const double mean = totals[2 * c] / rows;
+    double var = totals[2 * c + 1] / rows - mean * mean;
     if (var < 0) var = 0;
     const float sc = (float)((double)gamma[c] / sqrt(var + (double)eps));
     scale_shift[c] = sc;
     scale_shift[C + c] = (float)((double)beta[c] - mean * (double)sc);
-    const double unbiased = rows > 1 ? var * (double)rows / (double)(rows - 1) : var;
+    const double unbiased = rows > 1 ? var * rows / (rows - 1) : var;
     run_mean[c] = (float)((1.0 - (double)momentum) * (double)run_mean[c] + (double)momentum * mean);
     run_var[c] = (float)((1.0 - (double)momentum) * (double)run_var[c] + (double)momentum * unbiased);
   }
-  if (threadIdx.x == 0) *ticket = 0u;
 }
 
 // y = x * scale[c] + shift[c] (+ ReLU), in place; float4 over an (rows x C) matrix
@@ -388,13 +397,16 @@ namespace {
 
 constexpr int kBnMaxBlocks = 592;                 // 4 x 148 slabs at most
 constexpr int kBnTicket = 8;                      // ctx->counters word of the BatchNorm reduction
-constexpr int64_t kHdrFloats = (int64_t)kBnMaxBlocks * 384 * 2 * 2 + 1024;   // fp64 partials + scale/shift
+constexpr int64_t kHdrFloats = (int64_t)kBnMaxBlocks * 384 * 2 * 2 + 2048 + 1024;   // fp64 partials + totals + scale/shift
 constexpr int64_t kPerSample = (int64_t)kPH * kPW * 384;                       // R0 + R1 + R2 floats per sample
 
 struct EncWs {
   double* partial;
+  double* totals;
   float* scale_shift;
   float *r0, *r1, *r2;
+  const porl_fasternet_t* net;
+  porl_stream_t stream;
 };
 
 void conv1x1_group(GemmGroup& g, const float* A, int64_t rows, int K, const float* W, int N, float* C, int64_t ldc,
@@ -423,11 +435,21 @@ int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, con
   const size_t smem = (size_t)(kBnThreads / (C / 4)) * C * 2 * sizeof(double);
   {
     ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 4.0, st);
-    bn_stats_kernel<<<(unsigned)G, kBnThreads, smem, st>>>(x, rows, C, rpb, w.partial, ctx->counters + kBnTicket, bn.weight,
-                                                           bn.bias, bn.running_mean, bn.running_var, 1e-5f, 0.1f,
-                                                           w.scale_shift);
+    bn_stats_kernel<<<(unsigned)G, kBnThreads, smem, st>>>(x, rows, C, rpb, w.partial, ctx->counters + kBnTicket, w.totals);
     PORL_LAUNCHED(ctx);
   }
+  double rows_global = (double)rows;
+  if (w.net->world > 1) {
+    const int rc = w.net->stats_allreduce(w.net->stats_user, w.totals, 2 * (int64_t)C, w.stream);
+    if (rc != 0) {
+      set_error("fasternet: stats_allreduce callback returned %d", rc);
+      return PORL_ERR_INVALID;
+    }
+    rows_global *= (double)w.net->world;
+  }
+  bn_finalize_kernel<<<1, 128, 0, st>>>(w.totals, rows_global, C, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                                        1e-5f, 0.1f, w.scale_shift);
+  PORL_LAUNCHED(ctx);
   const int64_t n4 = rows * C / 4;
   int64_t grid = (n4 + 255) / 256;
   if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
@@ -498,11 +520,16 @@ extern "C" int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* n
                  (long long)workspace_floats, (long long)porl_fasternet_workspace_floats(B));
   PORL_CHECK_ARG(net->pe_w && net->merge_w && net->head_conv_w && net->head_w && net->head_b,
                  "porl_fasternet_forward: null weight");
+  PORL_CHECK_ARG(net->world <= 1 || net->stats_allreduce, "porl_fasternet_forward: world=%d needs stats_allreduce",
+                 net->world);
   cudaStream_t st = as_stream(stream);
   const int64_t rows0 = B * kPH * kPW, rows1 = rows0 / 4;
   EncWs w;
   w.partial = reinterpret_cast<double*>(workspace);
-  w.scale_shift = workspace + (int64_t)kBnMaxBlocks * 384 * 2 * 2;
+  w.totals = net->stats_buf ? net->stats_buf : w.partial + (int64_t)kBnMaxBlocks * 384 * 2;
+  w.scale_shift = workspace + (int64_t)kBnMaxBlocks * 384 * 2 * 2 + 2048;
+  w.net = net;
+  w.stream = stream;
   w.r0 = workspace + kHdrFloats;
   w.r1 = w.r0 + rows0 * 96;
   w.r2 = w.r1 + rows0 * 96;

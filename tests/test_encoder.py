@@ -258,3 +258,92 @@ def test_agent_with_backbone_vs_oracle(kind, mode):
                 assert int(sd["backbone." + k]) == 2 * steps
     finally:
         agent.ctx.set_gemm_mode(0)
+
+
+@pytest.mark.gpu
+def test_cuda_fasternet_data_parallel_batch_stats():
+    """Two 'ranks' (threads, one stream each, same GPU) run half of the batch each; the BatchNorm sums are
+    combined through porl_fasternet_t.stats_allreduce, so every rank reproduces the single-process features of
+    its rows and the single-process running statistics (what torch SyncBatchNorm would do for the reference)."""
+    import threading
+    from porl_b200 import _C
+    from porl_b200.agent.fasternet import FasterNet
+    from oracle import synth
+    B, W = 16, 2
+    st = torch.from_numpy(synth.laser_rows(B, 362, 91)[:, :362].copy())
+    sd = encoder.det_encoder_state_dict(13)
+    g = torch.Generator().manual_seed(4)
+    keeps = [None] + [torch.bernoulli(torch.full((B,), 1 - p), generator=g) / (1 - p) for p in encoder.drop_probs()[1:]]
+
+    def make():
+        net = FasterNet(3, 256)
+        net.load_state_dict(encoder.order_like({k: v.clone() for k, v in sd.items()}, net.state_dict().keys()))
+        return net.cuda()
+
+    ctx = _C.context(torch.device("cuda"))
+    ctx.set_gemm_mode(0)                 # per-rank row counts differ from the full batch: keep the FFMA contraction
+    whole = make()
+    want = whole(st.cuda(), keep_scales=keeps)
+    torch.cuda.synchronize()
+
+    nets = [make() for _ in range(W)]
+    slots, barrier, outs, errs = [None] * W, threading.Barrier(W), [None] * W, []
+    # The two "ranks" share one library context here (its reduction tickets and scratch are per context; real ranks
+    # are separate processes), so their GPU segments must not overlap: rank 1 runs each segment (the kernels
+    # between two reductions) only after rank 0 has finished the same segment.
+    cond, progress = threading.Condition(), {"rank0_calls": 0, "rank0_done": False}
+
+    def wait_rank0(calls):
+        with cond:
+            cond.wait_for(lambda: progress["rank0_calls"] >= calls or progress["rank0_done"], timeout=60)
+
+    def reducer(rank):
+        state = {"k": 0}
+
+        def fn(t):                                   # sum over "ranks" in rank order, in place
+            state["k"] += 1
+            torch.cuda.current_stream().synchronize()
+            if rank == 0:
+                with cond:
+                    progress["rank0_calls"] = state["k"]
+                    cond.notify_all()
+            slots[rank] = t.clone()
+            barrier.wait()
+            total = slots[0] + slots[1]
+            barrier.wait()
+            t.copy_(total)
+            torch.cuda.current_stream().synchronize()
+            if rank == 1:
+                wait_rank0(state["k"] + 1)
+        return fn
+
+    def work(rank):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                nets[rank].sync_batch_stats(W, reducer(rank))
+                rows = slice(rank * B // W, (rank + 1) * B // W)
+                x = st[rows].cuda()
+                ks = [None if k is None else k[rows].cuda() for k in keeps]
+                torch.cuda.current_stream().synchronize()
+                if rank == 1:
+                    wait_rank0(1)
+                outs[rank] = nets[rank](x, keep_scales=ks)
+                torch.cuda.current_stream().synchronize()
+                if rank == 0:
+                    with cond:
+                        progress["rank0_done"] = True
+                        cond.notify_all()
+        except Exception as e:                       # pragma: no cover
+            errs.append(e)
+            barrier.abort()
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(W)]
+    [t.start() for t in threads]
+    [t.join(120) for t in threads]
+    assert not errs, errs
+    got = torch.cat(outs)
+    assert rel(got.cpu(), want.cpu()) < 2e-6, rel(got.cpu(), want.cpu())
+    a, b = whole.state_dict(), nets[1].state_dict()
+    for k in a:
+        if "running" in k:
+            assert float((a[k] - b[k]).abs().max()) <= 1e-6 * float(a[k].abs().max()) + 1e-7, k
