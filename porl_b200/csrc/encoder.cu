@@ -510,8 +510,8 @@ extern "C" int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* n
                                       int64_t B, float* features, int64_t ld_feat, float* workspace,
                                       int64_t workspace_floats, porl_stream_t stream) {
   PORL_CHECK_ARG(ctx && net && state && features && workspace, "porl_fasternet_forward: null argument");
-  // rows * 2C must stay below 2^31 for the contraction's 32-bit extents: 1024 x 5760 x 192 = 1.13e9
-  PORL_CHECK_ARG(B >= 1 && B <= 1024, "porl_fasternet_forward: B=%lld outside [1, 1024]", (long long)B);
+  // rows = B * 5760 is a 32-bit extent of the contractions and B a grid dimension; offsets are 64-bit everywhere
+  PORL_CHECK_ARG(B >= 1 && B <= 16384, "porl_fasternet_forward: B=%lld outside [1, 16384]", (long long)B);
   PORL_CHECK_ARG(ld_state >= kState, "porl_fasternet_forward: ld_state=%lld", (long long)ld_state);
   const int F = net->feature_dim;
   PORL_CHECK_ARG(F >= 1 && ld_feat >= F, "porl_fasternet_forward: feature_dim=%d ld_feat=%lld", F, (long long)ld_feat);

@@ -8,7 +8,7 @@ from porl_b200.agent.fasternet import FasterNet
 from porl_b200.dataloader.dataset import synthetic_rows
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-QUICK = len(sys.argv) > 2 and sys.argv[2] == "quick"      # one warm-up + one forward in mode 1 (for ncu)
+QUICK = len(sys.argv) > 2 and sys.argv[2] in ("quick", "agree")      # one warm-up + one forward in mode 1 (for ncu)
 dev = torch.device("cuda:0")
 ctx = _C.context(dev)
 torch.manual_seed(0)
@@ -45,3 +45,14 @@ for mode in ((1,) if QUICK else (0, 1)):
             rate = v["work"] / v["ms"] * (1e-9 if k == "contraction" else 1e-6)
             print(f"    {k:12s} {v['launches']:3d} launches {v['ms']:8.3f} ms  {rate:8.1f} {unit}", flush=True)
 ctx.set_gemm_mode(0)
+if len(sys.argv) > 2 and sys.argv[2] == "agree":       # both contraction modes on the same batch (large-B index check)
+    outs = []
+    for mode in (0, 1):
+        ctx.set_gemm_mode(mode)
+        o = torch.empty(B, 256, device=dev)
+        net.forward_features(st, st.stride(0), B, o, keep_scales=[None, None, None])
+        torch.cuda.synchronize()
+        outs.append(o)
+    ctx.set_gemm_mode(0)
+    d = float((outs[0].double() - outs[1].double()).norm() / outs[0].double().norm())
+    print(f"B={B}: FFMA vs tcgen05 features relative L2 difference {d:.3e}", flush=True)
