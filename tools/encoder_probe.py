@@ -45,14 +45,19 @@ for mode in ((1,) if QUICK else (0, 1)):
             rate = v["work"] / v["ms"] * (1e-9 if k == "contraction" else 1e-6)
             print(f"    {k:12s} {v['launches']:3d} launches {v['ms']:8.3f} ms  {rate:8.1f} {unit}", flush=True)
 ctx.set_gemm_mode(0)
-if len(sys.argv) > 2 and sys.argv[2] == "agree":       # both contraction modes on the same batch (large-B index check)
-    outs = []
-    for mode in (0, 1):
-        ctx.set_gemm_mode(mode)
-        o = torch.empty(B, 256, device=dev)
-        net.forward_features(st, st.stride(0), B, o, keep_scales=[None, None, None])
-        torch.cuda.synchronize()
-        outs.append(o)
+if len(sys.argv) > 2 and sys.argv[2] == "agree":
+    # large-B index check (offsets beyond 2^31 elements from B = 1942): a batch made of R copies of the same 256
+    # states has the batch statistics of the 256-state batch, so every copy must reproduce its features
+    ctx.set_gemm_mode(1)
+    R = B // 256
+    base = st[:256].contiguous()
+    f256 = torch.empty(256, 256, device=dev)
+    net.forward_features(base.clone(), 362, 256, f256, keep_scales=[None, None, None])
+    big = base.repeat(R, 1).contiguous()
+    fbig = torch.empty(R * 256, 256, device=dev)
+    net.forward_features(big, 362, R * 256, fbig, keep_scales=[None, None, None])
+    torch.cuda.synchronize()
     ctx.set_gemm_mode(0)
-    d = float((outs[0].double() - outs[1].double()).norm() / outs[0].double().norm())
-    print(f"B={B}: FFMA vs tcgen05 features relative L2 difference {d:.3e}", flush=True)
+    d = max(float((fbig[i * 256:(i + 1) * 256].double() - f256.double()).norm() / f256.double().norm()) for i in range(R))
+    print(f"B={R * 256} ({R} copies of 256 states) vs B=256: max relative L2 difference of a copy {d:.3e}; "
+          f"peak memory {torch.cuda.max_memory_allocated() / 2**30:.1f} GiB", flush=True)
