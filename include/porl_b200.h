@@ -120,6 +120,15 @@ int porl_gather_soa(porl_ctx_t* ctx, const float* states, const float* next_stat
 int porl_pack_rows(porl_ctx_t* ctx, const float* src, int64_t ld_src, int64_t B, int32_t n,
                    float* dst, int64_t ld_dst, porl_stream_t stream);
 
+/* Device-side shuffled indices: out[i] = P(first + i mod n), i < count, where P is a pseudo-random
+ * bijection of [0, n) keyed by (seed, stream_id) -- an alternating Feistel network with cycle walking, O(1) per
+ * index, no table.  Consecutive windows of one key are the minibatches of one shuffled epoch (distinct rows);
+ * replaces the host-side torch.randperm of DataLoader(shuffle=True) (por_train.py:61) and the O(size)
+ * np.random.choice(size, B, replace=False) of ReplayBuffer.sample (src/porl/buffer/replaybuffer.py:61) on the
+ * throughput path.  Same distribution for SGD purposes, not the same index stream. */
+int porl_sample_permutation(porl_ctx_t* ctx, int64_t n, uint64_t seed, uint64_t stream_id, int64_t first,
+                            int64_t count, int64_t* out, porl_stream_t stream);
+
 /* ---- K2/K3: fused MLP forward / backward --------------------------------------------------- */
 /* util/util.py:29-47 mlp(): Linear[+LayerNorm]+ReLU per hidden layer, Linear[+Tanh] head.
  * n_nets > 1 evaluates structurally identical nets side by side on one input (TwinV.both,

@@ -86,6 +86,7 @@ _SIGNATURES = {
     "porl_gather_rows_f32": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p, _i64, _p]),
     "porl_gather_transitions": (C.c_int, [_p, _p, _i64, _i64, _i32, _i32, _p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _p]),
     "porl_gather_soa": (C.c_int, [_p, _p, _p, _p, _p, _p, _i64, _i32, _i64, _p, _i64, _p, _p, _i64, _p, _p, _p, _p]),
+    "porl_sample_permutation": (C.c_int, [_p, _i64, C.c_uint64, C.c_uint64, _i64, _i64, _p, _p]),
     "porl_pack_rows": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p]),
     "porl_mlp_create": (C.c_int, [_p, C.POINTER(MlpDesc), C.POINTER(_p)]),
     "porl_mlp_destroy": (C.c_int, [_p]),

@@ -123,6 +123,44 @@ class EpochSampler:
             yield perm[i:min(i + self.bs, end)]
 
 
+class DeviceSampler:
+    """Shuffled minibatch indices computed ON THE DEVICE (porl_sample_permutation): position i of epoch e is
+    P_e(i) for a keyed pseudo-random bijection P_e of [0, n_rows), so a batch costs O(B), needs no permutation
+    table and no host round-trip.  Same contract as DataLoader(shuffle=True) / RandomSampler (every row once per
+    epoch, consecutive batches, ragged last batch unless drop_last) and as
+    np.random.choice(size, B, replace=False) (distinct rows), not the same index stream -- the parity tests use
+    EpochSampler / recorded indices instead."""
+
+    def __init__(self, n_rows: int, batch_size: int, device="cuda", seed: int = 0, drop_last: bool = False):
+        self.n, self.bs, self.device = int(n_rows), int(batch_size), torch.device(device)
+        self.seed, self.drop_last = int(seed), drop_last
+        self.ctx = _C.context(self.device)
+        self.epoch = 0
+
+    def __len__(self) -> int:
+        return self.n // self.bs if self.drop_last else (self.n + self.bs - 1) // self.bs
+
+    def indices(self, epoch: int, first: int, count: int, out: torch.Tensor | None = None) -> torch.Tensor:
+        """P_epoch(first .. first + count - 1) as an int64 device tensor."""
+        if out is None:
+            out = torch.empty(count, dtype=torch.int64, device=self.device)
+        check(lib.porl_sample_permutation(self.ctx.handle, self.n, self.seed, epoch, first, count, out.data_ptr(),
+                                          _C.stream_ptr()))
+        return out
+
+    def draw(self, batch_size: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+        """One without-replacement draw of `batch_size` rows (the ReplayBuffer.sample contract): every call uses a
+        fresh key."""
+        self.epoch += 1
+        return self.indices(self.epoch, 0, batch_size or self.bs, out)
+
+    def __iter__(self):
+        self.epoch += 1
+        end = self.n - (self.n % self.bs) if self.drop_last else self.n
+        for first in range(0, end, self.bs):
+            yield self.indices(self.epoch, first, min(self.bs, end - first))
+
+
 def synthetic_rows(n: int, state_size: int, seed: int, action_size: int = 2) -> np.ndarray:
     """Synthetic LaserScan+goal transitions: scan beams in {U(0.13,3.5), 3.5, 10.0},
     goal within 3.5 m, done ~ Bernoulli(0.01), unit-scale rewards, actions U(-1,1)^A.  Vectorised numpy;

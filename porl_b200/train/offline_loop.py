@@ -22,7 +22,11 @@ from ..dataloader.dataset import EpochSampler, TransitionDataset, synthetic_rows
 
 def add_common_flags(parser) -> None:
     """Flags that do not exist in the reference (new names only; every reference flag keeps its name and default)."""
-    parser.add_argument("--dataset", type=str, default="", help=".npy or .pt file with (N, 2S+2+A) float32 rows")
+    parser.add_argument("--dataset", type=str, default="",
+                        help=".npy or .pt file with (N, 2S+2+A) float32 rows, or a directory of the reference's "
+                             "CSV / dict shards (checkpoint/)")
+    parser.add_argument("--device_sampler", action="store_true",
+                        help="shuffle on the device (Feistel permutation kernel) instead of torch.randperm on the host")
     parser.add_argument("--dataset_rows", type=int, default=100_000, help="rows of the synthetic dataset")
     parser.add_argument("--seed", type=int, default=0)
     parser.add_argument("--log_every", type=int, default=100, help="read the losses back every k updates")
@@ -33,6 +37,9 @@ def add_common_flags(parser) -> None:
 
 
 def load_rows(args, row_len: int) -> np.ndarray | torch.Tensor:
+    if args.dataset and os.path.isdir(args.dataset):       # the reference's shard directories (dataloader/ingest.py)
+        from ..dataloader.ingest import load_directory
+        return torch.from_numpy(load_directory(args.dataset, args.state_size, args.action_size))
     if args.dataset:
         rows = np.load(args.dataset) if args.dataset.endswith(".npy") else torch.load(args.dataset)
         rows = torch.as_tensor(rows, dtype=torch.float32)
@@ -51,7 +58,11 @@ def run(args, agent, step_fn, save_every: int, name: str) -> dict:
     if args.batch_size % world:
         raise ValueError(f"--batch_size {args.batch_size} is not divisible by the world size {world}")
     gen = torch.Generator().manual_seed(2000 + args.seed)           # same permutation on every rank
-    sampler = EpochSampler(len(ds), args.batch_size, device, generator=gen)
+    if getattr(args, "device_sampler", False):               # same key on every rank -> same global batch
+        from ..dataloader.dataset import DeviceSampler
+        sampler = DeviceSampler(len(ds), args.batch_size, device, seed=2000 + args.seed)
+    else:
+        sampler = EpochSampler(len(ds), args.batch_size, device, generator=gen)
     agent.ctx.set_gemm_mode(args.gemm_mode)
     pb = None
     done, t0 = 0, time.perf_counter()

@@ -49,6 +49,9 @@ def test_reference_flags_and_defaults_are_kept(script, flags):
     ["sorl_train.py", "--episodes", "2", "--dataset_rows", "1000", "--batch_size", "96", "--hidden_dim", "64",
      "--log_every", "5", "--evaluate", "--weights_dir", "/tmp/porl_b200_cli_weights"],
     ["scripts/train_cql.py", "--dataset_rows", "4096", "--num_iterations", "25", "--log_dir", "/tmp/porl_b200_cli_logs"],
+    # the literal sorl_train.py agent (FasterNet scan encoder, sorl_train.py:29-32) with the device-side shuffle
+    ["sorl_train.py", "--episodes", "1", "--updates", "6", "--dataset_rows", "512", "--batch_size", "32", "--hidden_dim", "64",
+     "--log_every", "3", "--backbone", "fasternet", "--device_sampler"],
 ])
 def test_cli_runs_end_to_end(cmd):
     r = subprocess.run([sys.executable, os.path.join(ROOT, cmd[0]), *cmd[1:]], cwd=ROOT, capture_output=True, text=True,
