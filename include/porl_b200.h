@@ -70,9 +70,12 @@ int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
 /* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
 int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
-/* tcgen05 kernel variant: 1 = the A operand's tf32 hi/lo planes are staged in tensor memory (tcgen05.st) and
- * the MMAs read A from TMEM; 0 = all four operand planes in shared memory */
-int porl_ctx_set_tc_variant(porl_ctx_t* ctx, int a_in_tmem);
+/* tcgen05 kernel variant (env PORL_TC_A_IN_TMEM sets the initial value): 0 (default) = all four operand planes in
+ * shared memory, four TMEM chunk accumulators; 1 = the A operand's tf32 hi/lo planes are staged in tensor memory
+ * (tcgen05.st) and the MMAs read A from TMEM; 2 = CTA pairs (clusters of 2, tcgen05.mma.cta_group::2, M = 256: each
+ * CTA stages half of the B tile), used for launches whose problems are all at least 256 rows high.  All three give
+ * bitwise identical results; 0 is the fastest on B200. */
+int porl_ctx_set_tc_variant(porl_ctx_t* ctx, int variant);
 /* profiling aid: device buffer of 16 x 148 uint64 that receives per-CTA globaltimer stamps (kernel start,
  * setup done, first/last TMA, first split, first/last MMA, chunk drain, epilogue, end; see gemm_tc.cu) of
  * every tcgen05 contraction launch (NULL disables) */

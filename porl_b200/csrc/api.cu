@@ -176,7 +176,7 @@ extern "C" int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks) {
 }
 
 extern "C" int porl_ctx_set_tc_variant(porl_ctx_t* ctx, int a_in_tmem) {
-  PORL_CHECK_ARG(ctx && (a_in_tmem == 0 || a_in_tmem == 1), "porl_ctx_set_tc_variant: a_in_tmem=%d", a_in_tmem);
+  PORL_CHECK_ARG(ctx && a_in_tmem >= 0 && a_in_tmem <= 2, "porl_ctx_set_tc_variant: variant=%d", a_in_tmem);
   ctx->tc_a_in_tmem = a_in_tmem;
   return PORL_OK;
 }

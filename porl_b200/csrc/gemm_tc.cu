@@ -38,11 +38,16 @@ constexpr int TC_SPLIT_THREADS = 192;
 // ATM = true: the splitters put A_hi / A_lo into TENSOR MEMORY (tcgen05.st, 64 columns per stage) and the
 // MMAs take A from TMEM, which removes the A reads from the shared-memory port (the measured limiter)
 // and the A_lo tile from the stage (stage = A_raw, B_raw, B_lo: 3 tiles, 4 stages).
-template <bool ATM>
+// PAIR (two CTAs per 256 x 128 tile): each CTA stages A (16 KB) and HALF of B (8 KB) raw plus their lo copies:
+// 48 KB per stage, 4 stages -- the ring is latency bound (TMA + split + MMA + commit per stage), so depth matters.
+template <bool ATM, bool PAIR = false>
 struct TcCfg {
-  static constexpr int STAGES = ATM ? 4 : 3;
-  static constexpr int STAGE_BYTES = (ATM ? 3 : 4) * TC_TILE_BYTES;
-  static constexpr int B_LO_OFF = (ATM ? 2 : 3) * TC_TILE_BYTES;
+  static constexpr int STAGES = (ATM || PAIR) ? 4 : 3;
+  static constexpr int B_BYTES = PAIR ? TC_TILE_BYTES / 2 : TC_TILE_BYTES;      // B rows staged per CTA: 64 or 128
+  static constexpr int RAW_BYTES = TC_TILE_BYTES + B_BYTES;                     // raw A, raw B (adjacent)
+  static constexpr int STAGE_BYTES = ATM ? 3 * TC_TILE_BYTES : 2 * RAW_BYTES;
+  static constexpr int A_LO_OFF = RAW_BYTES;                                    // lo A, lo B follow in the same order
+  static constexpr int B_LO_OFF = ATM ? 2 * TC_TILE_BYTES : RAW_BYTES + TC_TILE_BYTES;
   // chunk accumulators in TMEM: the MMAs may run NBUF chunks ahead of the accumulator warps, which matters while
   // those warps are busy with a tile's epilogue (short-K tiles: a whole next tile fits into four buffers)
   static constexpr int NBUF = ATM ? 2 : 4;
@@ -58,11 +63,13 @@ struct alignas(64) TcParams {
   CUtensorMap mapA[kMaxGroups];
   CUtensorMap mapB[kMaxGroups];
   CUtensorMap mapC[kMaxGroups];     // row-major C (n_store x M), box {32, 128}: the epilogue's TMA stores
+  CUtensorMap mapB2[kMaxGroups];    // pair mode: B with box {32, 64} (each CTA of a pair loads half of the B tile)
   GemmBatch batch;
   int tile_begin[kMaxGroups + 1];   // prefix sum of tiles per group
   int tiles_n[kMaxGroups];          // n-tiles per group
   int total_tiles;
   int chunk_kb;                     // k-blocks per TMEM accumulation chunk
+  int tile_m;                       // rows per work unit: 128, or 256 in pair mode (two CTAs x 128)
   float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
   unsigned long long* dbg;          // optional per-CTA timestamps (tools/gemm_probe.py), or null
 };
@@ -102,6 +109,39 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
                ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// ---- CTA-pair (cta_group::2) helpers
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {      // same smem offset in CTA `rank`
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {       // arrives on the barrier at this offset in BOTH CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -189,7 +229,7 @@ __device__ __forceinline__ bool tc_decode(const TcParams& P, int u, TcUnit& w) {
   w.g = g;
   w.tile = t;
   const int nt = P.tiles_n[g];
-  w.m0 = (t / nt) * TC_BM;
+  w.m0 = (t / nt) * P.tile_m;
   w.n0 = (t % nt) * TC_BN;
   const int nkb = (P.batch.g[g].K + TC_BK - 1) / TC_BK;
   w.kb0 = (int)((long long)w.split * nkb / P.batch.splits);
@@ -198,9 +238,15 @@ __device__ __forceinline__ bool tc_decode(const TcParams& P, int u, TcUnit& w) {
 }
 
 // ------------------------------------------------------------------------------------------ kernel
-template <bool ATM>
+// PAIR: two CTAs of a cluster work on one 256 x 128 tile with tcgen05.mma.cta_group::2 (M = 256): each CTA owns 128
+// rows of A and of the accumulator and stages only HALF of the B tile (64 rows), which the hardware shares between
+// the two tensor cores -- 25 % less shared-memory traffic per MMA, the measured limiter.  The leader CTA (rank 0)
+// issues the MMAs for both; the peer's splitters and accumulator warps signal the leader's barriers through the
+// cluster address space, tcgen05.commit multicasts completion to both CTAs.
+template <bool ATM, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams P) {
-  using C = TcCfg<ATM>;
+  static_assert(!(ATM && PAIR), "pair mode uses the shared-memory A operand");
+  using C = TcCfg<ATM, PAIR>;
   constexpr int TC_STAGES = C::STAGES, TC_STAGE_BYTES = C::STAGE_BYTES, TC_NUM_BARS = C::NUM_BARS;
   constexpr int TC_TMEM_COLS = C::TMEM_COLS, TC_NBUF = C::NBUF, TC_ACC_COLS = C::ACC_COLS;
   extern __shared__ uint8_t smem_raw[];
@@ -219,6 +265,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + TC_NBUF + b); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // CTA of the pair; rank 0 leads
+  const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_stride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  constexpr uint32_t B_BYTES = C::B_BYTES;
   unsigned long long* const dbg = P.dbg ? P.dbg + 16 * blockIdx.x : nullptr;   // [0] start [1] setup done
   // [2] first TMA issued [3] last TMA issued [6] last MMA commit; wait totals in SM clocks: [11] producer on empty
   // [12] splitters on raw_full [13] MMA on split_done [14] MMA on tmem_empty [4] accumulators on tmem_full [5] CTA clocks
@@ -234,24 +284,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     }
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(raw_full(s), 1);
-      mbar_init(split_done(s), TC_SPLIT_THREADS);
+      mbar_init(split_done(s), PAIR ? 2 * TC_SPLIT_THREADS : TC_SPLIT_THREADS);
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < TC_NBUF; ++b) {
       mbar_init(tmem_full(b), 1);
-      mbar_init(tmem_empty(b), 128);
+      mbar_init(tmem_empty(b), PAIR ? 256 : 128);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(TC_TMEM_COLS)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(TC_TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(TC_TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();         // barriers of both CTAs initialised before any remote arrive / multicast
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   if (dbg && threadIdx.x == 0) dbg[1] = gtime();
@@ -263,32 +321,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       int it = 0;
       long long w_prod = 0;
       TcUnit w;
-      for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+      for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
         for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
           const int s = it % TC_STAGES;
           const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
           const long long tw = dbg ? clock64() : 0;
           mbar_wait(empty_bar(s), ph ^ 1u);
           if (dbg) w_prod += clock64() - tw;
-          mbar_expect_tx(raw_full(s), 2 * TC_TILE_BYTES);
+          mbar_expect_tx(raw_full(s), TC_TILE_BYTES + B_BYTES);
           const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-          tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0);
-          tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+          tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
+          if (PAIR) tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
+          else tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
           if (dbg && it == 0) dbg[2] = gtime();
         }
       }
       if (dbg) { dbg[3] = gtime(); dbg[11] = (unsigned long long)w_prod; }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (pair mode: the leader CTA only) =====================
+    if (lane == 0 && rank == 0) {
       // instruction descriptor: D fp32, A/B tf32, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
       constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
-                                 ((uint32_t)(TC_BM >> 4) << 24);
+                                 ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24);
       int it = 0, chunk = 0;
       long long w_te = 0, w_sd = 0;
       TcUnit w;
-      for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+      for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
         int kb = w.kb0;
         while (kb < w.kb1) {
           const int buf = chunk % TC_NBUF;
@@ -322,23 +381,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
               for (int ks = 0; ks < TC_BK / 8; ++ks)
                 tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + (uint64_t)(2 * ks), idesc, 1u);
             } else {
-              const uint64_t a_hi = smem_desc(st), a_lo = smem_desc(st + 2 * TC_TILE_BYTES);
+              const uint64_t a_hi = smem_desc(st), a_lo = smem_desc(st + C::A_LO_OFF);
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks) {
                 const uint64_t o = (uint64_t)(2 * ks);
-                tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
-                acc = 1;
-                tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+                if (PAIR) {
+                  tc_mma_tf32_pair(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+                  acc = 1;
+                  tc_mma_tf32_pair(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+                } else {
+                  tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+                  acc = 1;
+                  tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+                }
               }
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks) {
                 const uint64_t o = (uint64_t)(2 * ks);
-                tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+                else tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
               }
             }
-            tc_commit(empty_bar(s));            // frees the stage once these MMAs have read it
+            if (PAIR) tc_commit_pair(empty_bar(s));   // frees the stage (in both CTAs) once these MMAs have read it
+            else tc_commit(empty_bar(s));
           }
-          tc_commit(tmem_full(buf));            // chunk accumulator complete
+          if (PAIR) tc_commit_pair(tmem_full(buf));   // chunk accumulator complete (both CTAs' halves)
+          else tc_commit(tmem_full(buf));
           ++chunk;
           kb += nk;
         }
@@ -351,7 +419,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     int it = 0;
     long long w_rf = 0;
     TcUnit w;
-    for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+    for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
       for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
         const int s = it % TC_STAGES;
         const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
@@ -394,18 +462,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           }
         } else {
           const float4* src = reinterpret_cast<const float4*>(stage);
-          float4* dst = reinterpret_cast<float4*>(stage + 2 * TC_TILE_BYTES);
+          float4* dst = reinterpret_cast<float4*>(stage + C::A_LO_OFF);
+          // raw A and raw B are adjacent (pair mode: only the first 64 rows of the B region are staged)
+          constexpr int RAW16 = (int)(TC_TILE_BYTES + B_BYTES) / 16;
 #pragma unroll
-          for (int i = 0; i < (2 * TC_TILE_BYTES / 16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
+          for (int i = 0; i < (RAW16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
             const int e = t + i * TC_SPLIT_THREADS;
-            if (e < 2 * TC_TILE_BYTES / 16) {
+            if (e < RAW16) {
               const float4 v = src[e];
               dst[e] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
             }
           }
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> tensor-core reads
-        mbar_arrive(split_done(s));
+        if (PAIR) {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic writes -> tensor-core reads (either SM)
+          if (rank == 0) mbar_arrive(split_done(s));
+          else mbar_arrive_cluster(mapa_rank(split_done(s), 0));       // the leader's MMA thread waits for both CTAs
+        } else {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic writes -> tensor-core reads
+          mbar_arrive(split_done(s));
+        }
       }
     }
     if (dbg && t == 0) dbg[12] = (unsigned long long)w_rf;
@@ -415,16 +491,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     int chunk = 0, sbuf = 0;
     long long w_tf = 0;
     TcUnit w;
-    for (int u = blockIdx.x; tc_decode(P, u, w); u += gridDim.x) {
+    for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
+      w.m0 += (int)rank * TC_BM;                            // pair mode: this CTA's 128 rows of the 256-row tile
       // this tile's problem, by value: loads through a reference into the parameter block would be
       // re-issued after every global store of the epilogue
       const GemmGroup& Gp = P.batch.g[w.g];
-      float* const gC = Gp.C;
       float* const gCt = Gp.Ct;
       const float* const gBias = Gp.bias;
       const float* const gRelu = Gp.relu_src;
       const int gM = Gp.M, gN = Gp.N, gNs = Gp.n_store, gEpi = Gp.epilogue;
-      const size_t ldc = (size_t)Gp.ldc, ldr = (size_t)Gp.ld_relu, ldct = (size_t)Gp.ldct;
+      const size_t ldr = (size_t)Gp.ld_relu, ldct = (size_t)Gp.ldct;
 
       float acc[TC_BN];
 #pragma unroll
@@ -446,18 +522,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           for (int j = 0; j < 32; ++j) acc[c0 + j] += v[j];
         }
         tc_fence_before();
-        mbar_arrive(tmem_empty(buf));
+        if (PAIR && rank != 0) mbar_arrive_cluster(mapa_rank(tmem_empty(buf), 0));
+        else mbar_arrive(tmem_empty(buf));
       }
 
-      if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[8] = gtime();
+      if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[8] = gtime();
       // ---- split-K: every slice parks its partial tile in the workspace; the LAST slice to arrive (ticket)
       // sums all partials in slice order -- a fixed order, so the result is bitwise reproducible whichever
       // CTA happens to be last -- and runs the epilogue.  No slice ever waits for another one.
       if (P.batch.splits > 1) {
         const int S = P.batch.splits;
-        const int gt = P.tile_begin[w.g] + w.tile;
+        // pair mode: each CTA's 128 x 128 half of the tile is its own split-K unit (workspace slot, ticket)
+        const int gt = (P.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
+        const int n_sub = P.total_tiles * (PAIR ? 2 : 1);
         const int r_in_tile = 32 * q + lane;
-        float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * P.total_tiles + gt) * (32 * 128) + r_in_tile;
+        float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
 #pragma unroll
         for (int c4 = 0; c4 < TC_BN; c4 += 4)
           wp[(c4 >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
@@ -484,7 +563,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             const float4 o = __ldcg(rp + (c4 >> 2) * 128);
             acc[c4] += o.x; acc[c4 + 1] += o.y; acc[c4 + 2] += o.z; acc[c4 + 3] += o.w;
           }
-          rp += (size_t)P.total_tiles * (32 * 128);
+          rp += (size_t)n_sub * (32 * 128);
         }
       }
       // Straight from the register accumulator (thread = output row): row-major C as 16-byte stores
@@ -559,18 +638,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(&P.mapC[w.g], smem_u32(buf), w.n0 + 32 * sl, w.m0);
         sbuf ^= 1;
       }
-      if (dbg && u == (int)blockIdx.x && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
+      if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
     if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();      // the peer may not exit (or free TMEM) while the leader's MMAs / multicasts target it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS)
-                 : "memory");
+    if (PAIR)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS)
+                   : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS)
+                   : "memory");
   }
   if (dbg && threadIdx.x == 0) { dbg[15] = gtime(); dbg[5] = (unsigned long long)(clock64() - clk0); }
 }
@@ -596,16 +680,16 @@ static EncodeTiledFn encode_fn() {
 
 struct MapKey {
   const void* ptr;
-  int outer, inner, ld;
+  int outer, inner, ld, box_rows;
   bool operator==(const MapKey& o) const {
-    return ptr == o.ptr && outer == o.outer && inner == o.inner && ld == o.ld;
+    return ptr == o.ptr && outer == o.outer && inner == o.inner && ld == o.ld && box_rows == o.box_rows;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.ptr);
     auto mix = [&](size_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld);
+    mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld); mix((size_t)k.box_rows);
     return h;
   }
 };
@@ -616,8 +700,8 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash>& map_cache() {
 
 // 2-D tensor map of a K-major fp32 operand (rows x K, K contiguous, row pitch ld floats):
 // box {32 k, 128 rows}, SWIZZLE_128B; out-of-bounds elements (k >= K, row >= rows) read as zero.
-static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, int ld) {
-  MapKey key{ptr, rows, k_extent, ld};
+static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, int ld, int box_rows = TC_BM) {
+  MapKey key{ptr, rows, k_extent, ld, box_rows};
   auto& cache = map_cache();
   auto it = cache.find(key);
   if (it != cache.end()) {
@@ -631,7 +715,7 @@ static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, 
   }
   cuuint64_t dims[2] = {(cuuint64_t)k_extent, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 4ull};
-  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)TC_BM};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -659,11 +743,40 @@ bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor) {
   return true;
 }
 
+// clusters of two CTAs that can be resident at once (pair mode grid); 0 when cluster launch is unavailable
+static int max_pairs(int smem_bytes) {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2, 1, 1);
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = (size_t)smem_bytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<false, true>, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  cached = n;
+  return cached;
+}
+
 int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
   bool can_split = true;
   int min_nkb = 1 << 30;
   TcParams P;
   int tiles = 0;
+  // pair mode (variant 2): every problem at least one full 256-row tile high, otherwise the second CTA idles
+  bool pair = ctx->tc_a_in_tmem == 2;
+  for (int i = 0; i < batch.n_groups && pair; ++i)
+    if (batch.g[i].M < 2 * TC_BM) pair = false;
+  P.tile_m = pair ? 2 * TC_BM : TC_BM;
   for (int i = 0; i < batch.n_groups; ++i) {
     const GemmGroup& g = batch.g[i];
     if (!gemm_tc_eligible(g, a_kmajor, b_kmajor)) return PORL_ERR_UNSUPPORTED;
@@ -672,7 +785,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
     if (g.epilogue != 0 || g.relu_src != nullptr) can_split = false;
     P.tile_begin[i] = tiles;
     P.tiles_n[i] = (g.n_store + TC_BN - 1) / TC_BN;
-    tiles += ((g.M + TC_BM - 1) / TC_BM) * P.tiles_n[i];
+    tiles += ((g.M + P.tile_m - 1) / P.tile_m) * P.tiles_n[i];
   }
   for (int i = batch.n_groups; i <= kMaxGroups; ++i) P.tile_begin[i] = tiles;
   for (int i = batch.n_groups; i < kMaxGroups; ++i) P.tiles_n[i] = 1;
@@ -682,20 +795,47 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
     int rc = make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
     if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
     if (rc == PORL_OK) rc = make_map(&P.mapC[i], g.C, g.n_store, g.M, g.ldc);
+    if (rc == PORL_OK && pair) rc = make_map(&P.mapB2[i], g.B, g.K, g.N, g.ldb, TC_BN / 2);
     if (rc != PORL_OK) return rc;
   }
-  const int sms = ctx->sm_count;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         TcCfg<false>::SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               TcCfg<true>::SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               TcCfg<false, true>::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
+      return PORL_ERR_CUDA;
+    }
+    configured = true;
+  }
+  int n_pairs = 0;
+  if (pair) {
+    n_pairs = max_pairs(TcCfg<false, true>::SMEM_BYTES);
+    if (n_pairs <= 0) {
+      set_error("pair mode: cluster launch of 2 CTAs is not available on this device");
+      return PORL_ERR_UNSUPPORTED;
+    }
+  }
+  // work slots: one per SM, or one per resident CTA pair; sub-tiles (128 x 128, one per CTA) for the split-K buffers
+  const int sms = pair ? n_pairs : ctx->sm_count;
+  const int sub = pair ? 2 : 1;
   int splits = 1;
   if (can_split && 2 * tiles <= sms) {
     int want = sms / tiles;
     int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
     splits = want < cap ? want : cap;
     const long long ws_tiles = (long long)(kTcWsFloats / (TC_BM * TC_BN));
-    if ((long long)splits * tiles > ws_tiles) splits = (int)(ws_tiles / tiles);
+    if ((long long)splits * tiles * sub > ws_tiles) splits = (int)(ws_tiles / ((long long)tiles * sub));
     if (splits > 32) splits = 32;
     if (splits < 1) splits = 1;
   }
-  if (tiles > kSemInts) splits = 1;
+  if ((long long)tiles * sub > kSemInts) splits = 1;
   batch.splits = splits;
   batch.sem = ctx->sem;
   batch.sem_stride = 0;
@@ -706,23 +846,29 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   const long long units = (long long)tiles * splits;
   const int grid = (int)(units < sms ? units : sms);
 
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         TcCfg<false>::SMEM_BYTES);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               TcCfg<true>::SMEM_BYTES);
+  if (pair) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * grid, 1, 1);
+    cfg.blockDim = dim3(TC_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = TcCfg<false, true>::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<false, true>, P);
     if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
+      set_error("cluster launch of the pair-mode contraction failed: %s", cudaGetErrorString(e));
       return PORL_ERR_CUDA;
     }
-    configured = true;
+  } else if (ctx->tc_a_in_tmem == 1) {
+    gemm_tc_kernel<true, false><<<grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream>>>(P);
+  } else {
+    gemm_tc_kernel<false, false><<<grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream>>>(P);
   }
-  if (ctx->tc_a_in_tmem)
-    gemm_tc_kernel<true><<<grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream>>>(P);
-  else
-    gemm_tc_kernel<false><<<grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream>>>(P);
   ctx->tc_launches++;
   PORL_LAUNCHED(ctx);
   return PORL_OK;
