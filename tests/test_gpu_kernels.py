@@ -146,6 +146,27 @@ def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=Fal
         assert bool((got[:, n_store:] == 7.0).all())                       # never written past n_store
     if colsum:
         np.testing.assert_allclose(cs.cpu().numpy(), Al.double().sum(1).numpy(), rtol=0, atol=3e-5 * math.sqrt(K))
+    return got
+
+
+@pytest.mark.parametrize("M,N,K,kw", [(4096, 512, 362, {}), (512, 512, 4096, {}), (1000, 200, 96, dict(bias=True, epilogue=1)),
+                                      (2048, 384, 512, dict(relu=True, transposed=True)), (300, 129, 640, dict(n_store=132))])
+def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
+    """The three tcgen05 kernel variants (operands in shared memory / A in tensor memory / CTA pairs with
+    cta_group::2) issue the same MMAs on the same values in the same order: identical bits, incl. split-K."""
+    ctx = env[1]
+    ctx.set_gemm_mode(1)
+    try:
+        outs = []
+        for variant in (0, 1, 2):
+            ctx.set_tc_variant(variant)
+            before = ctx.tc_launches
+            outs.append(_gemm(env, 1, 1, M, N, K, seed=5, **kw))
+            assert ctx.tc_launches == before + 1
+        assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    finally:
+        ctx.set_tc_variant(0)
+        ctx.set_gemm_mode(0)
 
 
 @pytest.mark.parametrize("mode", [0, 1])
