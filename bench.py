@@ -46,6 +46,7 @@ def parse():
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     p.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     p.add_argument("--also-batch", type=int, default=256, help="second batch size reported under 'also'")
+    p.add_argument("--other-configs", type=int, default=1, help="also time BASELINE configs 1 (POR) and 3 (CQL)")
     p.add_argument("--encoder-batch", type=int, default=256,
                    help="batch of the SORL + FasterNet scan-encoder workload reported under 'also_encoder' (0: skip)")
     return p.parse_args()
@@ -61,8 +62,10 @@ def hyper():
     return args, dict(max_steps=1_000_000, tau=0.9, alpha=10.0)
 
 
-def synth_rows_torch(n, device, seed):
-    """Synthetic LaserScan+goal transitions generated with torch on `device`."""
+def synth_rows_torch(n, device, seed, state_size=None):
+    """Synthetic LaserScan+goal transitions generated with torch on `device`; state_size > 362 puts
+    pose-like filler columns U(-3, 3) between the scan and the goal (the S = 365 rows of por_train.py)."""
+    state_size = state_size or S
     g = torch.Generator(device=device).manual_seed(seed)
     r = lambda *s: torch.rand(*s, generator=g, device=device)
     scan = 0.13 + (3.5 - 0.13) * r(n, 360)
@@ -71,10 +74,12 @@ def synth_rows_torch(n, device, seed):
     scan = torch.where(u > 0.97, torch.full_like(scan, 10.0), scan)
     rad, th = 0.2 + 3.3 * r(n), (2 * r(n) - 1) * 3.14159265
     goal = torch.stack([rad * torch.cos(th), rad * torch.sin(th)], 1)
+    if state_size > 362:
+        goal = torch.cat([6 * r(n, state_size - 362) - 3, goal], 1)
     nscan = (scan + 0.05 * torch.randn(n, 360, generator=g, device=device)).clamp(0.13, 3.5)
     nscan = torch.where(scan == 3.5, scan, nscan)
     nscan = torch.where(scan == 10.0, scan, nscan)
-    ngoal = goal + 0.05 * torch.randn(n, 2, generator=g, device=device)
+    ngoal = goal + 0.05 * torch.randn(n, goal.shape[1], generator=g, device=device)
     done = (r(n) < 0.01).float()
     sign = torch.where(r(n) < 0.5, -5.0, 5.0)
     rew = 0.1 * torch.randn(n, generator=g, device=device) + done * sign
@@ -296,6 +301,91 @@ def timed(runner, idx_warm, idx_timed, dist_on):
     return ms, launches
 
 
+def kernel_table(prof, pk):
+    """Per-category achieved rate of the launches recorded by porl_profile_*: flop categories against the measured
+    bf16 peak (and the fp32 SIMT pipe for the FFMA conv), byte categories against the measured HBM bandwidth."""
+    out = {}
+    flop_cats = {"contraction": pk["bf16_sustained"] * 1e12, "pconv": 74.0e12}
+    for name, v in prof.items():
+        if v["launches"] == 0:
+            continue
+        rate = v["work"] / (v["ms"] * 1e-3) if v["ms"] > 0 else 0.0
+        is_flop = name in flop_cats
+        peak = flop_cats[name] if is_flop else pk["hbm_gbs"] * 1e9
+        out[name] = {"launches": v["launches"], "ms_total": v["ms"], "achieved": rate / (1e12 if is_flop else 1e9),
+                     "unit": "TFLOP/s" if is_flop else "GB/s", "frac_of_peak": rate / peak}
+        if name == "pconv":
+            out[name]["peak_note"] = "fp32 FFMA pipe, 148 SMs x 128 lanes x 2 x 1.965 GHz = 74 TFLOP/s (nominal)"
+    return out
+
+
+def time_updates(step_fn, n_warm, n_timed):
+    for _ in range(n_warm):
+        step_fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n_timed):
+        step_fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n_timed
+
+
+def other_configs(a, device, table):
+    """BASELINE configs 1 (POR, S=365, H=1024, batch 256) and 3 (discrete CQL, QNetwork 362-64-128-64-5, batch 4096):
+    device-timed updates/s with a fresh gather every step, eager launches (no graph)."""
+    from types import SimpleNamespace
+    from porl_b200 import CQLTrainer, POR, QNetwork, TransitionDataset
+    out = {}
+    g = torch.Generator(device=device).manual_seed(7)
+    # config 1: POR on the 365-float rows of por_train.py (100k rows)
+    rows = synth_rows_torch(100_000, device, 20260101, state_size=365)
+    ds = TransitionDataset(rows, 365, A, device)
+    args = SimpleNamespace(state_size=365, hidden_dim=1024, n_hidden=N_HIDDEN, layer_norm=False, feature_dim=256, action_size=A)
+    for B in (256, 4096):
+        torch.manual_seed(1000)
+        agent = POR(args, max_steps=1_000_000, tau=0.9, alpha=10.0, device=device)
+        agent.ctx.set_gemm_mode(a.gemm_mode)
+        pb = ds.new_batch(B)
+
+        def step():
+            ds.gather_packed(torch.randint(0, len(ds), (B,), generator=g, device=device), pb)
+            agent.update_packed(pb)
+
+        ms = time_updates(step, 5, 50 if B == 256 else 20)
+        agent.read_losses()
+        out[f"por_mlp_S365_H1024_rows100k_b{B}"] = {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms,
+                                                     "achieved_tflops": 37.0e6 * B / (ms * 1e-3) * 1e-12}
+        del agent
+    del ds, rows
+    # config 3: discrete CQL on a replay buffer filled from the SORL table
+    t = CQLTrainer(state_size=S, action_size=5, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
+                   update_target_freq=10, device=device, network=QNetwork, log_dir="/tmp/porl_b200_bench_logs")
+    t.ctx.set_gemm_mode(a.gemm_mode)
+    n = min(len(table), 1_000_000)
+    from porl_b200.buffer.replaybuffer import ReplayBuffer
+    t.replay_buffer = ReplayBuffer(n, (S,), device)
+    idx = torch.arange(n, device=device)
+    rowsb = table.gather(idx)
+    t.replay_buffer.push_batch(rowsb[:, :S], torch.randint(0, 5, (n,), generator=g, device=device), rowsb[:, S],
+                               rowsb[:, S + 1:2 * S + 1], rowsb[:, 2 * S + 1])
+    del rowsb
+    B = 4096
+    state = {"pb": None, "i": 0}
+
+    def cql_step():
+        state["pb"] = t.replay_buffer.gather_packed(torch.randint(0, n, (B,), generator=g, device=device), state["pb"])
+        t.learn_packed(state["pb"], hard_every=10)
+        state["i"] += 1
+
+    ms = time_updates(cql_step, 5, 100)
+    t.read_losses()
+    out[f"cql_q362-64-128-64-5_rows1M_b{B}"] = {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms,
+                                                 "note": "launch-latency bound (1.1 GFLOP per update); eager launches"}
+    return out
+
+
 def run_b200(a):
     from porl_b200 import TransitionDataset, _C, dist as pdist
     rank, local, world = pdist.init_from_env()
@@ -370,15 +460,7 @@ def run_b200(a):
                             "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({pk['source']})",
                             "launches_per_step": c["launches"] / max(1, min(10, K)),
                             "share_of_step_ms": c["ms"] / max(1e-9, sum(v["ms"] for v in prof.values()))}
-        kern = {}
-        for name, v in prof.items():
-            if v["launches"] == 0:
-                continue
-            rate = v["work"] / (v["ms"] * 1e-3) if v["ms"] > 0 else 0.0
-            kern[name] = {"launches": v["launches"], "ms_total": v["ms"],
-                          "achieved": rate / (1e12 if name == "contraction" else 1e9),
-                          "unit": "TFLOP/s" if name == "contraction" else "GB/s",
-                          "frac_of_peak": rate / (peak * 1e12 if name == "contraction" else pk["hbm_gbs"] * 1e9)}
+        kern = kernel_table(prof, pk)
         line["kernels"] = kern
 
         # e2e: the public API with HOST buffers: pinned rows -> H2D -> agent.update() -> losses D2H
@@ -426,7 +508,14 @@ def run_b200(a):
             line["also_encoder"] = {"workload": f"sorl_fasternet_S{S}_F256_H{H}_rows1M_b{Be}", "value": 10 / (ms3 * 1e-3),
                                     "unit": UNIT, "ms_per_step": ms3 / 10, "gpu_launches": l3,
                                     "achieved_tflops": flop / (ms3 / 10 * 1e-3) * 1e-12, "graph": False}
+            ctx.profile(True)
+            r3.run(r3.indices(2, 2007))
+            torch.cuda.synchronize()
+            line["also_encoder"]["kernels"] = kernel_table(ctx.profile_read(), pk)
+            ctx.profile(False)
             del r3
+        if a.other_configs:
+            line["also_configs"] = other_configs(a, device, table)
 
         # CPU baseline beside it (bounded sample; reported, not the target)
         if a.cpu_seconds > 0:

@@ -86,7 +86,9 @@ int porl_ctx_set_tc_debug(porl_ctx_t* ctx, uint64_t* stamps_dev);
  * category together with its ALGORITHMIC work (flops for contractions, bytes for the HBM-bound
  * kernels).  porl_profile_read synchronises the recorded events and returns per-category sums. */
 enum { PORL_CAT_CONTRACTION = 0, PORL_CAT_GATHER = 1, PORL_CAT_LOSS = 2, PORL_CAT_OPTIMIZER = 3,
-       PORL_CAT_NORM = 4, PORL_CAT_TRANSPOSE = 5, PORL_CAT_HEAD = 6, PORL_CAT_ENCODER = 7, PORL_CAT_COUNT = 8 };
+       PORL_CAT_NORM = 4, PORL_CAT_TRANSPOSE = 5, PORL_CAT_HEAD = 6, PORL_CAT_ENCODER = 7 /* HBM-bound encoder passes */,
+       PORL_CAT_BATCHNORM = 8 /* encoder BatchNorm statistics + apply (bytes) */, PORL_CAT_PCONV = 9 /* 3x3 partial conv (flops) */,
+       PORL_CAT_COUNT = 10 };
 typedef struct {
   int64_t launches[PORL_CAT_COUNT];
   double ms[PORL_CAT_COUNT];       /* sum of per-launch device durations */

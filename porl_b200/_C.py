@@ -44,7 +44,7 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
-CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head", "encoder")
+CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head", "encoder", "batchnorm", "pconv")
 
 
 class Profile(C.Structure):

@@ -192,6 +192,22 @@ class ExpectileAgent(nn.Module):
     def value_update_packed(self, pb: PackedBatch) -> None:
         self._value_step(pb, *self._head_inputs(pb))
 
+    # ------------------------------------------------------------------ checkpoint extension
+    def training_state_dict(self) -> dict:
+        """Everything a bitwise-identical resume needs, on top of the reference-layout `state_dict()` that
+        por_train.py:97 / sorl_train.py:74 save: both Adam groups (moments, step, current LR of the cosine
+        recursion) and the device RNG state the encoder's DropPath draws from."""
+        return {"model": self.state_dict(), "v_optimizer": self.v_group.state_dict(),
+                "policy_optimizer": self.p_group.state_dict(),
+                "cuda_rng_state": torch.cuda.get_rng_state(self.device)}
+
+    def load_training_state_dict(self, sd: dict) -> None:
+        self.load_state_dict(sd["model"])
+        self.v_group.load_state_dict(sd["v_optimizer"])
+        self.p_group.load_state_dict(sd["policy_optimizer"])
+        if sd.get("cuda_rng_state") is not None:
+            torch.cuda.set_rng_state(sd["cuda_rng_state"].cpu(), self.device)
+
     def read_losses(self) -> tuple[float, float]:
         """Synchronising read of (v_loss, policy_loss) of the last update; raises on device flags."""
         self._host[0:1].copy_(self.v_group.tail[0:1], non_blocking=True)

@@ -34,6 +34,14 @@ class POR(ExpectileAgent):
     def _policy_target(agent, pb):
         return pb.next_obs, pb.ld_obs          # log_prob(next_observations), agent/por.py:103
 
+    def select_action(agent, observations):
+        """Mean of the goal policy for a batch of observations, as a numpy array (B, state_size).  The reference's
+        evaluation loop calls `agent.select_action(state[None, :])` (test.py:29) but its POR class has no such
+        method (only SORL does, agent/sorl.py:71-76); this is the same forward for POR's guide policy."""
+        if agent.backbone is not None:
+            observations = agent.backbone(observations)
+        return agent.goal_policy(observations).mean.cpu().numpy()
+
     def por_residual_update(agent, observations, next_observations, rewards, terminals):
         """agent/por.py:73-112.  Returns (v_loss, g_loss) as Python floats (one host sync)."""
         pb = agent.pack(observations, next_observations, rewards, terminals)

@@ -434,7 +434,7 @@ int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, con
   G = (rows + rpb - 1) / rpb;
   const size_t smem = (size_t)(kBnThreads / (C / 4)) * C * 2 * sizeof(double);
   {
-    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 4.0, st);
+    ProfScope prof(ctx, PORL_CAT_BATCHNORM, (double)rows * C * 4.0, st);
     bn_stats_kernel<<<(unsigned)G, kBnThreads, smem, st>>>(x, rows, C, rpb, w.partial, ctx->counters + kBnTicket, w.totals);
     PORL_LAUNCHED(ctx);
   }
@@ -453,7 +453,7 @@ int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, con
   const int64_t n4 = rows * C / 4;
   int64_t grid = (n4 + 255) / 256;
   if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
-  ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 8.0, st);
+  ProfScope prof(ctx, PORL_CAT_BATCHNORM, (double)rows * C * 8.0, st);
   bn_apply_kernel<<<(unsigned)grid, 256, 0, st>>>(x, n4, C / 4, w.scale_shift, C, relu);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
@@ -465,7 +465,8 @@ int mlp_block(porl_ctx* ctx, const EncWs& w, const porl_fn_block_t& blk, float* 
   PORL_CHECK_ARG(blk.pconv_w && blk.w1 && blk.w2, "fasternet: null block weight");
   const int64_t rows = B * H * W;
   {
-    ProfScope prof(ctx, PORL_CAT_ENCODER, (double)rows * C * 8.0, st);
+    const double cc = C / 4;
+    ProfScope prof(ctx, PORL_CAT_PCONV, (double)rows * 18.0 * cc * cc, st);      // 2 * 9 * (C/4)^2 flop per pixel
     const dim3 grid((W + 15) / 16, (H + 15) / 16, (unsigned)B);
     if (C == 96) pconv3_kernel<24><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);
     else pconv3_kernel<48><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);

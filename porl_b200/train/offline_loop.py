@@ -33,6 +33,8 @@ def add_common_flags(parser) -> None:
     parser.add_argument("--updates", type=int, default=0, help="stop after this many updates (0: run all episodes)")
     parser.add_argument("--gemm_mode", type=int, default=1, help="0 fp32 FFMA, 1 tcgen05 3xTF32 contractions")
     parser.add_argument("--weights_dir", type=str, default="weights")
+    parser.add_argument("--resume", type=str, default="",
+                        help="training checkpoint (train_{i}.pt: weights + optimizer + LR clocks) to continue from")
     parser.add_argument("--backbone", type=str, default="none", choices=["none", "fasternet"])
 
 
@@ -64,6 +66,8 @@ def run(args, agent, step_fn, save_every: int, name: str) -> dict:
     else:
         sampler = EpochSampler(len(ds), args.batch_size, device, generator=gen)
     agent.ctx.set_gemm_mode(args.gemm_mode)
+    if getattr(args, "resume", ""):
+        agent.load_training_state_dict(torch.load(args.resume, map_location=device, weights_only=False))
     pb = None
     done, t0 = 0, time.perf_counter()
     last = (float("nan"), float("nan"))
@@ -90,6 +94,7 @@ def run(args, agent, step_fn, save_every: int, name: str) -> dict:
         if save_every and (ep + 1) % save_every == 0 and rank == 0:
             os.makedirs(args.weights_dir, exist_ok=True)
             torch.save(agent.state_dict(), os.path.join(args.weights_dir, f"model_{ep}.pt"))   # por_train.py:97
+            torch.save(agent.training_state_dict(), os.path.join(args.weights_dir, f"train_{ep}.pt"))
             print("evaluate_policy: unavailable on this box (Gazebo/ROS roll-outs, test.py:8-53)", flush=True)
         if args.updates and done >= args.updates:
             break

@@ -256,3 +256,27 @@ def test_cql_device_side_hard_copy_matches_host_loop():
     torch.cuda.synchronize()
     assert torch.equal(a.q_group.params, b.q_group.params)
     assert torch.equal(a.target_network.flat, b.target_network.flat)
+
+
+@pytest.mark.parametrize("kind", ["sorl", "por"])
+def test_training_checkpoint_resumes_bitwise(kind, tmp_path):
+    """weights + both Adam groups + LR clocks in one checkpoint; a resumed run continues bit for bit
+    (the reference saves weights only, por_train.py:97, so its resume restarts the optimizers and the cosine LR)."""
+    S, H, A, B = 30, 64, 2, 32
+    rows = torch.from_numpy(synth.laser_rows(B * 6, S, 23, A)).to(DEV)
+    agent, _ = make_agent(kind, S, H, A, 50, 0.8, 3.0, 9)
+    for i in range(3):
+        step(agent, kind, slice_row(rows[i * B:(i + 1) * B], S, A))
+    path = tmp_path / "train.pt"
+    torch.save(agent.training_state_dict(), path)
+    tail = [step(agent, kind, slice_row(rows[i * B:(i + 1) * B], S, A)) for i in range(3, 6)]
+    fresh, _ = make_agent(kind, S, H, A, 50, 0.8, 3.0, 1234)             # different weights before the load
+    fresh.load_training_state_dict(torch.load(path, map_location=DEV, weights_only=False))
+    tail2 = [step(fresh, kind, slice_row(rows[i * B:(i + 1) * B], S, A)) for i in range(3, 6)]
+    assert tail == tail2
+    a, b = agent.state_dict(), fresh.state_dict()
+    assert all(torch.equal(a[k], b[k]) for k in a)
+    sched = (lambda ag: ag.goal_lr_schedule if kind == "por" else ag.lr_schedule)
+    assert sched(agent).get_last_lr() == sched(fresh).get_last_lr() and sched(fresh).last_epoch == 6
+    act = agent.select_action(rows[:5, :S])
+    assert act.shape == (5, S if kind == "por" else A) and np.isfinite(act).all()
