@@ -61,7 +61,8 @@ class ReplayBuffer:
         n = int(len(actions))
         if n > self.capacity:
             raise ValueError("batch larger than the buffer")
-        t = lambda a, dt: torch.as_tensor(np.asarray(a), dtype=dt).to(self.device)
+        t = lambda a, dt: (a.to(self.device, dt) if torch.is_tensor(a)
+                           else torch.as_tensor(np.asarray(a), dtype=dt).to(self.device))   # device tensors stay put
         pos = (self.position + torch.arange(n, device=self.device)) % self.capacity
         self._states[pos, :self.S] = t(states, torch.float32)
         self._next_states[pos, :self.S] = t(next_states, torch.float32)
