@@ -259,8 +259,8 @@ class Runner:
         self.agent.update_packed(self.pb)
 
     def capture(self):
-        """CUDA graph of gather + update on a static index buffer (single process only: the NCCL
-        all-reduce of the DP path stays outside graphs here)."""
+        """CUDA graph of gather + update on a static index buffer (single process, or DP with the gradient sum
+        fused into the Adam kernel; the NCCL all-reduce fallback stays outside graphs here)."""
         self.step(self.idx_static)                    # allocate workspaces outside capture
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
@@ -401,7 +401,8 @@ def run_b200(a):
     del rows
     runner = Runner(a, a.batch, device, rank, world, table)
     K, W = a.steps, max(a.warmup, 3)
-    use_graph = bool(a.graph) and not dist_on
+    peer_reduce = dist_on and all(g.peers is not None for g in (runner.agent.v_group, runner.agent.p_group))
+    use_graph = bool(a.graph) and (not dist_on or peer_reduce)   # the peer-sum Adam kernel is an ordinary launch
     if use_graph:
         runner.capture()
     idx_warm, idx_timed = runner.indices(W, 2000), runner.indices(K, 2001)
@@ -422,6 +423,9 @@ def run_b200(a):
                            "state_size": S, "hidden_dim": H, "parallelism": f"dp{world}" if dist_on else "single",
                            "contraction": "tcgen05 3xTF32" if a.gemm_mode == 1 else "fp32 FFMA",
                            "cuda_graph": use_graph, "inputs_larger_than_l2": True,
+                           "gradient_sum": ("none (single process)" if not dist_on else
+                                            "peer-memory loads fused into the Adam kernel (NVLink P2P)" if peer_reduce
+                                            else "NCCL all-reduce per optimizer group"),
                            "l2_note": "each step gathers fresh random rows of a 2.9 GB HBM table (>> 126 MB L2)"},
                 "clocks": clocks, "gpu_launches": launches * (1 if not use_graph else 1),
                 "final_losses": {"v_loss": v_loss, "g_loss": g_loss}}

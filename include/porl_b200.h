@@ -45,8 +45,9 @@ enum {
   PORL_FLAG_NONPOSITIVE_NLL = 2,  /* some per-sample NLL <= 0: where agent/por.py:104 drops into pdb */
   PORL_FLAG_BAD_INDEX = 4,        /* gather index outside [0, n_rows) (clamped) */
   PORL_FLAG_BAD_ACTION = 8,       /* discrete action outside [0, A) (clamped) */
-  PORL_FLAG_SCAN_RANGE = 16       /* scan value outside [0, 4.0001) u (8, inf): where state2costmap's scatter_ raises
+  PORL_FLAG_SCAN_RANGE = 16,      /* scan value outside [0, 4.0001) u (8, inf): where state2costmap's scatter_ raises
                                      (util/costmap.py:29); the beam is skipped */
+  PORL_FLAG_PEER_TIMEOUT = 32     /* a data-parallel peer did not signal within the wait budget (porl_adam_step_peer) */
 };
 
 typedef struct porl_ctx porl_ctx_t;
@@ -237,6 +238,44 @@ typedef struct {
 int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* m, float* v, int64_t n,
                    porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
                    float ema_beta, int32_t hard_every, porl_stream_t stream);
+
+/* ---- data-parallel step: gradient sum over NVLink peer memory fused into the Adam kernel ----
+ * (the reference has no distributed code.)  Every rank keeps its gradient bucket
+ * (n gradients | tail_floats loss scalars) in memory the other ranks of the node have mapped (CUDA IPC,
+ * NVLink P2P).  porl_adam_step_peer replaces   all_reduce(bucket); porl_adam_step(...)   by ONE kernel:
+ *   1. every rank tells every peer "my bucket of epoch e is complete" (st.release.sys into the peers' pads)
+ *      and waits for the same word from all of them,
+ *   2. each thread loads its gradient float4 from ALL ranks' buckets (own one included) and adds them in
+ *      rank order 0..world-1 -- the same order on every rank, so the replicas stay bitwise identical --
+ *      and runs the Adam / Polyak update of porl_adam_step on the sum; block 0 sums the tails into tail_out,
+ *   3. the last block tells the peers "I have read your bucket" and waits for theirs, so the kernel only
+ *      completes once nobody still reads this rank's bucket (the next backward may overwrite it).
+ * Traffic per rank: (world-1) * (n + tail) * 4 bytes over NVLink, no NCCL launch, no extra pass over HBM.
+ * A peer that never signals makes the kernel give up after wait_ms, set PORL_FLAG_PEER_TIMEOUT and finish. */
+#define PORL_MAX_PEERS 8
+#define PORL_PEER_PAD_WORDS (2 * PORL_MAX_PEERS)   /* ready[PORL_MAX_PEERS] | done[PORL_MAX_PEERS], zero-initialised */
+typedef struct porl_peer_group {
+  int32_t world, rank;
+  const float* bucket[PORL_MAX_PEERS];   /* bucket[r]: rank r's bucket as mapped in THIS process (bucket[rank] local) */
+  uint32_t* pad[PORL_MAX_PEERS];         /* pad[r]: rank r's signal pad, PORL_PEER_PAD_WORDS words */
+  uint32_t* epoch;                       /* local device word, zero-initialised, owned by this group */
+  float* tail_out;                       /* local: sum over ranks of the tails (tail_floats values) */
+  int32_t tail_floats;
+  int32_t wait_ms;                       /* give-up budget of each wait (0: 20000) */
+} porl_peer_group_t;
+
+/* device memory other processes of the node can map: cudaMalloc'ed (not from a pooled allocator), zero-filled */
+int porl_peer_alloc(porl_ctx_t* ctx, size_t bytes, void** out);
+int porl_peer_free(porl_ctx_t* ctx, void* ptr);
+/* handle: 64 opaque bytes (cudaIpcMemHandle_t) to send to the peers through any host channel */
+int porl_peer_export(porl_ctx_t* ctx, void* ptr, uint8_t handle[64]);
+/* maps a peer's allocation into this process (enables P2P access to its device); PORL_ERR_UNSUPPORTED when the
+ * two devices cannot reach each other */
+int porl_peer_open(porl_ctx_t* ctx, const uint8_t handle[64], void** out);
+int porl_peer_close(porl_ctx_t* ctx, void* ptr);
+int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_group_t* peers, float* m, float* v, int64_t n,
+                        porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
+                        float ema_beta, int32_t hard_every, porl_stream_t stream);
 
 /* ---- low-level contraction (exposed for tests and profiling) ------------------------------- */
 /* C[M,N] = opA(A)[M,K] * opB(B)[K,N] (+ bias[n]) with epilogue; trans flags:

@@ -44,6 +44,17 @@ class OptState(C.Structure):
                 ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
 
 
+MAX_PEERS = 8
+PEER_PAD_WORDS = 2 * MAX_PEERS
+FLAG_PEER_TIMEOUT = 32
+
+
+class PeerGroup(C.Structure):                      # porl_peer_group_t
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("bucket", C.c_void_p * MAX_PEERS),
+                ("pad", C.c_void_p * MAX_PEERS), ("epoch", C.c_void_p), ("tail_out", C.c_void_p),
+                ("tail_floats", C.c_int32), ("wait_ms", C.c_int32)]
+
+
 CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head", "encoder", "batchnorm", "pconv")
 
 
@@ -101,6 +112,12 @@ _SIGNATURES = {
                                      _p, _p, _p, _p]),
     "porl_cql_head": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _f, _f, _i64, _i32, _i64, _p, _p, _p]),
     "porl_adam_step": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
+    "porl_adam_step_peer": (C.c_int, [_p, _p, C.POINTER(PeerGroup), _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
+    "porl_peer_alloc": (C.c_int, [_p, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "porl_peer_free": (C.c_int, [_p, _p]),
+    "porl_peer_export": (C.c_int, [_p, _p, C.c_char_p]),
+    "porl_peer_open": (C.c_int, [_p, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "porl_peer_close": (C.c_int, [_p, _p]),
     "porl_gemm": (C.c_int, [_p, _i32, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p, _i64,
                             _i64, _p, _p, _i64, _p]),
     "porl_transpose": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p]),

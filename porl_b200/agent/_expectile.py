@@ -151,7 +151,6 @@ class ExpectileAgent(nn.Module):
             pb.rewards.data_ptr(), pb.dones.data_ptr(), self.discount, self.tau, B, b_norm, target_v.data_ptr(),
             dv.data_ptr(), dv.data_ptr() + net, self.v_group.loss_ptr, _C.stream_ptr()))
         mlp_backward(ctx, call_v, B, dv, self.v_group.grads)
-        pdist.allreduce_sum_(self.v_group.bucket)
         self.v_group.step(target=self._target.flat, ema_beta=self.beta)
 
     def _policy_step(self, pb: PackedBatch, x_obs, ld_obs, x: torch.Tensor, ld_x: int) -> None:
@@ -176,7 +175,6 @@ class ExpectileAgent(nn.Module):
             self._awr_mode, int(self._bounded), B, self.policy_out, b_norm, dz_p.data_ptr(),
             self.p_group.grads.data_ptr() + off, self.p_group.loss_ptr, _C.stream_ptr()))
         mlp_backward(ctx, call_p, B, dz_p, self.p_group.grads)
-        pdist.allreduce_sum_(self.p_group.bucket)
         self.p_group.step()
 
     def _policy_target(self, pb: PackedBatch):
@@ -227,5 +225,7 @@ class ExpectileAgent(nn.Module):
             if flags & _C.FLAG_SCAN_RANGE:
                 msgs.append("scan value outside [0, 4.0001) u (8, inf): state2costmap's scatter_ raises here "
                             "(util/costmap.py:29)")
+            if flags & _C.FLAG_PEER_TIMEOUT:
+                msgs.append("a data-parallel peer did not signal its gradient bucket in time (porl_adam_step_peer)")
             raise FloatingPointError("; ".join(msgs) or f"device status {flags}")
         return float(self._host[0]), float(self._host[1])

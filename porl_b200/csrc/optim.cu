@@ -5,6 +5,7 @@
 // float4 accesses, grid-stride, one pass.  The scalar maths follows torch/optim/adam.py
 // (_single_tensor_adam): bias corrections and step size in double, per-element work in fp32.
 #include <math.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -38,14 +39,78 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
   p = p - s.step_size * (m / denom);                  // addcdiv_(exp_avg, denom, value=-step_size)
 }
 
+// ---- peer-memory gradient sum (data parallel): signalling words live in every rank's pad ----
+struct PeerArgs {
+  int world, rank;
+  const float* bucket[PORL_MAX_PEERS];
+  uint32_t* pad[PORL_MAX_PEERS];
+  uint32_t* epoch;
+  float* tail_out;
+  int tail_floats;
+  unsigned long long wait_ns;
+  uint32_t* status;
+};
+
+__device__ __forceinline__ void peer_signal(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t peer_poll(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// spins until *addr has reached `epoch` (wrap-safe); gives up after wait_ns and raises the status flag
+__device__ __forceinline__ void peer_wait(const uint32_t* addr, uint32_t epoch, unsigned long long wait_ns,
+                                          uint32_t* status) {
+  if ((int)(peer_poll(addr) - epoch) >= 0) return;
+  const unsigned long long t0 = global_ns();
+  while ((int)(peer_poll(addr) - epoch) < 0) {
+    __nanosleep(64);
+    if (global_ns() - t0 > wait_ns) {
+      atomicOr(status, (uint32_t)PORL_FLAG_PEER_TIMEOUT);
+      return;
+    }
+  }
+}
+// gradients of the peers change between launches at fixed addresses: read them around L1
+__device__ __forceinline__ float4 peer_load4(const float* base, int64_t i4) {
+  return __ldcv(reinterpret_cast<const float4*>(base) + i4);
+}
+
+template <bool PEER>
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
             float* __restrict__ v, int64_t n, porl_opt_state_t* st, float beta1, float beta2, float eps,
-            float* __restrict__ target, float ema_beta, int hard_every) {
+            float* __restrict__ target, float ema_beta, int hard_every, const PeerArgs peers) {
   __shared__ AdamScalars sh;
-  if (threadIdx.x == 0) sh = adam_scalars(st, beta1, beta2, hard_every);
+  __shared__ uint32_t sh_epoch;
+  if (threadIdx.x == 0) {
+    sh = adam_scalars(st, beta1, beta2, hard_every);
+    if (PEER) sh_epoch = *reinterpret_cast<volatile uint32_t*>(peers.epoch) + 1u;
+  }
   __syncthreads();
   const AdamScalars s = sh;
+  if (PEER) {
+    // 1. "my bucket of this epoch is complete" -> every rank's pad (own one included); every block then waits for
+    //    all ranks' words in ITS OWN rank's pad, so no block depends on another block of the same grid.
+    const uint32_t e = sh_epoch;
+    if (blockIdx.x == 0 && threadIdx.x < peers.world) {
+      __threadfence_system();
+      peer_signal(peers.pad[threadIdx.x] + peers.rank, e);
+    }
+    if (threadIdx.x < peers.world) peer_wait(peers.pad[peers.rank] + threadIdx.x, e, peers.wait_ns, peers.status);
+    __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x < peers.tail_floats) {
+      float t = 0.f;
+      for (int r = 0; r < peers.world; ++r) t += __ldcv(peers.bucket[r] + n + threadIdx.x);
+      peers.tail_out[threadIdx.x] = t;
+    }
+  }
   const bool ema = (target != nullptr) && ema_beta > 0.f;
   const bool hard = (target != nullptr) && s.do_hard;
   const float keep = 1.f - ema_beta;
@@ -59,7 +124,19 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   float4* t4 = reinterpret_cast<float4*>(target);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pp = p4[i], mm = m4[i], vv = v4[i];
-    const float4 gg = g4[i];
+    float4 gg;
+    if (PEER) {
+      float4 gr[PORL_MAX_PEERS];
+#pragma unroll
+      for (int r = 0; r < PORL_MAX_PEERS; ++r)
+        if (r < peers.world) gr[r] = peer_load4(peers.bucket[r], i);
+      gg = gr[0];
+#pragma unroll
+      for (int r = 1; r < PORL_MAX_PEERS; ++r)
+        if (r < peers.world) { gg.x += gr[r].x; gg.y += gr[r].y; gg.z += gr[r].z; gg.w += gr[r].w; }
+    } else {
+      gg = g4[i];
+    }
     adam_elem(pp.x, gg.x, mm.x, vv.x, s, beta1, beta2, eps);
     adam_elem(pp.y, gg.y, mm.y, vv.y, s, beta1, beta2, eps);
     adam_elem(pp.z, gg.z, mm.z, vv.z, s, beta1, beta2, eps);
@@ -79,7 +156,14 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   // tail (n not a multiple of 4)
   for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     float pp = p[i], mm = m[i], vv = v[i];
-    adam_elem(pp, g[i], mm, vv, s, beta1, beta2, eps);
+    float gi;
+    if (PEER) {
+      gi = __ldcv(peers.bucket[0] + i);
+      for (int r = 1; r < peers.world; ++r) gi += __ldcv(peers.bucket[r] + i);
+    } else {
+      gi = g[i];
+    }
+    adam_elem(pp, gi, mm, vv, s, beta1, beta2, eps);
     p[i] = pp; m[i] = mm; v[i] = vv;
     if (ema) target[i] = fmaf(ema_beta, pp, target[i] * keep);
     else if (hard) target[i] = pp;
@@ -105,7 +189,19 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
         st->lr = lr;
       }
       st->step = e;
+      if (PEER) *reinterpret_cast<volatile uint32_t*>(peers.epoch) = sh_epoch;
       __threadfence();
+    }
+    if (PEER) sh.do_hard = (ticket == gridDim.x - 1);      // reuse as "this block closes the launch"
+  }
+  if (PEER) {
+    // 3. the closing block: "I have read your buckets" to every rank, then wait until every rank has read mine
+    __syncthreads();
+    if (sh.do_hard && threadIdx.x < peers.world) {
+      const uint32_t e = sh_epoch;
+      __threadfence_system();
+      peer_signal(peers.pad[threadIdx.x] + PORL_MAX_PEERS + peers.rank, e);
+      peer_wait(peers.pad[peers.rank] + PORL_MAX_PEERS + threadIdx.x, e, peers.wait_ns, peers.status);
     }
   }
 }
@@ -127,8 +223,93 @@ extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* 
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * (target ? 36.0 : 28.0), as_stream(stream));
-  adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, state_dev, beta1, beta2, eps,
-                                                          target, ema_beta, hard_every);
+  adam_kernel<false><<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, state_dev, beta1, beta2, eps,
+                                                                 target, ema_beta, hard_every, PeerArgs{});
   PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+extern "C" int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_group_t* pg, float* m, float* v,
+                                   int64_t n, porl_opt_state_t* state_dev, float beta1, float beta2, float eps,
+                                   float* target, float ema_beta, int32_t hard_every, porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && p && pg && m && v && state_dev, "porl_adam_step_peer: null argument");
+  PORL_CHECK_ARG(n > 0 && (n & 3) == 0, "porl_adam_step_peer: n=%lld must be a positive multiple of 4", (long long)n);
+  PORL_CHECK_ARG(pg->world >= 1 && pg->world <= PORL_MAX_PEERS && pg->rank >= 0 && pg->rank < pg->world,
+                 "porl_adam_step_peer: world=%d rank=%d", pg->world, pg->rank);
+  PORL_CHECK_ARG(pg->epoch && pg->tail_floats >= 0 && pg->tail_floats <= 256 && (pg->tail_floats == 0 || pg->tail_out),
+                 "porl_adam_step_peer: epoch / tail_out missing or tail_floats=%d outside [0, 256]", pg->tail_floats);
+  PORL_CHECK_ARG(aligned16(p) && aligned16(m) && aligned16(v) && (!target || aligned16(target)),
+                 "porl_adam_step_peer: buffers must be 16-byte aligned");
+  PORL_CHECK_ARG(!(ema_beta > 0.f && hard_every > 0), "porl_adam_step_peer: choose Polyak or hard target update");
+  PeerArgs a{};
+  a.world = pg->world;
+  a.rank = pg->rank;
+  for (int r = 0; r < pg->world; ++r) {
+    PORL_CHECK_ARG(pg->bucket[r] && pg->pad[r] && aligned16(pg->bucket[r]), "porl_adam_step_peer: bucket/pad of rank %d", r);
+    a.bucket[r] = pg->bucket[r];
+    a.pad[r] = pg->pad[r];
+  }
+  a.epoch = pg->epoch;
+  a.tail_out = pg->tail_out;
+  a.tail_floats = pg->tail_floats;
+  a.wait_ns = (unsigned long long)(pg->wait_ms > 0 ? pg->wait_ms : 20000) * 1000000ull;
+  a.status = ctx->counters;
+  int64_t blocks = ((n >> 2) + 255) / 256;
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * ((target ? 32.0 : 24.0) + 4.0 * pg->world), as_stream(stream));
+  adam_kernel<true><<<(int)blocks, 256, 0, as_stream(stream)>>>(p, pg->bucket[pg->rank], m, v, n, state_dev, beta1,
+                                                                beta2, eps, target, ema_beta, hard_every, a);
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+// ---- peer-mappable allocations (CUDA IPC) ----
+extern "C" int porl_peer_alloc(porl_ctx_t* ctx, size_t bytes, void** out) {
+  PORL_CHECK_ARG(ctx && out && bytes > 0, "porl_peer_alloc: null argument or zero size");
+  PORL_CUDA(cudaSetDevice(ctx->device));
+  void* ptr = nullptr;
+  PORL_CUDA(cudaMalloc(&ptr, bytes));
+  PORL_CUDA(cudaMemset(ptr, 0, bytes));
+  PORL_CUDA(cudaDeviceSynchronize());
+  *out = ptr;
+  return PORL_OK;
+}
+
+extern "C" int porl_peer_free(porl_ctx_t* ctx, void* ptr) {
+  PORL_CHECK_ARG(ctx, "porl_peer_free: null context");
+  if (ptr) PORL_CUDA(cudaFree(ptr));
+  return PORL_OK;
+}
+
+extern "C" int porl_peer_export(porl_ctx_t* ctx, void* ptr, uint8_t handle[64]) {
+  PORL_CHECK_ARG(ctx && ptr && handle, "porl_peer_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  cudaIpcMemHandle_t h;
+  PORL_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle, &h, 64);
+  return PORL_OK;
+}
+
+extern "C" int porl_peer_open(porl_ctx_t* ctx, const uint8_t handle[64], void** out) {
+  PORL_CHECK_ARG(ctx && handle && out, "porl_peer_open: null argument");
+  PORL_CUDA(cudaSetDevice(ctx->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  void* ptr = nullptr;
+  const cudaError_t err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+  if (err == cudaErrorPeerAccessUnsupported || err == cudaErrorInvalidDevice) {
+    cudaGetLastError();
+    set_error("porl_peer_open: the peer's device is not reachable from device %d (%s)", ctx->device, cudaGetErrorString(err));
+    return PORL_ERR_UNSUPPORTED;
+  }
+  PORL_CUDA(err);
+  *out = ptr;
+  return PORL_OK;
+}
+
+extern "C" int porl_peer_close(porl_ctx_t* ctx, void* ptr) {
+  PORL_CHECK_ARG(ctx, "porl_peer_close: null context");
+  if (ptr) PORL_CUDA(cudaIpcCloseMemHandle(ptr));
   return PORL_OK;
 }

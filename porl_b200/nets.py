@@ -12,12 +12,14 @@ PyTorch here is plumbing (allocation, views, checkpoint I/O); all arithmetic run
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Sequence
 
 import torch
 from torch import nn
 
 from . import _C
+from . import dist as pdist
 from ._C import check, lib
 
 GRAD_TAIL = 8  # floats after the gradients in a group's bucket: [loss, aux...] ride the DP all-reduce
@@ -86,13 +88,39 @@ class ParamGroup:
         self.n = pad_to(n_floats, 4)
         z = lambda k: torch.zeros(k, dtype=torch.float32, device=self.device)
         self.params, self.m, self.v = z(self.n), z(self.n), z(self.n)
-        self.bucket = z(self.n + GRAD_TAIL)          # gradients | loss tail
+        self.peers = None
+        self.bucket = None
+        if pdist.is_dp() and self.device.type == "cuda" and os.environ.get("PORL_PEER_REDUCE", "1") != "0":
+            self._init_peers()
+        if self.bucket is None:
+            self.bucket = z(self.n + GRAD_TAIL)      # gradients | loss tail
         self.grads = self.bucket[:self.n]
-        self.tail = self.bucket[self.n:]
+        self._local_tail = self.bucket[self.n:]
         self.betas, self.eps = betas, eps
         self.base_lr, self.t_max = float(lr), int(t_max)
         self.state = torch.zeros(C.sizeof(_C.OptState), dtype=torch.uint8, device=self.device)
         self.reset_clock(step=0, lr=float(lr))
+
+    def _init_peers(self) -> None:
+        """Collective (every rank builds its groups in the same order): put the bucket in peer-mappable memory and
+        map the other ranks' buckets, so that `step()` sums the gradients inside the Adam kernel
+        (porl_adam_step_peer).  Falls back to the NCCL all-reduce for big buckets or without a P2P path."""
+        from . import peer
+
+        world = pdist.world_size()
+        nbytes = (self.n + GRAD_TAIL) * 4
+        if world > _C.MAX_PEERS or (world - 1) * nbytes > peer.MAX_PEER_READ_BYTES:
+            return
+        bucket = peer.PeerBuffer(self.ctx, nbytes)
+        pad = peer.PeerBuffer(self.ctx, _C.PEER_PAD_WORDS * 4)
+        self.peers = peer.exchange(self.ctx, bucket, pad, GRAD_TAIL)
+        if self.peers is not None:
+            self.bucket = bucket.tensor(torch.float32)
+
+    @property
+    def tail(self) -> torch.Tensor:
+        """[loss, aux...] of the last update, summed over ranks once `step()` has run."""
+        return self.peers.tail_out if self.peers is not None else self._local_tail
 
     def reset_clock(self, step: int, lr: float) -> None:
         st = _C.OptState(step=step, lr=lr, base_lr=self.base_lr, t_max=self.t_max, blocks_done=0, pad_=0)
@@ -106,9 +134,19 @@ class ParamGroup:
 
     @property
     def loss_ptr(self) -> int:
-        return self.tail.data_ptr()
+        return self._local_tail.data_ptr()
 
     def step(self, target: torch.Tensor | None = None, ema_beta: float = 0.0, hard_every: int = 0) -> None:
+        """Sum the bucket over the data-parallel ranks, then Adam (+ target update).  With peer-mapped buckets both
+        happen in one kernel; otherwise one NCCL all-reduce precedes the single-rank kernel."""
+        tgt = target.data_ptr() if target is not None else None
+        if self.peers is not None:
+            check(lib.porl_adam_step_peer(self.ctx.handle, self.params.data_ptr(), C.byref(self.peers.struct),
+                                          self.m.data_ptr(), self.v.data_ptr(), self.n, self.state.data_ptr(),
+                                          self.betas[0], self.betas[1], self.eps, tgt, ema_beta, hard_every,
+                                          _C.stream_ptr()))
+            return
+        pdist.allreduce_sum_(self.bucket)
         check(lib.porl_adam_step(self.ctx.handle, self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
                                  self.v.data_ptr(), self.n, self.state.data_ptr(), self.betas[0], self.betas[1],
                                  self.eps, target.data_ptr() if target is not None else None, ema_beta,

@@ -71,7 +71,6 @@ class DQNTrainer:
                                 self.action_size, B * pdist.world_size(), dq.data_ptr(), self.q_group.loss_ptr,
                                 _C.stream_ptr()))
         mlp_backward(ctx, call_q, B, dq, self.q_group.grads)
-        pdist.allreduce_sum_(self.q_group.bucket)
         self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)
 
     def read_losses(self) -> tuple[float, float, float]:

@@ -360,6 +360,80 @@ def test_adam_matches_torch(env, n, t_max, ema, hard):
     assert float(grp.params[n:].abs().sum()) == 0.0      # padding stays zero
 
 
+@pytest.mark.parametrize("world,n", [(2, 4096), (3, 1028), (8, 2048), (1, 512)])
+def test_adam_peer_sum_equals_presummed_adam(env, world, n):
+    """porl_adam_step_peer: `world` replicas on `world` streams of ONE device (their buckets stand in for
+    peer-mapped memory; grids small enough to be co-resident).  Each replica must end up bitwise equal to
+    porl_adam_step on the gradients summed in rank order, the tails must add up, and six consecutive epochs
+    exercise both handshakes."""
+    from porl_b200.nets import ParamGroup, GRAD_TAIL
+    from porl_b200.peer import PeerReduce
+    _C, ctx, dev = env
+    g = torch.Generator().manual_seed(world * 100 + n)
+    p0 = torch.randn(n, generator=g).to(dev)
+    ref = ParamGroup(ctx, n, dev, lr=1e-3, t_max=5)
+    ref.params.copy_(p0)
+    ref_t = torch.zeros(n, device=dev)
+    reps = [ParamGroup(ctx, n, dev, lr=1e-3, t_max=5) for _ in range(world)]
+    tgts = [torch.zeros(n, device=dev) for _ in range(world)]
+    pads = [torch.zeros(_C.PEER_PAD_WORDS, dtype=torch.int32, device=dev) for _ in range(world)]
+    for r, grp in enumerate(reps):
+        grp.params.copy_(p0)
+        grp.peers = PeerReduce(ctx, r, [q.bucket.data_ptr() for q in reps], [q.data_ptr() for q in pads],
+                               GRAD_TAIL, wait_ms=5000)
+    streams = [torch.cuda.Stream(dev) for _ in range(world)]
+    for epoch in range(6):
+        grads = [torch.randn(n + GRAD_TAIL, generator=g).to(dev) for _ in range(world)]
+        total = grads[0].clone()
+        for r in range(1, world):
+            total += grads[r]
+        for r, grp in enumerate(reps):
+            grp.bucket.copy_(grads[r])
+        ref.bucket.copy_(total)
+        torch.cuda.synchronize()
+        for r in reversed(range(world)):                      # launch order != rank order
+            with torch.cuda.stream(streams[r]):
+                reps[r].step(target=tgts[r], ema_beta=0.005)
+        ref.step(target=ref_t, ema_beta=0.005)
+        torch.cuda.synchronize()
+        assert int(ctx.status_tensor()[0]) & _C.FLAG_PEER_TIMEOUT == 0
+        for r, grp in enumerate(reps):
+            assert torch.equal(grp.params, ref.params), (epoch, r)
+            assert torch.equal(tgts[r], ref_t)
+            assert torch.equal(grp.tail, total[n:])
+            assert torch.equal(grp.bucket, grads[r])          # the bucket itself is only read
+    assert all(grp.read_clock().step == 6 for grp in reps)
+
+
+def test_adam_peer_timeout_sets_flag_and_returns(env):
+    """A peer that never signals: the kernel gives up after wait_ms, raises PORL_FLAG_PEER_TIMEOUT, finishes."""
+    from porl_b200.nets import ParamGroup, GRAD_TAIL
+    from porl_b200.peer import PeerReduce
+    _C, ctx, dev = env
+    n = 256
+    grp, other = ParamGroup(ctx, n, dev, lr=1e-3), ParamGroup(ctx, n, dev, lr=1e-3)
+    pads = [torch.zeros(_C.PEER_PAD_WORDS, dtype=torch.int32, device=dev) for _ in range(2)]
+    grp.peers = PeerReduce(ctx, 0, [grp.bucket.data_ptr(), other.bucket.data_ptr()], [q.data_ptr() for q in pads],
+                           GRAD_TAIL, wait_ms=50)
+    status = ctx.status_tensor()
+    status.zero_()
+    grp.step()
+    torch.cuda.synchronize()
+    assert int(status[0]) & _C.FLAG_PEER_TIMEOUT
+    status.zero_()
+
+
+def test_peer_buffer_alloc_view_export(env):
+    from porl_b200.peer import PeerBuffer
+    _C, ctx, dev = env
+    buf = PeerBuffer(ctx, 4096)
+    t = buf.tensor(torch.float32)
+    assert t.shape == (1024,) and t.data_ptr() == buf.ptr and float(t.abs().sum()) == 0.0
+    t.fill_(3.0)
+    assert float(buf.tensor(torch.float32)[5]) == 3.0
+    assert len(buf.handle()) == 64
+
+
 # ------------------------------------------------------------------------------------------ K2 / K3
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("dims,n_nets,ln,tanh,B", [

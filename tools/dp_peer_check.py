@@ -1,0 +1,76 @@
+"""2+ GPU check of the peer-memory gradient sum (porl_adam_step_peer) against the NCCL all-reduce path.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        -m tools.dp_peer_check [steps]
+
+Both agents start from the same weights and see the same sharded minibatches.  Checks: (1) the peer path is
+active, (2) replicas stay BITWISE identical across ranks, (3) parameters / losses agree with the NCCL path to
+summation-order accuracy, (4) no timeout flag; then times both (eager and, for the peer path, graph replay).
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from porl_b200 import TransitionDataset, dist as pdist  # noqa: E402
+
+
+def build(a, device, rank, world, table, peer):
+    os.environ["PORL_PEER_REDUCE"] = "1" if peer else "0"
+    return bench.Runner(a, a.batch, device, rank, world, table)
+
+
+def main():
+    steps = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+    sys.argv = sys.argv[:1]
+    a = bench.parse()
+    a.rows = 200000
+    rank, local, world = pdist.init_from_env()
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    rows = bench.synth_rows_torch(a.rows, device, 20260102)
+    table = TransitionDataset(rows, bench.S, bench.A, device)
+    rp = build(a, device, rank, world, table, True)
+    rn = build(a, device, rank, world, table, False)
+    groups = lambda r: (r.agent.v_group, r.agent.p_group)
+    assert all(g.peers is not None for g in groups(rp)), "peer path not active"
+    assert all(g.peers is None for g in groups(rn))
+    idx = rp.indices(steps, 77)
+    rp.run(idx)
+    rn.run(idx)
+    lp, ln = rp.agent.read_losses(), rn.agent.read_losses()
+    worst = 0.0
+    for gp, gn in zip(groups(rp), groups(rn)):
+        rel = float((gp.params.double() - gn.params.double()).norm() / gn.params.double().norm())
+        worst = max(worst, rel)
+        gathered = [torch.empty_like(gp.params) for _ in range(world)]
+        dist.all_gather(gathered, gp.params)
+        assert all(torch.equal(gathered[0], t) for t in gathered), "replicas diverged bitwise"
+    assert worst < 2e-5, worst
+    assert abs(lp[0] - ln[0]) <= 2e-5 * abs(ln[0]) and abs(lp[1] - ln[1]) <= 2e-5 * abs(ln[1]), (lp, ln)
+
+    def rate(r, n=200):
+        ii = r.indices(n, 78)
+        ms, _ = bench.timed(r, ii[:10], ii, True)
+        return world * n / (ms * 1e-3)
+
+    eager_peer, eager_nccl = rate(rp), rate(rn)
+    rp.capture()
+    graph_peer = rate(rp)
+    rp.agent.read_losses()                                   # raises on PORL_FLAG_PEER_TIMEOUT
+    if rank == 0:
+        print(f"world {world}: after {steps} updates params rel-L2 peer vs nccl {worst:.2e}; losses {lp} vs {ln}; "
+              f"replicas bitwise identical")
+        print(f"updates/s (batch {a.batch}/GPU): nccl eager {eager_nccl:.0f} | peer eager {eager_peer:.0f} | "
+              f"peer graph {graph_peer:.0f}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
