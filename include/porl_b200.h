@@ -353,6 +353,73 @@ int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* net, float* 
                            int64_t B, float* features, int64_t ld_feat, float* workspace,
                            int64_t workspace_floats, porl_stream_t stream);
 
+/* ---- PointMLP scan encoder (agent/feature_pcl.py), forward in train mode -----------------------
+ * PointMLPModel.forward (feature_pcl.py:407-420): embedding Conv1d(3,E)-BN-ReLU, then per stage
+ *   LocalGrouper (feature_pcl.py:204-229): farthest-point sampling of S anchors (:69-89), k nearest neighbours by
+ *     square_distance + top-k (:28-48, :163-174), gather, "center"/"anchor" normalisation by the per-sample std,
+ *     affine, concat with the repeated anchor feature -> (B*S*k, 2C [+3]) rows,
+ *   PreExtraction (:304-333): Conv-BN-ReLU transfer + residual Conv-BN-ReLU blocks over those rows, max over k,
+ *   PosExtraction (:336-355): residual blocks over the (B*S, C') rows,
+ * global max over the anchors and the classifier Linear-BN-ReLU-Dropout x2 + Linear (:392-402).
+ * Activations are row-major (rows, channels) matrices; every Conv1d(k=1) / Linear is a K-major contraction.
+ * BatchNorm1d uses batch statistics (training mode) and updates running_mean / running_var in place.
+ * groups = 1 and ReLU only (the reference's defaults).  Single process (no cross-rank statistics). */
+typedef struct porl_pm_conv {
+  const float* weight;   /* (c_out, ld_w): Conv1d weight (c_out, c_in, 1) with rows padded to ld_w = pad4(c_in) */
+  const float* bias;     /* (pad4(c_out)) or null (bias=False) */
+  porl_bn_t bn;
+} porl_pm_conv_t;
+
+typedef struct porl_pm_res {   /* ConvBNReLURes1D (feature_pcl.py:263-301), groups = 1 */
+  porl_pm_conv_t net1, net2;
+  int32_t c_mid, pad_;   /* int(channel * res_expansion) */
+} porl_pm_res_t;
+
+#define PORL_PM_MAX_STAGES 4
+#define PORL_PM_MAX_BLOCKS 4
+typedef struct porl_pm_stage {
+  int32_t anchors, k;              /* S and kneighbors */
+  int32_t c_in, c_out;
+  const float* affine_alpha;       /* (c_in [+3]) or null when normalize is off */
+  const float* affine_beta;
+  porl_pm_conv_t transfer;         /* in: 2 c_in [+3] (ld_w = pad4 of it) -> c_out */
+  int32_t n_pre, n_pos;
+  porl_pm_res_t pre[PORL_PM_MAX_BLOCKS], pos[PORL_PM_MAX_BLOCKS];
+} porl_pm_stage_t;
+
+typedef struct porl_pointmlp {
+  int32_t points, embed_dim, n_stages, use_xyz;
+  int32_t normalize;               /* 0 none, 1 center, 2 anchor */
+  int32_t class_num, pad0_, pad1_;
+  porl_pm_conv_t embedding;        /* weight (embed_dim, 4): Conv1d(3, E) rows padded to 4 */
+  porl_pm_stage_t stage[PORL_PM_MAX_STAGES];
+  const float *fc1_w, *fc1_b;      /* (512, C_last), (512) */
+  porl_bn_t bn1;
+  const float *fc2_w, *fc2_b;      /* (256, 512), (256) */
+  porl_bn_t bn2;
+  const float *fc3_w, *fc3_b;      /* (class_num, 256), (pad4(class_num)) */
+  const float *drop1, *drop2;      /* (B, 512), (B, 256) multipliers mask / (1 - p) of nn.Dropout, or null */
+} porl_pointmlp_t;
+
+/* floats of workspace porl_pointmlp_forward needs for batch B (< 0: invalid configuration) */
+int64_t porl_pointmlp_workspace_floats(const porl_pointmlp_t* net, int64_t B);
+/* x: (B, 3, points) as the reference passes it (feature_pcl.py:408); fps_start: (n_stages, B) int64, the index
+ * each sample's farthest-point sampling starts from (the reference draws it with torch.randint, :81);
+ * out: (B, ld_out) receives class_num features per row. */
+int porl_pointmlp_forward(porl_ctx_t* ctx, const porl_pointmlp_t* net, const float* x, const int64_t* fps_start,
+                          int64_t B, float* out, int64_t ld_out, float* workspace, int64_t workspace_floats,
+                          porl_stream_t stream);
+/* the building blocks, exposed for tests: xyz (B, N, 3) row-major.
+ * porl_fps: idx (B, npoint) int32, bit-identical to farthest_point_sample on the same start indices.
+ * porl_knn: idx (B, S, k) int32: the k points nearest to each query (ascending distance, ties by index). */
+int porl_fps(porl_ctx_t* ctx, const float* xyz, int64_t B, int32_t N, int32_t npoint, const int64_t* start,
+             int32_t* idx, porl_stream_t stream);
+int porl_knn(porl_ctx_t* ctx, const float* xyz, const float* query, int64_t B, int32_t N, int32_t S, int32_t k,
+             int32_t* idx, porl_stream_t stream);
+/* (B, 362) laser-scan states -> (B, 3, 361) point sets: beam i -> (r cos i deg, r sin i deg, 0) with r > 8 (no
+ * return) collapsed to 0 as util/costmap.py:17 does, goal -> (gx, gy, 1): the intent of feature_pcl.py:113-138 */
+int porl_scan_to_points(porl_ctx_t* ctx, const float* state, int64_t ld_state, int64_t B, float* out, porl_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,13 @@ def sorl_cls():
     return SORL
 
 
+def pointmlp_module():
+    """agent.feature_pcl of the reference (PointMLPModel and its helpers)."""
+    prepare()
+    import agent.feature_pcl as m
+    return m
+
+
 def replay_buffer_cls():
     prepare()
     from porl.buffer.replaybuffer import ReplayBuffer

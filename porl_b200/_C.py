@@ -82,6 +82,32 @@ class FasterNetParams(C.Structure):                # porl_fasternet_t
 ALLREDUCE_F64_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p)   # porl_allreduce_f64_fn
 
 
+PM_MAX_STAGES, PM_MAX_BLOCKS = 4, 4
+
+
+class PmConv(C.Structure):                         # porl_pm_conv_t
+    _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("bn", BnParams)]
+
+
+class PmRes(C.Structure):                          # porl_pm_res_t
+    _fields_ = [("net1", PmConv), ("net2", PmConv), ("c_mid", C.c_int32), ("pad_", C.c_int32)]
+
+
+class PmStage(C.Structure):                        # porl_pm_stage_t
+    _fields_ = [("anchors", C.c_int32), ("k", C.c_int32), ("c_in", C.c_int32), ("c_out", C.c_int32),
+                ("affine_alpha", C.c_void_p), ("affine_beta", C.c_void_p), ("transfer", PmConv),
+                ("n_pre", C.c_int32), ("n_pos", C.c_int32), ("pre", PmRes * PM_MAX_BLOCKS), ("pos", PmRes * PM_MAX_BLOCKS)]
+
+
+class PointMlpParams(C.Structure):                 # porl_pointmlp_t
+    _fields_ = [("points", C.c_int32), ("embed_dim", C.c_int32), ("n_stages", C.c_int32), ("use_xyz", C.c_int32),
+                ("normalize", C.c_int32), ("class_num", C.c_int32), ("pad0_", C.c_int32), ("pad1_", C.c_int32),
+                ("embedding", PmConv), ("stage", PmStage * PM_MAX_STAGES),
+                ("fc1_w", C.c_void_p), ("fc1_b", C.c_void_p), ("bn1", BnParams),
+                ("fc2_w", C.c_void_p), ("fc2_b", C.c_void_p), ("bn2", BnParams),
+                ("fc3_w", C.c_void_p), ("fc3_b", C.c_void_p), ("drop1", C.c_void_p), ("drop2", C.c_void_p)]
+
+
 _SIGNATURES = {
     "porl_version": (C.c_int, []),
     "porl_last_error": (C.c_char_p, []),
@@ -112,6 +138,11 @@ _SIGNATURES = {
                                      _p, _p, _p, _p]),
     "porl_cql_head": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _f, _f, _i64, _i32, _i64, _p, _p, _p]),
     "porl_adam_step": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
+    "porl_pointmlp_workspace_floats": (_i64, [C.POINTER(PointMlpParams), _i64]),
+    "porl_pointmlp_forward": (C.c_int, [_p, C.POINTER(PointMlpParams), _p, _p, _i64, _p, _i64, _p, _i64, _p]),
+    "porl_fps": (C.c_int, [_p, _p, _i64, _i32, _i32, _p, _p, _p]),
+    "porl_knn": (C.c_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p]),
+    "porl_scan_to_points": (C.c_int, [_p, _p, _i64, _i64, _p, _p]),
     "porl_adam_step_peer": (C.c_int, [_p, _p, C.POINTER(PeerGroup), _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
     "porl_peer_alloc": (C.c_int, [_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "porl_peer_free": (C.c_int, [_p, _p]),

@@ -137,8 +137,102 @@ def run_encoder(seed, B):
     return out
 
 
+PM_CASES = {   # name: (seed, B, model kwargs)
+    "a": (61, 8, dict(points=64, class_num=10, embed_dim=8, k_neighbors=[8, 8, 8, 8])),                # defaults: center, xyz
+    "b": (62, 6, dict(points=48, class_num=7, embed_dim=8, k_neighbors=[6, 6], reducers=[2, 2], dim_expansion=[2, 2],
+                      pre_blocks=[1, 2], pos_blocks=[2, 1], normalize="anchor", use_xyz=False, bias=False,
+                      res_expansion=0.5)),
+}
+
+
+def pointmlp_inputs(seed, B, points):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.rand(B, 3, points, generator=g) * 4 - 2
+    x[:, 2] = (torch.rand(B, points, generator=g) < 0.1).float()      # a flag-like third coordinate
+    return x
+
+
+def run_pointmlp(name):
+    """The unmodified reference PointMLPModel in train mode.  Its two random draws are replayed from recorded
+    values: torch.randint (FPS start, feature_pcl.py:81) and the classifier's Dropout masks."""
+    from oracle import pointmlp
+    seed, B, kw = PM_CASES[name]
+    rm = refimport.pointmlp_module()
+    torch.manual_seed(seed)
+    m = rm.PointMLPModel(**kw)
+    keys = list(m.state_dict().keys())
+    m.load_state_dict(pointmlp.randomize_(m.state_dict(), seed + 1))
+    sd0 = {k: v.clone() for k, v in m.state_dict().items()}
+    x = pointmlp_inputs(seed, B, kw["points"])
+    n_stages = len(kw["k_neighbors"])
+    g = torch.Generator().manual_seed(seed + 2)
+    anchors, starts = kw["points"], []
+    for red in kw.get("reducers", [2, 2, 2, 2]):
+        starts.append(torch.randint(0, anchors, (B,), generator=g))
+        anchors //= red
+    starts = torch.stack(starts)
+    drops = [torch.bernoulli(torch.full((B, w), 0.5), generator=g) / 0.5 for w in (512, 256)]
+    queue, dq = list(starts), list(drops)
+    orig_randint, orig_dropout = torch.randint, torch.nn.functional.dropout
+
+    def randint(lo, hi, size, **k):
+        nonlocal queue, dq
+        v = queue.pop(0)
+        assert tuple(size) == tuple(v.shape) and int(v.max()) < hi
+        return v.clone()
+
+    def dropout(inp, p=0.5, training=True, inplace=False):
+        nonlocal queue, dq
+        assert training and p == 0.5
+        return inp * dq.pop(0)
+
+    m64 = rm.PointMLPModel(**kw).double()
+    m64.load_state_dict({k: (v.double() if v.is_floating_point() else v) for k, v in sd0.items()})
+    torch.randint, torch.nn.functional.dropout = randint, dropout
+    try:
+        m.train()
+        out = m(x.clone()).detach()
+        queue, dq = list(starts), [d.double() for d in drops]
+        out64 = m64.train()(x.double()).detach()
+    finally:
+        torch.randint, torch.nn.functional.dropout = orig_randint, orig_dropout
+    assert not queue and not dq
+    cfg = dict(points=kw["points"], k_neighbors=kw["k_neighbors"], reducers=kw.get("reducers", [2, 2, 2, 2]),
+               use_xyz=kw.get("use_xyz", True), normalize=kw.get("normalize", "center"))
+    rec = []
+    sd = {k: v.clone() for k, v in sd0.items()}
+    mine = pointmlp.pointmlp_forward(sd, x.clone(), cfg, starts, drops, record=rec)
+    margin = min(r["margin"] for r in rec if "margin" in r)
+    err = float((mine - out).norm() / out.norm())
+    sd64 = {k: (v.double() if v.is_floating_point() else v.clone()) for k, v in sd0.items()}
+    mine64 = pointmlp.pointmlp_forward(sd64, x.double(), cfg, starts, [d.double() for d in drops])
+    err64 = float((mine64 - out64).norm() / out64.norm())
+    gap = float((out.double() - out64).norm() / out64.norm())
+    print(f"pointmlp_{name}: oracle vs reference rel-L2 fp32 {err:.2e}, fp64 {err64:.2e}; reference fp32 vs fp64 {gap:.2e}; "
+          f"smallest kNN margin {margin:.2e}")
+    assert err < 1e-3 and err64 < 1e-10 and margin > 1e-4, (err, err64, margin)
+    ref_sd = m.state_dict()
+    for k in ref_sd:
+        if "running" in k:
+            assert torch.allclose(ref_sd[k], sd[k], rtol=2e-3, atol=1e-4), k
+    d = dict(meta=np.array([seed, B]), keys=np.array(keys), x=x.numpy(), fps_start=starts.numpy(),
+             drop1=drops[0].numpy(), drop2=drops[1].numpy(), out=out.numpy(), out64=out64.numpy(), kwargs=np.array(repr(kw)))
+    d.update(flat("sd0", sd0))
+    d.update(flat("stats", {k: v for k, v in ref_sd.items() if "running" in k or "tracked" in k}))
+    for i, r in enumerate(x for x in rec if "fps" in x):
+        d[f"fps.{i}"] = r["fps"].numpy().astype(np.int32)
+        d[f"knn.{i}"] = np.sort(r["knn"].numpy().astype(np.int32), axis=-1)
+    return d
+
+
 def main():
     assert refimport.available(), "needs /root/reference"
+    if len(sys.argv) > 1 and sys.argv[1] == "pointmlp":
+        for name in PM_CASES:
+            path = os.path.join(HERE, f"pointmlp_{name}.npz")
+            np.savez_compressed(path, **run_pointmlp(name))
+            print(f"pointmlp_{name}: {os.path.getsize(path) / 1024:.1f} KiB")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "encoder":
         d = run_encoder(51, 6)
         path = os.path.join(HERE, "encoder_small.npz")
