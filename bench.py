@@ -47,6 +47,8 @@ def parse():
     p.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     p.add_argument("--also-batch", type=int, default=256, help="second batch size reported under 'also'")
     p.add_argument("--other-configs", type=int, default=1, help="also time BASELINE configs 1 (POR) and 3 (CQL)")
+    p.add_argument("--pointmlp-batch", type=int, default=128,
+                   help="batch of the PointMLP (agent/feature_pcl.py) forward reported under 'also_pointmlp' (0: skip)")
     p.add_argument("--encoder-batch", type=int, default=256,
                    help="batch of the SORL + FasterNet scan-encoder workload reported under 'also_encoder' (0: skip)")
     return p.parse_args()
@@ -319,6 +321,60 @@ def kernel_table(prof, pk):
     return out
 
 
+def pointmlp_flops(points=361, embed=64, k=32, stages=4, blocks=2):
+    """Algorithmic flop of one PointMLPModel(points, default widths) forward per sample: every Conv1d / Linear as 2 M N K."""
+    f, n, c = 2.0 * points * 3 * embed, points, embed
+    for _ in range(stages):
+        n, out = n // 2, c * 2
+        f += 2.0 * n * k * ((2 * c + 3) * out + blocks * 2 * out * out)      # transfer + pre blocks on (S*k) rows
+        f += 2.0 * n * blocks * 2 * out * out                                 # pos blocks on S rows
+        c = out
+    return f + 2.0 * (c * 512 + 512 * 256 + 256 * 256)
+
+
+def pointmlp_leg(a, device, ctx, pk):
+    """The PointMLP scan encoder named by north_star (agent/feature_pcl.py), forward in train mode on scan point sets:
+    scan_to_points + PointMLPModel(points=361, class_num=256).  Unwired in the reference's agents, so
+    it is reported beside the update metric, not inside it."""
+    from porl_b200.agent.feature_pcl import PointMLPModel, scan_to_points
+    Bp = a.pointmlp_batch
+    torch.manual_seed(1234)
+    model = PointMLPModel(points=361, class_num=256).to(device).train()
+    states = synth_rows_torch(Bp, device, 77)[:, :S].contiguous()
+
+    def fwd():
+        return model(scan_to_points(states))
+
+    l0 = ctx.launches
+    fwd()
+    per = ctx.launches - l0
+    ms = time_updates(fwd, 2, 5)
+    flop = pointmlp_flops() * Bp
+    out = {"workload": f"pointmlp_points361_E64_k32_b{Bp}", "forward_ms": ms, "samples_per_s": Bp / (ms * 1e-3),
+           "gpu_launches_per_forward": per, "achieved_tflops": flop / (ms * 1e-3) * 1e-12,
+           "gflop_per_sample": pointmlp_flops() * 1e-9}
+    ctx.profile(True)
+    fwd()
+    torch.cuda.synchronize()
+    out["kernels"] = kernel_table(ctx.profile_read(), pk)
+    ctx.profile(False)
+    if a.cpu_seconds > 0:
+        from oracle import pointmlp as opm
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+        cfg = dict(points=361, k_neighbors=[32] * 4, reducers=[2] * 4, use_xyz=True, normalize="center")
+        xb = scan_to_points(states[:8]).cpu()
+        starts = torch.zeros(4, 8, dtype=torch.long)
+        t0, n = time.perf_counter(), 0
+        while n < 1 or time.perf_counter() - t0 < a.cpu_seconds / 3:
+            opm.pointmlp_forward(sd, xb, cfg, starts, None)
+            n += 1
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"samples_per_s": 8 * n / dt, "batch": 8, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"{n} forwards of batch 8 (oracle restatement of PointMLPModel.forward, eager torch fp32)"}
+    return out
+
+
 def time_updates(step_fn, n_warm, n_timed):
     for _ in range(n_warm):
         step_fn()
@@ -518,6 +574,8 @@ def run_b200(a):
             line["also_encoder"]["kernels"] = kernel_table(ctx.profile_read(), pk)
             ctx.profile(False)
             del r3
+        if a.pointmlp_batch:
+            line["also_pointmlp"] = pointmlp_leg(a, device, ctx, pk)
         if a.other_configs:
             line["also_configs"] = other_configs(a, device, table)
 
