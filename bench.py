@@ -266,8 +266,10 @@ class Runner:
         self.step(self.idx_static)                    # allocate workspaces outside capture
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
+        l0 = self.agent.ctx.launches
         with torch.cuda.graph(g):
             self.step(self.idx_static)
+        self.launches_per_step = self.agent.ctx.launches - l0    # kernels recorded in the graph = launched per replay
         self.graph = g
 
     def run(self, idx_all):

@@ -17,7 +17,7 @@ from . import _C
 from ._C import check, lib
 
 # one-shot reads cost (world-1) * bytes per rank over NVLink: beyond this NCCL's ring / NVLS wins
-MAX_PEER_READ_BYTES = int(os.environ.get("PORL_PEER_MAX_BYTES", str(24 << 20)))
+MAX_PEER_READ_BYTES = int(os.environ.get("PORL_PEER_MAX_BYTES", str(64 << 20)))
 
 
 class PeerBuffer:
