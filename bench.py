@@ -481,6 +481,7 @@ def run_b200(a):
                            "state_size": S, "hidden_dim": H, "parallelism": f"dp{world}" if dist_on else "single",
                            "contraction": "tcgen05 3xTF32" if a.gemm_mode == 1 else "fp32 FFMA",
                            "cuda_graph": use_graph, "inputs_larger_than_l2": True,
+                           "programmatic_dependent_launch": os.environ.get("PORL_PDL", "1") != "0",
                            "gradient_sum": ("none (single process)" if not dist_on else
                                             "peer-memory loads fused into the Adam kernel (NVLink P2P)" if peer_reduce
                                             else "NCCL all-reduce per optimizer group"),

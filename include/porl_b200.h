@@ -71,6 +71,10 @@ int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
 /* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
 int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
+/* Programmatic dependent launch of the update step's kernels (default on; env PORL_PDL=0 turns it off): each kernel
+ * lets its successor be scheduled while it runs and waits for its predecessor's completion before touching global
+ * memory, so launch latency hides behind the previous kernel's tail.  Results are unchanged. */
+int porl_ctx_set_pdl(porl_ctx_t* ctx, int enable);
 /* tcgen05 kernel variant (env PORL_TC_A_IN_TMEM sets the initial value): 0 (default) = all four operand planes in
  * shared memory, four TMEM chunk accumulators; 1 = the A operand's tf32 hi/lo planes are staged in tensor memory
  * (tcgen05.st) and the MMAs read A from TMEM; 2 = CTA pairs (clusters of 2, tcgen05.mma.cta_group::2, M = 256: each

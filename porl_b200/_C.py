@@ -158,6 +158,7 @@ _SIGNATURES = {
     "porl_ctx_set_tc_chunk": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_tc_debug": (C.c_int, [_p, _p]),
     "porl_ctx_set_tc_variant": (C.c_int, [_p, C.c_int]),
+    "porl_ctx_set_pdl": (C.c_int, [_p, C.c_int]),
 }
 
 EXPORTS = tuple(_SIGNATURES)
@@ -234,6 +235,9 @@ class Context:
 
     def set_tc_variant(self, a_in_tmem: int) -> None:
         check(lib.porl_ctx_set_tc_variant(self.handle, a_in_tmem))
+
+    def set_pdl(self, enable: bool) -> None:
+        check(lib.porl_ctx_set_pdl(self.handle, int(bool(enable))))
 
     def set_tc_debug(self, ptr) -> None:
         check(lib.porl_ctx_set_tc_debug(self.handle, ptr))

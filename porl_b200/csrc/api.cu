@@ -95,6 +95,8 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");
     ctx->tc_a_in_tmem = e ? atoi(e) : 0;
+    const char* pe = getenv("PORL_PDL");
+    ctx->pdl = pe ? (atoi(pe) != 0) : 1;
   }
   ctx->tc_ws = nullptr;
   ctx->tc_dbg = nullptr;
@@ -172,6 +174,12 @@ extern "C" int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx) { return ctx ? ctx-
 extern "C" int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks) {
   PORL_CHECK_ARG(ctx && k_blocks >= 1 && k_blocks <= 64, "porl_ctx_set_tc_chunk: k_blocks=%d", k_blocks);
   ctx->tc_chunk_kb = k_blocks;
+  return PORL_OK;
+}
+
+extern "C" int porl_ctx_set_pdl(porl_ctx_t* ctx, int enable) {
+  PORL_CHECK_ARG(ctx, "porl_ctx_set_pdl: null context");
+  ctx->pdl = enable ? 1 : 0;
   return PORL_OK;
 }
 

@@ -48,6 +48,7 @@ struct porl_ctx {
   int tc_a_in_tmem;         // tcgen05 kernel variant: A operand staged in tensor memory (default) or in shared memory
   int tc_chunk_kb;          // k-blocks per TMEM accumulation chunk of the tcgen05 kernel (1 or 2)
   unsigned long long* tc_dbg;  // optional per-CTA timestamps of the tcgen05 kernel (device memory), or null
+  int pdl;                  // launch the step's kernels with programmatic stream serialization (default 1)
 };
 
 #define PORL_CHECK_ARG(cond, ...)                \
@@ -131,6 +132,16 @@ __device__ __forceinline__ float block_sum(float v, float* smem32) {
   return r;
 }
 
+// Programmatic dependent launch (PDL).  Every kernel launched through launch_pdl() starts with pdl_entry():
+// it lets the NEXT kernel of the stream be scheduled as soon as all blocks of this grid are running (so its
+// launch latency and prologue hide behind this grid's tail), then blocks until the PREVIOUS grid has completed and
+// its writes are visible -- nothing of this kernel touches global memory before that, so the stream's order of
+// effects is unchanged.  Because every such kernel waits, completion stays transitive along the chain.
+__device__ __forceinline__ void pdl_entry() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -138,6 +149,23 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
 }
 __device__ __forceinline__ void st_release(int* p, int v) {
   asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// launch with the PDL attribute (ctx->pdl) -- the kernel MUST call pdl_entry() before its first global access
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(const porl_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = ctx->pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 }  // namespace porl

@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(256)
 gather_rows_kernel(const float* __restrict__ table, int64_t n_rows, int64_t row_stride, int row_len,
                    const int64_t* __restrict__ idx, int64_t B, float* __restrict__ out,
                    int64_t out_stride, uint32_t* status) {
+  pdl_entry();
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -57,6 +58,7 @@ gather_transitions_kernel(const float* __restrict__ table, int64_t n_rows, int64
                           float* __restrict__ next_obs, int64_t ld_obs, float* __restrict__ rewards,
                           float* __restrict__ dones, float* __restrict__ actions, int64_t ld_act,
                           uint32_t* status) {
+  pdl_entry();
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -87,6 +89,7 @@ gather_soa_kernel(const float* __restrict__ states, const float* __restrict__ ne
                   const int64_t* __restrict__ idx, int64_t B, float* __restrict__ o_states,
                   float* __restrict__ o_next, int64_t ld_out, int64_t* __restrict__ o_actions,
                   float* __restrict__ o_rewards, float* __restrict__ o_dones, uint32_t* status) {
+  pdl_entry();
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -111,6 +114,7 @@ gather_soa_kernel(const float* __restrict__ states, const float* __restrict__ ne
 __global__ void __launch_bounds__(256)
 pack_rows_kernel(const float* __restrict__ src, int64_t ld_src, int64_t B, int n,
                  float* __restrict__ dst, int64_t ld_dst) {
+  pdl_entry();
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -144,7 +148,7 @@ extern "C" int porl_gather_rows_f32(porl_ctx_t* ctx, const float* table, int64_t
                  (long long)n_rows, (long long)row_len, (long long)row_stride, (long long)out_stride);
   if (B == 0) return PORL_OK;
   ProfScope prof(ctx, PORL_CAT_GATHER, (double)B * (8.0 * row_len + 8.0), as_stream(stream));
-  gather_rows_kernel<<<gather_grid(ctx, B), 256, 0, as_stream(stream)>>>(
+  launch_pdl(ctx, gather_rows_kernel, gather_grid(ctx, B), 256, 0, as_stream(stream), 
       table, n_rows, row_stride, (int)row_len, idx, B, out, out_stride, ctx->counters);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
@@ -163,7 +167,7 @@ extern "C" int porl_gather_transitions(porl_ctx_t* ctx, const float* table, int6
                  S, A, (long long)row_stride, (long long)ld_obs, (long long)ld_act);
   if (B == 0) return PORL_OK;
   ProfScope prof(ctx, PORL_CAT_GATHER, (double)B * (8.0 * (2.0 * S + 2 + A) + 8.0), as_stream(stream));
-  gather_transitions_kernel<<<gather_grid(ctx, B), 256, 0, as_stream(stream)>>>(
+  launch_pdl(ctx, gather_transitions_kernel, gather_grid(ctx, B), 256, 0, as_stream(stream), 
       table, n_rows, row_stride, S, A, idx, B, obs, next_obs, ld_obs, rewards, dones, actions, ld_act,
       ctx->counters);
   PORL_LAUNCHED(ctx);
@@ -184,7 +188,7 @@ extern "C" int porl_gather_soa(porl_ctx_t* ctx, const float* states, const float
                  (long long)ld_state, (long long)ld_out, (long long)cap);
   if (B == 0) return PORL_OK;
   ProfScope prof(ctx, PORL_CAT_GATHER, (double)B * (8.0 * (2.0 * S + 2) + 16.0 + 8.0), as_stream(stream));
-  gather_soa_kernel<<<gather_grid(ctx, B), 256, 0, as_stream(stream)>>>(
+  launch_pdl(ctx, gather_soa_kernel, gather_grid(ctx, B), 256, 0, as_stream(stream), 
       states, next_states, actions, rewards, dones, cap, S, ld_state, idx, B, out_states,
       out_next_states, ld_out, out_actions, out_rewards, out_dones, ctx->counters);
   PORL_LAUNCHED(ctx);
@@ -198,7 +202,7 @@ extern "C" int porl_pack_rows(porl_ctx_t* ctx, const float* src, int64_t ld_src,
                  n, (long long)ld_src, (long long)ld_dst);
   if (B == 0) return PORL_OK;
   ProfScope prof(ctx, PORL_CAT_GATHER, (double)B * 8.0 * n, as_stream(stream));
-  pack_rows_kernel<<<gather_grid(ctx, B), 256, 0, as_stream(stream)>>>(src, ld_src, B, n, dst, ld_dst);
+  launch_pdl(ctx, pack_rows_kernel, gather_grid(ctx, B), 256, 0, as_stream(stream), src, ld_src, B, n, dst, ld_dst);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }

@@ -274,6 +274,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   // [12] splitters on raw_full [13] MMA on split_done [14] MMA on tmem_empty [4] accumulators on tmem_full [5] CTA clocks
   // [7] first chunk full [8] last chunk drained [9] first tile epilogue done [10] all tiles done [15] end
   const long long clk0 = clock64();
+  // PDL: the next kernel of the stream may be scheduled from here on; this one sets up barriers and tensor memory
+  // below and only then waits for the previous grid (nothing before the wait reads or writes its data)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (dbg && threadIdx.x == 0) dbg[0] = gtime();
 
   if (warp == 0 && lane == 0) {
@@ -311,6 +314,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   if (PAIR) cluster_sync_all();         // barriers of both CTAs initialised before any remote arrive / multicast
   else __syncthreads();
   tc_fence_after();
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   if (dbg && threadIdx.x == 0) dbg[1] = gtime();
   const int chunk_kb = P.chunk_kb;
@@ -865,9 +869,9 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
       return PORL_ERR_CUDA;
     }
   } else if (ctx->tc_a_in_tmem == 1) {
-    gemm_tc_kernel<true, false><<<grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream>>>(P);
+    launch_pdl(ctx, gemm_tc_kernel<true, false>, grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream, P);
   } else {
-    gemm_tc_kernel<false, false><<<grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream>>>(P);
+    launch_pdl(ctx, gemm_tc_kernel<false, false>, grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream, P);
   }
   ctx->tc_launches++;
   PORL_LAUNCHED(ctx);

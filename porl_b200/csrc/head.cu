@@ -19,45 +19,61 @@
 namespace porl {
 
 // ---------------------------------------------------------------- forward
+template <int RPW>   // rows a warp processes at once: 4 for large batches (loads in flight), 1 for small ones (more blocks)
 __global__ void __launch_bounds__(256) head_forward_kernel(const __grid_constant__ HeadFwdBatch hb) {
+  pdl_entry();
   const HeadFwdSeg& s = hb.seg[blockIdx.y];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n_out = s.n_out;
   const int Hp = (s.H + 3) & ~3;
-  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < hb.B; row += (int64_t)gridDim.x * 8) {
-    const float* hrow = s.h + row * s.ldh;
-    float acc[kHeadMax];
+  // a warp takes RPW rows at a time: RPW x (Hp / 128) independent 16-byte loads in flight per lane
+  for (int64_t row0 = ((int64_t)blockIdx.x * 8 + warp) * RPW; row0 < hb.B; row0 += (int64_t)gridDim.x * 8 * RPW) {
+    float acc[RPW][kHeadMax];
 #pragma unroll
-    for (int n = 0; n < kHeadMax; ++n) acc[n] = 0.f;
+    for (int u = 0; u < RPW; ++u)
+#pragma unroll
+      for (int n = 0; n < kHeadMax; ++n) acc[u][n] = 0.f;
     for (int c = lane * 4; c < Hp; c += 128) {
-      const float4 h4 = *reinterpret_cast<const float4*>(hrow + c);
+      float4 h4[RPW];
+#pragma unroll
+      for (int u = 0; u < RPW; ++u)
+        h4[u] = (row0 + u < hb.B) ? *reinterpret_cast<const float4*>(s.h + (row0 + u) * s.ldh + c)
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int n = 0; n < kHeadMax; ++n) {
         if (n < n_out) {
           const float4 w4 = __ldg(reinterpret_cast<const float4*>(s.W + (size_t)n * s.ldw + c));
-          acc[n] = fmaf(h4.x, w4.x, acc[n]);
-          acc[n] = fmaf(h4.y, w4.y, acc[n]);
-          acc[n] = fmaf(h4.z, w4.z, acc[n]);
-          acc[n] = fmaf(h4.w, w4.w, acc[n]);
+#pragma unroll
+          for (int u = 0; u < RPW; ++u) {
+            acc[u][n] = fmaf(h4[u].x, w4.x, acc[u][n]);
+            acc[u][n] = fmaf(h4[u].y, w4.y, acc[u][n]);
+            acc[u][n] = fmaf(h4[u].z, w4.z, acc[u][n]);
+            acc[u][n] = fmaf(h4[u].w, w4.w, acc[u][n]);
+          }
         }
       }
     }
-    float mine = 0.f;                      // lane n keeps output n
 #pragma unroll
-    for (int n = 0; n < kHeadMax; ++n) {
-      if (n < n_out) {
-        const float t = warp_sum(acc[n]);
-        if (lane == n) mine = t;
+    for (int u = 0; u < RPW; ++u) {
+      const int64_t row = row0 + u;
+      if (row >= hb.B) break;
+      float mine = 0.f;                      // lane n keeps output n
+#pragma unroll
+      for (int n = 0; n < kHeadMax; ++n) {
+        if (n < n_out) {
+          const float t = warp_sum(acc[u][n]);
+          if (lane == n) mine = t;
+        }
       }
-    }
-    if (lane < s.ld_out) {
-      float y = 0.f;
-      if (lane < n_out) {
-        y = mine + (s.bias ? s.bias[lane] : 0.f);
-        if (s.act == 1) y = fmaxf(y, 0.f);
-        else if (s.act == 2) y = tanhf(y);
+      if (lane < s.ld_out) {
+        float y = 0.f;
+        if (lane < n_out) {
+          y = mine + (s.bias ? s.bias[lane] : 0.f);
+          if (s.act == 1) y = fmaxf(y, 0.f);
+          else if (s.act == 2) y = tanhf(y);
+        }
+        s.out[row * s.ld_out + lane] = y;
       }
-      s.out[row * s.ld_out + lane] = y;
     }
   }
 }
@@ -74,11 +90,13 @@ int launch_head_forward(porl_ctx* ctx, const HeadFwdBatch& hb, cudaStream_t st) 
                    s.ldh, s.ldw, s.ld_out);
     bytes += 4.0 * hb.B * (s.H + s.ld_out);
   }
-  int64_t bx = (hb.B + 7) / 8;
+  const bool wide = hb.B >= 2048;
+  int64_t bx = wide ? (hb.B + 31) / 32 : (hb.B + 7) / 8;
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (bx > cap) bx = cap;
   ProfScope prof(ctx, PORL_CAT_HEAD, bytes, st);
-  head_forward_kernel<<<dim3((unsigned)bx, hb.n_seg), 256, 0, st>>>(hb);
+  if (wide) launch_pdl(ctx, head_forward_kernel<4>, dim3((unsigned)bx, hb.n_seg), 256, 0, st, hb);
+  else launch_pdl(ctx, head_forward_kernel<1>, dim3((unsigned)bx, hb.n_seg), 256, 0, st, hb);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }
@@ -88,6 +106,7 @@ int launch_head_forward(porl_ctx* ctx, const HeadFwdBatch& hb, cudaStream_t st) 
 // stride the rows of its row chunk.
 __global__ void __launch_bounds__(256) head_backward_kernel(const __grid_constant__ HeadBwdBatch hb, float* partials,
                                                            uint32_t* tickets) {
+  pdl_entry();
   __shared__ __align__(16) float sm[8][kHeadMax + 1][128];
   __shared__ float smb[8][kHeadMax];
   __shared__ int last_flag;
@@ -221,7 +240,7 @@ int launch_head_backward(porl_ctx* ctx, const HeadBwdBatch& hb, cudaStream_t st)
   PORL_CHECK_ARG((size_t)hb.n_seg * R * per_chunk <= (size_t)kPartialFloats && hb.n_seg * col_chunks <= kTickets,
                  "head backward: workspace too small for %d nets of width %d", hb.n_seg, hb.ldw);
   ProfScope prof(ctx, PORL_CAT_HEAD, 4.0 * hb.n_seg * (double)hb.B * hb.H * (hb.need_dz ? 2.0 : 1.0), st);
-  head_backward_kernel<<<dim3(col_chunks, R, hb.n_seg), 256, 0, st>>>(hb, ctx->partials, ctx->counters + kTicketBase);
+  launch_pdl(ctx, head_backward_kernel, dim3(col_chunks, R, hb.n_seg), 256, 0, st, hb, ctx->partials, ctx->counters + kTicketBase);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }

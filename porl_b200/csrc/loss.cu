@@ -36,6 +36,7 @@ expectile_kernel(const float* __restrict__ v1, const float* __restrict__ v2,
                  float tau, int64_t B, float inv_bn, float* __restrict__ target_v,
                  float* __restrict__ dv1, float* __restrict__ dv2, float* __restrict__ loss_out,
                  float* partials, uint32_t* counter, uint32_t* status) {
+  pdl_entry();
   __shared__ float red[32];
   __shared__ int flag;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -82,6 +83,7 @@ awr_nll_kernel(const float* __restrict__ mean, int64_t ld_mean, const float* __r
                int mode, int tanh_out, int64_t B, int D, float inv_bn, float* __restrict__ dz_out,
                float* __restrict__ dlog_std, float* __restrict__ loss_out, float* partials,
                uint32_t* counter, uint32_t* status) {
+  pdl_entry();
   extern __shared__ float sm[];                 // [kAwrWarps][D] log_std-gradient accumulators
   __shared__ float red[32];
   __shared__ int flag;
@@ -140,10 +142,14 @@ awr_nll_kernel(const float* __restrict__ mean, int64_t ld_mean, const float* __r
   if (threadIdx.x == 0) bp[D] = bl;
 
   if (last_block_ticket(counter, &flag)) {
+    // one warp per column: lanes take the block partials b = lane, lane + 32, ... in order, then a fixed shuffle
+    // tree -- order-fixed like a serial sum, without its chain of gridDim.x dependent L2 loads
     const int nb = gridDim.x;
-    for (int j = threadIdx.x; j <= D; j += blockDim.x) {
+    for (int j = warp; j <= D; j += kAwrWarps) {
       float s = 0.f;
-      for (int b = 0; b < nb; ++b) s += __ldcg(partials + (size_t)b * (D + 1) + j);
+      for (int b = lane; b < nb; b += 32) s += __ldcg(partials + (size_t)b * (D + 1) + j);
+      s = warp_sum(s);
+      if (lane != 0) continue;
       if (j < D) {
         const float raw = log_std[j];
         dlog_std[j] = (raw >= -5.f && raw <= 2.f) ? s : 0.f;
@@ -165,6 +171,7 @@ cql_head_kernel(const float* __restrict__ q, const float* __restrict__ qn, int64
                 const float* __restrict__ dones, float gamma, float alpha, int64_t B, int A,
                 float inv_bn, float* __restrict__ dq, float* __restrict__ losses_out, float* partials,
                 uint32_t* counter, uint32_t* status) {
+  pdl_entry();
   __shared__ float red[32];
   __shared__ int flag;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -238,7 +245,7 @@ extern "C" int porl_expectile_twin_loss(porl_ctx_t* ctx, const float* v1, const 
   const int64_t blocks = (B + 255) / 256;
   PORL_CHECK_ARG(blocks <= kPartialFloats, "porl_expectile_twin_loss: batch too large");
   ProfScope prof(ctx, PORL_CAT_LOSS, (double)B * 9.0 * 4.0, as_stream(stream));
-  expectile_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(
+  launch_pdl(ctx, expectile_kernel, (int)blocks, 256, 0, as_stream(stream), 
       v1, v2, nv1, nv2, ldv, rewards, dones, gamma, tau, B, 1.0f / (float)B_norm, target_v, dv1, dv2,
       loss_out, ctx->partials, ctx->counters + 1, ctx->counters);
   PORL_LAUNCHED(ctx);
@@ -258,13 +265,13 @@ extern "C" int porl_awr_gauss_nll(porl_ctx_t* ctx, const float* mean, int64_t ld
                  "porl_awr_gauss_nll: bad shape B=%lld D=%d ld_mean=%lld ld_x=%lld mode=%d",
                  (long long)B, D, (long long)ld_mean, (long long)ld_x, mode);
   int64_t blocks = (B + kAwrWarps - 1) / kAwrWarps;
-  const int64_t cap_sm = (int64_t)ctx->sm_count * 4;
+  const int64_t cap_sm = (int64_t)ctx->sm_count * (D > 64 ? 4 : 1);   // narrow rows: fewer partials to sum at the end
   const int64_t cap_ws = kPartialFloats / (D + 1);
   if (blocks > cap_sm) blocks = cap_sm;
   if (blocks > cap_ws) blocks = cap_ws;
   const size_t smem = (size_t)kAwrWarps * D * sizeof(float);
   ProfScope prof(ctx, PORL_CAT_LOSS, (double)B * (3.0 * D + 3.0) * 4.0, as_stream(stream));
-  awr_nll_kernel<<<(int)blocks, kAwrWarps * 32, smem, as_stream(stream)>>>(
+  launch_pdl(ctx, awr_nll_kernel, (int)blocks, kAwrWarps * 32, smem, as_stream(stream), 
       mean, ld_mean, log_std, x, ld_x, target_v, v1n, v2n, ldv, alpha, mode, tanh_out, B, D,
       1.0f / (float)B_norm, dz_out, dlog_std, loss_out, ctx->partials, ctx->counters + 2, ctx->counters);
   PORL_LAUNCHED(ctx);
@@ -282,7 +289,7 @@ extern "C" int porl_cql_head(porl_ctx_t* ctx, const float* q, const float* q_nex
   const int64_t blocks = (B + 255) / 256;
   PORL_CHECK_ARG(2 * blocks <= kPartialFloats, "porl_cql_head: batch too large");
   ProfScope prof(ctx, PORL_CAT_LOSS, (double)B * (3.0 * A * 4.0 + 16.0), as_stream(stream));
-  cql_head_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(
+  launch_pdl(ctx, cql_head_kernel, (int)blocks, 256, 0, as_stream(stream), 
       q, q_next_tgt, ldq, actions, rewards, dones, gamma, alpha, B, A, 1.0f / (float)B_norm, dq,
       losses_out, ctx->partials, ctx->counters + 3, ctx->counters);
   PORL_LAUNCHED(ctx);

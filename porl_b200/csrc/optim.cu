@@ -87,8 +87,26 @@ __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
             float* __restrict__ v, int64_t n, porl_opt_state_t* st, float beta1, float beta2, float eps,
             float* __restrict__ target, float ema_beta, int hard_every, const PeerArgs peers) {
+  pdl_entry();
   __shared__ AdamScalars sh;
   __shared__ uint32_t sh_epoch;
+  const bool ema = (target != nullptr) && ema_beta > 0.f;
+  const int64_t n4 = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float4* p4 = reinterpret_cast<float4*>(p);
+  const float4* g4 = reinterpret_cast<const float4*>(g);
+  float4* m4 = reinterpret_cast<float4*>(m);
+  float4* v4 = reinterpret_cast<float4*>(v);
+  float4* t4 = reinterpret_cast<float4*>(target);
+  // the first element's loads are issued before the (double-precision) bias corrections of thread 0, so every
+  // block's HBM latency overlaps that scalar work instead of following it
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float4 pp0 = make_float4(0.f, 0.f, 0.f, 0.f), mm0 = pp0, vv0 = pp0, gg0 = pp0, tt0 = pp0;
+  if (i0 < n4) {
+    pp0 = p4[i0]; mm0 = m4[i0]; vv0 = v4[i0];
+    if (!PEER) gg0 = g4[i0];
+    if (ema) tt0 = t4[i0];
+  }
   if (threadIdx.x == 0) {
     sh = adam_scalars(st, beta1, beta2, hard_every);
     if (PEER) sh_epoch = *reinterpret_cast<volatile uint32_t*>(peers.epoch) + 1u;
@@ -111,19 +129,13 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
       peers.tail_out[threadIdx.x] = t;
     }
   }
-  const bool ema = (target != nullptr) && ema_beta > 0.f;
   const bool hard = (target != nullptr) && s.do_hard;
   const float keep = 1.f - ema_beta;
 
-  const int64_t n4 = n >> 2;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  float4* p4 = reinterpret_cast<float4*>(p);
-  const float4* g4 = reinterpret_cast<const float4*>(g);
-  float4* m4 = reinterpret_cast<float4*>(m);
-  float4* v4 = reinterpret_cast<float4*>(v);
-  float4* t4 = reinterpret_cast<float4*>(target);
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    float4 pp = p4[i], mm = m4[i], vv = v4[i];
+  for (int64_t i = i0; i < n4; i += stride) {
+    float4 pp, mm, vv;
+    if (i == i0) { pp = pp0; mm = mm0; vv = vv0; }
+    else { pp = p4[i]; mm = m4[i]; vv = v4[i]; }
     float4 gg;
     if (PEER) {
       float4 gr[PORL_MAX_PEERS];
@@ -135,7 +147,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
       for (int r = 1; r < PORL_MAX_PEERS; ++r)
         if (r < peers.world) { gg.x += gr[r].x; gg.y += gr[r].y; gg.z += gr[r].z; gg.w += gr[r].w; }
     } else {
-      gg = g4[i];
+      gg = (i == i0) ? gg0 : g4[i];
     }
     adam_elem(pp.x, gg.x, mm.x, vv.x, s, beta1, beta2, eps);
     adam_elem(pp.y, gg.y, mm.y, vv.y, s, beta1, beta2, eps);
@@ -143,7 +155,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     adam_elem(pp.w, gg.w, mm.w, vv.w, s, beta1, beta2, eps);
     p4[i] = pp; m4[i] = mm; v4[i] = vv;
     if (ema) {
-      float4 tt = t4[i];
+      float4 tt = (i == i0) ? tt0 : t4[i];
       tt.x = fmaf(ema_beta, pp.x, tt.x * keep);       // mul_(1-beta).add_(src, alpha=beta)
       tt.y = fmaf(ema_beta, pp.y, tt.y * keep);
       tt.z = fmaf(ema_beta, pp.z, tt.z * keep);
@@ -223,7 +235,7 @@ extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* 
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * (target ? 36.0 : 28.0), as_stream(stream));
-  adam_kernel<false><<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, state_dev, beta1, beta2, eps,
+  launch_pdl(ctx, adam_kernel<false>, (int)blocks, 256, 0, as_stream(stream), p, g, m, v, n, state_dev, beta1, beta2, eps,
                                                                  target, ema_beta, hard_every, PeerArgs{});
   PORL_LAUNCHED(ctx);
   return PORL_OK;
@@ -258,7 +270,7 @@ extern "C" int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_gr
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * ((target ? 32.0 : 24.0) + 4.0 * pg->world), as_stream(stream));
-  adam_kernel<true><<<(int)blocks, 256, 0, as_stream(stream)>>>(p, pg->bucket[pg->rank], m, v, n, state_dev, beta1,
+  launch_pdl(ctx, adam_kernel<true>, (int)blocks, 256, 0, as_stream(stream), p, pg->bucket[pg->rank], m, v, n, state_dev, beta1,
                                                                 beta2, eps, target, ema_beta, hard_every, a);
   PORL_LAUNCHED(ctx);
   return PORL_OK;

@@ -8,6 +8,7 @@ namespace porl {
 // ---------------------------------------------------------------- batched transpose
 // dst (cols, ld_dst) = src (rows, ld_src)^T through a 32x33 shared-memory tile; both sides coalesced.
 __global__ void __launch_bounds__(256) transpose_kernel(const __grid_constant__ TransposeBatch tb) {
+  pdl_entry();
   __shared__ float tile[32][33];
   const TransposeSeg& s = tb.seg[blockIdx.z];
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;       // c0: source column block, r0: source row block
@@ -41,7 +42,7 @@ int launch_transpose(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st) {
   }
   PORL_CHECK_ARG((max_r + 31) / 32 <= 65535, "transpose: too many rows (%d)", max_r);
   ProfScope prof(ctx, PORL_CAT_TRANSPOSE, bytes, st);
-  transpose_kernel<<<dim3((max_c + 31) / 32, (max_r + 31) / 32, tb.n_seg), 256, 0, st>>>(tb);
+  launch_pdl(ctx, transpose_kernel, dim3((max_c + 31) / 32, (max_r + 31) / 32, tb.n_seg), 256, 0, st, tb);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }
@@ -51,6 +52,7 @@ int launch_transpose(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st) {
 // of a column chunk (ticket) adds the row-chunk partials in index order -> deterministic.
 __global__ void __launch_bounds__(256) colsum_kernel(const __grid_constant__ ColsumBatch cb, float* partials,
                                                      uint32_t* tickets) {
+  pdl_entry();
   __shared__ float sm[8][33];
   __shared__ int last_flag;
   const ColsumSeg& s = cb.seg[blockIdx.z];
@@ -94,6 +96,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const __grid_constant__ Col
   if (last_flag && warp == 0 && col < s.n) {
     __threadfence();
     float t = 0.f;
+#pragma unroll 8
     for (int r = 0; r < R; ++r) t += __ldcg(partials + ((size_t)blockIdx.z * R + r) * cb.max_n + col);
     s.out[col] = t;
   }
@@ -113,13 +116,13 @@ int launch_colsum(porl_ctx* ctx, ColsumBatch& cb, cudaStream_t st) {
   }
   cb.max_n = max_n;
   const int col_chunks = (max_n + 31) / 32;
-  int R = (int)((max_rows + 255) / 256);      // >= 256 rows per block
+  int R = (int)((max_rows + 127) / 128);      // >= 128 rows per block
   if (R > 32) R = 32;
   if (R < 1) R = 1;
   PORL_CHECK_ARG((int64_t)cb.n_seg * R * max_n <= kPartialFloats && cb.n_seg * col_chunks <= kTickets,
                  "colsum: workspace too small for %d segments of width %d", cb.n_seg, max_n);
   ProfScope prof(ctx, PORL_CAT_LOSS, bytes, st);
-  colsum_kernel<<<dim3(col_chunks, R, cb.n_seg), 256, 0, st>>>(cb, ctx->partials, ctx->counters + kTicketBase);
+  launch_pdl(ctx, colsum_kernel, dim3(col_chunks, R, cb.n_seg), 256, 0, st, cb, ctx->partials, ctx->counters + kTicketBase);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
 }
