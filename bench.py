@@ -390,9 +390,19 @@ def time_updates(step_fn, n_warm, n_timed):
     return e0.elapsed_time(e1) / n_timed
 
 
+def graph_of(step_fn):
+    """CUDA graph of one update (workspaces are allocated by a first eager call)."""
+    step_fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        step_fn()
+    return g
+
+
 def other_configs(a, device, table):
-    """BASELINE configs 1 (POR, S=365, H=1024, batch 256) and 3 (discrete CQL, QNetwork 362-64-128-64-5, batch 4096):
-    device-timed updates/s with a fresh gather every step, eager launches (no graph)."""
+    """BASELINE configs 1 (POR, S=365, H=1024, batch 256 and 4096) and 3 (discrete CQL, QNetwork 362-64-128-64-5, batch
+    4096): device-timed updates/s, fresh random rows every step, one CUDA graph replay per update (--graph 1)."""
     from types import SimpleNamespace
     from porl_b200 import CQLTrainer, POR, QNetwork, TransitionDataset
     out = {}
@@ -406,16 +416,26 @@ def other_configs(a, device, table):
         agent = POR(args, max_steps=1_000_000, tau=0.9, alpha=10.0, device=device)
         agent.ctx.set_gemm_mode(a.gemm_mode)
         pb = ds.new_batch(B)
+        idx = torch.zeros(B, dtype=torch.int64, device=device)
+
+        def update():
+            ds.gather_packed(idx, pb)
+            agent.update_packed(pb)
+
+        l0 = agent.ctx.launches
+        graph = graph_of(update) if a.graph else None
+        launches = (agent.ctx.launches - l0) // 2 if a.graph else None
 
         def step():
-            ds.gather_packed(torch.randint(0, len(ds), (B,), generator=g, device=device), pb)
-            agent.update_packed(pb)
+            torch.randint(0, len(ds), (B,), generator=g, device=device, out=idx)
+            graph.replay() if graph is not None else update()
 
         ms = time_updates(step, 5, 50 if B == 256 else 20)
         agent.read_losses()
         out[f"por_mlp_S365_H1024_rows100k_b{B}"] = {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms,
-                                                     "achieved_tflops": 37.0e6 * B / (ms * 1e-3) * 1e-12}
-        del agent
+                                                     "achieved_tflops": 37.0e6 * B / (ms * 1e-3) * 1e-12,
+                                                     "cuda_graph": bool(a.graph), "launches_per_step": launches}
+        del agent, graph
     del ds, rows
     # config 3: discrete CQL on a replay buffer filled from the SORL table
     t = CQLTrainer(state_size=S, action_size=5, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
@@ -428,19 +448,41 @@ def other_configs(a, device, table):
     rowsb = table.gather(idx)
     t.replay_buffer.push_batch(rowsb[:, :S], torch.randint(0, 5, (n,), generator=g, device=device), rowsb[:, S],
                                rowsb[:, S + 1:2 * S + 1], rowsb[:, 2 * S + 1])
-    del rowsb
-    B = 4096
-    state = {"pb": None, "i": 0}
+    del rowsb, idx
+    for B in (4096, 256):
+        idx = torch.zeros(B, dtype=torch.int64, device=device)
+        update = lambda: t.learn_indices(idx, hard_every=10)
+        l0 = t.ctx.launches
+        graph = graph_of(update) if a.graph else None
+        launches = (t.ctx.launches - l0) // 2 if a.graph else None
 
-    def cql_step():
-        state["pb"] = t.replay_buffer.gather_packed(torch.randint(0, n, (B,), generator=g, device=device), state["pb"])
-        t.learn_packed(state["pb"], hard_every=10)
-        state["i"] += 1
+        def cql_step():
+            torch.randint(0, n, (B,), generator=g, device=device, out=idx)
+            graph.replay() if graph is not None else update()
 
-    ms = time_updates(cql_step, 5, 100)
-    t.read_losses()
-    out[f"cql_q362-64-128-64-5_rows1M_b{B}"] = {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms,
-                                                 "note": "launch-latency bound (1.1 GFLOP per update); eager launches"}
+        ms = time_updates(cql_step, 10, 300)
+        t.read_losses()
+        prof = None
+        if t.fused:                                   # kernel time of the fused update, CUDA events inside the library
+            t.ctx.profile(True)
+            for _ in range(20):
+                torch.randint(0, n, (B,), generator=g, device=device, out=idx)
+                update()
+            torch.cuda.synchronize()
+            pr = t.ctx.profile_read()
+            t.ctx.profile(False)
+            c = pr["contraction"]
+            us = c["ms"] / max(c["launches"], 1) * 1e3
+            prof = {"kernel": "cql_fused_kernel (gather + 2 forwards + head + backward, fp32 FFMA)",
+                    "us_per_launch": us, "achieved_tflops": c["work"] / (c["ms"] * 1e-3) * 1e-12,
+                    "frac_of_ffma_peak": c["work"] / (c["ms"] * 1e-3) / 74.0e12,
+                    "gather_gbs": 2.0 * B * S * 4 / (us * 1e-6) * 1e-9}
+        out[f"cql_q362-64-128-64-5_rows1M_b{B}"] = {
+            "value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "cuda_graph": bool(a.graph),
+            "launches_per_step": launches, "fused_kernel": prof,
+            "note": "one persistent kernel per update (csrc/cql_fused.cu) + partial sum + Adam" if t.fused
+                    else "layer-by-layer kernels"}
+        del graph
     return out
 
 

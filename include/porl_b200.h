@@ -165,6 +165,8 @@ int porl_mlp_param_layout(const porl_mlp_t* mlp, int32_t net, int32_t layer, int
 int64_t porl_mlp_saved_floats(const porl_mlp_t* mlp, int64_t B);
 /* padded leading dimension of the output rows, per net: out is (n_nets, B, ld_out) */
 int64_t porl_mlp_out_ld(const porl_mlp_t* mlp);
+/* copy of the descriptor the plan was created from */
+int porl_mlp_desc(const porl_mlp_t* mlp, porl_mlp_desc_t* out);
 
 typedef struct {
   porl_mlp_t* mlp;
@@ -220,6 +222,22 @@ int porl_cql_head(porl_ctx_t* ctx, const float* q, const float* q_next_tgt, int6
                   const int64_t* actions, const float* rewards, const float* dones, float gamma,
                   float alpha, int64_t B, int32_t A, int64_t B_norm, float* dq, float* losses_out,
                   porl_stream_t stream);
+
+/* ---- Fused CQL gradient (SURVEY.md 8b porl_cql_step; src/porl/train/cql_trainer.py:88-124) -- */
+/* One persistent kernel per update for the QNetwork S -> 64 -> 128 -> 64 -> A of src/porl/net/q_network.py:8-30:
+ * gathers rows idx[0..B) of the SoA replay arrays (replaybuffer.py:61-70; idx == NULL takes rows 0..B-1 of an already
+ * gathered batch), evaluates the target net on next_states and the online net on states with the weights staged in
+ * shared memory, applies the TD + conservative head of porl_cql_head and back-propagates; a second kernel sums the
+ * per-CTA gradient partials in CTA order (deterministic) into `grads` (flat parameter layout of porl_mlp_param_layout)
+ * and writes losses_out[0..2] = loss, td, penalty.  The caller follows with porl_adam_step on the same bucket.
+ * states / next_states: (n_rows, ld_states) rows padded to PORL_PAD floats with zero pad columns.
+ * PORL_ERR_UNSUPPORTED for any other network shape (porl_cql_fused_supported() == 0): use porl_mlp_* + porl_cql_head. */
+int porl_cql_fused_supported(const porl_mlp_t* mlp);
+int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const float* params, const float* target_params,
+                        const float* states, const float* next_states, int64_t ld_states, const int64_t* actions,
+                        const float* rewards, const float* dones, const int64_t* idx, int64_t n_rows, float gamma,
+                        float alpha, int64_t B, int64_t B_norm, float* grads, float* losses_out,
+                        porl_stream_t stream);
 
 /* ---- K7: fused Adam (+ Polyak / hard target update) ---------------------------------------- */
 /* Device-resident optimizer state so that a captured CUDA graph can be replayed: the step

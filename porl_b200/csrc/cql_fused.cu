@@ -1,0 +1,550 @@
+// Fused discrete-CQL gradient: replay-buffer gather + target forward + online forward + TD/CQL head + backward of the
+// QNetwork S -> 64 -> 128 -> 64 -> A (src/porl/net/q_network.py:8-30) in ONE persistent kernel, weights staged in
+// shared memory, fp32 FFMA (the whole net is 160 KB: src/porl/train/cql_trainer.py:88-124 is launch-latency bound
+// when every layer is its own launch).  A second small kernel sums the per-CTA gradient partials in CTA order
+// (deterministic) into the optimizer bucket and finalises the three loss scalars.
+//
+//   tile = 32 transitions per CTA pass; 256 threads; shared memory (floats, KP = pad32(S)):
+//     XS  [32][KP+4]     next_obs rows (target pass), then obs rows (kept for dW0)
+//     WS  max(64*(KP+4), 17696)   W0, then {W1 [128][68], W2 [64][132], W3 [8][68]} of the net being evaluated
+//     H1  [32][68]  H2 [32][132]  H3 [32][68]    activations, overwritten in place by dz on the way back
+//     BS  [264] biases, QS/DQ [32][8], NMAX [32]
+//   Row strides are = 4 (mod 32) floats: the 8 sample rows / 4 neuron rows a warp touches per LDS.128 fall in
+//   distinct banks.
+#include <math.h>
+
+#include "common.cuh"
+
+extern "C" int porl_mlp_desc(const porl_mlp_t* mlp, porl_mlp_desc_t* out);
+
+namespace porl {
+namespace {
+
+constexpr int kT = 32;            // transitions per tile
+constexpr int kThreads = 256;
+constexpr int kH1 = 64, kH2 = 128, kH3 = 64;
+constexpr int kLd1 = kH1 + 4, kLd2 = kH2 + 4, kLd3 = kH3 + 4;
+constexpr int kAP = 8;            // padded action count (A <= 8)
+constexpr int kW1Floats = kH2 * kLd1, kW2Floats = kH3 * kLd2, kW3Floats = kAP * kLd3;
+constexpr int kW123Floats = kW1Floats + kW2Floats + kW3Floats;
+constexpr int kBiasFloats = kH1 + kH2 + kH3 + kAP;
+
+struct CqlArgs {
+  const float* params;
+  const float* target;
+  int64_t w_off[4], b_off[4];
+  const float* states;
+  const float* next_states;
+  int64_t ld_states;
+  const int64_t* actions;
+  const float* rewards;
+  const float* dones;
+  const int64_t* idx;      // rows to take (null: row i = i)
+  int64_t n_rows;
+  int64_t B;
+  int KP;                  // pad32(S)
+  int A;
+  float gamma, alpha, inv_bn;
+  float* partials;         // [gridDim.x][part_stride]: gradient in the flat parameter layout, then td, penalty
+  int64_t part_stride;
+  int64_t n_floats;
+  uint32_t* status;
+};
+
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_but_last() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+__device__ __forceinline__ float dot4(const float4& a, const float4& w, float acc) {
+  acc = fmaf(a.x, w.x, acc);
+  acc = fmaf(a.y, w.y, acc);
+  acc = fmaf(a.z, w.z, acc);
+  acc = fmaf(a.w, w.w, acc);
+  return acc;
+}
+
+// rows of the tile -> XS (asynchronous; rows past B are zero)
+__device__ __forceinline__ void load_rows(float* XS, int ldx, const float* table, int64_t ld, const int* rowsel,
+                                          int KP) {
+  const int c4 = KP >> 2;
+  for (int e = threadIdx.x; e < kT * c4; e += kThreads) {
+    const int s = e / c4, c = e - s * c4;
+    float* d = XS + s * ldx + 4 * c;
+    const int r = rowsel[s];
+    if (r >= 0) cp_async16(d, table + (int64_t)r * ld + 4 * c);
+    else *reinterpret_cast<float4*>(d) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+// dense (rows, cols) -> shared (rows, lds), cols % 4 == 0 (asynchronous)
+__device__ __forceinline__ void load_mat(float* dst, int lds, const float* src, int rows, int cols) {
+  const int c4 = cols >> 2;
+  for (int e = threadIdx.x; e < rows * c4; e += kThreads) {
+    const int r = e / c4, c = e - r * c4;
+    cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
+  }
+}
+
+__device__ __forceinline__ void load_w123(float* WS, const float* p, const int64_t* w_off, int A) {
+  load_mat(WS, kLd1, p + w_off[1], kH2, kH1);
+  load_mat(WS + kW1Floats, kLd2, p + w_off[2], kH3, kH2);
+  load_mat(WS + kW1Floats + kW2Floats, kLd3, p + w_off[3], A, kH3);
+  for (int e = threadIdx.x; e < (kAP - A) * kLd3; e += kThreads) WS[kW1Floats + kW2Floats + A * kLd3 + e] = 0.f;
+}
+
+__device__ __forceinline__ void load_bias(float* BS, const float* p, const int64_t* b_off, int A) {
+  for (int e = threadIdx.x; e < kBiasFloats; e += kThreads) {
+    float v;
+    if (e < kH1) v = p[b_off[0] + e];
+    else if (e < kH1 + kH2) v = p[b_off[1] + e - kH1];
+    else if (e < kH1 + kH2 + kH3) v = p[b_off[2] + e - kH1 - kH2];
+    else v = (e - kH1 - kH2 - kH3) < A ? p[b_off[3] + e - kH1 - kH2 - kH3] : 0.f;
+    BS[e] = v;
+  }
+}
+
+// out[s][n] = relu(b[n] + sum_k a[s][k] w[n][k]); thread tile 4 samples (sg + 8i) x NJ neurons (ng + 32j)
+template <int N>
+__device__ __forceinline__ void fwd_layer(const float* a, int lda, int K, const float* w, int ldw, const float* b,
+                                          float* out, int ldo) {
+  constexpr int NJ = N / 32;
+  const int sg = threadIdx.x & 7, ng = threadIdx.x >> 3;
+  float acc[4][NJ];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) acc[i][j] = 0.f;
+  const float* ap = a + sg * lda;
+  const float* wp = w + ng * ldw;
+#pragma unroll 2
+  for (int k = 0; k < K; k += 4) {
+    float4 av[4], wv[NJ];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) av[i] = *reinterpret_cast<const float4*>(ap + i * 8 * lda + k);
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) wv[j] = *reinterpret_cast<const float4*>(wp + j * 32 * ldw + k);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) acc[i][j] = dot4(av[i], wv[j], acc[i][j]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) out[(sg + 8 * i) * ldo + ng + 32 * j] = fmaxf(acc[i][j] + b[ng + 32 * j], 0.f);
+}
+
+// q[s][a] = b[a] + sum_k h3[s][k] w3[a][k]   (no activation), a < kAP (rows >= A of w3 and b are zero)
+__device__ __forceinline__ void head_fwd(const float* h3, const float* w3, const float* b, float* q) {
+  const int s = threadIdx.x >> 3, a = threadIdx.x & 7;
+  float acc = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < kH3; k += 4)
+    acc = dot4(*reinterpret_cast<const float4*>(h3 + s * kLd3 + k), *reinterpret_cast<const float4*>(w3 + a * kLd3 + k),
+               acc);
+  q[s * kAP + a] = acc + b[a];
+}
+
+// h[s][k] <- (sum_n dz[s][n] w[n][k]) * [h[s][k] > 0], in place; thread tile 2 samples (sg, sg+16) x CJ float4 columns
+template <int K, int N>
+__device__ __forceinline__ void dh_layer(const float* dz, int ldz, const float* w, int ldw, float* h, int ldh) {
+  constexpr int CJ = (K / 4) / 16;
+  const int cg = threadIdx.x & 15, sg = threadIdx.x >> 4;
+  float4 acc[2][CJ];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < CJ; ++j) acc[i][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int n = 0; n < N; n += 4) {
+    float4 d[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) d[i] = *reinterpret_cast<const float4*>(dz + (sg + 16 * i) * ldz + n);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+#pragma unroll
+      for (int j = 0; j < CJ; ++j) {
+        const float4 wv = *reinterpret_cast<const float4*>(w + (n + q) * ldw + 4 * (cg + 16 * j));
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const float dv = q == 0 ? d[i].x : q == 1 ? d[i].y : q == 2 ? d[i].z : d[i].w;
+          acc[i][j].x = fmaf(dv, wv.x, acc[i][j].x);
+          acc[i][j].y = fmaf(dv, wv.y, acc[i][j].y);
+          acc[i][j].z = fmaf(dv, wv.z, acc[i][j].z);
+          acc[i][j].w = fmaf(dv, wv.w, acc[i][j].w);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < CJ; ++j) {
+      float4* hp = reinterpret_cast<float4*>(h + (sg + 16 * i) * ldh + 4 * (cg + 16 * j));
+      const float4 hv = *hp;
+      float4 o;
+      o.x = hv.x > 0.f ? acc[i][j].x : 0.f;
+      o.y = hv.y > 0.f ? acc[i][j].y : 0.f;
+      o.z = hv.z > 0.f ? acc[i][j].z : 0.f;
+      o.w = hv.w > 0.f ? acc[i][j].w : 0.f;
+      *hp = o;
+    }
+}
+
+// gw[n][k] (+)= sum_s dz[s][n] a[s][k];  gb[n] (+)= sum_s dz[s][n].   thread tile 4 n x CJ float4 columns of k
+template <int N, int CJ>
+__device__ __forceinline__ void dw_layer(const float* dz, int ldz, const float* a, int lda, int K, float* gw, float* gb,
+                                         bool accumulate) {
+  constexpr int NG = N / 4, TK = kThreads / NG;
+  const int kg = threadIdx.x % TK, ngp = threadIdx.x / TK;
+  const int kc = K >> 2;
+  float4 acc[4][CJ];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int j = 0; j < CJ; ++j) acc[q][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int s = 0; s < kT; ++s) {
+    const float4 d = *reinterpret_cast<const float4*>(dz + s * ldz + 4 * ngp);
+#pragma unroll
+    for (int j = 0; j < CJ; ++j) {
+      const int c = kg + TK * j;
+      if (c < kc) {
+        const float4 av = *reinterpret_cast<const float4*>(a + s * lda + 4 * c);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float dv = q == 0 ? d.x : q == 1 ? d.y : q == 2 ? d.z : d.w;
+          acc[q][j].x = fmaf(dv, av.x, acc[q][j].x);
+          acc[q][j].y = fmaf(dv, av.y, acc[q][j].y);
+          acc[q][j].z = fmaf(dv, av.z, acc[q][j].z);
+          acc[q][j].w = fmaf(dv, av.w, acc[q][j].w);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int j = 0; j < CJ; ++j) {
+      const int c = kg + TK * j;
+      if (c < kc) {
+        float4* gp = reinterpret_cast<float4*>(gw + (int64_t)(4 * ngp + q) * K + 4 * c);
+        float4 o = acc[q][j];
+        if (accumulate) {
+          const float4 p = *gp;
+          o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+        }
+        *gp = o;
+      }
+    }
+  if (threadIdx.x < N) {
+    float sb = 0.f;
+    for (int s = 0; s < kT; ++s) sb += dz[s * ldz + threadIdx.x];
+    gb[threadIdx.x] = accumulate ? gb[threadIdx.x] + sb : sb;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p) {
+  pdl_entry();
+  extern __shared__ __align__(16) float smem[];
+  const int KP = p.KP, ldx = KP + 4;
+  const int ws_floats = max(kH1 * ldx, kW123Floats);
+  float* XS = smem;
+  float* WS = XS + kT * ldx;
+  float* H1 = WS + ws_floats;
+  float* H2 = H1 + kT * kLd1;
+  float* H3 = H2 + kT * kLd2;
+  float* BS = H3 + kT * kLd3;
+  float* QS = BS + kBiasFloats;
+  float* DQ = QS + kT * kAP;
+  float* NMAX = DQ + kT * kAP;
+  int* ROW = reinterpret_cast<int*>(NMAX + kT);
+  float* W1s = WS;
+  float* W2s = WS + kW1Floats;
+  float* W3s = WS + kW1Floats + kW2Floats;
+  float* B1 = BS, *B2 = BS + kH1, *B3 = BS + kH1 + kH2, *B4 = BS + kH1 + kH2 + kH3;
+
+  float* part = p.partials + (int64_t)blockIdx.x * p.part_stride;
+  const int64_t n_tiles = (p.B + kT - 1) / kT;
+  float td_sum = 0.f, pen_sum = 0.f;     // thread 0 only
+  bool acc = false;
+
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, acc = true) {
+    // ---- which rows
+    if (threadIdx.x < kT) {
+      const int64_t i = tile * kT + threadIdx.x;
+      int r = -1;
+      if (i < p.B) {
+        int64_t rr = p.idx ? p.idx[i] : i;
+        if (rr < 0 || rr >= p.n_rows) {
+          atomicOr(p.status, (uint32_t)PORL_FLAG_BAD_INDEX);
+          rr = rr < 0 ? 0 : p.n_rows - 1;
+        }
+        r = (int)rr;
+      }
+      ROW[threadIdx.x] = r;
+    }
+    __syncthreads();
+    // ---- target network on next_states: max_a Q_tgt(s', a)     (cql_trainer.py:94-98)
+    load_rows(XS, ldx, p.next_states, p.ld_states, ROW, KP);
+    load_mat(WS, ldx, p.target + p.w_off[0], kH1, KP);
+    load_bias(BS, p.target, p.b_off, p.A);
+    cp_async_wait_all();
+    __syncthreads();
+    fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    __syncthreads();
+    load_w123(WS, p.target, p.w_off, p.A);
+    cp_async_commit();
+    load_rows(XS, ldx, p.states, p.ld_states, ROW, KP);      // obs rows arrive behind the target's upper layers
+    cp_async_commit();
+    cp_async_wait_but_last();
+    __syncthreads();
+    fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    __syncthreads();
+    fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    __syncthreads();
+    head_fwd(H3, W3s, B4, QS);
+    __syncthreads();
+    if (threadIdx.x < kT) {
+      float m = -INFINITY;
+      for (int a = 0; a < p.A; ++a) m = fmaxf(m, QS[threadIdx.x * kAP + a]);
+      NMAX[threadIdx.x] = m;
+    }
+    // ---- online network on states                                (cql_trainer.py:100)
+    load_mat(WS, ldx, p.params + p.w_off[0], kH1, KP);
+    load_bias(BS, p.params, p.b_off, p.A);
+    cp_async_wait_all();
+    __syncthreads();
+    fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    __syncthreads();
+    load_w123(WS, p.params, p.w_off, p.A);
+    cp_async_wait_all();
+    __syncthreads();
+    fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    __syncthreads();
+    fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    __syncthreads();
+    head_fwd(H3, W3s, B4, QS);
+    __syncthreads();
+    // ---- TD + conservative penalty and dL/dq                     (cql_trainer.py:72-86,101-108)
+    if (threadIdx.x < kT) {
+      const int s = threadIdx.x;
+      const int r = ROW[s];
+      float td_i = 0.f, pen_i = 0.f;
+      float dq[kAP];
+#pragma unroll
+      for (int a = 0; a < kAP; ++a) dq[a] = 0.f;
+      if (r >= 0) {
+        const float* qr = QS + s * kAP;
+        float qmax = -INFINITY;
+        for (int a = 0; a < p.A; ++a) qmax = fmaxf(qmax, qr[a]);
+        const float t = p.rewards[r] + (p.gamma * NMAX[s]) * (1.f - p.dones[r]);
+        int64_t ai = p.actions[r];
+        if (ai < 0 || ai >= p.A) {
+          atomicOr(p.status, (uint32_t)PORL_FLAG_BAD_ACTION);
+          ai = ai < 0 ? 0 : p.A - 1;
+        }
+        float se = 0.f;
+        for (int a = 0; a < p.A; ++a) se += expf(qr[a] - qmax);
+        const float lse = qmax + logf(se);
+        const float qa = qr[ai];
+        const float diff = qa - t;
+        td_i = diff * diff;
+        pen_i = lse - logf((float)p.A) - qa;
+#pragma unroll
+        for (int a = 0; a < kAP; ++a)
+          if (a < p.A) {
+            const float onehot = (a == (int)ai) ? 1.f : 0.f;
+            dq[a] = p.inv_bn * (2.f * diff * onehot + p.alpha * (expf(qr[a] - lse) - onehot));
+          }
+      }
+#pragma unroll
+      for (int a = 0; a < kAP; ++a) DQ[s * kAP + a] = dq[a];
+      td_i = warp_sum(td_i);
+      pen_i = warp_sum(pen_i);
+      if (s == 0) {
+        td_sum += td_i;
+        pen_sum += pen_i;
+      }
+    }
+    __syncthreads();
+    // ---- backward
+    {  // dW3 (A x 64), db3
+      float* gw = part + p.w_off[3];
+      for (int o = threadIdx.x; o < p.A * kH3; o += kThreads) {
+        const int a = o / kH3, k = o - a * kH3;
+        float sacc = 0.f;
+        for (int s = 0; s < kT; ++s) sacc = fmaf(DQ[s * kAP + a], H3[s * kLd3 + k], sacc);
+        gw[o] = acc ? gw[o] + sacc : sacc;
+      }
+      if (threadIdx.x < kAP) {   // the bias block is pad4(A) <= 8 floats; pad entries stay zero
+        const int a = threadIdx.x;
+        if (a < ((p.A + 3) & ~3)) {
+          float sb = 0.f;
+          for (int s = 0; s < kT; ++s) sb += DQ[s * kAP + a];
+          float* gb = part + p.b_off[3];
+          gb[a] = acc ? gb[a] + sb : sb;
+        }
+      }
+    }
+    __syncthreads();
+    dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
+    __syncthreads();
+    dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
+    __syncthreads();
+    dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
+    __syncthreads();
+    dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
+    __syncthreads();
+    dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
+    __syncthreads();
+    dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    part[p.n_floats] = td_sum;
+    part[p.n_floats + 1] = pen_sum;
+  }
+}
+
+// grads[j] = sum over CTAs (in CTA order) of partial[c][j]; block 0 also finalises loss, td, penalty
+__global__ void __launch_bounds__(256)
+cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_stride, int64_t n_floats,
+                  float* __restrict__ grads, float* __restrict__ losses_out, float inv_bn, float alpha,
+                  uint32_t* status) {
+  pdl_entry();
+  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (j < n_floats) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int c = 0; c < n_part; ++c) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(partials + c * part_stride + j));
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(grads + j) = s;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float st = 0.f, sp = 0.f;
+    for (int c = 0; c < n_part; ++c) {
+      st += __ldcg(partials + c * part_stride + n_floats);
+      sp += __ldcg(partials + c * part_stride + n_floats + 1);
+    }
+    const float td = st * inv_bn, pen = sp * inv_bn;
+    const float loss = td + alpha * pen;
+    losses_out[0] = loss;
+    losses_out[1] = td;
+    losses_out[2] = pen;
+    if (!isfinite(loss)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
+  }
+}
+
+size_t cql_smem_bytes(int KP) {
+  const int ldx = KP + 4;
+  const int ws = kH1 * ldx > kW123Floats ? kH1 * ldx : kW123Floats;
+  const size_t floats = (size_t)kT * ldx + ws + kT * (kLd1 + kLd2 + kLd3) + kBiasFloats + 2 * kT * kAP + kT + kT;
+  return floats * sizeof(float);
+}
+
+}  // namespace
+}  // namespace porl
+
+using namespace porl;
+
+extern "C" int porl_cql_fused_supported(const porl_mlp_t* mlp) {
+  porl_mlp_desc_t d;
+  if (!mlp || porl_mlp_desc(mlp, &d) != PORL_OK) return 0;
+  if (d.n_nets != 1 || d.n_layers != 4 || d.layer_norm || d.out_act) return 0;
+  if (d.dims[1] != kH1 || d.dims[2] != kH2 || d.dims[3] != kH3) return 0;
+  if (d.dims[4] < 1 || d.dims[4] > kAP || d.dims[0] < 1) return 0;
+  const int KP = (int)round_up(d.dims[0], PORL_PAD);
+  return cql_smem_bytes(KP) <= 227 * 1024 ? 1 : 0;
+}
+
+extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const float* params,
+                                   const float* target_params, const float* states, const float* next_states,
+                                   int64_t ld_states, const int64_t* actions, const float* rewards,
+                                   const float* dones, const int64_t* idx, int64_t n_rows, float gamma, float alpha,
+                                   int64_t B, int64_t B_norm, float* grads, float* losses_out,
+                                   porl_stream_t stream) {
+  PORL_CHECK_ARG(ctx && mlp && params && target_params && states && next_states && actions && rewards && dones &&
+                 grads && losses_out, "porl_cql_fused_grad: null argument");
+  if (!porl_cql_fused_supported(mlp)) {
+    set_error("porl_cql_fused_grad: the fused kernel serves one ReLU net S -> 64 -> 128 -> 64 -> A (A <= 8, "
+              "pad32(S) <= 384) without LayerNorm");
+    return PORL_ERR_UNSUPPORTED;
+  }
+  porl_mlp_desc_t d;
+  porl_mlp_desc(mlp, &d);
+  const int KP = (int)round_up(d.dims[0], PORL_PAD);
+  PORL_CHECK_ARG(B > 0 && B_norm >= B && n_rows > 0 && n_rows < ((int64_t)1 << 31) && (idx || n_rows >= B),
+                 "porl_cql_fused_grad: B=%lld B_norm=%lld n_rows=%lld", (long long)B, (long long)B_norm,
+                 (long long)n_rows);
+  PORL_CHECK_ARG(ld_states >= KP && (ld_states & 3) == 0 && aligned16(states) && aligned16(next_states) &&
+                 aligned16(params) && aligned16(target_params) && aligned16(grads),
+                 "porl_cql_fused_grad: state rows must be padded to %d floats (pad columns zero) and 16-byte "
+                 "aligned (ld=%lld)", KP, (long long)ld_states);
+  CqlArgs a;
+  a.params = params;
+  a.target = target_params;
+  for (int l = 0; l < 4; ++l) {
+    int64_t ld = 0;
+    int rc = porl_mlp_param_layout(mlp, 0, l, PORL_PARAM_WEIGHT, &a.w_off[l], &ld);
+    if (rc == PORL_OK) rc = porl_mlp_param_layout(mlp, 0, l, PORL_PARAM_BIAS, &a.b_off[l], &ld);
+    if (rc != PORL_OK) return rc;
+  }
+  a.states = states;
+  a.next_states = next_states;
+  a.ld_states = ld_states;
+  a.actions = actions;
+  a.rewards = rewards;
+  a.dones = dones;
+  a.idx = idx;
+  a.n_rows = n_rows;
+  a.B = B;
+  a.KP = KP;
+  a.A = d.dims[4];
+  a.gamma = gamma;
+  a.alpha = alpha;
+  a.inv_bn = 1.0f / (float)B_norm;
+  a.n_floats = porl_mlp_param_floats(mlp);
+  a.part_stride = round_up(a.n_floats + 2, 4);
+  a.partials = ctx->tc_ws;
+  a.status = ctx->counters;
+  const int64_t n_tiles = (B + kT - 1) / kT;
+  const int grid = (int)(n_tiles < ctx->sm_count ? n_tiles : ctx->sm_count);
+  if ((int64_t)grid * a.part_stride > (int64_t)kTcWsFloats) {
+    set_error("porl_cql_fused_grad: %d gradient partials of %lld floats exceed the workspace", grid,
+              (long long)a.part_stride);
+    return PORL_ERR_WORKSPACE;
+  }
+  const size_t smem = cql_smem_bytes(KP);
+  static bool configured = false;
+  if (!configured) {
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  cudaStream_t st = as_stream(stream);
+  {
+    // algorithmic flop of SURVEY 8d: 2 forwards + dW of every layer + dX of layers 2..4
+    double mac = 0.0, dx = 0.0;
+    for (int l = 0; l < 4; ++l) {
+      mac += (double)d.dims[l] * d.dims[l + 1];
+      if (l > 0) dx += (double)d.dims[l] * d.dims[l + 1];
+    }
+    ProfScope prof(ctx, PORL_CAT_CONTRACTION, 2.0 * (double)B * (3.0 * mac + dx), st);
+    PORL_CUDA(launch_pdl(ctx, cql_fused_kernel, grid, kThreads, smem, st, a));
+    PORL_LAUNCHED(ctx);
+  }
+  {
+    ProfScope prof(ctx, PORL_CAT_LOSS, (double)(grid + 1) * a.n_floats * 4.0, st);
+    const int blocks = (int)((a.n_floats / 4 + 255) / 256);
+    PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel, blocks, 256, 0, st, (const float*)a.partials, grid, a.part_stride,
+                         a.n_floats, grads, losses_out, a.inv_bn, alpha, ctx->counters));
+    PORL_LAUNCHED(ctx);
+  }
+  return PORL_OK;
+}

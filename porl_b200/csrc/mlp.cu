@@ -254,6 +254,12 @@ extern "C" int64_t porl_mlp_saved_floats(const porl_mlp_t* mlp, int64_t B) {
 
 extern "C" int64_t porl_mlp_out_ld(const porl_mlp_t* mlp) { return mlp ? mlp->ld_out : -1; }
 
+extern "C" int porl_mlp_desc(const porl_mlp_t* mlp, porl_mlp_desc_t* out) {
+  PORL_CHECK_ARG(mlp && out, "porl_mlp_desc: null argument");
+  *out = mlp->d;
+  return PORL_OK;
+}
+
 
 static void clear_group(GemmGroup& g) {
   g.A = g.B = nullptr;

@@ -54,9 +54,7 @@ class CQLTrainer(DQNTrainer):
 
     def learn(self) -> float:
         """cql_trainer.py:88-124: TD MSE + alpha * conservative penalty, one Adam step."""
-        idx = torch.as_tensor(self.replay_buffer.draw_indices(self.batch_size))
-        self._pb = self.replay_buffer.gather_packed(idx, getattr(self, "_pb", None))
-        self.learn_packed(self._pb)
+        self.learn_indices(torch.as_tensor(self.replay_buffer.draw_indices(self.batch_size)))
         loss, td, pen = self.read_losses()
         if hasattr(self, "logger"):                                     # cql_trainer.py:116-122
             self.logger.writer.add_scalar("Loss/TD", td, self.training_step)

@@ -1,6 +1,7 @@
 """DQN base trainer: constructor + offline loop of src/porl/train/dqn_trainer.py:35-91,93-117,182-231."""
 from __future__ import annotations
 
+import os
 from typing import List, Type
 
 import numpy as np
@@ -54,9 +55,41 @@ class DQNTrainer:
         self.training_step = 0
 
     # ------------------------------------------------------------------ one update on a device batch
+    @property
+    def fused(self) -> bool:
+        """The single-kernel update (porl_cql_fused_grad) serves this network shape and is not switched off."""
+        if not hasattr(self, "_fused_ok"):
+            self._fused_ok = bool(lib.porl_cql_fused_supported(self.q_network.plan.handle))
+        return self._fused_ok and os.environ.get("PORL_CQL_FUSED", "1") != "0"
+
+    def _fused_grad(self, states, next_states, ld, actions, rewards, dones, idx, n_rows: int, B: int) -> None:
+        check(lib.porl_cql_fused_grad(self.ctx.handle, self.q_network.plan.handle, self.q_group.params.data_ptr(),
+                                      self.target_network.flat.data_ptr(), states.data_ptr(), next_states.data_ptr(),
+                                      ld, actions.data_ptr(), rewards.data_ptr(), dones.data_ptr(),
+                                      idx.data_ptr() if idx is not None else None, n_rows, self.gamma,
+                                      float(self.cql_alpha), B, B * pdist.world_size(), self.q_group.grads.data_ptr(),
+                                      self.q_group.loss_ptr, _C.stream_ptr()))
+
+    def learn_indices(self, idx: torch.Tensor, hard_every: int = 0) -> None:
+        """TD (+ CQL) update on rows `idx` of the replay buffer; asynchronous.  With the fused kernel the rows go
+        from the HBM-resident buffer straight into shared memory (no gathered copy of the minibatch exists)."""
+        rb = self.replay_buffer
+        if not self.fused:
+            self._pb = rb.gather_packed(idx, getattr(self, "_pb", None))
+            return self.learn_packed(self._pb, hard_every)
+        if idx.device != self.device or idx.dtype != torch.int64 or not idx.is_contiguous():
+            idx = idx.to(self.device, torch.int64).contiguous()
+        self._fused_grad(rb._states, rb._next_states, rb.ld, rb.actions, rb.rewards, rb.dones, idx, rb.capacity,
+                         int(idx.shape[0]))
+        self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)
+
     def learn_packed(self, pb: PackedBatch, hard_every: int = 0) -> None:
         """TD (+ CQL) update on a packed minibatch; asynchronous.  losses land in q_group.tail[0:3]."""
         ctx, B, plan = self.ctx, pb.B, self.q_network.plan
+        if self.fused:
+            self._fused_grad(pb.obs, pb.next_obs, pb.ld_obs, pb.actions, pb.rewards, pb.dones, None, B, B)
+            self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)
+            return
         ws = self._ws
         scratch_t = ws.get(("scratch_t", B), plan.saved_floats(B))
         saved_q = ws.get(("saved_q", B), plan.saved_floats(B))
@@ -81,9 +114,7 @@ class DQNTrainer:
 
     def learn(self) -> float:
         """One gradient update on a batch drawn from the replay buffer (dqn_trainer.py:93-117)."""
-        idx = torch.as_tensor(self.replay_buffer.draw_indices(self.batch_size))
-        self._pb = self.replay_buffer.gather_packed(idx, getattr(self, "_pb", None))
-        self.learn_packed(self._pb)
+        self.learn_indices(torch.as_tensor(self.replay_buffer.draw_indices(self.batch_size)))
         return self.read_losses()[0]
 
     def sync_target(self) -> None:

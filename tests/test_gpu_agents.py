@@ -191,10 +191,13 @@ def test_free_running_drift_vs_oracle():
     np.testing.assert_allclose(la, l64, rtol=1e-3)
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, "fused"])
 @pytest.mark.parametrize("name", ["cql_small", "cql_real"])
-def test_cql_matches_reference_golden(golden, name, mode):
+def test_cql_matches_reference_golden(golden, name, mode, monkeypatch):
+    """mode 0 / 1: layer-by-layer kernels with FFMA / tcgen05 contractions; "fused": the single-kernel update."""
     from porl_b200 import CQLTrainer, QNetwork
+    monkeypatch.setenv("PORL_CQL_FUSED", "1" if mode == "fused" else "0")
+    mode = 0 if mode == "fused" else mode
     g = golden(name)
     S, A, B, n_rows, iters, freq, seed = (int(x) for x in g["meta"])
     t = CQLTrainer(state_size=S, action_size=A, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,

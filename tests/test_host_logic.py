@@ -120,7 +120,7 @@ def test_agent_state_dict_layout_and_kernel_sequence(dry_porl, kind):
     assert awr[14] == (S if kind == "por" else A)
 
 
-def test_cql_trainer_host_plumbing(dry_porl, tmp_path):
+def test_cql_trainer_host_plumbing(dry_porl, tmp_path, monkeypatch):
     from porl_b200 import CQLTrainer, QNetwork
     t = CQLTrainer(state_size=22, action_size=5, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
                    update_target_freq=10, device=torch.device("cpu"), network=QNetwork, log_dir=str(tmp_path))
@@ -138,10 +138,18 @@ def test_cql_trainer_host_plumbing(dry_porl, tmp_path):
                                s["next_observations"], s["terminals"])
     assert len(t.replay_buffer) == 100
     dry_porl.clear()
+    assert t.fused                                      # 22 -> 64 -> 128 -> 64 -> 5 is served by the single-kernel update
+    t.learn()
+    assert [c[0] for c in dry_porl] == ["porl_cql_fused_grad", "porl_adam_step"]
+    fused = dry_porl[0][1]
+    assert fused[6] == 32 and fused[11] == 100000 and fused[14] == 64 and fused[15] == 64   # ld, rows, B, B_norm
+    assert t.training_step == 1
+    monkeypatch.setenv("PORL_CQL_FUSED", "0")            # layer-by-layer path, kept for other network shapes
+    dry_porl.clear()
     t.learn()
     assert [c[0] for c in dry_porl] == ["porl_gather_soa", "porl_mlp_forward", "porl_cql_head",
                                        "porl_mlp_backward", "porl_adam_step"]
-    assert t.training_step == 1
+    assert t.training_step == 2
 
 
 def test_epoch_sampler_reproduces_dataloader_stream():
