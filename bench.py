@@ -473,7 +473,8 @@ def other_configs(a, device, table):
             t.ctx.profile(False)
             c = pr["contraction"]
             us = c["ms"] / max(c["launches"], 1) * 1e3
-            prof = {"kernel": "cql_fused_kernel (gather + 2 forwards + head + backward, fp32 FFMA)",
+            prof = {"kernel": "cql_fused_kernel (gather + 2 forwards + head + backward, "
+                              + ("mma.sync 3xTF32 tiles)" if a.gemm_mode == 1 else "fp32 FFMA tiles)"),
                     "us_per_launch": us, "achieved_tflops": c["work"] / (c["ms"] * 1e-3) * 1e-12,
                     "frac_of_ffma_peak": c["work"] / (c["ms"] * 1e-3) / 74.0e12,
                     "gather_gbs": 2.0 * B * S * 4 / (us * 1e-6) * 1e-9}

@@ -12,6 +12,7 @@
 //   Row strides are = 4 (mod 32) floats: the 8 sample rows / 4 neuron rows a warp touches per LDS.128 fall in
 //   distinct banks.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -69,13 +70,13 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& w, float ac
 
 // rows of the tile -> XS (asynchronous; rows past B are zero)
 __device__ __forceinline__ void load_rows(float* XS, int ldx, const float* table, int64_t ld, const int* rowsel,
-                                          int KP) {
+                                          int KP, int k0 = 0) {
   const int c4 = KP >> 2;
   for (int e = threadIdx.x; e < kT * c4; e += kThreads) {
     const int s = e / c4, c = e - s * c4;
-    float* d = XS + s * ldx + 4 * c;
+    float* d = XS + s * ldx + k0 + 4 * c;
     const int r = rowsel[s];
-    if (r >= 0) cp_async16(d, table + (int64_t)r * ld + 4 * c);
+    if (r >= 0) cp_async16(d, table + (int64_t)r * ld + k0 + 4 * c);
     else *reinterpret_cast<float4*>(d) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
@@ -86,6 +87,14 @@ __device__ __forceinline__ void load_mat(float* dst, int lds, const float* src, 
   for (int e = threadIdx.x; e < rows * c4; e += kThreads) {
     const int r = e / c4, c = e - r * c4;
     cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
+  }
+}
+// columns [k0, k0 + kc) of a dense (rows, ld_src) matrix
+__device__ __forceinline__ void load_mat_cols(float* dst, int lds, const float* src, int ld_src, int rows, int k0, int kc) {
+  const int c4 = kc >> 2;
+  for (int e = threadIdx.x; e < rows * c4; e += kThreads) {
+    const int r = e / c4, c = e - r * c4;
+    cp_async16(dst + r * lds + k0 + 4 * c, src + (int64_t)r * ld_src + k0 + 4 * c);
   }
 }
 
@@ -248,6 +257,171 @@ __device__ __forceinline__ void dw_layer(const float* dz, int ldz, const float* 
   }
 }
 
+
+// ---------------------------------------------------------------- warp-level 3xTF32 contractions (mma.sync m16n8k8)
+// fp32 operands are split in registers into tf32 hi + tf32 lo; acc += lo*hi + hi*lo + hi*hi keeps fp32-grade accuracy
+// (same scheme as the tcgen05 contraction of gemm_tc.cu).  Fragment reads are 32-bit LDS: with row strides = 4 (mod 32)
+// the 8 x 4 (row, k) pattern of a fragment covers the 32 banks exactly once.
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  // hi = x rounded to nearest tf32 (10 mantissa bits) by integer arithmetic on the bit pattern -- the carry of the
+  // rounding add propagates into the exponent as it should; lo = x - hi is exact in fp32 and is handed to the tensor
+  // core as is (it reads the upper 19 bits).  cvt.rna.tf32.f32 compiles to 4 instructions with an Inf/NaN guard that
+  // finite activations do not need: 3 full-rate ALU operations per element instead of 9.
+  hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// c (16 x 8 NB) += sum_k A(m, k) B(k, n) with A(m, k) = a[m a_ms + k a_ks], B(k, n) = b[k b_ks + n b_ns];
+// `a` / `b` already point at the tile's first row / column.  Thread (g = lane / 4, t = lane % 4) ends up with
+// c[nb][0..3] = C(g, 8 nb + 2t), C(g, 8 nb + 2t + 1), C(g + 8, 8 nb + 2t), C(g + 8, 8 nb + 2t + 1).
+template <int NB>
+__device__ __forceinline__ void warp_gemm(float (&c)[NB][4], const float* a, int a_ms, int a_ks, const float* b,
+                                          int b_ks, int b_ns, int K) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* ap = a + g * a_ms + t * a_ks;
+  const float* bp = b + t * b_ks + g * b_ns;
+#pragma unroll 2
+  for (int k = 0; k < K; k += 8) {
+    uint32_t ah[4], al[4];
+    split_tf32(ap[k * a_ks], ah[0], al[0]);
+    split_tf32(ap[8 * a_ms + k * a_ks], ah[1], al[1]);
+    split_tf32(ap[(k + 4) * a_ks], ah[2], al[2]);
+    split_tf32(ap[8 * a_ms + (k + 4) * a_ks], ah[3], al[3]);
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      uint32_t bh[2], bl[2];
+      split_tf32(bp[k * b_ks + nb * 8 * b_ns], bh[0], bl[0]);
+      split_tf32(bp[(k + 4) * b_ks + nb * 8 * b_ns], bh[1], bl[1]);
+      mma_tf32(c[nb], al, bh);
+      mma_tf32(c[nb], ah, bl);
+      mma_tf32(c[nb], ah, bh);
+    }
+  }
+}
+
+template <int NB>
+__device__ __forceinline__ void zero_acc(float (&c)[NB][4]) {
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[nb][i] = 0.f;
+}
+
+// out (32 x N) = relu(a (32 x K) w^T + bias), w (N x K); 8 warps: rows 16 (w & 1), columns (N / 4) (w >> 1)
+template <int N>
+__device__ __forceinline__ void fwd_layer_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
+                                              float* out, int ldo) {
+  constexpr int NB = N / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
+  float c[NB][4];
+  zero_acc<NB>(c);
+  warp_gemm<NB>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int n = n0 + 8 * nb + 2 * t;
+    const float b0 = b[n], b1 = b[n + 1];
+    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) = make_float2(fmaxf(c[nb][0] + b0, 0.f), fmaxf(c[nb][1] + b1, 0.f));
+    *reinterpret_cast<float2*>(out + (m0 + g + 8) * ldo + n) =
+        make_float2(fmaxf(c[nb][2] + b0, 0.f), fmaxf(c[nb][3] + b1, 0.f));
+  }
+}
+
+// wait until at most n of the most recently committed cp.async groups are still in flight
+__device__ __forceinline__ void cp_async_wait_pending(int n) {
+  if (n <= 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
+  else if (n == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
+  else if (n == 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
+  else asm volatile("cp.async.wait_group 3;" ::: "memory");
+}
+
+// Layer 0 with its operands still arriving: rows and W0 are loaded as column chunks of kChunk floats, one cp.async group
+// each; chunk c is multiplied while chunks c+1.. are in flight.  `younger` = groups committed after the chunk groups.
+constexpr int kChunk = 128;
+template <int N>
+__device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
+                                               float* out, int ldo, int younger) {
+  constexpr int NB = N / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
+  const int n_chunks = (K + kChunk - 1) / kChunk;
+  float c[NB][4];
+  zero_acc<NB>(c);
+  for (int ch = 0; ch < n_chunks; ++ch) {
+    cp_async_wait_pending(n_chunks - 1 - ch + younger);
+    __syncthreads();
+    const int k0 = ch * kChunk, kc = min(kChunk, K - k0);
+    warp_gemm<NB>(c, a + m0 * lda + k0, lda, 1, w + n0 * ldw + k0, 1, ldw, kc);
+  }
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int n = n0 + 8 * nb + 2 * t;
+    const float b0 = b[n], b1 = b[n + 1];
+    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) = make_float2(fmaxf(c[nb][0] + b0, 0.f), fmaxf(c[nb][1] + b1, 0.f));
+    *reinterpret_cast<float2*>(out + (m0 + g + 8) * ldo + n) =
+        make_float2(fmaxf(c[nb][2] + b0, 0.f), fmaxf(c[nb][3] + b1, 0.f));
+  }
+}
+
+// h (32 x K) <- (dz (32 x N) w) * [h > 0] in place, w (N x K): contraction over the layer's OUTPUT index n
+template <int K, int N>
+__device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const float* w, int ldw, float* h, int ldh) {
+  constexpr int NB = K / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int m0 = 16 * (warp & 1), n0 = (K / 4) * (warp >> 1);
+  float c[NB][4];
+  zero_acc<NB>(c);
+  warp_gemm<NB>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int n = n0 + 8 * nb + 2 * t;
+    float2* p0 = reinterpret_cast<float2*>(h + (m0 + g) * ldh + n);
+    float2* p1 = reinterpret_cast<float2*>(h + (m0 + g + 8) * ldh + n);
+    const float2 h0 = *p0, h1 = *p1;
+    *p0 = make_float2(h0.x > 0.f ? c[nb][0] : 0.f, h0.y > 0.f ? c[nb][1] : 0.f);
+    *p1 = make_float2(h1.x > 0.f ? c[nb][2] : 0.f, h1.y > 0.f ? c[nb][3] : 0.f);
+  }
+}
+
+// gw (N x K) (+)= dz^T (N x 32) a (32 x K); gb (N) (+)= column sums of dz.  Work units of 16 rows x 8 NB columns.
+template <int N, int NB>
+__device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const float* a, int lda, int K, float* gw,
+                                             float* gb, bool accumulate) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int col_units = K / (8 * NB), units = (N / 16) * col_units;
+  for (int u = warp; u < units; u += kThreads / 32) {
+    const int m0 = 16 * (u / col_units), n0 = 8 * NB * (u % col_units);
+    float c[NB][4];
+    zero_acc<NB>(c);
+    warp_gemm<NB>(c, dz + m0, 1, ldz, a + n0, lda, 1, kT);
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      const int n = n0 + 8 * nb + 2 * t;
+      float2* p0 = reinterpret_cast<float2*>(gw + (int64_t)(m0 + g) * K + n);
+      float2* p1 = reinterpret_cast<float2*>(gw + (int64_t)(m0 + g + 8) * K + n);
+      float2 o0 = make_float2(c[nb][0], c[nb][1]), o1 = make_float2(c[nb][2], c[nb][3]);
+      if (accumulate) {
+        const float2 q0 = *p0, q1 = *p1;
+        o0.x += q0.x; o0.y += q0.y; o1.x += q1.x; o1.y += q1.y;
+      }
+      *p0 = o0;
+      *p1 = o1;
+    }
+  }
+  if (threadIdx.x < N) {
+    float sb = 0.f;
+    for (int s = 0; s < kT; ++s) sb += dz[s * ldz + threadIdx.x];
+    gb[threadIdx.x] = accumulate ? gb[threadIdx.x] + sb : sb;
+  }
+}
+
+template <bool MMA>
 __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p) {
   pdl_entry();
   extern __shared__ __align__(16) float smem[];
@@ -290,12 +464,23 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     }
     __syncthreads();
     // ---- target network on next_states: max_a Q_tgt(s', a)     (cql_trainer.py:94-98)
-    load_rows(XS, ldx, p.next_states, p.ld_states, ROW, KP);
-    load_mat(WS, ldx, p.target + p.w_off[0], kH1, KP);
-    load_bias(BS, p.target, p.b_off, p.A);
-    cp_async_wait_all();
-    __syncthreads();
-    fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    if (MMA) {
+      for (int k0 = 0; k0 < KP; k0 += kChunk) {
+        const int kc = min(kChunk, KP - k0);
+        load_rows(XS, ldx, p.next_states, p.ld_states, ROW, kc, k0);
+        load_mat_cols(WS, ldx, p.target + p.w_off[0], KP, kH1, k0, kc);
+        cp_async_commit();
+      }
+      load_bias(BS, p.target, p.b_off, p.A);
+      fwd_layer0_mma<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);
+    } else {
+      load_rows(XS, ldx, p.next_states, p.ld_states, ROW, KP);
+      load_mat(WS, ldx, p.target + p.w_off[0], kH1, KP);
+      load_bias(BS, p.target, p.b_off, p.A);
+      cp_async_wait_all();
+      __syncthreads();
+      fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    }
     __syncthreads();
     load_w123(WS, p.target, p.w_off, p.A);
     cp_async_commit();
@@ -303,9 +488,9 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     cp_async_commit();
     cp_async_wait_but_last();
     __syncthreads();
-    fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -315,18 +500,27 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
       NMAX[threadIdx.x] = m;
     }
     // ---- online network on states                                (cql_trainer.py:100)
-    load_mat(WS, ldx, p.params + p.w_off[0], kH1, KP);
-    load_bias(BS, p.params, p.b_off, p.A);
-    cp_async_wait_all();
-    __syncthreads();
-    fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    if (MMA) {
+      for (int k0 = 0; k0 < KP; k0 += kChunk) {
+        load_mat_cols(WS, ldx, p.params + p.w_off[0], KP, kH1, k0, min(kChunk, KP - k0));
+        cp_async_commit();
+      }
+      load_bias(BS, p.params, p.b_off, p.A);
+      fwd_layer0_mma<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);   // the obs rows' group is older than the chunks
+    } else {
+      load_mat(WS, ldx, p.params + p.w_off[0], kH1, KP);
+      load_bias(BS, p.params, p.b_off, p.A);
+      cp_async_wait_all();
+      __syncthreads();
+      fwd_layer<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1);
+    }
     __syncthreads();
     load_w123(WS, p.params, p.w_off, p.A);
     cp_async_wait_all();
     __syncthreads();
-    fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -392,17 +586,20 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
       }
     }
     __syncthreads();
-    dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
+    if (MMA) dh_layer_mma<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
     __syncthreads();
-    dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
+    if (MMA) dw_layer_mma<kH3, 8>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
+    else dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
     __syncthreads();
-    dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
+    if (MMA) dh_layer_mma<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
     __syncthreads();
-    dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
+    if (MMA) dw_layer_mma<kH2, 8>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
+    else dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
     __syncthreads();
-    dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
+    if (MMA) dh_layer_mma<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
     __syncthreads();
-    dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
+    if (MMA) dw_layer_mma<kH1, 4>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
+    else dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
     __syncthreads();
   }
   if (threadIdx.x == 0) {
@@ -524,7 +721,8 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
   const size_t smem = cql_smem_bytes(KP);
   static bool configured = false;
   if (!configured) {
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   cudaStream_t st = as_stream(stream);
@@ -536,7 +734,11 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
       if (l > 0) dx += (double)d.dims[l] * d.dims[l + 1];
     }
     ProfScope prof(ctx, PORL_CAT_CONTRACTION, 2.0 * (double)B * (3.0 * mac + dx), st);
-    PORL_CUDA(launch_pdl(ctx, cql_fused_kernel, grid, kThreads, smem, st, a));
+    // contraction mode of the context: 0 = fp32 FFMA, 1 = tensor cores (mma.sync 3xTF32 here; PORL_CQL_MMA overrides)
+    static const int env_mma = getenv("PORL_CQL_MMA") ? atoi(getenv("PORL_CQL_MMA")) : -1;
+    const bool use_mma = env_mma >= 0 ? env_mma != 0 : ctx->gemm_mode == 1;
+    if (use_mma) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true>, grid, kThreads, smem, st, a));
+    else PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<false>, grid, kThreads, smem, st, a));
     PORL_LAUNCHED(ctx);
   }
   {

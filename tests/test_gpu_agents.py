@@ -191,13 +191,13 @@ def test_free_running_drift_vs_oracle():
     np.testing.assert_allclose(la, l64, rtol=1e-3)
 
 
-@pytest.mark.parametrize("mode", [0, 1, "fused"])
+@pytest.mark.parametrize("mode", [0, 1, "fused", "fused_mma"])
 @pytest.mark.parametrize("name", ["cql_small", "cql_real"])
 def test_cql_matches_reference_golden(golden, name, mode, monkeypatch):
-    """mode 0 / 1: layer-by-layer kernels with FFMA / tcgen05 contractions; "fused": the single-kernel update."""
+    """mode 0 / 1: layer-by-layer kernels with FFMA / tcgen05 contractions; "fused" / "fused_mma": the single-kernel update with FFMA / mma.sync 3xTF32 tiles."""
     from porl_b200 import CQLTrainer, QNetwork
-    monkeypatch.setenv("PORL_CQL_FUSED", "1" if mode == "fused" else "0")
-    mode = 0 if mode == "fused" else mode
+    monkeypatch.setenv("PORL_CQL_FUSED", "1" if str(mode).startswith("fused") else "0")
+    mode = {"fused": 0, "fused_mma": 1}.get(mode, mode)
     g = golden(name)
     S, A, B, n_rows, iters, freq, seed = (int(x) for x in g["meta"])
     t = CQLTrainer(state_size=S, action_size=A, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
@@ -217,7 +217,8 @@ def test_cql_matches_reference_golden(golden, name, mode, monkeypatch):
                                  bool(b["terminals"][i]))
         np.random.seed(seed + 3)
         losses = t.train_offline(num_iterations=iters, verbose=False)
-        np.testing.assert_allclose(losses, g["losses"], rtol=1e-5)
+        # the loss is td + penalty with the penalty a small difference of O(1) terms: absolute floor of a few fp32 ulps
+        np.testing.assert_allclose(losses, g["losses"], rtol=1e-5, atol=2e-7)
         for k, v in t.q_network.state_dict().items():
             assert_params_close(v, g["q/" + k], lr=5e-4, n_steps=iters, name=k)
         for k, v in t.target_network.state_dict().items():

@@ -1,6 +1,6 @@
 """A few fused CQL updates at the bench shape (QNetwork 362-64-128-64-5, 1M-row buffer), for ncu / timing.
 
-    python -m tools.cql_probe [batch] [updates]
+    python -m tools.cql_probe [batch] [updates] [mode: 0 FFMA tiles, 1 mma.sync 3xTF32 tiles]
 """
 import sys
 
@@ -12,6 +12,7 @@ sys.path.insert(0, ".")
 def main():
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
     n_upd = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+    mode = int(sys.argv[3]) if len(sys.argv) > 3 else 1
     from porl_b200 import CQLTrainer, QNetwork
     from porl_b200.buffer.replaybuffer import ReplayBuffer
     dev = torch.device("cuda:0")
@@ -25,6 +26,8 @@ def main():
                                0.1 * torch.randn(n, generator=g, device=dev),
                                st + 0.05 * torch.randn(n, S, generator=g, device=dev),
                                (torch.rand(n, generator=g, device=dev) < 0.01).float())
+    t.ctx.set_gemm_mode(mode)
+    t.ctx.set_pdl(False)                       # per-launch event times must not include the wait for the predecessor
     t.ctx.profile(True)
     for _ in range(n_upd):
         t.learn_indices(torch.randint(0, n, (B,), generator=g, device=dev), hard_every=10)
