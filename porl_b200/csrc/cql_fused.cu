@@ -71,31 +71,36 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& w, float ac
 // rows of the tile -> XS (asynchronous; rows past B are zero)
 __device__ __forceinline__ void load_rows(float* XS, int ldx, const float* table, int64_t ld, const int* rowsel,
                                           int KP, int k0 = 0) {
-  const int c4 = KP >> 2;
-  for (int e = threadIdx.x; e < kT * c4; e += kThreads) {
-    const int s = e / c4, c = e - s * c4;
-    float* d = XS + s * ldx + k0 + 4 * c;
+  const int c4 = KP >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int s = warp; s < kT; s += kThreads / 32) {
     const int r = rowsel[s];
-    if (r >= 0) cp_async16(d, table + (int64_t)r * ld + k0 + 4 * c);
-    else *reinterpret_cast<float4*>(d) = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = table + (int64_t)(r >= 0 ? r : 0) * ld + k0;
+    float* d = XS + s * ldx + k0;
+    for (int c = lane; c < c4; c += 32) {
+      if (r >= 0) cp_async16(d + 4 * c, src + 4 * c);
+      else *reinterpret_cast<float4*>(d + 4 * c) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
 }
 
 // dense (rows, cols) -> shared (rows, lds), cols % 4 == 0 (asynchronous)
 __device__ __forceinline__ void load_mat(float* dst, int lds, const float* src, int rows, int cols) {
   const int c4 = cols >> 2;
-  for (int e = threadIdx.x; e < rows * c4; e += kThreads) {
-    const int r = e / c4, c = e - r * c4;
-    cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
+  if (c4 >= 32) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int r = warp; r < rows; r += kThreads / 32)
+      for (int c = lane; c < c4; c += 32) cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
+  } else {          // 16 float4 per row (64-wide matrices): half a warp per row
+    const int lane = threadIdx.x & 15, hw = threadIdx.x >> 4;
+    for (int r = hw; r < rows; r += kThreads / 16)
+      for (int c = lane; c < c4; c += 16) cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
   }
 }
 // columns [k0, k0 + kc) of a dense (rows, ld_src) matrix
 __device__ __forceinline__ void load_mat_cols(float* dst, int lds, const float* src, int ld_src, int rows, int k0, int kc) {
-  const int c4 = kc >> 2;
-  for (int e = threadIdx.x; e < rows * c4; e += kThreads) {
-    const int r = e / c4, c = e - r * c4;
-    cp_async16(dst + r * lds + k0 + 4 * c, src + (int64_t)r * ld_src + k0 + 4 * c);
-  }
+  const int c4 = kc >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int r = warp; r < rows; r += kThreads / 32)
+    for (int c = lane; c < c4; c += 32) cp_async16(dst + r * lds + k0 + 4 * c, src + (int64_t)r * ld_src + k0 + 4 * c);
 }
 
 __device__ __forceinline__ void load_w123(float* WS, const float* p, const int64_t* w_off, int A) {
@@ -280,13 +285,35 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], 
 // c (16 x 8 NB) += sum_k A(m, k) B(k, n) with A(m, k) = a[m a_ms + k a_ks], B(k, n) = b[k b_ks + n b_ns];
 // `a` / `b` already point at the tile's first row / column.  Thread (g = lane / 4, t = lane % 4) ends up with
 // c[nb][0..3] = C(g, 8 nb + 2t), C(g, 8 nb + 2t + 1), C(g + 8, 8 nb + 2t), C(g + 8, 8 nb + 2t + 1).
-template <int NB>
-__device__ __forceinline__ void warp_gemm(float (&c)[NB][4], const float* a, int a_ms, int a_ks, const float* b,
+// The three partial products go to NC separate accumulator chains (lo*hi, hi*lo, hi*hi -> chain 0, 1 % NC, 2 % NC):
+// consecutive HMMAs then do not wait on each other, and the small terms are summed among themselves first.
+template <int NB, int NC>
+struct Acc {
+  float c[NC][NB][4];
+  __device__ __forceinline__ void zero() {
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) c[q][nb][i] = 0.f;
+  }
+  // total of the chains, small-term chains first
+  __device__ __forceinline__ float get(int nb, int i) const {
+    float v = c[0][nb][i];
+#pragma unroll
+    for (int q = 1; q < NC; ++q) v += c[q][nb][i];
+    return v;
+  }
+};
+
+template <int NB, int NC, int UNROLL>
+__device__ __forceinline__ void warp_gemm(Acc<NB, NC>& acc, const float* a, int a_ms, int a_ks, const float* b,
                                           int b_ks, int b_ns, int K) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const float* ap = a + g * a_ms + t * a_ks;
   const float* bp = b + t * b_ks + g * b_ns;
-#pragma unroll 2
+#pragma unroll UNROLL
   for (int k = 0; k < K; k += 8) {
     uint32_t ah[4], al[4];
     split_tf32(ap[k * a_ks], ah[0], al[0]);
@@ -298,19 +325,11 @@ __device__ __forceinline__ void warp_gemm(float (&c)[NB][4], const float* a, int
       uint32_t bh[2], bl[2];
       split_tf32(bp[k * b_ks + nb * 8 * b_ns], bh[0], bl[0]);
       split_tf32(bp[(k + 4) * b_ks + nb * 8 * b_ns], bh[1], bl[1]);
-      mma_tf32(c[nb], al, bh);
-      mma_tf32(c[nb], ah, bl);
-      mma_tf32(c[nb], ah, bh);
+      mma_tf32(acc.c[0][nb], al, bh);
+      mma_tf32(acc.c[1 % NC][nb], ah, bl);
+      mma_tf32(acc.c[2 % NC][nb], ah, bh);
     }
   }
-}
-
-template <int NB>
-__device__ __forceinline__ void zero_acc(float (&c)[NB][4]) {
-#pragma unroll
-  for (int nb = 0; nb < NB; ++nb)
-#pragma unroll
-    for (int i = 0; i < 4; ++i) c[nb][i] = 0.f;
 }
 
 // out (32 x N) = relu(a (32 x K) w^T + bias), w (N x K); 8 warps: rows 16 (w & 1), columns (N / 4) (w >> 1)
@@ -320,16 +339,17 @@ __device__ __forceinline__ void fwd_layer_mma(const float* a, int lda, int K, co
   constexpr int NB = N / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
-  float c[NB][4];
-  zero_acc<NB>(c);
-  warp_gemm<NB>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
+  Acc<NB, (NB <= 2 ? 3 : 2)> c;
+  c.zero();
+  warp_gemm<NB, (NB <= 2 ? 3 : 2), 4>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
     const int n = n0 + 8 * nb + 2 * t;
     const float b0 = b[n], b1 = b[n + 1];
-    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) = make_float2(fmaxf(c[nb][0] + b0, 0.f), fmaxf(c[nb][1] + b1, 0.f));
+    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) =
+        make_float2(fmaxf(c.get(nb, 0) + b0, 0.f), fmaxf(c.get(nb, 1) + b1, 0.f));
     *reinterpret_cast<float2*>(out + (m0 + g + 8) * ldo + n) =
-        make_float2(fmaxf(c[nb][2] + b0, 0.f), fmaxf(c[nb][3] + b1, 0.f));
+        make_float2(fmaxf(c.get(nb, 2) + b0, 0.f), fmaxf(c.get(nb, 3) + b1, 0.f));
   }
 }
 
@@ -351,21 +371,22 @@ __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
   const int n_chunks = (K + kChunk - 1) / kChunk;
-  float c[NB][4];
-  zero_acc<NB>(c);
+  Acc<NB, 3> c;
+  c.zero();
   for (int ch = 0; ch < n_chunks; ++ch) {
     cp_async_wait_pending(n_chunks - 1 - ch + younger);
     __syncthreads();
     const int k0 = ch * kChunk, kc = min(kChunk, K - k0);
-    warp_gemm<NB>(c, a + m0 * lda + k0, lda, 1, w + n0 * ldw + k0, 1, ldw, kc);
+    warp_gemm<NB, 3, 4>(c, a + m0 * lda + k0, lda, 1, w + n0 * ldw + k0, 1, ldw, kc);
   }
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
     const int n = n0 + 8 * nb + 2 * t;
     const float b0 = b[n], b1 = b[n + 1];
-    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) = make_float2(fmaxf(c[nb][0] + b0, 0.f), fmaxf(c[nb][1] + b1, 0.f));
+    *reinterpret_cast<float2*>(out + (m0 + g) * ldo + n) =
+        make_float2(fmaxf(c.get(nb, 0) + b0, 0.f), fmaxf(c.get(nb, 1) + b1, 0.f));
     *reinterpret_cast<float2*>(out + (m0 + g + 8) * ldo + n) =
-        make_float2(fmaxf(c[nb][2] + b0, 0.f), fmaxf(c[nb][3] + b1, 0.f));
+        make_float2(fmaxf(c.get(nb, 2) + b0, 0.f), fmaxf(c.get(nb, 3) + b1, 0.f));
   }
 }
 
@@ -375,17 +396,17 @@ __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const flo
   constexpr int NB = K / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int m0 = 16 * (warp & 1), n0 = (K / 4) * (warp >> 1);
-  float c[NB][4];
-  zero_acc<NB>(c);
-  warp_gemm<NB>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
+  Acc<NB, (NB <= 2 ? 3 : 2)> c;
+  c.zero();
+  warp_gemm<NB, (NB <= 2 ? 3 : 2), 4>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
     const int n = n0 + 8 * nb + 2 * t;
     float2* p0 = reinterpret_cast<float2*>(h + (m0 + g) * ldh + n);
     float2* p1 = reinterpret_cast<float2*>(h + (m0 + g + 8) * ldh + n);
     const float2 h0 = *p0, h1 = *p1;
-    *p0 = make_float2(h0.x > 0.f ? c[nb][0] : 0.f, h0.y > 0.f ? c[nb][1] : 0.f);
-    *p1 = make_float2(h1.x > 0.f ? c[nb][2] : 0.f, h1.y > 0.f ? c[nb][3] : 0.f);
+    *p0 = make_float2(h0.x > 0.f ? c.get(nb, 0) : 0.f, h0.y > 0.f ? c.get(nb, 1) : 0.f);
+    *p1 = make_float2(h1.x > 0.f ? c.get(nb, 2) : 0.f, h1.y > 0.f ? c.get(nb, 3) : 0.f);
   }
 }
 
@@ -397,15 +418,15 @@ __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const flo
   const int col_units = K / (8 * NB), units = (N / 16) * col_units;
   for (int u = warp; u < units; u += kThreads / 32) {
     const int m0 = 16 * (u / col_units), n0 = 8 * NB * (u % col_units);
-    float c[NB][4];
-    zero_acc<NB>(c);
-    warp_gemm<NB>(c, dz + m0, 1, ldz, a + n0, lda, 1, kT);
+    Acc<NB, (NB <= 4 ? 2 : 1)> c;
+    c.zero();
+    warp_gemm<NB, (NB <= 4 ? 2 : 1), 4>(c, dz + m0, 1, ldz, a + n0, lda, 1, kT);
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
       const int n = n0 + 8 * nb + 2 * t;
       float2* p0 = reinterpret_cast<float2*>(gw + (int64_t)(m0 + g) * K + n);
       float2* p1 = reinterpret_cast<float2*>(gw + (int64_t)(m0 + g + 8) * K + n);
-      float2 o0 = make_float2(c[nb][0], c[nb][1]), o1 = make_float2(c[nb][2], c[nb][3]);
+      float2 o0 = make_float2(c.get(nb, 0), c.get(nb, 1)), o1 = make_float2(c.get(nb, 2), c.get(nb, 3));
       if (accumulate) {
         const float2 q0 = *p0, q1 = *p1;
         o0.x += q0.x; o0.y += q0.y; o1.x += q1.x; o1.y += q1.y;
@@ -608,18 +629,30 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
   }
 }
 
-// grads[j] = sum over CTAs (in CTA order) of partial[c][j]; block 0 also finalises loss, td, penalty
+// grads[j] = sum over the CTAs' partials, in a fixed order (8 interleaved groups of CTAs summed in CTA order, then the
+// groups in group order): deterministic.  256 threads = 32 float4 columns x 8 groups; block 0 also finalises the losses.
 __global__ void __launch_bounds__(256)
 cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_stride, int64_t n_floats,
                   float* __restrict__ grads, float* __restrict__ losses_out, float inv_bn, float alpha,
                   uint32_t* status) {
   pdl_entry();
-  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  __shared__ float4 red[8][32];
+  const int col = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  const int64_t j = ((int64_t)blockIdx.x * 32 + col) * 4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (j < n_floats) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
-    for (int c = 0; c < n_part; ++c) {
+    for (int c = grp; c < n_part; c += 8) {
       const float4 v = __ldcg(reinterpret_cast<const float4*>(partials + c * part_stride + j));
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  }
+  red[grp][col] = s;
+  __syncthreads();
+  if (grp == 0 && j < n_floats) {
+#pragma unroll
+    for (int q = 1; q < 8; ++q) {
+      const float4 v = red[q][col];
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
     *reinterpret_cast<float4*>(grads + j) = s;
@@ -743,7 +776,7 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
   }
   {
     ProfScope prof(ctx, PORL_CAT_LOSS, (double)(grid + 1) * a.n_floats * 4.0, st);
-    const int blocks = (int)((a.n_floats / 4 + 255) / 256);
+    const int blocks = (int)((a.n_floats / 4 + 31) / 32);
     PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel, blocks, 256, 0, st, (const float*)a.partials, grid, a.part_stride,
                          a.n_floats, grads, losses_out, a.inv_bn, alpha, ctx->counters));
     PORL_LAUNCHED(ctx);
