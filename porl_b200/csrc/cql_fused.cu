@@ -209,9 +209,9 @@ __device__ __forceinline__ void dh_layer(const float* dz, int ldz, const float* 
     }
 }
 
-// gw[n][k] (+)= sum_s dz[s][n] a[s][k];  gb[n] (+)= sum_s dz[s][n].   thread tile 4 n x CJ float4 columns of k
+// gw[n][k] (+)= sum_s dz[s][n] a[s][k];   thread tile 4 n x CJ float4 columns of k
 template <int N, int CJ>
-__device__ __forceinline__ void dw_layer(const float* dz, int ldz, const float* a, int lda, int K, float* gw, float* gb,
+__device__ __forceinline__ void dw_layer(const float* dz, int ldz, const float* a, int lda, int K, float* gw,
                                          bool accumulate) {
   constexpr int NG = N / 4, TK = kThreads / NG;
   const int kg = threadIdx.x % TK, ngp = threadIdx.x / TK;
@@ -255,11 +255,6 @@ __device__ __forceinline__ void dw_layer(const float* dz, int ldz, const float* 
         *gp = o;
       }
     }
-  if (threadIdx.x < N) {
-    float sb = 0.f;
-    for (int s = 0; s < kT; ++s) sb += dz[s * ldz + threadIdx.x];
-    gb[threadIdx.x] = accumulate ? gb[threadIdx.x] + sb : sb;
-  }
 }
 
 
@@ -410,10 +405,10 @@ __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const flo
   }
 }
 
-// gw (N x K) (+)= dz^T (N x 32) a (32 x K); gb (N) (+)= column sums of dz.  Work units of 16 rows x 8 NB columns.
+// gw (N x K) (+)= dz^T (N x 32) a (32 x K).  Work units of 16 rows x 8 NB columns.
 template <int N, int NB>
 __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const float* a, int lda, int K, float* gw,
-                                             float* gb, bool accumulate) {
+                                             bool accumulate) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int col_units = K / (8 * NB), units = (N / 16) * col_units;
   for (int u = warp; u < units; u += kThreads / 32) {
@@ -434,11 +429,6 @@ __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const flo
       *p0 = o0;
       *p1 = o1;
     }
-  }
-  if (threadIdx.x < N) {
-    float sb = 0.f;
-    for (int s = 0; s < kT; ++s) sb += dz[s * ldz + threadIdx.x];
-    gb[threadIdx.x] = accumulate ? gb[threadIdx.x] + sb : sb;
   }
 }
 
@@ -609,18 +599,39 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     __syncthreads();
     if (MMA) dh_layer_mma<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
     __syncthreads();
-    if (MMA) dw_layer_mma<kH3, 8>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
-    else dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], part + p.b_off[2], acc);
+    if (MMA) dw_layer_mma<kH3, 8>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
+    else dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
     __syncthreads();
     if (MMA) dh_layer_mma<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
     __syncthreads();
-    if (MMA) dw_layer_mma<kH2, 8>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
-    else dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], part + p.b_off[1], acc);
+    if (MMA) dw_layer_mma<kH2, 8>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
+    else dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
     __syncthreads();
     if (MMA) dh_layer_mma<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
     __syncthreads();
-    if (MMA) dw_layer_mma<kH1, 4>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
-    else dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], part + p.b_off[0], acc);
+    if (MMA) dw_layer_mma<kH1, 4>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
+    else dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
+    {  // bias gradients of the hidden layers: column sums of dz1 | dz2 | dz3, which the backward pass left in
+       // H1 | H2 | H3 -- 64 + 128 + 64 columns, one per thread
+      static_assert(kH1 + kH2 + kH3 == kThreads, "one thread per hidden unit");
+      const int tid = threadIdx.x;
+      const float* src;
+      int ld;
+      float* gb;
+      if (tid < kH1) { src = H1 + tid; ld = kLd1; gb = part + p.b_off[0] + tid; }
+      else if (tid < kH1 + kH2) { src = H2 + tid - kH1; ld = kLd2; gb = part + p.b_off[1] + tid - kH1; }
+      else { src = H3 + tid - kH1 - kH2; ld = kLd3; gb = part + p.b_off[2] + tid - kH1 - kH2; }
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int r = 0; r < kT; r += 4) {
+        s0 += src[r * ld];
+        s1 += src[(r + 1) * ld];
+        s2 += src[(r + 2) * ld];
+        s3 += src[(r + 3) * ld];
+      }
+      const float sb = (s0 + s1) + (s2 + s3);
+      *gb = acc ? *gb + sb : sb;
+    }
     __syncthreads();
   }
   if (threadIdx.x == 0) {
