@@ -328,7 +328,7 @@ __device__ __forceinline__ void warp_gemm(Acc<NB, NC>& acc, const float* a, int 
 }
 
 // out (32 x N) = relu(a (32 x K) w^T + bias), w (N x K); 8 warps: rows 16 (w & 1), columns (N / 4) (w >> 1)
-template <int N>
+template <int N, int U>
 __device__ __forceinline__ void fwd_layer_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
                                               float* out, int ldo) {
   constexpr int NB = N / 32;
@@ -336,7 +336,7 @@ __device__ __forceinline__ void fwd_layer_mma(const float* a, int lda, int K, co
   const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
   Acc<NB, (NB <= 2 ? 3 : 2)> c;
   c.zero();
-  warp_gemm<NB, (NB <= 2 ? 3 : 2), 4>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
+  warp_gemm<NB, (NB <= 2 ? 3 : 2), U>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
     const int n = n0 + 8 * nb + 2 * t;
@@ -359,7 +359,7 @@ __device__ __forceinline__ void cp_async_wait_pending(int n) {
 // Layer 0 with its operands still arriving: rows and W0 are loaded as column chunks of kChunk floats, one cp.async group
 // each; chunk c is multiplied while chunks c+1.. are in flight.  `younger` = groups committed after the chunk groups.
 constexpr int kChunk = 128;
-template <int N>
+template <int N, int U>
 __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
                                                float* out, int ldo, int younger) {
   constexpr int NB = N / 32;
@@ -372,7 +372,7 @@ __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, c
     cp_async_wait_pending(n_chunks - 1 - ch + younger);
     __syncthreads();
     const int k0 = ch * kChunk, kc = min(kChunk, K - k0);
-    warp_gemm<NB, 3, 4>(c, a + m0 * lda + k0, lda, 1, w + n0 * ldw + k0, 1, ldw, kc);
+    warp_gemm<NB, 3, U>(c, a + m0 * lda + k0, lda, 1, w + n0 * ldw + k0, 1, ldw, kc);
   }
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
@@ -386,14 +386,14 @@ __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, c
 }
 
 // h (32 x K) <- (dz (32 x N) w) * [h > 0] in place, w (N x K): contraction over the layer's OUTPUT index n
-template <int K, int N>
+template <int K, int N, int U>
 __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const float* w, int ldw, float* h, int ldh) {
   constexpr int NB = K / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int m0 = 16 * (warp & 1), n0 = (K / 4) * (warp >> 1);
   Acc<NB, (NB <= 2 ? 3 : 2)> c;
   c.zero();
-  warp_gemm<NB, (NB <= 2 ? 3 : 2), 4>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
+  warp_gemm<NB, (NB <= 2 ? 3 : 2), U>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
     const int n = n0 + 8 * nb + 2 * t;
@@ -406,7 +406,7 @@ __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const flo
 }
 
 // gw (N x K) (+)= dz^T (N x 32) a (32 x K).  Work units of 16 rows x 8 NB columns.
-template <int N, int NB>
+template <int N, int NB, int U>
 __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const float* a, int lda, int K, float* gw,
                                              bool accumulate) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
@@ -415,7 +415,7 @@ __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const flo
     const int m0 = 16 * (u / col_units), n0 = 8 * NB * (u % col_units);
     Acc<NB, (NB <= 4 ? 2 : 1)> c;
     c.zero();
-    warp_gemm<NB, (NB <= 4 ? 2 : 1), 4>(c, dz + m0, 1, ldz, a + n0, lda, 1, kT);
+    warp_gemm<NB, (NB <= 4 ? 2 : 1), (U > 2 ? 4 : 1)>(c, dz + m0, 1, ldz, a + n0, lda, 1, kT);
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
       const int n = n0 + 8 * nb + 2 * t;
@@ -432,7 +432,7 @@ __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const flo
   }
 }
 
-template <bool MMA>
+template <bool MMA, int U>
 __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p) {
   pdl_entry();
   extern __shared__ __align__(16) float smem[];
@@ -483,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
         cp_async_commit();
       }
       load_bias(BS, p.target, p.b_off, p.A);
-      fwd_layer0_mma<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);
+      fwd_layer0_mma<kH1, U>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);
     } else {
       load_rows(XS, ldx, p.next_states, p.ld_states, ROW, KP);
       load_mat(WS, ldx, p.target + p.w_off[0], kH1, KP);
@@ -499,9 +499,9 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     cp_async_commit();
     cp_async_wait_but_last();
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2, U>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3, U>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
         cp_async_commit();
       }
       load_bias(BS, p.params, p.b_off, p.A);
-      fwd_layer0_mma<kH1>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);   // the obs rows' group is older than the chunks
+      fwd_layer0_mma<kH1, U>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);   // the obs rows' group is older than the chunks
     } else {
       load_mat(WS, ldx, p.params + p.w_off[0], kH1, KP);
       load_bias(BS, p.params, p.b_off, p.A);
@@ -529,9 +529,9 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     load_w123(WS, p.params, p.w_off, p.A);
     cp_async_wait_all();
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2, U>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3, U>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -597,19 +597,19 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
       }
     }
     __syncthreads();
-    if (MMA) dh_layer_mma<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
+    if (MMA) dh_layer_mma<kH3, kAP, U>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
     __syncthreads();
-    if (MMA) dw_layer_mma<kH3, 8>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
+    if (MMA) dw_layer_mma<kH3, 8, U>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
     else dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
     __syncthreads();
-    if (MMA) dh_layer_mma<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
+    if (MMA) dh_layer_mma<kH2, kH3, U>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
     __syncthreads();
-    if (MMA) dw_layer_mma<kH2, 8>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
+    if (MMA) dw_layer_mma<kH2, 8, U>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
     else dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
     __syncthreads();
-    if (MMA) dh_layer_mma<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
+    if (MMA) dh_layer_mma<kH1, kH2, U>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
     __syncthreads();
-    if (MMA) dw_layer_mma<kH1, 4>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
+    if (MMA) dw_layer_mma<kH1, 4, U>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
     else dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
     {  // bias gradients of the hidden layers: column sums of dz1 | dz2 | dz3, which the backward pass left in
        // H1 | H2 | H3 -- 64 + 128 + 64 columns, one per thread
@@ -765,8 +765,9 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
   const size_t smem = cql_smem_bytes(KP);
   static bool configured = false;
   if (!configured) {
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   cudaStream_t st = as_stream(stream);
@@ -781,8 +782,12 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
     // contraction mode of the context: 0 = fp32 FFMA, 1 = tensor cores (mma.sync 3xTF32 here; PORL_CQL_MMA overrides)
     static const int env_mma = getenv("PORL_CQL_MMA") ? atoi(getenv("PORL_CQL_MMA")) : -1;
     const bool use_mma = env_mma >= 0 ? env_mma != 0 : ctx->gemm_mode == 1;
-    if (use_mma) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true>, grid, kThreads, smem, st, a));
-    else PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<false>, grid, kThreads, smem, st, a));
+    // PORL_CQL_UNROLL: k8-steps per loop body of the mma.sync variant (4: deep unrolling, 2: compact code -- the
+    // kernel runs most of its code once per tile, so instruction fetch is a first-order cost)
+    static const int env_unroll = getenv("PORL_CQL_UNROLL") ? atoi(getenv("PORL_CQL_UNROLL")) : 4;
+    if (use_mma && env_unroll <= 2) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 2>, grid, kThreads, smem, st, a));
+    else if (use_mma) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 4>, grid, kThreads, smem, st, a));
+    else PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<false, 4>, grid, kThreads, smem, st, a));
     PORL_LAUNCHED(ctx);
   }
   {

@@ -180,3 +180,27 @@ def test_fused_flags_bad_rows_and_actions(mode):
     t.read_losses()
     assert int(status[0]) & _C.FLAG_BAD_INDEX and not int(status[0]) & _C.FLAG_BAD_ACTION
     status.zero_()
+
+
+def test_fused_data_parallel_shards_sum_to_the_global_gradient(monkeypatch, mode):
+    """two ranks take halves of one global minibatch and scale by 1/B_global; the sum of their buckets
+    (what the peer-memory / NCCL gradient sum produces) equals the single-process gradient on all rows up to
+    summation order (<= 1e-6 rel-L2), and the summed loss tails equal the global losses."""
+    from porl_b200 import dist as pdist
+    S, A, B, n_rows = 362, 5, 512, 2000
+    t, o, b, acts = make(S, A, n_rows, 21)
+    idx = torch.as_tensor(np.random.default_rng(2).choice(n_rows, B, replace=False)).to(DEV)
+    rb = t.replay_buffer
+    args = (rb._states, rb._next_states, rb.ld, rb.actions, rb.rewards, rb.dones)
+    t._fused_grad(*args, idx, rb.capacity, B)
+    torch.cuda.synchronize()
+    g_all, l_all = t.q_group.grads.clone(), t.q_group.tail[0:3].clone()
+    monkeypatch.setattr(pdist, "world_size", lambda: 2)
+    parts, tails = [], []
+    for r in range(2):
+        t._fused_grad(*args, idx[r * B // 2:(r + 1) * B // 2].contiguous(), rb.capacity, B // 2)
+        torch.cuda.synchronize()
+        parts.append(t.q_group.grads.clone())
+        tails.append(t.q_group._local_tail[0:3].clone())
+    assert rel_l2(parts[0] + parts[1], g_all) <= 1e-6
+    np.testing.assert_allclose((tails[0] + tails[1]).cpu().numpy(), l_all.cpu().numpy(), rtol=2e-6, atol=1e-8)

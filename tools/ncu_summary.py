@@ -19,6 +19,7 @@ METRICS = [
     "launch__shared_mem_per_block_dynamic", "launch__cluster_size", "dram__bytes_read.sum", "dram__bytes_write.sum",
     "sm__pipe_tc_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__inst_executed_pipe_tc.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",   # legacy HMMA path (mma.sync)
     "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -35,6 +36,13 @@ METRICS = [
     "smsp__average_warp_latency_issue_stalled_not_selected.ratio",
     "smsp__average_warp_latency_issue_stalled_wait.ratio",
     "smsp__average_warp_latency_issue_stalled_sleeping.ratio",
+    "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active",
 ]
 
 
