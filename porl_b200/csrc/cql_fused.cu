@@ -72,7 +72,7 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& w, float ac
 __device__ __forceinline__ void load_rows(float* XS, int ldx, const float* table, int64_t ld, const int* rowsel,
                                           int KP, int k0 = 0) {
   const int c4 = KP >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int s = warp; s < kT; s += kThreads / 32) {
+  for (int s = warp; s < kT; s += (int)(blockDim.x >> 5)) {
     const int r = rowsel[s];
     const float* src = table + (int64_t)(r >= 0 ? r : 0) * ld + k0;
     float* d = XS + s * ldx + k0;
@@ -88,18 +88,18 @@ __device__ __forceinline__ void load_mat(float* dst, int lds, const float* src, 
   const int c4 = cols >> 2;
   if (c4 >= 32) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int r = warp; r < rows; r += kThreads / 32)
+    for (int r = warp; r < rows; r += (int)(blockDim.x >> 5))
       for (int c = lane; c < c4; c += 32) cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
   } else {          // 16 float4 per row (64-wide matrices): half a warp per row
     const int lane = threadIdx.x & 15, hw = threadIdx.x >> 4;
-    for (int r = hw; r < rows; r += kThreads / 16)
+    for (int r = hw; r < rows; r += (int)(blockDim.x >> 4))
       for (int c = lane; c < c4; c += 16) cp_async16(dst + r * lds + 4 * c, src + (int64_t)r * cols + 4 * c);
   }
 }
 // columns [k0, k0 + kc) of a dense (rows, ld_src) matrix
 __device__ __forceinline__ void load_mat_cols(float* dst, int lds, const float* src, int ld_src, int rows, int k0, int kc) {
   const int c4 = kc >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int r = warp; r < rows; r += kThreads / 32)
+  for (int r = warp; r < rows; r += (int)(blockDim.x >> 5))
     for (int c = lane; c < c4; c += 32) cp_async16(dst + r * lds + k0 + 4 * c, src + (int64_t)r * ld_src + k0 + 4 * c);
 }
 
@@ -107,11 +107,11 @@ __device__ __forceinline__ void load_w123(float* WS, const float* p, const int64
   load_mat(WS, kLd1, p + w_off[1], kH2, kH1);
   load_mat(WS + kW1Floats, kLd2, p + w_off[2], kH3, kH2);
   load_mat(WS + kW1Floats + kW2Floats, kLd3, p + w_off[3], A, kH3);
-  for (int e = threadIdx.x; e < (kAP - A) * kLd3; e += kThreads) WS[kW1Floats + kW2Floats + A * kLd3 + e] = 0.f;
+  for (int e = threadIdx.x; e < (kAP - A) * kLd3; e += (int)blockDim.x) WS[kW1Floats + kW2Floats + A * kLd3 + e] = 0.f;
 }
 
 __device__ __forceinline__ void load_bias(float* BS, const float* p, const int64_t* b_off, int A) {
-  for (int e = threadIdx.x; e < kBiasFloats; e += kThreads) {
+  for (int e = threadIdx.x; e < kBiasFloats; e += (int)blockDim.x) {
     float v;
     if (e < kH1) v = p[b_off[0] + e];
     else if (e < kH1 + kH2) v = p[b_off[1] + e - kH1];
@@ -154,6 +154,7 @@ __device__ __forceinline__ void fwd_layer(const float* a, int lda, int K, const 
 
 // q[s][a] = b[a] + sum_k h3[s][k] w3[a][k]   (no activation), a < kAP (rows >= A of w3 and b are zero)
 __device__ __forceinline__ void head_fwd(const float* h3, const float* w3, const float* b, float* q) {
+  if (threadIdx.x >= kT * kAP) return;
   const int s = threadIdx.x >> 3, a = threadIdx.x & 7;
   float acc = 0.f;
 #pragma unroll 4
@@ -328,12 +329,12 @@ __device__ __forceinline__ void warp_gemm(Acc<NB, NC>& acc, const float* a, int 
 }
 
 // out (32 x N) = relu(a (32 x K) w^T + bias), w (N x K); 8 warps: rows 16 (w & 1), columns (N / 4) (w >> 1)
-template <int N, int U>
+template <int N, int U, int NW>
 __device__ __forceinline__ void fwd_layer_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
                                               float* out, int ldo) {
-  constexpr int NB = N / 32;
+  constexpr int NB = N / (4 * NW);         // NW / 2 column groups of 8 NB columns
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
+  const int m0 = 16 * (warp & 1), n0 = 8 * NB * (warp >> 1);
   Acc<NB, (NB <= 2 ? 3 : 2)> c;
   c.zero();
   warp_gemm<NB, (NB <= 2 ? 3 : 2), U>(c, a + m0 * lda, lda, 1, w + n0 * ldw, 1, ldw, K);
@@ -359,12 +360,12 @@ __device__ __forceinline__ void cp_async_wait_pending(int n) {
 // Layer 0 with its operands still arriving: rows and W0 are loaded as column chunks of kChunk floats, one cp.async group
 // each; chunk c is multiplied while chunks c+1.. are in flight.  `younger` = groups committed after the chunk groups.
 constexpr int kChunk = 128;
-template <int N, int U>
+template <int N, int U, int NW>
 __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, const float* w, int ldw, const float* b,
                                                float* out, int ldo, int younger) {
-  constexpr int NB = N / 32;
+  constexpr int NB = N / (4 * NW);         // NW / 2 column groups of 8 NB columns
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int m0 = 16 * (warp & 1), n0 = (N / 4) * (warp >> 1);
+  const int m0 = 16 * (warp & 1), n0 = 8 * NB * (warp >> 1);
   const int n_chunks = (K + kChunk - 1) / kChunk;
   Acc<NB, 3> c;
   c.zero();
@@ -386,11 +387,11 @@ __device__ __forceinline__ void fwd_layer0_mma(const float* a, int lda, int K, c
 }
 
 // h (32 x K) <- (dz (32 x N) w) * [h > 0] in place, w (N x K): contraction over the layer's OUTPUT index n
-template <int K, int N, int U>
+template <int K, int N, int U, int NW>
 __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const float* w, int ldw, float* h, int ldh) {
-  constexpr int NB = K / 32;
+  constexpr int NB = K / (4 * NW);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int m0 = 16 * (warp & 1), n0 = (K / 4) * (warp >> 1);
+  const int m0 = 16 * (warp & 1), n0 = 8 * NB * (warp >> 1);
   Acc<NB, (NB <= 2 ? 3 : 2)> c;
   c.zero();
   warp_gemm<NB, (NB <= 2 ? 3 : 2), U>(c, dz + m0 * ldz, ldz, 1, w + n0, ldw, 1, N);
@@ -406,12 +407,12 @@ __device__ __forceinline__ void dh_layer_mma(const float* dz, int ldz, const flo
 }
 
 // gw (N x K) (+)= dz^T (N x 32) a (32 x K).  Work units of 16 rows x 8 NB columns.
-template <int N, int NB, int U>
+template <int N, int NB, int U, int NW>
 __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const float* a, int lda, int K, float* gw,
                                              bool accumulate) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int col_units = K / (8 * NB), units = (N / 16) * col_units;
-  for (int u = warp; u < units; u += kThreads / 32) {
+  for (int u = warp; u < units; u += NW) {
     const int m0 = 16 * (u / col_units), n0 = 8 * NB * (u % col_units);
     Acc<NB, (NB <= 4 ? 2 : 1)> c;
     c.zero();
@@ -432,8 +433,8 @@ __device__ __forceinline__ void dw_layer_mma(const float* dz, int ldz, const flo
   }
 }
 
-template <bool MMA, int U>
-__global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p) {
+template <bool MMA, int U, int NW>
+__global__ void __launch_bounds__(NW * 32, 1) cql_fused_kernel(const CqlArgs p) {
   pdl_entry();
   extern __shared__ __align__(16) float smem[];
   const int KP = p.KP, ldx = KP + 4;
@@ -483,7 +484,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
         cp_async_commit();
       }
       load_bias(BS, p.target, p.b_off, p.A);
-      fwd_layer0_mma<kH1, U>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);
+      fwd_layer0_mma<kH1, U, NW>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);
     } else {
       load_rows(XS, ldx, p.next_states, p.ld_states, ROW, KP);
       load_mat(WS, ldx, p.target + p.w_off[0], kH1, KP);
@@ -499,9 +500,9 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     cp_async_commit();
     cp_async_wait_but_last();
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH2, U>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2, U, NW>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH3, U>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3, U, NW>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -517,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
         cp_async_commit();
       }
       load_bias(BS, p.params, p.b_off, p.A);
-      fwd_layer0_mma<kH1, U>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);   // the obs rows' group is older than the chunks
+      fwd_layer0_mma<kH1, U, NW>(XS, ldx, KP, WS, ldx, B1, H1, kLd1, 0);   // the obs rows' group is older than the chunks
     } else {
       load_mat(WS, ldx, p.params + p.w_off[0], kH1, KP);
       load_bias(BS, p.params, p.b_off, p.A);
@@ -529,9 +530,9 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     load_w123(WS, p.params, p.w_off, p.A);
     cp_async_wait_all();
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH2, U>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
+    if (MMA) fwd_layer_mma<kH2, U, NW>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2); else fwd_layer<kH2>(H1, kLd1, kH1, W1s, kLd1, B2, H2, kLd2);
     __syncthreads();
-    if (MMA) fwd_layer_mma<kH3, U>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
+    if (MMA) fwd_layer_mma<kH3, U, NW>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3); else fwd_layer<kH3>(H2, kLd2, kH2, W2s, kLd2, B3, H3, kLd3);
     __syncthreads();
     head_fwd(H3, W3s, B4, QS);
     __syncthreads();
@@ -580,7 +581,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
     // ---- backward
     {  // dW3 (A x 64), db3
       float* gw = part + p.w_off[3];
-      for (int o = threadIdx.x; o < p.A * kH3; o += kThreads) {
+      for (int o = threadIdx.x; o < p.A * kH3; o += (int)blockDim.x) {
         const int a = o / kH3, k = o - a * kH3;
         float sacc = 0.f;
         for (int s = 0; s < kT; ++s) sacc = fmaf(DQ[s * kAP + a], H3[s * kLd3 + k], sacc);
@@ -597,24 +598,24 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
       }
     }
     __syncthreads();
-    if (MMA) dh_layer_mma<kH3, kAP, U>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
+    if (MMA) dh_layer_mma<kH3, kAP, U, NW>(DQ, kAP, W3s, kLd3, H3, kLd3); else dh_layer<kH3, kAP>(DQ, kAP, W3s, kLd3, H3, kLd3);                       // H3 <- dz3
     __syncthreads();
-    if (MMA) dw_layer_mma<kH3, 8, U>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
+    if (MMA) dw_layer_mma<kH3, (NW > 8 ? 4 : 8), U, NW>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
     else dw_layer<kH3, 2>(H3, kLd3, H2, kLd2, kH2, part + p.w_off[2], acc);
     __syncthreads();
-    if (MMA) dh_layer_mma<kH2, kH3, U>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
+    if (MMA) dh_layer_mma<kH2, kH3, U, NW>(H3, kLd3, W2s, kLd2, H2, kLd2); else dh_layer<kH2, kH3>(H3, kLd3, W2s, kLd2, H2, kLd2);                      // H2 <- dz2
     __syncthreads();
-    if (MMA) dw_layer_mma<kH2, 8, U>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
+    if (MMA) dw_layer_mma<kH2, (NW > 8 ? 4 : 8), U, NW>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
     else dw_layer<kH2, 2>(H2, kLd2, H1, kLd1, kH1, part + p.w_off[1], acc);
     __syncthreads();
-    if (MMA) dh_layer_mma<kH1, kH2, U>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
+    if (MMA) dh_layer_mma<kH1, kH2, U, NW>(H2, kLd2, W1s, kLd1, H1, kLd1); else dh_layer<kH1, kH2>(H2, kLd2, W1s, kLd1, H1, kLd1);                      // H1 <- dz1
     __syncthreads();
-    if (MMA) dw_layer_mma<kH1, 4, U>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
+    if (MMA) dw_layer_mma<kH1, 4, U, NW>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
     else dw_layer<kH1, 6>(H1, kLd1, XS, ldx, KP, part + p.w_off[0], acc);
     {  // bias gradients of the hidden layers: column sums of dz1 | dz2 | dz3, which the backward pass left in
        // H1 | H2 | H3 -- 64 + 128 + 64 columns, one per thread
       static_assert(kH1 + kH2 + kH3 == kThreads, "one thread per hidden unit");
-      const int tid = threadIdx.x;
+      const int tid = threadIdx.x < kThreads ? threadIdx.x : 0;      // warps past the first 8 repeat column 0 and skip the store
       const float* src;
       int ld;
       float* gb;
@@ -630,7 +631,7 @@ __global__ void __launch_bounds__(kThreads, 1) cql_fused_kernel(const CqlArgs p)
         s3 += src[(r + 3) * ld];
       }
       const float sb = (s0 + s1) + (s2 + s3);
-      *gb = acc ? *gb + sb : sb;
+      if (threadIdx.x < kThreads) *gb = acc ? *gb + sb : sb;
     }
     __syncthreads();
   }
@@ -765,9 +766,9 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
   const size_t smem = cql_smem_bytes(KP);
   static bool configured = false;
   if (!configured) {
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<false, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    PORL_CUDA(cudaFuncSetAttribute(cql_fused_kernel<true, 2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   cudaStream_t st = as_stream(stream);
@@ -780,14 +781,16 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
     }
     ProfScope prof(ctx, PORL_CAT_CONTRACTION, 2.0 * (double)B * (3.0 * mac + dx), st);
     // contraction mode of the context: 0 = fp32 FFMA, 1 = tensor cores (mma.sync 3xTF32 here; PORL_CQL_MMA overrides)
-    static const int env_mma = getenv("PORL_CQL_MMA") ? atoi(getenv("PORL_CQL_MMA")) : -1;
+    const int env_mma = getenv("PORL_CQL_MMA") ? atoi(getenv("PORL_CQL_MMA")) : -1;
     const bool use_mma = env_mma >= 0 ? env_mma != 0 : ctx->gemm_mode == 1;
-    // PORL_CQL_UNROLL: k8-steps per loop body of the mma.sync variant (4: deep unrolling, 2: compact code -- the
-    // kernel runs most of its code once per tile, so instruction fetch is a first-order cost)
-    static const int env_unroll = getenv("PORL_CQL_UNROLL") ? atoi(getenv("PORL_CQL_UNROLL")) : 4;
-    if (use_mma && env_unroll <= 2) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 2>, grid, kThreads, smem, st, a));
-    else if (use_mma) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 4>, grid, kThreads, smem, st, a));
-    else PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<false, 4>, grid, kThreads, smem, st, a));
+    // PORL_CQL_WARPS: 8 (256 threads, 16 x 16 warp tiles, default) or 16 (512 threads, 16 x 8 tiles, <= 128 registers).
+    // Measured equal within 3 % (53 vs 55 us at batch 4096): the contraction phases are bound by the legacy HMMA rate --
+    // 48 HMMA.1688.TF32 per SM take ~205 cycles with either warp count, i.e. ~17 cycles per instruction and
+    // sub-partition -- not by latency, so more resident warps do not help.
+    const int env_warps = getenv("PORL_CQL_WARPS") ? atoi(getenv("PORL_CQL_WARPS")) : 8;
+    if (use_mma && env_warps >= 16) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 2, 16>, grid, 512, smem, st, a));
+    else if (use_mma) PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<true, 4, 8>, grid, kThreads, smem, st, a));
+    else PORL_CUDA(launch_pdl(ctx, cql_fused_kernel<false, 4, 8>, grid, kThreads, smem, st, a));
     PORL_LAUNCHED(ctx);
   }
   {

@@ -17,13 +17,15 @@ from oracle.steps import OracleCQL  # noqa: E402
 DEV = "cuda:0"
 
 
-@pytest.fixture(params=[0, 1], ids=["ffma", "mma3xtf32"])
-def mode(request):
-    """Contraction mode of the context: 0 = fp32 FFMA tiles, 1 = mma.sync 3xTF32 tiles inside the fused kernel."""
+@pytest.fixture(params=[(0, 8), (1, 16), (1, 8)], ids=["ffma", "mma3xtf32_16warps", "mma3xtf32"])
+def mode(request, monkeypatch):
+    """Contraction mode of the context: 0 = fp32 FFMA tiles, 1 = mma.sync 3xTF32 tiles inside the fused kernel (as a
+    256-thread CTA with 16 x 16 warp tiles, the default, or a 512-thread CTA with 16 x 8 warp tiles)."""
     from porl_b200 import _C
     ctx = _C.context(torch.device(DEV))
-    ctx.set_gemm_mode(request.param)
-    yield request.param
+    ctx.set_gemm_mode(request.param[0])
+    monkeypatch.setenv("PORL_CQL_WARPS", str(request.param[1]))
+    yield request.param[0]
     ctx.set_gemm_mode(0)
 
 
