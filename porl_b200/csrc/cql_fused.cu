@@ -641,20 +641,23 @@ __global__ void __launch_bounds__(NW * 32, 1) cql_fused_kernel(const CqlArgs p) 
   }
 }
 
-// grads[j] = sum over the CTAs' partials, in a fixed order (8 interleaved groups of CTAs summed in CTA order, then the
-// groups in group order): deterministic.  256 threads = 32 float4 columns x 8 groups; block 0 also finalises the losses.
-__global__ void __launch_bounds__(256)
+// grads[j] = sum over the CTAs' partials, in a fixed order (32 interleaved groups of CTAs summed in CTA order, then the
+// groups in group order): deterministic.  256 threads = 8 float4 columns x 32 groups, so every thread has at most
+// ceil(n_part / 32) independent 16-byte loads in flight (the partials are L2-resident: the fused kernel has just
+// written them); block 0 also finalises the losses.
+constexpr int kRedCols = 8, kRedGroups = 32;
+__global__ void __launch_bounds__(kRedCols * kRedGroups)
 cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_stride, int64_t n_floats,
                   float* __restrict__ grads, float* __restrict__ losses_out, float inv_bn, float alpha,
                   uint32_t* status) {
   pdl_entry();
-  __shared__ float4 red[8][32];
-  const int col = threadIdx.x & 31, grp = threadIdx.x >> 5;
-  const int64_t j = ((int64_t)blockIdx.x * 32 + col) * 4;
+  __shared__ float4 red[kRedGroups][kRedCols];
+  const int col = threadIdx.x % kRedCols, grp = threadIdx.x / kRedCols;
+  const int64_t j = ((int64_t)blockIdx.x * kRedCols + col) * 4;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (j < n_floats) {
 #pragma unroll 4
-    for (int c = grp; c < n_part; c += 8) {
+    for (int c = grp; c < n_part; c += kRedGroups) {
       const float4 v = __ldcg(reinterpret_cast<const float4*>(partials + c * part_stride + j));
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
@@ -663,24 +666,28 @@ cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_s
   __syncthreads();
   if (grp == 0 && j < n_floats) {
 #pragma unroll
-    for (int q = 1; q < 8; ++q) {
+    for (int q = 1; q < kRedGroups; ++q) {
       const float4 v = red[q][col];
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
     *reinterpret_cast<float4*>(grads + j) = s;
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
     float st = 0.f, sp = 0.f;
-    for (int c = 0; c < n_part; ++c) {
+    for (int c = threadIdx.x; c < n_part; c += 32) {
       st += __ldcg(partials + c * part_stride + n_floats);
       sp += __ldcg(partials + c * part_stride + n_floats + 1);
     }
-    const float td = st * inv_bn, pen = sp * inv_bn;
-    const float loss = td + alpha * pen;
-    losses_out[0] = loss;
-    losses_out[1] = td;
-    losses_out[2] = pen;
-    if (!isfinite(loss)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
+    st = warp_sum(st);
+    sp = warp_sum(sp);
+    if (threadIdx.x == 0) {
+      const float td = st * inv_bn, pen = sp * inv_bn;
+      const float loss = td + alpha * pen;
+      losses_out[0] = loss;
+      losses_out[1] = td;
+      losses_out[2] = pen;
+      if (!isfinite(loss)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
+    }
   }
 }
 
@@ -795,8 +802,8 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
   }
   {
     ProfScope prof(ctx, PORL_CAT_LOSS, (double)(grid + 1) * a.n_floats * 4.0, st);
-    const int blocks = (int)((a.n_floats / 4 + 31) / 32);
-    PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel, blocks, 256, 0, st, (const float*)a.partials, grid, a.part_stride,
+    const int blocks = (int)((a.n_floats / 4 + kRedCols - 1) / kRedCols);
+    PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel, blocks, kRedCols * kRedGroups, 0, st, (const float*)a.partials, grid, a.part_stride,
                          a.n_floats, grads, losses_out, a.inv_bn, alpha, ctx->counters));
     PORL_LAUNCHED(ctx);
   }
