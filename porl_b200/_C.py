@@ -201,6 +201,8 @@ class Context:
         sp = _p()
         check(lib.porl_ctx_status_ptr(self.handle, C.byref(sp)))
         self.status_ptr = sp.value
+        self.epoch = 0            # bumped by every option setter: CUDA graphs captured under older options are stale
+        self.profiling = False
 
     def status_tensor(self):
         """Zero-copy int32 torch view of the device status word (PORL_FLAG_* bits)."""
@@ -218,6 +220,7 @@ class Context:
 
     def profile(self, enable: bool) -> None:
         check(lib.porl_profile_enable(self.handle, int(enable)))
+        self.profiling, self.epoch = bool(enable), self.epoch + 1
 
     def profile_read(self) -> dict:
         """{category: {"launches", "ms", "work"}} of the launches recorded since profile(True)."""
@@ -232,18 +235,23 @@ class Context:
 
     def set_gemm_mode(self, mode: int) -> None:
         check(lib.porl_ctx_set_gemm_mode(self.handle, mode))
+        self.epoch += 1
 
     def set_tc_chunk(self, k_blocks: int) -> None:
         check(lib.porl_ctx_set_tc_chunk(self.handle, k_blocks))
+        self.epoch += 1
 
     def set_tc_variant(self, a_in_tmem: int) -> None:
         check(lib.porl_ctx_set_tc_variant(self.handle, a_in_tmem))
+        self.epoch += 1
 
     def set_pdl(self, enable: bool) -> None:
         check(lib.porl_ctx_set_pdl(self.handle, int(bool(enable))))
+        self.epoch += 1
 
     def set_tc_debug(self, ptr) -> None:
         check(lib.porl_ctx_set_tc_debug(self.handle, ptr))
+        self.epoch += 1
 
     @property
     def gemm_mode(self) -> int:

@@ -16,6 +16,8 @@ Kernel sequence of one update (all on the caller's current CUDA stream, no host 
 """
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import nn
 
@@ -96,6 +98,7 @@ class ExpectileAgent(nn.Module):
         self._status = self.ctx.status_tensor()
         self._packed: dict[int, PackedBatch] = {}
         self._features: dict[int, tuple[torch.Tensor, torch.Tensor]] = {}
+        self._graphs: dict[tuple, object] = {}
 
     # ------------------------------------------------------------------ batch packing
     def pack(self, observations, next_observations, rewards, terminals, actions=None) -> PackedBatch:
@@ -189,6 +192,38 @@ class ExpectileAgent(nn.Module):
 
     def value_update_packed(self, pb: PackedBatch) -> None:
         self._value_step(pb, *self._head_inputs(pb))
+
+    def _graphable(self) -> bool:
+        """The update may be replayed from a CUDA graph: MLP-only heads (the encoder's DropPath draws from torch's device
+        generator), no profiling, and no NCCL call inside the step (single process, or the peer-memory gradient sum)."""
+        if self.device.type != "cuda" or self.backbone is not None or os.environ.get("PORL_UPDATE_GRAPH", "1") == "0":
+            return False
+        if getattr(self.ctx, "profiling", False) or torch.cuda.is_current_stream_capturing():
+            return False
+        return not pdist.is_dp() or (self.v_group.peers is not None and self.p_group.peers is not None)
+
+    def _run_update(self, pb: PackedBatch, value_only: bool = False) -> None:
+        """`update_packed(pb)` on the agent's own packed minibatch (stable addresses) as ONE CUDA graph launch from the
+        third call at a batch size on: the reference-facing `update()` issues ~25 kernels, whose launch cost is what a
+        small-batch update is made of.  First call eager (allocates the workspaces), second call captures.  Graphs are
+        keyed by everything the launches bake in: batch size, the context's option epoch and the scalar
+        hyper-parameters (learning rates and step counters live on the device)."""
+        fn = self.value_update_packed if value_only else self.update_packed
+        if not self._graphable():
+            return fn(pb)
+        key = (pb.B, value_only, getattr(self.ctx, "epoch", 0), self.tau, self.alpha, self.discount, self.beta)
+        entry = self._graphs.get(key)
+        if entry is None:
+            if len(self._graphs) >= 16:
+                self._graphs.clear()
+            self._graphs[key] = False
+            return fn(pb)
+        if entry is False:
+            entry = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(entry):
+                fn(pb)
+            self._graphs[key] = entry
+        entry.replay()
 
     # ------------------------------------------------------------------ checkpoint extension (SURVEY.md 8f-4)
     def training_state_dict(self) -> dict:

@@ -45,5 +45,5 @@ class POR(ExpectileAgent):
     def por_residual_update(agent, observations, next_observations, rewards, terminals):
         """agent/por.py:73-112.  Returns (v_loss, g_loss) as Python floats (one host sync)."""
         pb = agent.pack(observations, next_observations, rewards, terminals)
-        agent.update_packed(pb)
+        agent._run_update(pb)
         return agent.read_losses()

@@ -40,11 +40,11 @@ class SORL(ExpectileAgent):
     def update(agent, observations, actions, rewards, next_observations, terminals):
         """agent/sorl.py:78-128.  Returns (v_loss, g_loss) as Python floats (one host sync)."""
         pb = agent.pack(observations, next_observations, rewards, terminals, actions)
-        agent.update_packed(pb)
+        agent._run_update(pb)
         return agent.read_losses()
 
     def vf_update(agent, observations, actions, rewards, next_observations, terminals):
         """agent/sorl.py:130-152: value step + Polyak update only; returns v_loss."""
         pb = agent.pack(observations, next_observations, rewards, terminals, actions)
-        agent.value_update_packed(pb)
+        agent._run_update(pb, value_only=True)
         return agent.read_losses()[0]

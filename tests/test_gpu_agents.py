@@ -284,3 +284,31 @@ def test_training_checkpoint_resumes_bitwise(kind, tmp_path):
     assert sched(agent).get_last_lr() == sched(fresh).get_last_lr() and sched(fresh).last_epoch == 6
     act = agent.select_action(rows[:5, :S])
     assert act.shape == (5, S if kind == "por" else A) and np.isfinite(act).all()
+
+
+@pytest.mark.parametrize("kind", ["sorl", "por"])
+def test_update_graph_replay_is_bitwise_equal_to_eager_launches(kind, monkeypatch):
+    """`agent.update()` replays its ~25 launches as one CUDA graph from the third call at a batch size on
+    (`_run_update`); same kernels, same arguments, so losses and parameters equal the eager path bit for bit, also across
+    a change of batch size, of a hyper-parameter baked into the launches, and of a context option."""
+    S, H, A, B = 30, 64, 2, 32
+    rows = torch.from_numpy(synth.laser_rows(B * 12, S, 31, A)).to(DEV)
+    graphed, _ = make_agent(kind, S, H, A, 50, 0.8, 3.0, 9)
+    eager, _ = make_agent(kind, S, H, A, 50, 0.8, 3.0, 9)
+    for i in range(10):
+        lo, hi = (i * B, (i + 1) * B) if i != 6 else (i * B, i * B + 17)        # one ragged batch in between
+        b = slice_row(rows[lo:hi], S, A)
+        if i == 4:
+            graphed.tau = eager.tau = 0.6
+        if i == 8:
+            graphed.ctx.set_pdl(False)
+        monkeypatch.setenv("PORL_UPDATE_GRAPH", "1")
+        lg = step(graphed, kind, b)
+        monkeypatch.setenv("PORL_UPDATE_GRAPH", "0")
+        le = step(eager, kind, b)
+        assert lg == le, (i, lg, le)
+    graphed.ctx.set_pdl(True)
+    assert any(isinstance(g, torch.cuda.CUDAGraph) for g in graphed._graphs.values())
+    assert not eager._graphs
+    for (k, a), (_, b) in zip(graphed.state_dict().items(), eager.state_dict().items()):
+        assert torch.equal(a, b), k

@@ -1,0 +1,115 @@
+"""2+ GPU check and timing of the data-parallel CQL update (BASELINE config 3: batch 4096, data-parallel).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        -m tools.dp_cql_check [steps]
+
+Every rank holds the same replay buffer and weights; each update takes a global batch of 4096 rows, rank r runs the
+fused kernel on its 4096 / world rows (gradients scaled by 1 / 4096) and the gradient sum over the ranks happens inside
+the Adam kernel over NVLink peer memory (porl_adam_step_peer) -- no NCCL call in the step, so it replays as one CUDA
+graph.  Checks: replicas stay bitwise identical, parameters agree with a single-process run on the same global batches
+to summation-order accuracy; then times strong scaling (global batch fixed) and weak scaling (4096 rows per rank).
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from porl_b200 import CQLTrainer, QNetwork, dist as pdist  # noqa: E402
+from porl_b200.buffer.replaybuffer import ReplayBuffer  # noqa: E402
+
+S, A, N_ROWS, B_GLOBAL = 362, 5, 200_000, 4096
+
+
+def make(device, dp: bool):
+    real = pdist.world_size, pdist.is_dp
+    if not dp:                                  # a single-process trainer inside the DP job: hide the process group
+        pdist.world_size, pdist.is_dp = (lambda: 1), (lambda: False)
+    try:
+        torch.manual_seed(1000)
+        t = CQLTrainer(state_size=S, action_size=A, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
+                       update_target_freq=10, device=device, network=QNetwork, log_dir="/tmp/porl_b200_dp_cql_logs")
+    finally:
+        pdist.world_size, pdist.is_dp = real
+    t.ctx.set_gemm_mode(1)
+    g = torch.Generator(device=device).manual_seed(3)
+    t.replay_buffer = ReplayBuffer(N_ROWS, (S,), device)
+    st = 3.5 * torch.rand(N_ROWS, S, generator=g, device=device)
+    t.replay_buffer.push_batch(st, torch.randint(0, A, (N_ROWS,), generator=g, device=device),
+                               0.1 * torch.randn(N_ROWS, generator=g, device=device),
+                               st + 0.05 * torch.randn(N_ROWS, S, generator=g, device=device),
+                               (torch.rand(N_ROWS, generator=g, device=device) < 0.01).float())
+    return t
+
+
+def main():
+    steps = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+    rank, local, world = pdist.init_from_env()
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    dp, single = make(device, True), make(device, False)
+    single.q_network.load_state_dict(dp.q_network.state_dict())
+    single.target_network.load_state_dict(dp.target_network.state_dict())
+    assert dp.q_group.peers is not None, "peer-memory gradient sum not active"
+    g = torch.Generator(device=device).manual_seed(5)          # same stream on every rank
+    shard = B_GLOBAL // world
+    for _ in range(steps):
+        idx = torch.randint(0, N_ROWS, (B_GLOBAL,), generator=g, device=device)
+        dp.learn_indices(idx[rank * shard:(rank + 1) * shard].contiguous(), hard_every=10)
+        real = pdist.world_size, pdist.is_dp
+        pdist.world_size, pdist.is_dp = (lambda: 1), (lambda: False)
+        try:
+            single.learn_indices(idx, hard_every=10)
+        finally:
+            pdist.world_size, pdist.is_dp = real
+    l_dp, l_one = dp.read_losses(), single.read_losses()
+    gathered = [torch.empty_like(dp.q_group.params) for _ in range(world)]
+    dist.all_gather(gathered, dp.q_group.params)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "replicas diverged bitwise"
+    rel = float((dp.q_group.params.double() - single.q_group.params.double()).norm() / single.q_group.params.double().norm())
+    worst = float((dp.q_group.params - single.q_group.params).abs().max())
+    assert worst <= 2 * 5e-4 * steps, worst                      # oracle/compare.py: rounding noise -> +-lr Adam steps
+
+    def rate(per_rank, n=300):
+        idx = torch.zeros(per_rank, dtype=torch.int64, device=device)
+        upd = lambda: dp.learn_indices(idx, hard_every=10)
+        upd()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            upd()
+        gi = torch.Generator(device=device).manual_seed(100 + rank)
+
+        def run(k):
+            for _ in range(k):
+                torch.randint(0, N_ROWS, (per_rank,), generator=gi, device=device, out=idx)
+                graph.replay()
+
+        run(10)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        run(n)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dp.read_losses()                                         # raises on PORL_FLAG_PEER_TIMEOUT
+        return n / (float(ms[0]) * 1e-3)
+
+    strong, weak = rate(shard), rate(B_GLOBAL)
+    if rank == 0:
+        print(f"world {world}: after {steps} updates DP vs single-process params rel-L2 {rel:.2e} (max abs {worst:.2e}); "
+              f"losses {l_dp} vs {l_one}; replicas bitwise identical")
+        print(f"CQL updates/s, graph replay, gradient sum inside the Adam kernel: global batch {B_GLOBAL} "
+              f"({shard}/GPU) {strong:.0f} | {B_GLOBAL}/GPU {weak:.0f} updates/s = {weak * world:.0f} batch-4096 units/s")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
