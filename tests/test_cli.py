@@ -62,3 +62,16 @@ def test_cli_runs_end_to_end(cmd):
         import torch
         sd = torch.load("/tmp/porl_b200_cli_weights/model_1.pt")
         assert "v_net.v1.0.weight" in sd and "policy.log_std" in sd and "v_tgt.v2.4.bias" in sd
+
+
+def test_sweep_grid_assignment():
+    """por_sweep.py (BASELINE config 5): replica -> (seed, tau), row-major over seeds x taus, wrapping."""
+    import por_sweep
+    taus, seeds = [0.5, 0.7, 0.9], [0, 1]
+    got = [por_sweep.grid_point(r, taus, seeds) for r in range(8)]
+    assert got == [(0, 0.5), (0, 0.7), (0, 0.9), (1, 0.5), (1, 0.7), (1, 0.9), (0, 0.5), (0, 0.7)]
+    a = por_sweep.parse(["--taus", "0.6,0.8", "--seeds", "3,4,5", "--rows", "1000"])
+    assert a.taus == [0.6, 0.8] and a.seeds == [3, 4, 5] and a.state_size == 365 and a.hidden_dim == 1024
+    import pytest
+    with pytest.raises(ValueError):
+        por_sweep.grid_point(0, [], [1])
