@@ -1,16 +1,21 @@
 // Fused discrete-CQL gradient: replay-buffer gather + target forward + online forward + TD/CQL head + backward of the
 // QNetwork S -> 64 -> 128 -> 64 -> A (src/porl/net/q_network.py:8-30) in ONE persistent kernel, weights staged in
-// shared memory, fp32 FFMA (the whole net is 160 KB: src/porl/train/cql_trainer.py:88-124 is launch-latency bound
-// when every layer is its own launch).  A second small kernel sums the per-CTA gradient partials in CTA order
+// shared memory (the whole net is 160 KB: src/porl/train/cql_trainer.py:88-124 is launch-latency bound when every
+// layer is its own launch).  A second small kernel sums the per-CTA gradient partials in a fixed order
 // (deterministic) into the optimizer bucket and finalises the three loss scalars.
 //
-//   tile = 32 transitions per CTA pass; 256 threads; shared memory (floats, KP = pad32(S)):
+// Two tile variants of the contractions, chosen by the context's gemm mode:
+//   mode 1  warp-level mma.sync m16n8k8 TF32 with the 3xTF32 hi/lo split done in registers (warp_gemm, *_mma)
+//   mode 0  register-tiled fp32 FFMA (fwd_layer, dh_layer, dw_layer) -- the exact-arithmetic yardstick
+//
+//   tile = 32 transitions per CTA pass; 256 threads (512 with PORL_CQL_WARPS=16); shared memory (floats, KP = pad32(S)):
 //     XS  [32][KP+4]     next_obs rows (target pass), then obs rows (kept for dW0)
 //     WS  max(64*(KP+4), 17696)   W0, then {W1 [128][68], W2 [64][132], W3 [8][68]} of the net being evaluated
 //     H1  [32][68]  H2 [32][132]  H3 [32][68]    activations, overwritten in place by dz on the way back
-//     BS  [264] biases, QS/DQ [32][8], NMAX [32]
-//   Row strides are = 4 (mod 32) floats: the 8 sample rows / 4 neuron rows a warp touches per LDS.128 fall in
-//   distinct banks.
+//     BS  [264] biases, QS/DQ [32][8], NMAX [32], ROW [32]
+//   Row strides are = 4 (mod 32) floats: an MMA fragment's 8 x 4 (row, k) reads cover the 32 banks once, and the 8
+//   sample rows / 4 neuron rows a warp touches per LDS.128 of the FFMA variant fall in distinct banks.
+// Measurements, the per-phase profile and what bounds the kernel: DESIGN.md section 3, profiles/r01_cql_fused_ncu.txt.
 #include <math.h>
 #include <stdlib.h>
 
