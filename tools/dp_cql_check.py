@@ -7,7 +7,8 @@ Every rank holds the same replay buffer and weights; each update takes a global 
 fused kernel on its 4096 / world rows (gradients scaled by 1 / 4096) and the gradient sum over the ranks happens inside
 the Adam kernel over NVLink peer memory (porl_adam_step_peer) -- no NCCL call in the step, so it replays as one CUDA
 graph.  Checks: replicas stay bitwise identical, parameters agree with a single-process run on the same global batches
-to summation-order accuracy; then times strong scaling (global batch fixed) and weak scaling (4096 rows per rank).
+to summation-order accuracy over the first updates (and within the Adam noise bound of oracle/compare.py after 30
+free-running ones); then times strong scaling (global batch fixed) and weak scaling (4096 rows per rank).
 """
 from __future__ import annotations
 
@@ -56,7 +57,13 @@ def main():
     assert dp.q_group.peers is not None, "peer-memory gradient sum not active"
     g = torch.Generator(device=device).manual_seed(5)          # same stream on every rank
     shard = B_GLOBAL // world
-    for _ in range(steps):
+    rel_l2 = lambda: float((dp.q_group.params.double() - single.q_group.params.double()).norm() /
+                           single.q_group.params.double().norm())
+    early = None
+    for it in range(steps):
+        if it == 5:         # before the first ReLU unit lands on different sides in the two runs: summation order only
+            early = rel_l2()
+            assert early <= 1e-6, early
         idx = torch.randint(0, N_ROWS, (B_GLOBAL,), generator=g, device=device)
         dp.learn_indices(idx[rank * shard:(rank + 1) * shard].contiguous(), hard_every=10)
         real = pdist.world_size, pdist.is_dp
@@ -69,7 +76,7 @@ def main():
     gathered = [torch.empty_like(dp.q_group.params) for _ in range(world)]
     dist.all_gather(gathered, dp.q_group.params)
     assert all(torch.equal(gathered[0], t) for t in gathered), "replicas diverged bitwise"
-    rel = float((dp.q_group.params.double() - single.q_group.params.double()).norm() / single.q_group.params.double().norm())
+    rel = rel_l2()
     worst = float((dp.q_group.params - single.q_group.params).abs().max())
     assert worst <= 2 * 5e-4 * steps, worst                      # oracle/compare.py: rounding noise -> +-lr Adam steps
 
@@ -103,7 +110,9 @@ def main():
 
     strong, weak = rate(shard), rate(B_GLOBAL)
     if rank == 0:
-        print(f"world {world}: after {steps} updates DP vs single-process params rel-L2 {rel:.2e} (max abs {worst:.2e}); "
+        print(f"world {world}: DP vs single-process params rel-L2 {early:.2e} after 5 updates (gradients agree to 1e-7; asserted "
+              f"<= 1e-6), {rel:.2e} after {steps} free-running updates (max abs {worst:.2e}: once one ReLU unit of one sample "
+              f"takes different sides -- parameters 2e-8 apart -- the gradient moves by O(1/B) and Adam amplifies it); "
               f"losses {l_dp} vs {l_one}; replicas bitwise identical")
         print(f"CQL updates/s, graph replay, gradient sum inside the Adam kernel: global batch {B_GLOBAL} "
               f"({shard}/GPU) {strong:.0f} | {B_GLOBAL}/GPU {weak:.0f} updates/s = {weak * world:.0f} batch-4096 units/s")
