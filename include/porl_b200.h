@@ -299,6 +299,56 @@ int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_group_t* peer
                         porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
                         float ema_beta, int32_t hard_every, porl_stream_t stream);
 
+/* ---- whole-update entry points (porl_sorl_step / porl_por_step) ----------------
+ * One POR / SORL gradient update as ONE call: the launch sequence of agent/por.py:73-112 and
+ * agent/sorl.py:78-128 (target + online TwinV forward, TD target and twin expectile loss, value backward,
+ * Adam + Polyak, online TwinV with the new weights + policy forward, advantage-weighted Gaussian NLL, policy
+ * backward, Adam with the cosine LR recursion) enqueued on `stream`; nothing synchronises, so the call can be
+ * captured into a CUDA graph.  All buffers are caller-owned device memory. */
+typedef struct {
+  float* params;               /* flat parameters of the optimizer group (policy group: MLP parameters | log_std) */
+  float* grads;                /* gradient bucket, same layout (every element rewritten each update) */
+  float* m;                    /* Adam exp_avg */
+  float* v;                    /* Adam exp_avg_sq */
+  int64_t n;                   /* floats in the group, a multiple of 4 */
+  porl_opt_state_t* state;     /* device-side optimizer clock */
+  float* loss;                 /* device scalar the loss kernel overwrites (data parallel: the bucket's tail, so the
+                                  loss rides the gradient sum) */
+  float beta1, beta2, eps;     /* torch.optim.Adam defaults .9, .999, 1e-8 (agent/por.py:61,64) */
+  int32_t pad_;
+  const porl_peer_group_t* peers;  /* data parallel: gradient sum inside the Adam kernel (porl_adam_step_peer), or NULL */
+} porl_opt_group_t;
+
+typedef struct {
+  porl_mlp_t* value_mlp;       /* TwinV (agent/value_functions.py:31-42): n_nets = 2, F -> H.. -> 1 */
+  porl_mlp_t* policy_mlp;      /* GaussianPolicy / BoundedGaussianPolicy mean net (agent/policy.py:12-49): F -> H.. -> D */
+  porl_opt_group_t value;      /* v_optimizer = Adam(vf.parameters(), value_lr) */
+  porl_opt_group_t policy;     /* Adam(policy.parameters(), policy_lr) + CosineAnnealingLR(max_steps) */
+  float* target_params;        /* v_target: deepcopy(vf), updated by the Polyak step only */
+  int64_t log_std_offset;      /* floats from policy.params to log_std (D values) */
+  float discount, tau, alpha, ema_beta;   /* gamma, expectile, AWR temperature, Polyak beta (util/util.py:54-56) */
+  int32_t awr_mode;            /* PORL_AWR_POR / PORL_AWR_SORL */
+  int32_t tanh_out;            /* 1: BoundedGaussianPolicy (SORL) */
+  int32_t policy_out;          /* D: state_size for POR's guide policy, action_size for SORL */
+  int32_t world;               /* data-parallel ranks sharing the global batch (losses are scaled by 1 / (B * world)) */
+} porl_agent_step_t;
+
+/* floats of scratch one update at batch B needs (saved activations of the four MLP evaluations, head outputs,
+ * loss gradients, TD targets); the same workspace serves every update at that batch size */
+int64_t porl_step_workspace_floats(const porl_agent_step_t* agent, int64_t B);
+/* SORL.update (agent/sorl.py:78-128) / SORL.vf_update (:130-152, value_only = 1) on a packed minibatch:
+ * x_obs / x_next (B, ld_x) are what the heads read (the padded states, or the scan encoder's features of obs and
+ * next_obs), actions (B, ld_act) the behaviour actions the policy regresses on. */
+int porl_sorl_step(porl_ctx_t* ctx, const porl_agent_step_t* agent, int64_t B, const float* x_obs,
+                   const float* x_next, int64_t ld_x, const float* actions, int64_t ld_act, const float* rewards,
+                   const float* dones, float* workspace, int64_t workspace_floats, int32_t value_only,
+                   porl_stream_t stream);
+/* POR.por_residual_update (agent/por.py:73-112): the guide policy regresses on the RAW next observations
+ * next_obs (B, ld_next) (after state2costmap's in-place clamp when an encoder is used), whatever the heads read. */
+int porl_por_step(porl_ctx_t* ctx, const porl_agent_step_t* agent, int64_t B, const float* x_obs,
+                  const float* x_next, int64_t ld_x, const float* next_obs, int64_t ld_next, const float* rewards,
+                  const float* dones, float* workspace, int64_t workspace_floats, porl_stream_t stream);
+
 /* ---- low-level contraction (exposed for tests and profiling) ------------------------------- */
 /* C[M,N] = opA(A)[M,K] * opB(B)[K,N] (+ bias[n]) with epilogue; trans flags:
  *   a_kmajor: A(m,k) = A[m*lda+k] else A[k*lda+m];  b_kmajor: B(k,n) = B[n*ldb+k] else B[k*ldb+n].

@@ -14,6 +14,13 @@ def train(args):
     device = torch.device(args.device)
     if device.type != "cuda":
         raise SystemExit("porl_b200 runs on CUDA (sm_100a) only; use the reference for --device cpu")
+    # torchrun: the process group and THIS rank's device come first -- the agent allocates its parameter and
+    # gradient buffers (and maps its peers' gradient buckets) at construction
+    from porl_b200 import dist as pdist
+    _, local, world = pdist.init_from_env()
+    if world > 1 or device.index is None:
+        device = torch.device("cuda", local if world > 1 else torch.cuda.current_device())
+    torch.cuda.set_device(device)
     torch.manual_seed(1000 + args.seed)
     backbone = None
     if args.backbone == "fasternet":                    # BASELINE config 4: POR with the FasterNet scan encoder

@@ -55,6 +55,19 @@ class PeerGroup(C.Structure):                      # porl_peer_group_t
                 ("tail_floats", C.c_int32), ("wait_ms", C.c_int32)]
 
 
+class OptGroup(C.Structure):                       # porl_opt_group_t
+    _fields_ = [("params", C.c_void_p), ("grads", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("n", C.c_int64),
+                ("state", C.c_void_p), ("loss", C.c_void_p), ("beta1", C.c_float), ("beta2", C.c_float),
+                ("eps", C.c_float), ("pad_", C.c_int32), ("peers", C.POINTER(PeerGroup))]
+
+
+class AgentStep(C.Structure):                      # porl_agent_step_t
+    _fields_ = [("value_mlp", C.c_void_p), ("policy_mlp", C.c_void_p), ("value", OptGroup), ("policy", OptGroup),
+                ("target_params", C.c_void_p), ("log_std_offset", C.c_int64), ("discount", C.c_float),
+                ("tau", C.c_float), ("alpha", C.c_float), ("ema_beta", C.c_float), ("awr_mode", C.c_int32),
+                ("tanh_out", C.c_int32), ("policy_out", C.c_int32), ("world", C.c_int32)]
+
+
 CATEGORIES = ("contraction", "gather", "loss", "optimizer", "norm", "transpose", "head", "encoder", "batchnorm", "pconv")
 
 
@@ -152,6 +165,9 @@ _SIGNATURES = {
     "porl_peer_export": (C.c_int, [_p, _p, C.c_char_p]),
     "porl_peer_open": (C.c_int, [_p, C.c_char_p, C.POINTER(C.c_void_p)]),
     "porl_peer_close": (C.c_int, [_p, _p]),
+    "porl_step_workspace_floats": (_i64, [C.POINTER(AgentStep), _i64]),
+    "porl_sorl_step": (C.c_int, [_p, C.POINTER(AgentStep), _i64, _p, _p, _i64, _p, _i64, _p, _p, _p, _i64, _i32, _p]),
+    "porl_por_step": (C.c_int, [_p, C.POINTER(AgentStep), _i64, _p, _p, _i64, _p, _i64, _p, _p, _p, _i64, _p]),
     "porl_gemm": (C.c_int, [_p, _i32, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p, _i64,
                             _i64, _p, _p, _i64, _p]),
     "porl_transpose": (C.c_int, [_p, _p, _i64, _i64, _i64, _p, _i64, _p]),

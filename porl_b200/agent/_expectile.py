@@ -16,6 +16,7 @@ Kernel sequence of one update (all on the caller's current CUDA stream, no host 
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 
 import torch
@@ -183,14 +184,56 @@ class ExpectileAgent(nn.Module):
     def _policy_target(self, pb: PackedBatch):
         raise NotImplementedError
 
+    def _whole_step(self) -> bool:
+        """The update runs through the C ABI's whole-step entry point (porl_sorl_step / porl_por_step) unless a host-side
+        NCCL all-reduce has to be issued between backward and optimizer (data parallel without peer-mapped buckets)."""
+        if os.environ.get("PORL_WHOLE_STEP", "1") == "0":
+            return False
+        return not pdist.is_dp() or (self.v_group.peers is not None and self.p_group.peers is not None)
+
+    def _step_desc(self) -> _C.AgentStep:
+        d = self.__dict__.get("_desc")
+        if d is None:
+            d = _C.AgentStep()
+            d.value_mlp, d.policy_mlp = self._value.plan.handle.value, self._policy.plan.handle.value
+            d.value, d.policy = self.v_group.c_group(), self.p_group.c_group()
+            d.target_params = self._target.flat.data_ptr()
+            d.log_std_offset = self._policy.log_std_offset
+            d.awr_mode, d.tanh_out, d.policy_out = self._awr_mode, int(self._bounded), self.policy_out
+            self.__dict__["_desc"] = d
+        d.discount, d.tau, d.alpha, d.ema_beta = self.discount, self.tau, self.alpha, self.beta   # plain attributes
+        d.world = pdist.world_size()
+        return d
+
+    def _c_step(self, pb: PackedBatch, value_only: bool) -> None:
+        x_obs, x_next, ld = self._head_inputs(pb)
+        d = self._step_desc()
+        n = int(lib.porl_step_workspace_floats(C.byref(d), pb.B))
+        ws = self._ws.get(("step", pb.B), n)
+        x, ld_x = self._policy_target(pb)
+        if self._awr_mode == _C.AWR_SORL:
+            check(lib.porl_sorl_step(self.ctx.handle, C.byref(d), pb.B, x_obs.data_ptr(), x_next.data_ptr(), ld,
+                                     x.data_ptr(), ld_x, pb.rewards.data_ptr(), pb.dones.data_ptr(), ws.data_ptr(), n,
+                                     int(value_only), _C.stream_ptr()))
+        elif value_only:
+            raise NotImplementedError("the reference's POR has no value-only update (SORL.vf_update, agent/sorl.py:130)")
+        else:
+            check(lib.porl_por_step(self.ctx.handle, C.byref(d), pb.B, x_obs.data_ptr(), x_next.data_ptr(), ld,
+                                    x.data_ptr(), ld_x, pb.rewards.data_ptr(), pb.dones.data_ptr(), ws.data_ptr(), n,
+                                    _C.stream_ptr()))
+
     def update_packed(self, pb: PackedBatch) -> None:
         """One gradient update on a packed device minibatch; asynchronous, returns nothing."""
+        if self._whole_step():
+            return self._c_step(pb, False)
         x_obs, x_next, ld = self._head_inputs(pb)
         self._value_step(pb, x_obs, x_next, ld)
         x, ld_x = self._policy_target(pb)
         self._policy_step(pb, x_obs, ld, x, ld_x)
 
     def value_update_packed(self, pb: PackedBatch) -> None:
+        if self._whole_step() and self._awr_mode == _C.AWR_SORL:
+            return self._c_step(pb, True)
         self._value_step(pb, *self._head_inputs(pb))
 
     def _graphable(self) -> bool:
@@ -227,9 +270,11 @@ class ExpectileAgent(nn.Module):
 
     # ------------------------------------------------------------------ checkpoint extension
     def training_state_dict(self) -> dict:
-        """Everything a bitwise-identical resume needs, on top of the reference-layout `state_dict()` that
+        """The agent's share of a bitwise-identical resume, on top of the reference-layout `state_dict()` that
         por_train.py:97 / sorl_train.py:74 save: both Adam groups (moments, step, current LR of the cosine
-        recursion) and the device RNG state the encoder's DropPath draws from."""
+        recursion) and the device RNG state the encoder's DropPath draws from.  The data order (sampler generator
+        state or device-sampler epoch, update and episode counters) is added by the training loop under "loop"
+        (porl_b200/train/offline_loop.py)."""
         return {"model": self.state_dict(), "v_optimizer": self.v_group.state_dict(),
                 "policy_optimizer": self.p_group.state_dict(),
                 "cuda_rng_state": torch.cuda.get_rng_state(self.device)}

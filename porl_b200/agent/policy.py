@@ -1,10 +1,9 @@
 """Gaussian policy heads (agent/policy.py:12-59) over one flat HBM buffer."""
 from __future__ import annotations
 
-import math
-
 import torch
 from torch import nn
+from torch.distributions import MultivariateNormal
 
 from .. import _C
 from ..nets import FlatMLP, InferenceMixin, MLPParams, pad_to
@@ -13,23 +12,13 @@ LOG_STD_MIN = -5.0  # agent/policy.py:8
 LOG_STD_MAX = 2.0   # agent/policy.py:9
 
 
-class DiagGaussian:
-    """What `policy(obs)` returns: the reference builds MultivariateNormal(mean, diag(std))
-    (agent/policy.py:18-23); only `.mean` (select_action, agent/sorl.py:76) and `.log_prob`
-    are used by its callers.  Convenience object, not on the update path."""
-
-    def __init__(self, mean: torch.Tensor, log_std: torch.Tensor):
-        self.mean = mean
-        self.log_std = log_std.clamp(LOG_STD_MIN, LOG_STD_MAX)
-        self.stddev = self.log_std.exp()
-
-    def log_prob(self, value: torch.Tensor) -> torch.Tensor:
-        z = (value - self.mean) / self.stddev
-        d = self.mean.shape[-1]
-        return -0.5 * (z * z).sum(-1) - self.log_std.sum() - 0.5 * d * math.log(2.0 * math.pi)
-
-    def sample(self) -> torch.Tensor:
-        return self.mean + self.stddev * torch.randn_like(self.mean)
+def policy_distribution(mean: torch.Tensor, log_std: torch.Tensor) -> MultivariateNormal:
+    """What `policy(obs)` returns: the reference's MultivariateNormal(mean, scale_tril=diag(std)) with
+    std = exp(clamp(log_std, -5, 2)) (agent/policy.py:18-23, :42-49), so `.mean`, `.log_prob`, `.sample`,
+    `.rsample`, `.entropy`, `.covariance_matrix` behave as there.  A convenience object for callers of the module
+    API (select_action, evaluation); the update path evaluates the same log-likelihood inside porl_awr_gauss_nll."""
+    std = torch.exp(log_std.clamp(LOG_STD_MIN, LOG_STD_MAX))
+    return MultivariateNormal(mean, scale_tril=torch.diag(std))
 
 
 class GaussianPolicy(nn.Module, InferenceMixin):
@@ -64,7 +53,7 @@ class GaussianPolicy(nn.Module, InferenceMixin):
 
     def forward(self, obs):
         mean = self._infer(self.plan, self.flat, obs)[0]
-        return DiagGaussian(mean, self.log_std.detach())
+        return policy_distribution(mean, self.log_std.detach())
 
     def act(self, obs, deterministic: bool = False, enable_grad: bool = False):
         dist = self(obs)

@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libporl_b200.so")
-SOURCES = ["api.cu", "cql_fused.cu", "encoder.cu", "gather.cu", "gemm_simt.cu", "gemm_tc.cu", "head.cu", "loss.cu", "mlp.cu", "optim.cu", "sampler.cu", "pointmlp.cu", "transpose.cu"]
+SOURCES = ["api.cu", "cql_fused.cu", "encoder.cu", "gather.cu", "gemm_simt.cu", "gemm_tc.cu", "head.cu", "loss.cu", "mlp.cu", "optim.cu", "sampler.cu", "pointmlp.cu", "step.cu", "transpose.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--threads", "0"]
 

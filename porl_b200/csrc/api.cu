@@ -199,6 +199,7 @@ extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, in
                          const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                          const float* bias, int32_t epilogue, const float* relu_src, int64_t ld_relu,
                          int64_t n_store, float* colsum, float* Ct, int64_t ldct, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx, "porl_gemm: null ctx");
   PORL_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1 << 24) && N < (1 << 24) && K < (1 << 24),
                  "porl_gemm: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);

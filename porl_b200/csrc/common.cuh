@@ -68,6 +68,19 @@ struct porl_ctx {
     }                                                                                \
   } while (0)
 
+// Entry points launch on the CURRENT device with the caller's pointers: a context created for another device would
+// silently run on the wrong GPU with foreign addresses (one process per GPU must cudaSetDevice before it builds
+// anything).  Refuse instead.
+#define PORL_ON_DEVICE(ctx)                                                          \
+  do {                                                                               \
+    int d_ = -1;                                                                     \
+    if ((ctx) != nullptr && (cudaGetDevice(&d_) != cudaSuccess || d_ != (ctx)->device)) { \
+      porl::set_error("%s: the context belongs to device %d but the current device is %d (call cudaSetDevice / " \
+                      "torch.cuda.set_device first)", __func__, (ctx)->device, d_); \
+      return PORL_ERR_INVALID;                                                       \
+    }                                                                                \
+  } while (0)
+
 // after a kernel launch: count it and surface launch-configuration errors
 #define PORL_LAUNCHED(ctx)                                                           \
   do {                                                                               \

@@ -724,6 +724,7 @@ extern "C" int porl_cql_fused_grad(porl_ctx_t* ctx, const porl_mlp_t* mlp, const
                                    const float* dones, const int64_t* idx, int64_t n_rows, float gamma, float alpha,
                                    int64_t B, int64_t B_norm, float* grads, float* losses_out,
                                    porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && mlp && params && target_params && states && next_states && actions && rewards && dones &&
                  grads && losses_out, "porl_cql_fused_grad: null argument");
   if (!porl_cql_fused_supported(mlp)) {

@@ -384,6 +384,7 @@ int mlp_block(porl_ctx* ctx, const EncWs& w, const porl_fn_block_t& blk, float* 
 using namespace porl;
 
 extern "C" int porl_costmap(porl_ctx_t* ctx, float* state, int64_t ld_state, int64_t B, float* out, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && state && out, "porl_costmap: null argument");
   PORL_CHECK_ARG(B >= 0 && B <= 65535 && ld_state >= kState, "porl_costmap: B=%lld ld_state=%lld", (long long)B,
                  (long long)ld_state);
@@ -401,6 +402,7 @@ extern "C" int64_t porl_fasternet_workspace_floats(int64_t B) { return B < 0 ? -
 extern "C" int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* net, float* state, int64_t ld_state,
                                       int64_t B, float* features, int64_t ld_feat, float* workspace,
                                       int64_t workspace_floats, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && net && state && features && workspace, "porl_fasternet_forward: null argument");
   // rows = B * 5760 is a 32-bit extent of the contractions and B a grid dimension; offsets are 64-bit everywhere
   PORL_CHECK_ARG(B >= 1 && B <= 16384, "porl_fasternet_forward: B=%lld outside [1, 16384]", (long long)B);

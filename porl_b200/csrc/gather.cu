@@ -141,6 +141,7 @@ using namespace porl;
 extern "C" int porl_gather_rows_f32(porl_ctx_t* ctx, const float* table, int64_t n_rows,
                                     int64_t row_stride, int64_t row_len, const int64_t* idx,
                                     int64_t B, float* out, int64_t out_stride, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && table && idx && out, "porl_gather_rows_f32: null argument");
   PORL_CHECK_ARG(n_rows > 0 && row_len > 0 && row_len <= row_stride && row_len <= out_stride && B >= 0 &&
                      row_len < (1 << 30),
@@ -159,6 +160,7 @@ extern "C" int porl_gather_transitions(porl_ctx_t* ctx, const float* table, int6
                                        int64_t B, float* obs, float* next_obs, int64_t ld_obs,
                                        float* rewards, float* dones, float* actions, int64_t ld_act,
                                        porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && table && idx && obs && next_obs && rewards && dones && actions,
                  "porl_gather_transitions: null argument");
   PORL_CHECK_ARG(S > 0 && A >= 0 && A <= 32 && row_stride >= 2 * (int64_t)S + 2 + A && ld_obs >= S &&
@@ -180,6 +182,7 @@ extern "C" int porl_gather_soa(porl_ctx_t* ctx, const float* states, const float
                                float* out_states, float* out_next_states, int64_t ld_out,
                                int64_t* out_actions, float* out_rewards, float* out_dones,
                                porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && states && next_states && actions && rewards && dones && idx && out_states &&
                      out_next_states && out_actions && out_rewards && out_dones,
                  "porl_gather_soa: null argument");
@@ -197,6 +200,7 @@ extern "C" int porl_gather_soa(porl_ctx_t* ctx, const float* states, const float
 
 extern "C" int porl_pack_rows(porl_ctx_t* ctx, const float* src, int64_t ld_src, int64_t B, int32_t n,
                               float* dst, int64_t ld_dst, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && src && dst, "porl_pack_rows: null argument");
   PORL_CHECK_ARG(n > 0 && ld_src >= n && ld_dst >= n && B >= 0, "porl_pack_rows: bad shape n=%d ld_src=%lld ld_dst=%lld",
                  n, (long long)ld_src, (long long)ld_dst);

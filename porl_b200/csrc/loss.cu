@@ -238,6 +238,7 @@ extern "C" int porl_expectile_twin_loss(porl_ctx_t* ctx, const float* v1, const 
                                         const float* rewards, const float* dones, float gamma, float tau,
                                         int64_t B, int64_t B_norm, float* target_v, float* dv1,
                                         float* dv2, float* loss_out, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && v1 && v2 && nv1 && nv2 && rewards && dones && target_v && dv1 && dv2 && loss_out,
                  "porl_expectile_twin_loss: null argument");
   PORL_CHECK_ARG(B > 0 && B_norm >= B && ldv >= 1, "porl_expectile_twin_loss: bad B=%lld B_norm=%lld",
@@ -258,6 +259,7 @@ extern "C" int porl_awr_gauss_nll(porl_ctx_t* ctx, const float* mean, int64_t ld
                                   float alpha, int32_t mode, int32_t tanh_out, int64_t B, int32_t D,
                                   int64_t B_norm, float* dz_out, float* dlog_std, float* loss_out,
                                   porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && mean && log_std && x && target_v && v1n && v2n && dz_out && dlog_std && loss_out,
                  "porl_awr_gauss_nll: null argument");
   PORL_CHECK_ARG(B > 0 && B_norm >= B && D > 0 && D <= kAwrMaxD && ld_mean >= D && ld_x >= D && ldv >= 1 &&
@@ -282,6 +284,7 @@ extern "C" int porl_cql_head(porl_ctx_t* ctx, const float* q, const float* q_nex
                              const int64_t* actions, const float* rewards, const float* dones,
                              float gamma, float alpha, int64_t B, int32_t A, int64_t B_norm, float* dq,
                              float* losses_out, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && q && q_next_tgt && actions && rewards && dones && dq && losses_out,
                  "porl_cql_head: null argument");
   PORL_CHECK_ARG(B > 0 && B_norm >= B && A > 0 && A <= kCqlMaxA && ldq >= A,

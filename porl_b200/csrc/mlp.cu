@@ -277,6 +277,7 @@ static void clear_group(GemmGroup& g) {
 
 extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp_call_t* calls, int64_t B,
                                 porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && calls && n_calls >= 1 && n_calls <= PORL_MAX_CALLS, "porl_mlp_forward: n_calls=%d", n_calls);
   PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_forward: B=%lld", (long long)B);
   int max_layers = 0, total_nets = 0;
@@ -386,6 +387,7 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
 
 extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, int64_t B, float* dout,
                                  float* grads, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && call && call->mlp && dout && grads && call->params && call->x && call->saved,
                  "porl_mlp_backward: null argument");
   PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_backward: B=%lld", (long long)B);

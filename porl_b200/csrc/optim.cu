@@ -64,18 +64,19 @@ __device__ __forceinline__ unsigned long long global_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-// spins until *addr has reached `epoch` (wrap-safe); gives up after wait_ns and raises the status flag
-__device__ __forceinline__ void peer_wait(const uint32_t* addr, uint32_t epoch, unsigned long long wait_ns,
+// spins until *addr has reached `epoch` (wrap-safe); gives up after wait_ns, raises the status flag and returns false
+__device__ __forceinline__ bool peer_wait(const uint32_t* addr, uint32_t epoch, unsigned long long wait_ns,
                                           uint32_t* status) {
-  if ((int)(peer_poll(addr) - epoch) >= 0) return;
+  if ((int)(peer_poll(addr) - epoch) >= 0) return true;
   const unsigned long long t0 = global_ns();
   while ((int)(peer_poll(addr) - epoch) < 0) {
     __nanosleep(64);
     if (global_ns() - t0 > wait_ns) {
       atomicOr(status, (uint32_t)PORL_FLAG_PEER_TIMEOUT);
-      return;
+      return false;
     }
   }
+  return true;
 }
 // gradients of the peers change between launches at fixed addresses: read them around L1
 __device__ __forceinline__ float4 peer_load4(const float* base, int64_t i4) {
@@ -90,6 +91,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   pdl_entry();
   __shared__ AdamScalars sh;
   __shared__ uint32_t sh_epoch;
+  __shared__ int sh_timeout;
   const bool ema = (target != nullptr) && ema_beta > 0.f;
   const int64_t n4 = n >> 2;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -110,9 +112,11 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   if (threadIdx.x == 0) {
     sh = adam_scalars(st, beta1, beta2, hard_every);
     if (PEER) sh_epoch = *reinterpret_cast<volatile uint32_t*>(peers.epoch) + 1u;
+    sh_timeout = 0;
   }
   __syncthreads();
   const AdamScalars s = sh;
+  bool skip = false;
   if (PEER) {
     // 1. "my bucket of this epoch is complete" -> every rank's pad (own one included); every block then waits for
     //    all ranks' words in ITS OWN rank's pad, so no block depends on another block of the same grid.
@@ -121,9 +125,15 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
       __threadfence_system();
       peer_signal(peers.pad[threadIdx.x] + peers.rank, e);
     }
-    if (threadIdx.x < peers.world) peer_wait(peers.pad[peers.rank] + threadIdx.x, e, peers.wait_ns, peers.status);
+    if (threadIdx.x < peers.world && !peer_wait(peers.pad[peers.rank] + threadIdx.x, e, peers.wait_ns, peers.status))
+      sh_timeout = 1;
     __syncthreads();
-    if (blockIdx.x == 0 && threadIdx.x < peers.tail_floats) {
+    // A peer that never signalled: its bucket is not the gradient of this update.  The launch then leaves parameters,
+    // moments, target net and the optimizer clock untouched (every block decides from the device status word, which
+    // stays set until the host reads it, so blocks that started after the flag was raised skip as well) -- the step is
+    // lost, not corrupted, and the next loss read raises PORL_FLAG_PEER_TIMEOUT.
+    skip = sh_timeout || (*reinterpret_cast<volatile uint32_t*>(peers.status) & (uint32_t)PORL_FLAG_PEER_TIMEOUT);
+    if (!skip && blockIdx.x == 0 && threadIdx.x < peers.tail_floats) {
       float t = 0.f;
       for (int r = 0; r < peers.world; ++r) t += __ldcv(peers.bucket[r] + n + threadIdx.x);
       peers.tail_out[threadIdx.x] = t;
@@ -132,7 +142,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   const bool hard = (target != nullptr) && s.do_hard;
   const float keep = 1.f - ema_beta;
 
-  for (int64_t i = i0; i < n4; i += stride) {
+  for (int64_t i = i0; i < n4 && !skip; i += stride) {
     float4 pp, mm, vv;
     if (i == i0) { pp = pp0; mm = mm0; vv = vv0; }
     else { pp = p4[i]; mm = m4[i]; vv = v4[i]; }
@@ -166,7 +176,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     }
   }
   // tail (n not a multiple of 4)
-  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n && !skip; i += stride) {
     float pp = p[i], mm = m[i], vv = v[i];
     float gi;
     if (PEER) {
@@ -186,7 +196,8 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   __syncthreads();
   if (threadIdx.x == 0) {
     const uint32_t ticket = atomicAdd(&st->blocks_done, 1u);
-    if (ticket == gridDim.x - 1) {
+    if (ticket == gridDim.x - 1 && skip) st->blocks_done = 0;
+    if (ticket == gridDim.x - 1 && !skip) {
       st->blocks_done = 0;
       const long long e = st->step + 1;   // scheduler.last_epoch after its step()
       if (st->t_max > 0) {
@@ -204,7 +215,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
       if (PEER) *reinterpret_cast<volatile uint32_t*>(peers.epoch) = sh_epoch;
       __threadfence();
     }
-    if (PEER) sh.do_hard = (ticket == gridDim.x - 1);      // reuse as "this block closes the launch"
+    if (PEER) sh.do_hard = (ticket == gridDim.x - 1) && !skip;      // reuse as "this block closes the launch"
   }
   if (PEER) {
     // 3. the closing block: "I have read your buckets" to every rank, then wait until every rank has read mine
@@ -225,6 +236,7 @@ using namespace porl;
 extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* m, float* v, int64_t n,
                               porl_opt_state_t* state_dev, float beta1, float beta2, float eps,
                               float* target, float ema_beta, int32_t hard_every, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && p && g && m && v && state_dev, "porl_adam_step: null argument");
   PORL_CHECK_ARG(n > 0, "porl_adam_step: n=%lld", (long long)n);
   PORL_CHECK_ARG(aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v) && (!target || aligned16(target)),
@@ -244,6 +256,7 @@ extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* 
 extern "C" int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_group_t* pg, float* m, float* v,
                                    int64_t n, porl_opt_state_t* state_dev, float beta1, float beta2, float eps,
                                    float* target, float ema_beta, int32_t hard_every, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && p && pg && m && v && state_dev, "porl_adam_step_peer: null argument");
   PORL_CHECK_ARG(n > 0 && (n & 3) == 0, "porl_adam_step_peer: n=%lld must be a positive multiple of 4", (long long)n);
   PORL_CHECK_ARG(pg->world >= 1 && pg->world <= PORL_MAX_PEERS && pg->rank >= 0 && pg->rank < pg->world,

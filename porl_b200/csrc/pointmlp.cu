@@ -503,18 +503,21 @@ extern "C" int64_t porl_pointmlp_workspace_floats(const porl_pointmlp_t* net, in
 
 extern "C" int porl_fps(porl_ctx_t* ctx, const float* xyz, int64_t B, int32_t N, int32_t npoint, const int64_t* start,
                         int32_t* idx, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && xyz && start && idx && B >= 1, "porl_fps: null argument");
   return launch_fps(ctx, xyz, B, N, npoint, start, idx, as_stream(stream));
 }
 
 extern "C" int porl_knn(porl_ctx_t* ctx, const float* xyz, const float* query, int64_t B, int32_t N, int32_t S, int32_t k,
                         int32_t* idx, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && xyz && query && idx && B >= 1, "porl_knn: null argument");
   return launch_knn(ctx, xyz, query, B, N, S, k, idx, as_stream(stream));
 }
 
 extern "C" int porl_scan_to_points(porl_ctx_t* ctx, const float* state, int64_t ld_state, int64_t B, float* out,
                                    porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && state && out && B >= 1 && ld_state >= 362, "porl_scan_to_points: bad argument");
   ProfScope prof(ctx, PORL_CAT_ENCODER, (double)B * (362 + 3 * 361) * 4.0, as_stream(stream));
   scan_to_points_kernel<<<(unsigned)B, 128, 0, as_stream(stream)>>>(state, ld_state, out);
@@ -525,6 +528,7 @@ extern "C" int porl_scan_to_points(porl_ctx_t* ctx, const float* state, int64_t 
 extern "C" int porl_pointmlp_forward(porl_ctx_t* ctx, const porl_pointmlp_t* netp, const float* x, const int64_t* fps_start,
                                      int64_t B, float* out, int64_t ld_out, float* workspace, int64_t workspace_floats,
                                      porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && netp && x && fps_start && out && workspace, "porl_pointmlp_forward: null argument");
   const porl_pointmlp_t& net = *netp;
   PmPlan pl;

@@ -64,6 +64,7 @@ using namespace porl;
 
 extern "C" int porl_sample_permutation(porl_ctx_t* ctx, int64_t n, uint64_t seed, uint64_t stream_id, int64_t first,
                                        int64_t count, int64_t* out, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && out, "porl_sample_permutation: null argument");
   PORL_CHECK_ARG(n >= 1 && n < ((int64_t)1 << 62) && first >= 0 && count >= 0, "porl_sample_permutation: n=%lld first=%lld count=%lld",
                  (long long)n, (long long)first, (long long)count);

@@ -133,6 +133,7 @@ using namespace porl;
 
 extern "C" int porl_transpose(porl_ctx_t* ctx, const float* src, int64_t rows, int64_t cols, int64_t ld_src,
                               float* dst, int64_t ld_dst, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
   PORL_CHECK_ARG(ctx && rows > 0 && cols > 0 && rows < (1 << 30) && cols < (1 << 30), "porl_transpose: bad shape");
   TransposeBatch tb;
   tb.n_seg = 1;

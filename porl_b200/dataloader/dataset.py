@@ -116,6 +116,16 @@ class EpochSampler:
     def __len__(self) -> int:
         return self.n // self.bs if self.drop_last else (self.n + self.bs - 1) // self.bs
 
+    def state_dict(self) -> dict:
+        """What a resumed run needs to continue the same index stream: the generator state BEFORE the next epoch's
+        permutation is drawn (checkpoints are written between epochs)."""
+        g = self.generator if self.generator is not None else torch.default_generator
+        return {"kind": "epoch", "rng_state": g.get_state()}
+
+    def load_state_dict(self, sd: dict) -> None:
+        g = self.generator if self.generator is not None else torch.default_generator
+        g.set_state(sd["rng_state"].cpu())
+
     def __iter__(self):
         perm = torch.randperm(self.n, generator=self.generator).to(self.device, non_blocking=True)
         end = self.n - (self.n % self.bs) if self.drop_last else self.n
@@ -147,6 +157,12 @@ class DeviceSampler:
         check(lib.porl_sample_permutation(self.ctx.handle, self.n, self.seed, epoch, first, count, out.data_ptr(),
                                           _C.stream_ptr()))
         return out
+
+    def state_dict(self) -> dict:
+        return {"kind": "device", "seed": self.seed, "epoch": self.epoch}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.seed, self.epoch = int(sd["seed"]), int(sd["epoch"])
 
     def draw(self, batch_size: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
         """One without-replacement draw of `batch_size` rows (the ReplayBuffer.sample contract): every call uses a

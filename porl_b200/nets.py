@@ -152,6 +152,15 @@ class ParamGroup:
                                  self.eps, target.data_ptr() if target is not None else None, ema_beta,
                                  hard_every, _C.stream_ptr()))
 
+    def c_group(self) -> _C.OptGroup:
+        """porl_opt_group_t view of this group for the whole-update entry points (porl_sorl_step / porl_por_step)."""
+        g = _C.OptGroup()
+        g.params, g.grads, g.m, g.v = self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr()
+        g.n, g.state, g.loss = self.n, self.state.data_ptr(), self.loss_ptr
+        g.beta1, g.beta2, g.eps = self.betas[0], self.betas[1], self.eps
+        g.peers = C.pointer(self.peers.struct) if self.peers is not None else None
+        return g
+
     # --- torch.optim-like surface used by trainers / checkpoint extensions -------------------
     @property
     def param_groups(self):

@@ -20,7 +20,7 @@ from .. import dist as pdist
 from ..dataloader.dataset import EpochSampler, TransitionDataset, synthetic_rows
 
 
-def add_common_flags(parser) -> None:
+def add_common_flags(parser, default_backbone: str = "none") -> None:
     """Flags that do not exist in the reference (new names only; every reference flag keeps its name and default)."""
     parser.add_argument("--dataset", type=str, default="",
                         help=".npy or .pt file with (N, 2S+2+A) float32 rows, or a directory of the reference's "
@@ -35,7 +35,9 @@ def add_common_flags(parser) -> None:
     parser.add_argument("--weights_dir", type=str, default="weights")
     parser.add_argument("--resume", type=str, default="",
                         help="training checkpoint (train_{i}.pt: weights + optimizer + LR clocks) to continue from")
-    parser.add_argument("--backbone", type=str, default="none", choices=["none", "fasternet"])
+    parser.add_argument("--backbone", type=str, default=default_backbone, choices=["none", "fasternet"],
+                        help="scan encoder in front of the heads (sorl_train.py:29-32 always builds FasterNet; "
+                             "por_train.py never does)")
 
 
 def load_rows(args, row_len: int) -> np.ndarray | torch.Tensor:
@@ -66,12 +68,18 @@ def run(args, agent, step_fn, save_every: int, name: str) -> dict:
     else:
         sampler = EpochSampler(len(ds), args.batch_size, device, generator=gen)
     agent.ctx.set_gemm_mode(args.gemm_mode)
+    done, ep0 = 0, 0
     if getattr(args, "resume", ""):
-        agent.load_training_state_dict(torch.load(args.resume, map_location=device, weights_only=False))
+        ck = torch.load(args.resume, map_location=device, weights_only=False)
+        agent.load_training_state_dict(ck)
+        loop = ck.get("loop")
+        if loop is not None:          # data order continues where the checkpointed run stopped (saved at episode ends)
+            sampler.load_state_dict(loop["sampler"])
+            done, ep0 = int(loop["updates"]), int(loop["episode"]) + 1
     pb = None
-    done, t0 = 0, time.perf_counter()
+    t0, done0 = time.perf_counter(), done
     last = (float("nan"), float("nan"))
-    for ep in range(args.episodes):
+    for ep in range(ep0, args.episodes):
         ep_v, ep_g = [], []
         for idx in sampler:
             if idx.numel() % world:                                   # ragged tail: drop the remainder rows
@@ -88,16 +96,19 @@ def run(args, agent, step_fn, save_every: int, name: str) -> dict:
                 if rank == 0:
                     dt = time.perf_counter() - t0
                     print(f"{name} episode:{ep}||update:{done}||v_loss: {statistics.fmean(ep_v):.4f}||"
-                          f"g_loss: {statistics.fmean(ep_g):.4f}||{done / dt:.1f} updates/s", flush=True)
+                          f"g_loss: {statistics.fmean(ep_g):.4f}||{(done - done0) / dt:.1f} updates/s", flush=True)
             if args.updates and done >= args.updates:
                 break
         if save_every and (ep + 1) % save_every == 0 and rank == 0:
             os.makedirs(args.weights_dir, exist_ok=True)
             torch.save(agent.state_dict(), os.path.join(args.weights_dir, f"model_{ep}.pt"))   # por_train.py:97
-            torch.save(agent.training_state_dict(), os.path.join(args.weights_dir, f"train_{ep}.pt"))
+            ck = agent.training_state_dict()
+            ck["loop"] = {"sampler": sampler.state_dict(), "updates": done, "episode": ep}
+            torch.save(ck, os.path.join(args.weights_dir, f"train_{ep}.pt"))
             print("evaluate_policy: unavailable on this box (Gazebo/ROS roll-outs, test.py:8-53)", flush=True)
         if args.updates and done >= args.updates:
             break
     last = agent.read_losses()
     dt = time.perf_counter() - t0
-    return {"updates": done, "seconds": dt, "updates_per_s": done / max(dt, 1e-9), "v_loss": last[0], "g_loss": last[1]}
+    return {"updates": done, "seconds": dt, "updates_per_s": (done - done0) / max(dt, 1e-9), "v_loss": last[0],
+            "g_loss": last[1]}

@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """SORL offline training on B200: same flags and loop shape as the reference sorl_train.py:20-106
 (agent.update(obs, actions, rewards, next_obs, dones)).  The reference always wraps the heads in a FasterNet
-encoder (sorl_train.py:29-32): pass --backbone fasternet for that; the default (--backbone none) is the
-MLP-only variant of sorl_train_v0.py.  New flags: see porl_b200/train/offline_loop.py."""
+encoder (sorl_train.py:29-32), so --backbone fasternet is the default here and model_{i}.pt carries the
+reference's backbone.* keys; --backbone none is the MLP-only variant of sorl_train_v0.py.  New flags: see porl_b200/train/offline_loop.py."""
 import argparse
 
 import torch
@@ -15,6 +15,13 @@ def train(args):
     device = torch.device(args.device)
     if device.type != "cuda":
         raise SystemExit("porl_b200 runs on CUDA (sm_100a) only; use the reference for --device cpu")
+    # torchrun: the process group and THIS rank's device come first -- the agent allocates its parameter and
+    # gradient buffers (and maps its peers' gradient buckets) at construction
+    from porl_b200 import dist as pdist
+    _, local, world = pdist.init_from_env()
+    if world > 1 or device.index is None:
+        device = torch.device("cuda", local if world > 1 else torch.cuda.current_device())
+    torch.cuda.set_device(device)
     torch.manual_seed(1000 + args.seed)
     backbone = None
     if args.backbone == "fasternet":
@@ -51,5 +58,5 @@ if __name__ == "__main__":
     parser.add_argument("--policy_lr", type=float, default=1e-4)
     parser.add_argument("--alpha", type=float, default=10.0)
     parser.add_argument("--evaluate", action="store_true")
-    add_common_flags(parser)
+    add_common_flags(parser, default_backbone="fasternet")   # sorl_train.py:29-40: SORL(backbone=FasterNet(3, feature_dim))
     train(parser.parse_args())

@@ -406,7 +406,8 @@ def test_adam_peer_sum_equals_presummed_adam(env, world, n):
 
 
 def test_adam_peer_timeout_sets_flag_and_returns(env):
-    """A peer that never signals: the kernel gives up after wait_ms, raises PORL_FLAG_PEER_TIMEOUT, finishes."""
+    """A peer that never signals: the kernel gives up after wait_ms, raises PORL_FLAG_PEER_TIMEOUT and finishes
+    WITHOUT applying the update (the other rank's bucket is not this step's gradient)."""
     from porl_b200.nets import ParamGroup, GRAD_TAIL
     from porl_b200.peer import PeerReduce
     _C, ctx, dev = env
@@ -417,9 +418,16 @@ def test_adam_peer_timeout_sets_flag_and_returns(env):
                            GRAD_TAIL, wait_ms=50)
     status = ctx.status_tensor()
     status.zero_()
-    grp.step()
+    grp.params.normal_()
+    grp.bucket.normal_()
+    before = grp.params.clone()
+    tgt = torch.ones(grp.n, device=dev)
+    grp.step(target=tgt, ema_beta=0.5)
     torch.cuda.synchronize()
     assert int(status[0]) & _C.FLAG_PEER_TIMEOUT
+    # the lost step leaves parameters, moments, target net and the optimizer clock untouched
+    assert torch.equal(grp.params, before) and float(grp.m.abs().sum()) == 0.0 and float(grp.v.abs().sum()) == 0.0
+    assert torch.equal(tgt, torch.ones_like(tgt)) and grp.read_clock().step == 0
     status.zero_()
 
 

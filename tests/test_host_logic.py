@@ -73,8 +73,44 @@ def test_mlp_geometry_is_padded_and_aligned():
 
 
 @pytest.mark.parametrize("kind", ["por", "sorl"])
-def test_agent_state_dict_layout_and_kernel_sequence(dry_porl, kind):
+def test_update_goes_through_the_whole_step_entry_point(dry_porl, kind):
+    """update() = pack + ONE call of porl_por_step / porl_sorl_step (include/porl_b200.h) whose descriptor carries the
+    agent's buffers and hyper-parameters; attribute changes (sweeps set tau / alpha) reach the next call."""
+    import ctypes
+    from porl_b200 import POR, SORL, _C
+    S, H, A, B = 22, 32, 2, 16
+    args = dims(S, H, 2, False, 256, A)
+    agent = (POR if kind == "por" else SORL)(args, max_steps=7, tau=0.9, alpha=10.0, device=torch.device("cpu"))
+    b = slice_row(torch.from_numpy(synth.laser_rows(B, S, 1, A)), S, A)
+    agent.tau = 0.7
+    dry_porl.clear()
+    if kind == "por":
+        agent.por_residual_update(b["observations"], b["next_observations"], b["rewards"], b["terminals"])
+    else:
+        agent.update(b["observations"], b["actions"], b["rewards"], b["next_observations"], b["terminals"])
+    names = [c[0] for c in dry_porl]
+    assert names == ["porl_pack_rows"] * (4 if kind == "por" else 5) + [f"porl_{kind}_step"]
+    a = dry_porl[-1][1]
+    d = ctypes.cast(a[1], ctypes.POINTER(_C.AgentStep)).contents
+    assert a[2] == B and d.world == 1 and d.tau == pytest.approx(0.7) and d.alpha == pytest.approx(10.0)
+    assert d.awr_mode == (0 if kind == "por" else 1) and d.tanh_out == (0 if kind == "por" else 1)
+    assert d.policy_out == (S if kind == "por" else A)
+    assert d.value.params == agent.v_group.params.data_ptr() and d.value.grads == agent.v_group.grads.data_ptr()
+    assert d.policy.loss == agent.p_group.loss_ptr and d.value.n == agent.v_group.n and not d.value.peers
+    tgt = agent.v_target if kind == "por" else agent.v_tgt
+    assert d.target_params == tgt.flat.data_ptr() and d.ema_beta == pytest.approx(0.005)
+    assert d.log_std_offset == (agent.goal_policy if kind == "por" else agent.policy).log_std_offset
+    ws_floats = a[11] if kind == "por" else a[11]
+    assert ws_floats == _C.lib.porl_step_workspace_floats(ctypes.byref(d), B) > 0
+    pb = agent._packed[B]
+    assert a[3] == pb.obs.data_ptr() and a[4] == pb.next_obs.data_ptr() and a[5] == pb.ld_obs
+    assert a[6] == (pb.next_obs.data_ptr() if kind == "por" else pb.actions.data_ptr())
+
+
+@pytest.mark.parametrize("kind", ["por", "sorl"])
+def test_agent_state_dict_layout_and_kernel_sequence(dry_porl, kind, monkeypatch):
     from porl_b200 import POR, SORL
+    monkeypatch.setenv("PORL_WHOLE_STEP", "0")        # the host-sequenced path (kept for the NCCL all-reduce fallback)
     S, H, A, B = 22, 32, 2, 16
     args = dims(S, H, 2, False, 256, A)
     cls, ocls = (POR, OraclePOR) if kind == "por" else (SORL, OracleSORL)
