@@ -49,6 +49,12 @@ def parse():
     p.add_argument("--other-configs", type=int, default=1, help="also time BASELINE configs 1 (POR) and 3 (CQL)")
     p.add_argument("--pointmlp-batch", type=int, default=128,
                    help="batch of the PointMLP (agent/feature_pcl.py) forward reported under 'also_pointmlp' (0: skip)")
+    p.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                   help="N > 1: weak = --batch rows per GPU (global batch grows with N); strong = --batch rows in total")
+    p.add_argument("--cfg4-batch", type=int, default=-1,
+                   help="N > 1: per-GPU batch of the POR + FasterNet leg (BASELINE config 4: 65536 over 8 GPUs); "
+                        "-1 = 8192 when N == 8, else skipped; 0 = skip")
+    p.add_argument("--ceilings", type=int, default=1, help="measure the TF32 ceilings (cuBLAS TF32, own kernel 1-pass)")
     p.add_argument("--encoder-batch", type=int, default=256,
                    help="batch of the SORL + FasterNet scan-encoder workload reported under 'also_encoder' (0: skip)")
     return p.parse_args()
@@ -149,6 +155,81 @@ def peaks():
         return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback"}
 
 
+def measure_ceilings(ctx, device):
+    """Measured denominators of the 3xTF32 contraction ("the bench measures them the same way"):
+    cuBLAS TF32 (torch.matmul with allow_tf32, 8192^3, best of 5 -- a library call used ONLY as the yardstick) and this
+    repo's tcgen05 kernel issuing one TF32 pass instead of three (porl_ctx_set_tc_terms(1)) on the same problem.  The
+    3xTF32 mode issues three MMAs per product: its ceiling is a third of the single-pass TF32 rate."""
+    import ctypes as C
+    from porl_b200 import _C
+    n = 8192
+    g = torch.Generator(device=device).manual_seed(5)
+    x = torch.randn(n, n, generator=g, device=device)
+    w = torch.randn(n, n, generator=g, device=device)
+    out = torch.empty(n, n, device=device)
+    flop = 2.0 * n * n * n
+
+    def best(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        t = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t.append(e0.elapsed_time(e1))
+        return flop / (min(t) * 1e-3) * 1e-12
+
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        cublas_tf32 = best(lambda: torch.matmul(x, w.t(), out=out))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+    cublas_fp32 = best(lambda: torch.matmul(x, w.t(), out=out), reps=2)
+
+    def own():
+        _C.check(_C.lib.porl_gemm(ctx.handle, 1, 1, n, n, n, x.data_ptr(), n, w.data_ptr(), n, out.data_ptr(), n, None, 0,
+                                  None, 0, n, None, None, 0, _C.stream_ptr()))
+    mode = ctx.gemm_mode
+    ctx.set_gemm_mode(1)
+    try:
+        own3 = best(own)
+        ctx.set_tc_terms(1)
+        own1 = best(own)
+    finally:
+        ctx.set_tc_terms(3)
+        ctx.set_gemm_mode(mode)
+    del x, w, out
+    return {"shape": "8192^3 fp32 operands, best of 5, CUDA events", "cublas_tf32_tflops": cublas_tf32,
+            "cublas_fp32_tflops": cublas_fp32, "own_kernel_1xtf32_tflops": own1, "own_kernel_3xtf32_tflops": own3,
+            "ceiling_3xtf32_tflops": cublas_tf32 / 3.0,
+            "note": "3xTF32 issues 3 MMAs per product: its ceiling is measured cuBLAS TF32 / 3"}
+
+
+def traffic_record(gemm_mode):
+    """dram bytes per launch of gemm_tc_kernel from the committed `ncu --set full` capture, only if that capture was
+    taken from the kernel source as it is now (sha256 of csrc/gemm_tc.cu stored beside it); a stale capture reads null."""
+    import hashlib
+    if gemm_mode != 1:
+        return None, "no capture for the FFMA mode"
+    try:
+        with open(os.path.join(ROOT, "porl_b200", "csrc", "gemm_tc.cu"), "rb") as f:
+            sha = hashlib.sha256(f.read()).hexdigest()
+        best = None
+        for name in sorted(os.listdir(os.path.join(ROOT, "profiles"))):
+            if name.endswith("_gemm_tc_traffic.json"):
+                with open(os.path.join(ROOT, "profiles", name)) as f:
+                    d = json.load(f)
+                if d.get("source_sha256") == sha:
+                    best = (d["mean_bytes_per_launch"], f"profiles/{name} (ncu --set full, source hash matches)")
+        return best if best else (None, "no ncu capture of the current gemm_tc.cu (source hash differs): traffic not claimed")
+    except Exception as e:
+        return None, f"traffic record unreadable: {e}"
+
+
 # ------------------------------------------------------------------------------------------ CPU arm
 def cpu_reference_updates(batch, steps, warmup, seconds=None):
     """The reference's CPU path for this workload: the oracle restatement of agent/sorl.py (eager
@@ -244,6 +325,17 @@ class Runner:
         self.pb = self.ds.new_batch(batch)
         self.idx_static = torch.zeros(batch, dtype=torch.int64, device=device)
         self.graph = None
+
+    def indices_global(self, n_steps, seed):
+        """(n_steps, world * B): the global minibatches; rank r's share is columns [r * B, (r + 1) * B)."""
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        total = n_steps * self.B * self.world
+        chunks = []
+        while total > 0:
+            perm = torch.randperm(len(self.ds), generator=g, device=self.device)
+            chunks.append(perm[:total])
+            total -= chunks[-1].numel()
+        return torch.cat(chunks).view(n_steps, self.world * self.B)
 
     def indices(self, n_steps, seed):
         g = torch.Generator(device=self.device).manual_seed(seed)
@@ -487,6 +579,127 @@ def other_configs(a, device, table):
     return out
 
 
+def param_checksum(agent):
+    """(int64 sum of the fp32 bit patterns, float64 sum) over both optimizer groups: equal digests <=> bitwise equal
+    replicas for all practical purposes; printed so that runs can be compared."""
+    flat = torch.cat([agent.v_group.params, agent.p_group.params])
+    return int(flat.view(torch.int32).to(torch.int64).sum()), float(flat.double().sum())
+
+
+def cql_dp_leg(a, device, rank, world):
+    """BASELINE config 3 under bench.py --gpus N: discrete CQL (QNetwork 362-64-128-64-5), global batch 4096 split over
+    the ranks (strong) and 4096 rows per rank (weak); fused gradient kernel per rank, gradient sum inside the Adam
+    kernel over NVLink peer memory, one CUDA graph per update; device-timed, max over ranks."""
+    import torch.distributed as dist
+    from porl_b200 import CQLTrainer, QNetwork
+    from porl_b200.buffer.replaybuffer import ReplayBuffer
+    n = 200_000
+    torch.manual_seed(1000)
+    t = CQLTrainer(state_size=S, action_size=5, gamma=0.99, epsilon=1.0, epsilon_min=0.05, epsilon_decay=0.99,
+                   update_target_freq=10, device=device, network=QNetwork, log_dir="/tmp/porl_b200_bench_logs")
+    t.ctx.set_gemm_mode(a.gemm_mode)
+    g = torch.Generator(device=device).manual_seed(3)
+    t.replay_buffer = ReplayBuffer(n, (S,), device)
+    st = 3.5 * torch.rand(n, S, generator=g, device=device)
+    t.replay_buffer.push_batch(st, torch.randint(0, 5, (n,), generator=g, device=device),
+                               0.1 * torch.randn(n, generator=g, device=device),
+                               st + 0.05 * torch.randn(n, S, generator=g, device=device),
+                               (torch.rand(n, generator=g, device=device) < 0.01).float())
+    del st
+    out = {"gradient_sum": "inside the Adam kernel (NVLink peer memory)" if t.q_group.peers is not None else "NCCL all-reduce"}
+    graphable = t.q_group.peers is not None
+    for label, per_rank in (("strong_global4096", 4096 // world), ("weak_4096_per_gpu", 4096)):
+        idx = torch.zeros(per_rank, dtype=torch.int64, device=device)
+        upd = lambda: t.learn_indices(idx, hard_every=10)
+        graph = graph_of(upd) if (a.graph and graphable) else None
+        gi = torch.Generator(device=device).manual_seed(100 + rank)
+
+        def step():
+            torch.randint(0, n, (per_rank,), generator=gi, device=device, out=idx)
+            graph.replay() if graph is not None else upd()
+
+        for _ in range(10):
+            step()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(300):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        t.read_losses()
+        ups = 300 / (float(ms[0]) * 1e-3)
+        out[label] = {"gradient_updates_per_s": ups, "samples_per_s": ups * per_rank * world, "rows_per_gpu": per_rank,
+                      "global_batch": per_rank * world, "ms_per_update": float(ms[0]) / 300, "cuda_graph": graph is not None}
+        del graph
+    digest = torch.tensor([int(t.q_group.params.view(torch.int32).to(torch.int64).sum())], device=device)
+    all_d = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(all_d, digest)
+    out["replicas_bitwise_identical"] = all(int(d) == int(all_d[0]) for d in all_d)
+    return out
+
+
+def config4_leg(a, device, rank, world, table, per_gpu):
+    """BASELINE config 4: POR with the FasterNet scan encoder, large batch data-parallel (65536 over 8 GPUs = 8192 per
+    GPU).  Every BatchNorm of the encoder sees the GLOBAL batch (cross-rank sums between the statistics and the
+    normalisation), gradients of the heads are summed over the ranks; device-timed, max over ranks."""
+    import torch.distributed as dist
+    from types import SimpleNamespace
+    from porl_b200 import POR
+    from porl_b200.agent.fasternet import FasterNet
+    args = SimpleNamespace(state_size=S, hidden_dim=1024, n_hidden=N_HIDDEN, layer_norm=False, feature_dim=256, action_size=A)
+    torch.manual_seed(1000)
+    agent = POR(args, max_steps=1_000_000, tau=0.9, alpha=10.0, device=device, backbone=FasterNet(3, args.feature_dim))
+    agent.ctx.set_gemm_mode(a.gemm_mode)
+    pb = table.new_batch(per_gpu)           # (data parallel: the encoder picks up the default process group by itself)
+    g = torch.Generator(device=device).manual_seed(4000 + rank)
+    idx = torch.zeros(per_gpu, dtype=torch.int64, device=device)
+
+    def step():
+        torch.randint(0, len(table), (per_gpu,), generator=g, device=device, out=idx)
+        table.gather_packed(idx, pb)
+        agent.update_packed(pb)
+
+    ctx = agent.ctx
+    for _ in range(2):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    n = 5
+    l0 = ctx.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    losses = agent.read_losses()
+    ms_step = float(ms[0]) / n
+    out = {"workload": f"por_fasternet_S{S}_F256_H1024_b{per_gpu}x{world}", "global_batch": per_gpu * world,
+           "rows_per_gpu": per_gpu, "gradient_updates_per_s": 1e3 / ms_step, "samples_per_s": per_gpu * world * 1e3 / ms_step,
+           "ms_per_update": ms_step, "gpu_launches_per_update": (ctx.launches - l0) // n, "final_losses": losses,
+           # per sample: two encoder forwards (0.860 GMAC each, SURVEY.md 8a row a16) + the heads on 256 features
+           # (ten value-net and three policy-net forward-equivalents: 18.2 MMAC)
+           "achieved_tflops_per_gpu": (2 * 2 * 0.860e9 + 36.3e6) * per_gpu / (ms_step * 1e-3) * 1e-12,
+           "sync_batchnorm": "per-channel sums all-reduced across ranks between statistics and normalisation" if world > 1 else "single process"}
+    ctx.profile(True)
+    step()
+    torch.cuda.synchronize()
+    prof = ctx.profile_read()
+    ctx.profile(False)
+    tot = sum(v["ms"] for v in prof.values())
+    out["kernel_time_fractions"] = {k: round(v["ms"] / tot, 4) for k, v in prof.items() if v["launches"]}
+    out["kernel_ms"] = {k: round(v["ms"], 3) for k, v in prof.items() if v["launches"]}
+    return out
+
+
 def run_b200(a):
     from porl_b200 import TransitionDataset, _C, dist as pdist
     rank, local, world = pdist.init_from_env()
@@ -496,11 +709,15 @@ def run_b200(a):
     torch.cuda.set_device(device)
     dist_on = world > 1
     pk = peaks()
+    strong = dist_on and a.scaling == "strong"
+    if strong and a.batch % world:
+        raise SystemExit(f"--scaling strong: batch {a.batch} is not divisible by {world} ranks")
+    b_local = a.batch // world if strong else a.batch
 
     rows = synth_rows_torch(a.rows, device, 20260102)          # same replica on every rank
     table = TransitionDataset(rows, S, A, device)
     del rows
-    runner = Runner(a, a.batch, device, rank, world, table)
+    runner = Runner(a, b_local, device, rank, world, table)
     K, W = a.steps, max(a.warmup, 3)
     peer_reduce = dist_on and all(g.peers is not None for g in (runner.agent.v_group, runner.agent.p_group))
     use_graph = bool(a.graph) and (not dist_on or peer_reduce)   # the peer-sum Adam kernel is an ordinary launch
@@ -512,15 +729,31 @@ def run_b200(a):
         ms, launches = timed(runner, idx_warm, idx_timed, dist_on)
     v_loss, g_loss = runner.agent.read_losses()
     clocks = clk.summary()
-    value = world * K / (ms * 1e-3)
+    updates_per_s = K / (ms * 1e-3)                 # optimizer steps per second (every rank takes the same step)
+    # `value`: weak scaling counts batch-`--batch` minibatches per second over all ranks (per-GPU work fixed, the
+    # global batch grows with N); strong scaling keeps the global batch, so value = gradient updates per second
+    value = updates_per_s if strong else world * updates_per_s
+    digest, fsum = param_checksum(runner.agent)
+    identical = True
+    if dist_on:
+        import torch.distributed as dist
+        d = torch.tensor([digest], device=device)
+        all_d = [torch.zeros_like(d) for _ in range(world)]
+        dist.all_gather(all_d, d)
+        identical = all(int(x) == int(all_d[0]) for x in all_d)
+        assert identical, f"data-parallel replicas diverged: parameter digests {[int(x) for x in all_d]}"
 
     line = None
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic",
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if strong else "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "gradient_updates_per_s": updates_per_s, "samples_per_s": updates_per_s * b_local * world,
+                "value_definition": ("gradient updates/s at a fixed global batch" if strong or not dist_on else
+                                     f"batch-{a.batch} minibatches/s summed over {world} ranks (weak scaling: every "
+                                     f"optimizer step consumes {world} of them; gradient_updates_per_s is the step rate)"),
                 "config": {"workload": workload_name(a.batch), "algo": "SORL (agent/sorl.py, MLP-only heads)",
-                           "batch_per_gpu": a.batch, "global_batch": a.batch * world, "rows": a.rows,
+                           "batch_per_gpu": b_local, "global_batch": b_local * world, "rows": a.rows,
                            "state_size": S, "hidden_dim": H, "parallelism": f"dp{world}" if dist_on else "single",
                            "contraction": "tcgen05 3xTF32" if a.gemm_mode == 1 else "fp32 FFMA",
                            "cuda_graph": use_graph, "inputs_larger_than_l2": True,
@@ -530,7 +763,8 @@ def run_b200(a):
                                             else "NCCL all-reduce per optimizer group"),
                            "l2_note": "each step gathers fresh random rows of a 2.9 GB HBM table (>> 126 MB L2)"},
                 "clocks": clocks, "gpu_launches": launches * (1 if not use_graph else 1),
-                "final_losses": {"v_loss": v_loss, "g_loss": g_loss}}
+                "final_losses": {"v_loss": v_loss, "g_loss": g_loss},
+                "replicas_bitwise_identical": identical, "param_checksum": {"int64_bit_sum": digest, "f64_sum": fsum}}
         if use_graph:
             # graph replays re-issue the captured launches; count them from the capture
             line["gpu_launches"] = runner.launches_per_step * K if hasattr(runner, "launches_per_step") else launches
@@ -553,15 +787,15 @@ def run_b200(a):
         c = prof["contraction"]
         achieved = c["work"] / (c["ms"] * 1e-3) / 1e12 if c["ms"] > 0 else 0.0
         peak = pk["bf16_sustained"]
-        traffic = None
-        try:   # dram__bytes_read+write per launch of this kernel from the committed ncu --set full capture
-            with open(os.path.join(ROOT, "profiles", "r01_gemm_tc_traffic.json")) as f:
-                traffic = json.load(f)["mean_bytes_per_launch"] if a.gemm_mode == 1 else None
-        except Exception:
-            pass
+        traffic, traffic_note = traffic_record(a.gemm_mode)
+        ceil = measure_ceilings(ctx, device) if a.ceilings else None
+        ceiling3 = ceil["ceiling_3xtf32_tflops"] if ceil else peak / 6.0
         line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                            "frac": achieved / peak, "traffic": traffic,
-                            "frac_of_3xtf32_ceiling": achieved / (peak / 6.0),
+                            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
+                            "frac_of_3xtf32_ceiling": achieved / ceiling3,
+                            "ceiling_3xtf32_tflops": ceiling3,
+                            "ceiling_source": "measured in this run: cuBLAS TF32 8192^3 / 3" if ceil else "bf16 sustained / 6 (not measured)",
+                            "measured_ceilings": ceil,
                             "kernel": "gemm_tc_kernel (tcgen05 3xTF32)" if a.gemm_mode == 1 else "gemm_simt_kernel (fp32 FFMA)",
                             "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({pk['source']})",
                             "launches_per_step": c["launches"] / max(1, min(10, K)),
@@ -569,45 +803,74 @@ def run_b200(a):
         kern = kernel_table(prof, pk)
         line["kernels"] = kern
 
-        # e2e: the public API with HOST buffers: pinned rows -> H2D -> agent.update() -> losses D2H
+        # e2e: the public API with HOST buffers: pinned rows -> H2D -> agent.update_async() -> losses D2H, every step.
+        # Three device row buffers: while update(i) runs, the rows of steps i+1 and i+2 travel host -> device on a side
+        # stream (a DataLoader with pin_memory and prefetch_factor 2), and the losses of update(i-1) are read on the host
+        # -- one step late, each through its own event -- so the compute stream never drains.  Every step's H2D copy and
+        # its loss read-back lie inside the timed region.  SORL.update() (the reference's blocking signature) is timed
+        # beside it.
         Ke = a.e2e_steps or K
-        ring = 8
+        ring, depth = 8, 2
         host = torch.empty(ring, a.batch, table.row_len, dtype=torch.float32).pin_memory()
         src_idx = runner.indices(ring, 2002)
         for r in range(ring):
             host[r].copy_(table.gather(src_idx[r]).cpu())
-        # two device buffers: while update(i) runs, the rows of step i+1 travel host -> device on a side stream (what a
-        # DataLoader with pin_memory and one batch of prefetch does); every step's copy and loss read-back is inside the
-        # timed region.  agent.update() returns Python floats, i.e. it synchronises once per step.
-        dev_rows = [torch.empty(a.batch, table.row_len, dtype=torch.float32, device=device) for _ in range(2)]
+        nbuf = depth + 1
+        dev_rows = [torch.empty(a.batch, table.row_len, dtype=torch.float32, device=device) for _ in range(nbuf)]
         copy_stream = torch.cuda.Stream(device=device)
-        arrived = [torch.cuda.Event(), torch.cuda.Event()]
+        arrived = [torch.cuda.Event() for _ in range(nbuf)]
+        consumed = [torch.cuda.Event() for _ in range(nbuf)]
+        main = torch.cuda.current_stream()
 
         def prefetch(i):
             with torch.cuda.stream(copy_stream):
-                dev_rows[i % 2].copy_(host[i % ring], non_blocking=True)
-                arrived[i % 2].record(copy_stream)
+                copy_stream.wait_event(consumed[i % nbuf])        # the update that last read this buffer has been issued and run
+                dev_rows[i % nbuf].copy_(host[i % ring], non_blocking=True)
+                arrived[i % nbuf].record(copy_stream)
 
-        def e2e_step(i):
-            torch.cuda.current_stream().wait_event(arrived[i % 2])
-            prefetch(i + 1)             # buffer (i+1) % 2 is free: update(i-1) has returned its losses
-            rows = dev_rows[i % 2]
-            obs, rew = rows[:, :S], rows[:, S]
-            nxt, done, act = rows[:, S + 1:2 * S + 1], rows[:, 2 * S + 1], rows[:, 2 * S + 2:]
-            return runner.agent.update(obs, act, rew, nxt, done)
-        prefetch(0)
-        for i in range(3):
-            e2e_step(i)
-        torch.cuda.synchronize()
+        def views(rows):
+            return rows[:, :S], rows[:, 2 * S + 2:], rows[:, S], rows[:, S + 1:2 * S + 1], rows[:, 2 * S + 1]
+
+        def e2e_loop(n, blocking):
+            for bslot in range(nbuf):
+                consumed[bslot].record(main)
+            for j in range(depth):
+                prefetch(j)
+            pending, losses = None, None
+            for i in range(n):
+                main.wait_event(arrived[i % nbuf])
+                if blocking:
+                    losses = runner.agent.update(*views(dev_rows[i % nbuf]))
+                else:
+                    h = runner.agent.update_async(*views(dev_rows[i % nbuf]))
+                consumed[i % nbuf].record(main)
+                prefetch(i + depth)
+                if not blocking:
+                    if pending is not None:
+                        losses = pending.result()            # losses of update(i-1), read while update(i) runs
+                    pending = h
+            if pending is not None:
+                losses = pending.result()
+            torch.cuda.synchronize()
+            return losses
+
+        e2e_loop(5, False)
         t0 = time.perf_counter()
-        for i in range(3, 3 + Ke):
-            e2e_step(i)
-        torch.cuda.synchronize()
+        e2e_loop(Ke, False)
         dt = time.perf_counter() - t0
+        e2e_loop(3, True)
+        t0 = time.perf_counter()
+        e2e_loop(Ke, True)
+        dt_block = time.perf_counter() - t0
         line["e2e"] = {"value": Ke / dt, "unit": UNIT, "h2d_bytes_per_step": a.batch * table.row_len * 4,
                        "d2h_bytes_per_step": 12, "steps": Ke,
-                       "h2d_overlap": "rows of step i+1 are copied on a side stream while update(i) runs",
-                       "api": "SORL.update(observations, actions, rewards, next_observations, terminals) -> (float, float)"}
+                       "h2d_overlap": "rows of steps i+1, i+2 are copied on a side stream while update(i) runs",
+                       "api": "SORL.update_async(observations, actions, rewards, next_observations, terminals) -> handle; "
+                              "handle.result() -> (float, float), read one step late (every step's losses are read)",
+                       "blocking_api": {"value": Ke / dt_block, "unit": UNIT,
+                                        "api": "SORL.update(...) -> (float, float): the reference's signature, one host "
+                                               "synchronisation per step"},
+                       "frac_of_device_value": (Ke / dt) / value}
 
         # second batch size of the metric (batch 256)
         if a.also_batch and a.also_batch != a.batch:
@@ -655,10 +918,19 @@ def run_b200(a):
                               "back-propagates through the encoder)"}
                 line["also_encoder"]["samples_per_s"] = line["also_encoder"]["value"] * a.encoder_batch
     else:
+        cql = cql_dp_leg(a, device, rank, world) if a.other_configs else None
+        per4 = a.cfg4_batch if a.cfg4_batch >= 0 else (8192 if world == 8 else 0)
+        cfg4 = config4_leg(a, device, rank, world, table, per4) if per4 > 0 else None
         if rank == 0:
-            # DP e2e: same public API per rank is exercised in the single-GPU run; report device-timed value
+            # the host-buffer end-to-end figure is an N=1 measurement; at N>1 the inputs are device-resident
             line["e2e"] = {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
-                           "note": "multi-GPU run: device-resident inputs; host-buffer e2e is measured at N=1"}
+                           "copies_declared": False,
+                           "note": "multi-GPU run: device-resident inputs, NOT an end-to-end figure (this repeats the "
+                                   "device-timed value); the host-buffer e2e is measured at N=1"}
+            if cql is not None:
+                line["also_cql_dp"] = cql
+            if cfg4 is not None:
+                line["also_config4"] = cfg4
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist_on:

@@ -71,6 +71,10 @@ int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
 /* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
 int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
+/* Measurement aid (bench.py's measured TF32 ceiling): 3 (default) = the 3xTF32 product mode; 1 = the same kernel
+ * issuing only the hi*hi MMAs with the operand split skipped, i.e. a plain single-pass TF32 contraction whose
+ * rate bounds what the 3-pass mode can reach (1/3 of it).  Results in mode 1 are TF32-accurate only (~1e-3). */
+int porl_ctx_set_tc_terms(porl_ctx_t* ctx, int terms);
 /* Programmatic dependent launch of the update step's kernels (default on; env PORL_PDL=0 turns it off): each kernel
  * lets its successor be scheduled while it runs and waits for its predecessor's completion before touching global
  * memory, so launch latency hides behind the previous kernel's tail.  Results are unchanged. */

@@ -286,13 +286,24 @@ class ExpectileAgent(nn.Module):
         if sd.get("cuda_rng_state") is not None:
             torch.cuda.set_rng_state(sd["cuda_rng_state"].cpu(), self.device)
 
-    def read_losses(self) -> tuple[float, float]:
-        """Synchronising read of (v_loss, policy_loss) of the last update; raises on device flags."""
-        self._host[0:1].copy_(self.v_group.tail[0:1], non_blocking=True)
-        self._host[1:2].copy_(self.p_group.tail[0:1], non_blocking=True)
-        self._host_status.copy_(self._status, non_blocking=True)
-        _C.sync_stream()
-        flags = int(self._host_status[0])
+    def losses_async(self) -> "PendingLosses":
+        """Enqueue the device->host copy of (v_loss, policy_loss, status word) of the update just issued into a pinned
+        slot and return a handle; `handle.result()` waits for THAT copy only, so a caller can keep several updates in
+        flight and read each step's losses one or two steps late (what `update_async` is for)."""
+        ring = self.__dict__.get("_loss_ring")
+        if ring is None:     # eight slots: a handle stays valid until eight later updates have been issued
+            ring = [(_C.pinned(2, torch.float32), _C.pinned(1, torch.int32), torch.cuda.Event()) for _ in range(8)]
+            self.__dict__["_loss_ring"], self.__dict__["_loss_next"] = ring, 0
+        k = self.__dict__["_loss_next"]
+        host, status, event = ring[k % len(ring)]
+        self.__dict__["_loss_next"] = k + 1
+        host[0:1].copy_(self.v_group.tail[0:1], non_blocking=True)
+        host[1:2].copy_(self.p_group.tail[0:1], non_blocking=True)
+        status.copy_(self._status, non_blocking=True)
+        event.record()
+        return PendingLosses(self, host, status, event)
+
+    def _raise_on_flags(self, flags: int) -> None:
         if flags:
             self._status.zero_()
             msgs = []
@@ -308,4 +319,24 @@ class ExpectileAgent(nn.Module):
             if flags & _C.FLAG_PEER_TIMEOUT:
                 msgs.append("a data-parallel peer did not signal its gradient bucket in time (porl_adam_step_peer)")
             raise FloatingPointError("; ".join(msgs) or f"device status {flags}")
+
+    def read_losses(self) -> tuple[float, float]:
+        """Synchronising read of (v_loss, policy_loss) of the last update; raises on device flags."""
+        self._host[0:1].copy_(self.v_group.tail[0:1], non_blocking=True)
+        self._host[1:2].copy_(self.p_group.tail[0:1], non_blocking=True)
+        self._host_status.copy_(self._status, non_blocking=True)
+        _C.sync_stream()
+        self._raise_on_flags(int(self._host_status[0]))
         return float(self._host[0]), float(self._host[1])
+
+
+class PendingLosses:
+    """Losses of one update on their way to the host (see ExpectileAgent.losses_async)."""
+
+    def __init__(self, agent, host, status, event):
+        self.agent, self.host, self.status, self.event = agent, host, status, event
+
+    def result(self) -> tuple[float, float]:
+        self.event.synchronize()
+        self.agent._raise_on_flags(int(self.status[0]))
+        return float(self.host[0]), float(self.host[1])

@@ -47,3 +47,10 @@ class POR(ExpectileAgent):
         pb = agent.pack(observations, next_observations, rewards, terminals)
         agent._run_update(pb)
         return agent.read_losses()
+
+    def por_residual_update_async(agent, observations, next_observations, rewards, terminals):
+        """`por_residual_update` without the host synchronisation; returns a handle whose `.result()` gives
+        (v_loss, g_loss) of this update (see SORL.update_async)."""
+        pb = agent.pack(observations, next_observations, rewards, terminals)
+        agent._run_update(pb)
+        return agent.losses_async()

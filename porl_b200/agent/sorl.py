@@ -43,6 +43,15 @@ class SORL(ExpectileAgent):
         agent._run_update(pb)
         return agent.read_losses()
 
+    def update_async(agent, observations, actions, rewards, next_observations, terminals):
+        """`update` without the host synchronisation: enqueues the same work and returns a handle whose `.result()`
+        gives (v_loss, g_loss) once THIS update's losses have reached the host.  Lets a training loop keep the next
+        minibatch's host->device copy and the next update in flight while it logs the previous losses (extension; the
+        reference's update() blocks on .item(), agent/sorl.py:127-128)."""
+        pb = agent.pack(observations, next_observations, rewards, terminals, actions)
+        agent._run_update(pb)
+        return agent.losses_async()
+
     def vf_update(agent, observations, actions, rewards, next_observations, terminals):
         """agent/sorl.py:130-152: value step + Polyak update only; returns v_loss."""
         pb = agent.pack(observations, next_observations, rewards, terminals, actions)

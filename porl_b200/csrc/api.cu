@@ -92,6 +92,7 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->partials = nullptr;
   ctx->counters = nullptr;
   ctx->tc_chunk_kb = 1;
+  ctx->tc_terms = 3;
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");
     ctx->tc_a_in_tmem = e ? atoi(e) : 0;
@@ -170,6 +171,12 @@ extern "C" int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode) {
 }
 
 extern "C" int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx) { return ctx ? ctx->gemm_mode : -1; }
+
+extern "C" int porl_ctx_set_tc_terms(porl_ctx_t* ctx, int terms) {
+  PORL_CHECK_ARG(ctx && (terms == 1 || terms == 3), "porl_ctx_set_tc_terms: terms=%d (1 or 3)", terms);
+  ctx->tc_terms = terms;
+  return PORL_OK;
+}
 
 extern "C" int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks) {
   PORL_CHECK_ARG(ctx && k_blocks >= 1 && k_blocks <= 64, "porl_ctx_set_tc_chunk: k_blocks=%d", k_blocks);

@@ -69,6 +69,7 @@ struct alignas(64) TcParams {
   int tiles_n[kMaxGroups];          // n-tiles per group
   int total_tiles;
   int chunk_kb;                     // k-blocks per TMEM accumulation chunk
+  int terms;                        // 3: 3xTF32; 1: hi*hi MMAs only, no operand split (ceiling probe)
   int tile_m;                       // rows per work unit: 128, or 256 in pair mode (two CTAs x 128)
   float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
   unsigned long long* dbg;          // optional per-CTA timestamps (tools/gemm_probe.py), or null
@@ -318,6 +319,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   if (dbg && threadIdx.x == 0) dbg[1] = gtime();
   const int chunk_kb = P.chunk_kb;
+  const bool three = P.terms != 1;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -387,7 +389,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             } else {
               const uint64_t a_hi = smem_desc(st), a_lo = smem_desc(st + C::A_LO_OFF);
 #pragma unroll
-              for (int ks = 0; ks < TC_BK / 8; ++ks) {
+              for (int ks = 0; ks < TC_BK / 8 && three; ++ks) {
                 const uint64_t o = (uint64_t)(2 * ks);
                 if (PAIR) {
                   tc_mma_tf32_pair(d_tmem, a_lo + o, b_hi + o, idesc, acc);
@@ -402,8 +404,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks) {
                 const uint64_t o = (uint64_t)(2 * ks);
-                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
-                else tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, 1u);
+                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + o, b_hi + o, idesc, acc);
+                else tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, acc);
+                acc = 1;
               }
             }
             if (PAIR) tc_commit_pair(empty_bar(s));   // frees the stage (in both CTAs) once these MMAs have read it
@@ -472,7 +475,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
 #pragma unroll
           for (int i = 0; i < (RAW16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
             const int e = t + i * TC_SPLIT_THREADS;
-            if (e < RAW16) {
+            if (e < RAW16 && three) {
               const float4 v = src[e];
               dst[e] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
             }
@@ -772,10 +775,15 @@ static int max_pairs(int smem_bytes) {
 }
 
 int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
-  bool can_split = true;
+  // Split-K whenever the tiles alone would leave most SMs idle: weight gradients (K = batch) and, at small batches,
+  // the forward / input-gradient contractions too -- the last slice to arrive sums the partials in slice order and
+  // runs the whole epilogue (bias, ReLU, ReLU mask, transposed copy), so a batch-256 layer is 100+ short units instead
+  // of 32 tiles with a 16-k-block serial loop each.  The split factor is decided from the 128-row tile count and the
+  // SM count alone, so all kernel variants cut K at the same places (bitwise identical results).
+  const bool can_split = true;
   int min_nkb = 1 << 30;
   TcParams P;
-  int tiles = 0;
+  int tiles = 0, tiles128 = 0;
   // pair mode (variant 2): every problem at least one full 256-row tile high, otherwise the second CTA idles
   bool pair = ctx->tc_a_in_tmem == 2;
   for (int i = 0; i < batch.n_groups && pair; ++i)
@@ -786,7 +794,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
     if (!gemm_tc_eligible(g, a_kmajor, b_kmajor)) return PORL_ERR_UNSUPPORTED;
     const int nkb = (g.K + TC_BK - 1) / TC_BK;
     min_nkb = nkb < min_nkb ? nkb : min_nkb;
-    if (g.epilogue != 0 || g.relu_src != nullptr) can_split = false;
+    tiles128 += ((g.M + TC_BM - 1) / TC_BM) * ((g.n_store + TC_BN - 1) / TC_BN);
     P.tile_begin[i] = tiles;
     P.tiles_n[i] = (g.n_store + TC_BN - 1) / TC_BN;
     tiles += ((g.M + P.tile_m - 1) / P.tile_m) * P.tiles_n[i];
@@ -830,8 +838,8 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   const int sms = pair ? n_pairs : ctx->sm_count;
   const int sub = pair ? 2 : 1;
   int splits = 1;
-  if (can_split && 2 * tiles <= sms) {
-    int want = sms / tiles;
+  if (can_split && 2 * tiles128 <= ctx->sm_count) {
+    int want = ctx->sm_count / tiles128;
     int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
     splits = want < cap ? want : cap;
     const long long ws_tiles = (long long)(kTcWsFloats / (TC_BM * TC_BN));
@@ -846,6 +854,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   P.ws = ctx->tc_ws;
   P.batch = batch;
   P.chunk_kb = ctx->tc_chunk_kb > 0 ? ctx->tc_chunk_kb : 1;
+  P.terms = ctx->tc_terms == 1 ? 1 : 3;
   P.dbg = ctx->tc_dbg;
   const long long units = (long long)tiles * splits;
   const int grid = (int)(units < sms ? units : sms);

@@ -1,7 +1,7 @@
 """2+ GPU check and timing of the data-parallel CQL update (BASELINE config 3: batch 4096, data-parallel).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-        -m tools.dp_cql_check [steps]
+        tools/dp_cql_check.py [--updates N] [--no-timing]
 
 Every rank holds the same replay buffer and weights; each update takes a global batch of 4096 rows, rank r runs the
 fused kernel on its 4096 / world rows (gradients scaled by 1 / 4096) and the gradient sum over the ranks happens inside
@@ -47,7 +47,13 @@ def make(device, dp: bool):
 
 
 def main():
-    steps = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("steps", nargs="?", type=int, default=30)
+    ap.add_argument("--updates", type=int, default=0)
+    ap.add_argument("--no-timing", action="store_true")
+    cli = ap.parse_args()
+    steps = cli.updates or cli.steps
     rank, local, world = pdist.init_from_env()
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
@@ -108,7 +114,7 @@ def main():
         dp.read_losses()                                         # raises on PORL_FLAG_PEER_TIMEOUT
         return n / (float(ms[0]) * 1e-3)
 
-    strong, weak = rate(shard), rate(B_GLOBAL)
+    strong, weak = (0.0, 0.0) if cli.no_timing else (rate(shard), rate(B_GLOBAL))
     if rank == 0:
         print(f"world {world}: DP vs single-process params rel-L2 {early:.2e} after 5 updates (gradients agree to 1e-7; asserted "
               f"<= 1e-6), {rel:.2e} after {steps} free-running updates (max abs {worst:.2e}: once one ReLU unit of one sample "
@@ -116,6 +122,9 @@ def main():
               f"losses {l_dp} vs {l_one}; replicas bitwise identical")
         print(f"CQL updates/s, graph replay, gradient sum inside the Adam kernel: global batch {B_GLOBAL} "
               f"({shard}/GPU) {strong:.0f} | {B_GLOBAL}/GPU {weak:.0f} updates/s = {weak * world:.0f} batch-4096 units/s")
+    dp.read_losses()
+    if rank == 0:
+        print("OK dp_cql_check")
     dist.barrier()
     dist.destroy_process_group()
 
