@@ -288,6 +288,13 @@ typedef struct porl_peer_group {
   float* tail_out;                       /* local: sum over ranks of the tails (tail_floats values) */
   int32_t tail_floats;
   int32_t wait_ms;                       /* give-up budget of each wait (0: 20000) */
+  /* Two-shot (sharded) mode, selected when params[0] != NULL: rank r sums shard r of the bucket over all ranks, runs
+   * Adam / Polyak on that shard only and STORES the new parameters (and target-net values) into every rank's buffers.
+   * Link traffic per rank and step: (world-1)/world * n floats read + as much (twice with a target net) written,
+   * instead of (world-1) * n read; Adam's HBM traffic drops to 1/world; each rank keeps the Adam moments of ITS shard
+   * only (gather them for a checkpoint).  Replicas are bitwise identical by construction.  All NULL: one-shot mode. */
+  float* params[PORL_MAX_PEERS];         /* params[r]: rank r's flat parameter buffer as mapped here (params[rank] = p) */
+  float* target[PORL_MAX_PEERS];         /* same for the target net; NULL entries when the group has none */
 } porl_peer_group_t;
 
 /* device memory other processes of the node can map: cudaMalloc'ed (not from a pooled allocator), zero-filled */
@@ -302,6 +309,19 @@ int porl_peer_close(porl_ctx_t* ctx, void* ptr);
 int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_group_t* peers, float* m, float* v, int64_t n,
                         porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
                         float ema_beta, int32_t hard_every, porl_stream_t stream);
+
+/* Test aid: `world` ranks of the two-shot step on ONE GPU as a single cooperative launch (blockIdx.y = rank), so the
+ * blocks that wait for one another are co-resident by construction.  ranks[r].peers->rank must be r. */
+typedef struct {
+  float* p;
+  float* m;
+  float* v;
+  float* target;                         /* or NULL */
+  porl_opt_state_t* state;
+  const porl_peer_group_t* peers;
+} porl_peer_rank_t;
+int porl_adam_step_peer_emulated(porl_ctx_t* ctx, int32_t world, const porl_peer_rank_t* ranks, int64_t n, float beta1,
+                                 float beta2, float eps, float ema_beta, int32_t hard_every, porl_stream_t stream);
 
 /* ---- whole-update entry points (porl_sorl_step / porl_por_step) ----------------
  * One POR / SORL gradient update as ONE call: the launch sequence of agent/por.py:73-112 and

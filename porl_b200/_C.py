@@ -52,7 +52,13 @@ FLAG_PEER_TIMEOUT = 32
 class PeerGroup(C.Structure):                      # porl_peer_group_t
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("bucket", C.c_void_p * MAX_PEERS),
                 ("pad", C.c_void_p * MAX_PEERS), ("epoch", C.c_void_p), ("tail_out", C.c_void_p),
-                ("tail_floats", C.c_int32), ("wait_ms", C.c_int32)]
+                ("tail_floats", C.c_int32), ("wait_ms", C.c_int32),
+                ("params", C.c_void_p * MAX_PEERS), ("target", C.c_void_p * MAX_PEERS)]   # two-shot mode when params[0]
+
+
+class PeerRank(C.Structure):                       # porl_peer_rank_t (single-GPU emulation of several ranks, tests)
+    _fields_ = [("p", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("target", C.c_void_p), ("state", C.c_void_p),
+                ("peers", C.POINTER(PeerGroup))]
 
 
 class OptGroup(C.Structure):                       # porl_opt_group_t
@@ -160,6 +166,7 @@ _SIGNATURES = {
     "porl_knn": (C.c_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _p]),
     "porl_scan_to_points": (C.c_int, [_p, _p, _i64, _i64, _p, _p]),
     "porl_adam_step_peer": (C.c_int, [_p, _p, C.POINTER(PeerGroup), _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
+    "porl_adam_step_peer_emulated": (C.c_int, [_p, _i32, C.POINTER(PeerRank), _i64, _f, _f, _f, _f, _i32, _p]),
     "porl_peer_alloc": (C.c_int, [_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "porl_peer_free": (C.c_int, [_p, _p]),
     "porl_peer_export": (C.c_int, [_p, _p, C.c_char_p]),

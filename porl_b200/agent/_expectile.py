@@ -58,7 +58,7 @@ class ExpectileAgent(nn.Module):
 
         # --- value group: online TwinV parameters in the group's flat buffer; private target buffer
         probe = TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, init=False)  # geometry only
-        self.v_group = ParamGroup(self.ctx, probe.plan.n_floats, dev, lr=value_lr)
+        self.v_group = ParamGroup(self.ctx, probe.plan.n_floats, dev, lr=value_lr, with_target=True, sharded=True)
         policy_cls = BoundedGaussianPolicy if self._bounded else GaussianPolicy
         # construction order follows the reference so that the global torch RNG is consumed alike:
         # POR builds goal_policy then vf (por.py:35-45); SORL builds v_net then policy (sorl.py:36-45)
@@ -69,7 +69,7 @@ class ExpectileAgent(nn.Module):
         def make_policy():
             pol_probe = policy_cls(S_heads, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, init=False)
             n = policy_cls.group_floats(pol_probe.plan, self.policy_out)
-            self.p_group = ParamGroup(self.ctx, n, dev, lr=policy_lr, t_max=int(max_steps))
+            self.p_group = ParamGroup(self.ctx, n, dev, lr=policy_lr, t_max=int(max_steps), sharded=True)
             return policy_cls(S_heads, self.policy_out, H, n_hidden, ctx=self.ctx, device=dev, flat=self.p_group.params,
                               grads=self.p_group.grads)
 
@@ -77,7 +77,8 @@ class ExpectileAgent(nn.Module):
             policy, value = make_policy(), make_value()
         else:
             value, policy = make_value(), make_policy()
-        target = TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, trainable=False, init=False)
+        target = TwinV(S_heads, args.layer_norm, H, n_hidden, ctx=self.ctx, device=dev, trainable=False, init=False,
+                       flat=self.v_group.target)        # the group's own buffer: peer-mapped in the two-shot DP step
         target.flat.copy_(self.v_group.params[:target.flat.numel()])       # deepcopy(vf).requires_grad_(False)
         # registration order = the reference's attribute order, so state_dict() key order matches
         first, second = ((self._policy_name, policy), (self._value_name, value))

@@ -83,15 +83,23 @@ class ParamGroup:
     """
 
     def __init__(self, ctx: _C.Context, n_floats: int, device, lr: float, t_max: int = 0,
-                 betas=(0.9, 0.999), eps: float = 1e-8):
+                 betas=(0.9, 0.999), eps: float = 1e-8, with_target: bool = False, sharded: bool = False):
+        """with_target: the group owns a target-net buffer of the same geometry (`self.target`); sharded: in a
+        data-parallel job take the two-shot step (every rank updates one shard and stores it into all ranks' buffers,
+        porl_peer_group_t.params) -- parameters and target then live in peer-mappable memory."""
         self.ctx, self.device = ctx, torch.device(device)
         self.n = pad_to(n_floats, 4)
         z = lambda k: torch.zeros(k, dtype=torch.float32, device=self.device)
-        self.params, self.m, self.v = z(self.n), z(self.n), z(self.n)
+        self.m, self.v = z(self.n), z(self.n)
         self.peers = None
-        self.bucket = None
+        self.bucket = self.params = self.target = None
         if pdist.is_dp() and self.device.type == "cuda" and os.environ.get("PORL_PEER_REDUCE", "1") != "0":
-            self._init_peers()
+            two_shot = sharded and os.environ.get("PORL_PEER_MODE", "2") != "1"
+            self._init_peers(two_shot, with_target)
+        if self.params is None:
+            self.params = z(self.n)
+        if with_target and self.target is None:
+            self.target = z(self.n)
         if self.bucket is None:
             self.bucket = z(self.n + GRAD_TAIL)      # gradients | loss tail
         self.grads = self.bucket[:self.n]
@@ -101,21 +109,29 @@ class ParamGroup:
         self.state = torch.zeros(C.sizeof(_C.OptState), dtype=torch.uint8, device=self.device)
         self.reset_clock(step=0, lr=float(lr))
 
-    def _init_peers(self) -> None:
+    def _init_peers(self, two_shot: bool, with_target: bool) -> None:
         """Collective (every rank builds its groups in the same order): put the bucket in peer-mappable memory and
         map the other ranks' buckets, so that `step()` sums the gradients inside the Adam kernel
-        (porl_adam_step_peer).  Falls back to the NCCL all-reduce for big buckets or without a P2P path."""
+        (porl_adam_step_peer).  two_shot: parameters and target net are peer-mapped too and every rank updates one shard
+        (traffic ~2-3x the bucket whatever the world size).  One-shot reads cost (world-1)x the bucket per rank: big
+        buckets then fall back to the NCCL all-reduce, as does a node without a P2P path."""
         from . import peer
 
         world = pdist.world_size()
         nbytes = (self.n + GRAD_TAIL) * 4
-        if world > _C.MAX_PEERS or (world - 1) * nbytes > peer.MAX_PEER_READ_BYTES:
+        if world > _C.MAX_PEERS or (not two_shot and (world - 1) * nbytes > peer.MAX_PEER_READ_BYTES):
             return
         bucket = peer.PeerBuffer(self.ctx, nbytes)
         pad = peer.PeerBuffer(self.ctx, _C.PEER_PAD_WORDS * 4)
-        self.peers = peer.exchange(self.ctx, bucket, pad, GRAD_TAIL)
+        params = peer.PeerBuffer(self.ctx, self.n * 4) if two_shot else None
+        target = peer.PeerBuffer(self.ctx, self.n * 4) if (two_shot and with_target) else None
+        self.peers = peer.exchange(self.ctx, bucket, pad, GRAD_TAIL, params=params, target=target)
         if self.peers is not None:
             self.bucket = bucket.tensor(torch.float32)
+            if two_shot:
+                self.params = params.tensor(torch.float32)
+                if target is not None:
+                    self.target = target.tensor(torch.float32)
 
     @property
     def tail(self) -> torch.Tensor:
@@ -140,6 +156,10 @@ class ParamGroup:
         """Sum the bucket over the data-parallel ranks, then Adam (+ target update).  With peer-mapped buckets both
         happen in one kernel; otherwise one NCCL all-reduce precedes the single-rank kernel."""
         tgt = target.data_ptr() if target is not None else None
+        if self.peers is not None and getattr(self.peers, "sharded", False) and target is not None \
+                and target.data_ptr() != (self.target.data_ptr() if self.target is not None else 0):
+            raise ValueError("two-shot data-parallel step: the target net must be the group's own peer-mapped buffer "
+                             "(ParamGroup(with_target=True).target)")
         if self.peers is not None:
             check(lib.porl_adam_step_peer(self.ctx.handle, self.params.data_ptr(), C.byref(self.peers.struct),
                                           self.m.data_ptr(), self.v.data_ptr(), self.n, self.state.data_ptr(),
@@ -166,10 +186,25 @@ class ParamGroup:
     def param_groups(self):
         return [{"lr": self.read_clock().lr, "betas": self.betas, "eps": self.eps, "initial_lr": self.base_lr}]
 
+    def _full_moments(self):
+        """(exp_avg, exp_avg_sq) of the whole group.  In the two-shot data-parallel step every rank keeps the moments of
+        its own shard only: the full vectors are assembled with one sum all-reduce of the masked shards (collective)."""
+        if self.peers is None or not getattr(self.peers, "sharded", False):
+            return self.m.clone(), self.v.clone()
+        from . import peer
+        s0, s1 = peer.shard_range(self.n, self.peers.world, self.peers.rank)
+        out = []
+        for t in (self.m, self.v):
+            full = torch.zeros_like(t)
+            full[s0:s1] = t[s0:s1]
+            pdist.allreduce_sum_(full)
+            out.append(full)
+        return out[0], out[1]
+
     def state_dict(self):
         c = self.read_clock()
-        return {"step": c.step, "lr": c.lr, "base_lr": self.base_lr, "t_max": self.t_max,
-                "exp_avg": self.m.clone(), "exp_avg_sq": self.v.clone()}
+        m, v = self._full_moments()
+        return {"step": c.step, "lr": c.lr, "base_lr": self.base_lr, "t_max": self.t_max, "exp_avg": m, "exp_avg_sq": v}
 
     def load_state_dict(self, sd) -> None:
         self.m.copy_(sd["exp_avg"])

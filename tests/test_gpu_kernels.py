@@ -405,6 +405,91 @@ def test_adam_peer_sum_equals_presummed_adam(env, world, n):
     assert all(grp.read_clock().step == 6 for grp in reps)
 
 
+@pytest.mark.parametrize("world,n,ema,hard", [(2, 4096, 0.005, 0), (3, 1028, 0.0, 0), (8, 20480, 0.005, 0), (4, 512, 0.0, 2),
+                                              (8, 132, 0.005, 0)])
+def test_adam_two_shot_sharded_step_equals_presummed_adam(env, world, n, ema, hard):
+    """Two-shot data-parallel step (porl_peer_group_t.params set): `world` ranks emulated on ONE device as a single
+    cooperative launch (blockIdx.y = rank; porl_adam_step_peer_emulated), each with its own parameter / target /
+    moment / bucket buffers.  Every rank must end up with parameters and target net BITWISE equal to porl_adam_step on
+    the gradients summed in rank order, moments equal on the shard it owns and untouched elsewhere, tails summed, over
+    six epochs (both handshakes, LR recursion, hard target copy every 2 steps)."""
+    import ctypes as C
+    from porl_b200.nets import ParamGroup, GRAD_TAIL
+    from porl_b200.peer import PeerReduce, shard_range
+    _C, ctx, dev = env
+    g = torch.Generator().manual_seed(world * 1000 + n)
+    p0 = torch.randn(n, generator=g).to(dev)
+    use_t = ema > 0 or hard > 0
+    ref = ParamGroup(ctx, n, dev, lr=1e-3, t_max=5, with_target=True)
+    ref.params.copy_(p0)
+    reps = [ParamGroup(ctx, n, dev, lr=1e-3, t_max=5, with_target=True) for _ in range(world)]
+    pads = [torch.zeros(_C.PEER_PAD_WORDS, dtype=torch.int32, device=dev) for _ in range(world)]
+    for r, grp in enumerate(reps):
+        grp.params.copy_(p0)
+        grp.peers = PeerReduce(ctx, r, [q.bucket.data_ptr() for q in reps], [q.data_ptr() for q in pads], GRAD_TAIL,
+                               wait_ms=5000, params=[q.params.data_ptr() for q in reps],
+                               targets=[q.target.data_ptr() for q in reps])
+    ranks = (_C.PeerRank * world)()
+    for r, grp in enumerate(reps):
+        ranks[r].p, ranks[r].m, ranks[r].v = grp.params.data_ptr(), grp.m.data_ptr(), grp.v.data_ptr()
+        ranks[r].target = grp.target.data_ptr() if use_t else None
+        ranks[r].state = grp.state.data_ptr()
+        ranks[r].peers = C.pointer(grp.peers.struct)
+    ctx.status_tensor().zero_()
+    for epoch in range(6):
+        grads = [torch.randn(n + GRAD_TAIL, generator=g).to(dev) for _ in range(world)]
+        total = grads[0].clone()
+        for r in range(1, world):
+            total += grads[r]
+        for r, grp in enumerate(reps):
+            grp.bucket.copy_(grads[r])
+        ref.bucket.copy_(total)
+        torch.cuda.synchronize()
+        _C.check(_C.lib.porl_adam_step_peer_emulated(ctx.handle, world, ranks, n, 0.9, 0.999, 1e-8, ema, hard,
+                                                     _C.stream_ptr()))
+        ref.step(target=ref.target if use_t else None, ema_beta=ema, hard_every=hard)
+        torch.cuda.synchronize()
+        assert int(ctx.status_tensor()[0]) & _C.FLAG_PEER_TIMEOUT == 0
+        for r, grp in enumerate(reps):
+            assert torch.equal(grp.params, ref.params), (epoch, r)
+            assert torch.equal(grp.target, ref.target), (epoch, r)
+            assert torch.equal(grp.peers.tail_out, total[n:])
+            assert torch.equal(grp.bucket, grads[r])          # the bucket itself is only read
+            s0, s1 = shard_range(n, world, r)
+            assert torch.equal(grp.m[s0:s1], ref.m[s0:s1]) and torch.equal(grp.v[s0:s1], ref.v[s0:s1])
+            assert float(grp.m[:s0].abs().sum()) == 0.0 and float(grp.m[s1:].abs().sum()) == 0.0   # other shards untouched
+    assert all(grp.read_clock().step == 6 for grp in reps)
+    clocks = [grp.read_clock().lr for grp in reps]
+    assert all(abs(c - ref.read_clock().lr) == 0.0 for c in clocks)
+    # the shards tile the group exactly
+    cover = sorted(shard_range(n, world, r) for r in range(world))
+    assert cover[0][0] == 0 and cover[-1][1] == n and all(a[1] == b[0] for a, b in zip(cover, cover[1:]))
+
+
+def test_adam_two_shot_timeout_skips_the_step(env):
+    """Two-shot step, a peer that never signals: flag raised, nothing written (neither here nor into the peer)."""
+    from porl_b200.nets import ParamGroup, GRAD_TAIL
+    from porl_b200.peer import PeerReduce
+    _C, ctx, dev = env
+    n = 512
+    grp, other = (ParamGroup(ctx, n, dev, lr=1e-3, with_target=True) for _ in range(2))
+    pads = [torch.zeros(_C.PEER_PAD_WORDS, dtype=torch.int32, device=dev) for _ in range(2)]
+    grp.peers = PeerReduce(ctx, 0, [grp.bucket.data_ptr(), other.bucket.data_ptr()], [q.data_ptr() for q in pads], GRAD_TAIL,
+                           wait_ms=50, params=[grp.params.data_ptr(), other.params.data_ptr()],
+                           targets=[grp.target.data_ptr(), other.target.data_ptr()])
+    status = ctx.status_tensor()
+    status.zero_()
+    grp.params.normal_()
+    grp.bucket.normal_()
+    before = grp.params.clone()
+    grp.step(target=grp.target, ema_beta=0.5)
+    torch.cuda.synchronize()
+    assert int(status[0]) & _C.FLAG_PEER_TIMEOUT
+    assert torch.equal(grp.params, before) and float(other.params.abs().sum()) == 0.0
+    assert float(grp.m.abs().sum()) == 0.0 and float(grp.target.abs().sum()) == 0.0 and grp.read_clock().step == 0
+    status.zero_()
+
+
 def test_adam_peer_timeout_sets_flag_and_returns(env):
     """A peer that never signals: the kernel gives up after wait_ms, raises PORL_FLAG_PEER_TIMEOUT and finishes
     WITHOUT applying the update (the other rank's bucket is not this step's gradient)."""

@@ -77,7 +77,11 @@ def traffic(rep, kernel):
     per = [int(float(r[rd].replace(",", "")) * scale[units[rd]] + float(r[wr].replace(",", "")) * scale[units[wr]])
            for r in rows if kernel in r[hdr.index("Kernel Name")]]
     dur = [float(r[du].replace(",", "")) for r in rows if kernel in r[hdr.index("Kernel Name")]]
+    import hashlib, os
+    src = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "porl_b200", "csrc", "gemm_tc.cu")
+    sha = hashlib.sha256(open(src, "rb").read()).hexdigest() if "gemm_tc" in kernel else None
     print(json.dumps({"kernel": kernel, "source": f"{rep.split('/')[-1]} (ncu --set full --clock-control none)",
+                      "source_sha256": sha,
                       "dram_bytes_per_launch": per, "duration_us_under_ncu": dur,
                       "mean_bytes_per_launch": sum(per) // max(len(per), 1)}, indent=1))
 
