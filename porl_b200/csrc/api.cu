@@ -215,6 +215,7 @@ extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, in
   GemmGroup& g = b.g[0];
   g.A = A; g.B = B; g.C = C; g.A_lo = nullptr; g.B_lo = nullptr; g.C_lo = nullptr; g.bias = bias; g.relu_src = relu_src; g.colsum = colsum;
   g.Ct = Ct; g.ldct = (int)ldct;
+  g.bits_out = nullptr; g.bits_in = nullptr; g.ld_bits = 0;
   g.M = (int)M; g.N = (int)N; g.K = (int)K;
   g.lda = (int)lda; g.ldb = (int)ldb; g.ldc = (int)ldc; g.ld_relu = (int)ld_relu;
   g.n_store = (int)(n_store > 0 ? n_store : N);

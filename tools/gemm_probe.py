@@ -107,6 +107,48 @@ def time_shapes():
         ctx.set_gemm_mode(0)
 
 
+def epi():
+    """python tools/gemm_probe.py epi: cost of the epilogue features on the step's shapes (tensor-core mode)."""
+    for (M, N, K) in ((4096, 512, 512), (16384, 512, 512), (16384, 512, 384), (8192, 512, 512)):
+        A, B = operands(1, 1, M, N, K)
+        Ad, Bd = A.to(dev), B.to(dev)
+        Cd = torch.randn(M, pad(N), device=dev)
+        Ct = torch.zeros(N, pad(M), device=dev)
+        bias = torch.randn(pad(N), device=dev)
+        stamps = torch.zeros(16 * 148, dtype=torch.int64, device=dev)
+        ctx.set_gemm_mode(1)
+        for name, kw in (("plain", {}), ("bias+relu", dict(bias=1, epi=1)), ("bias+relu+Ct", dict(bias=1, epi=1, ct=1)),
+                         ("mask(in place)+Ct", dict(mask=1, ct=1)), ("mask(in place)", dict(mask=1)), ("Ct", dict(ct=1))):
+            def go():
+                _C.check(_C.lib.porl_gemm(ctx.handle, 1, 1, M, N, K, Ad.data_ptr(), Ad.stride(0), Bd.data_ptr(), Bd.stride(0),
+                                          Cd.data_ptr(), Cd.stride(0), bias.data_ptr() if kw.get("bias") else None,
+                                          kw.get("epi", 0), Cd.data_ptr() if kw.get("mask") else None, Cd.stride(0), N, None,
+                                          Ct.data_ptr() if kw.get("ct") else None, Ct.stride(0), _C.stream_ptr()))
+            ctx.set_tc_debug(stamps.data_ptr())
+            for _ in range(3):
+                go()
+            torch.cuda.synchronize()
+            ctx.profile(True)
+            for _ in range(20):
+                Cd.normal_()
+                go()
+            torch.cuda.synchronize()
+            c = ctx.profile_read()["contraction"]
+            ctx.profile(False)
+            us = c["ms"] / c["launches"] * 1e3
+            t = stamps.cpu().view(148, 16)
+            t = t[t[:, 15] > 0]
+            d = t[:, 15] - t[:, 0]
+            print(f"epi M={M} N={N} K={K} {name:20s} {us:7.1f} us/launch {2.0*M*N*K/us*1e-6:6.1f} TFLOP/s  cta_us mean/max "
+                  f"{float(d.double().mean())/1e3:.1f}/{float(d.max())/1e3:.1f}  cta0: first tile drained "
+                  f"{(int(t[0,8])-int(t[0,0]))/1e3:.1f} epilogue done {(int(t[0,9])-int(t[0,0]))/1e3:.1f} all {(int(t[0,10])-int(t[0,0]))/1e3:.1f}"
+                  f"  waits mma/tmem_empty={int(t[0,14])/max(int(t[0,5]),1):.2f} mma/split_done={int(t[0,13])/max(int(t[0,5]),1):.2f} "
+                  f"acc/tmem_full={int(t[0,4])/max(int(t[0,5]),1):.2f} prod/empty={int(t[0,11])/max(int(t[0,5]),1):.2f}", flush=True)
+            stamps.zero_()
+        ctx.set_tc_debug(None)
+        ctx.set_gemm_mode(0)
+
+
 def one():
     """python tools/gemm_probe.py one M N K [atm]: three launches of one shape in tensor-core mode (for ncu)."""
     M, N, K = (int(x) for x in sys.argv[2:5])
@@ -122,4 +164,4 @@ def one():
 
 
 if __name__ == "__main__" and len(sys.argv) > 1:
-    {"acc": acc, "time": time_shapes, "one": one}[sys.argv[1]]()
+    {"acc": acc, "time": time_shapes, "one": one, "epi": epi}[sys.argv[1]]()
