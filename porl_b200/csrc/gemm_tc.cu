@@ -24,6 +24,8 @@
 // waits for another one.
 #include <cuda.h>
 
+#include <stdlib.h>
+
 #include <type_traits>
 #include <unordered_map>
 
@@ -71,6 +73,7 @@ struct alignas(64) TcParams {
   int total_tiles;
   int chunk_kb;                     // k-blocks per TMEM accumulation chunk
   int terms;                        // 3: 3xTF32; 1: hi*hi MMAs only, no operand split (ceiling probe)
+  int dist_fix;                     // split-K: one unit per CTA, the slices of a tile share its final sum (see the epilogue)
   int a_mn, b_mn;                   // operand is MN-major in memory (A[k*lda + m] / B[k*ldb + n]): no transposed copy needed
   int tile_m;                       // rows per work unit: 128, or 256 in pair mode (two CTAs x 128)
   float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
@@ -382,6 +385,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // 16-byte units the start address advances per 8-wide k-step: 32 bytes along a K-major row, one 1024-byte
       // k-group of an MN-major tile
       const uint64_t a_step = P.a_mn ? 64u : 2u, b_step = P.b_mn ? 64u : 2u;
+      // descriptor templates without the start address (this thread alone paces the tensor pipe: nothing that can be
+      // decided per launch is recomputed per k-block); stage addresses are 1024-byte aligned, so adding (bytes >> 4)
+      // to a descriptor moves its 14-bit start-address field only
+      const uint64_t tmpl_a = (P.a_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)(base >> 4);
+      const uint64_t tmpl_b = (P.b_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)((base + TC_TILE_BYTES) >> 4);
       int it = 0, chunk = 0;
       long long w_te = 0, w_sd = 0;
       TcUnit w;
@@ -403,9 +411,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             mbar_wait(split_done(s), ph);
             if (dbg) w_sd += clock64() - tw1;
             tc_fence_after();
-            const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-            const uint64_t b_hi = P.b_mn ? smem_desc_mn(st + TC_TILE_BYTES) : smem_desc(st + TC_TILE_BYTES);
-            const uint64_t b_lo = P.b_mn ? smem_desc_mn(st + C::B_LO_OFF) : smem_desc(st + C::B_LO_OFF);
+            const uint64_t st16 = (uint64_t)((uint32_t)s * (TC_STAGE_BYTES >> 4));
+            const uint64_t b_hi = tmpl_b + st16;
+            const uint64_t b_lo = b_hi + (uint64_t)((C::B_LO_OFF - TC_TILE_BYTES) >> 4);
             // small terms first (they meet the smallest accumulator), then the hi*hi terms
             if (ATM) {
               const uint32_t a_hi = tmem_base + (uint32_t)(TC_ACC_COLS + s * 64), a_lo = a_hi + 32u;
@@ -420,19 +428,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
               for (int ks = 0; ks < TC_BK / 8; ++ks)
                 tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + b_step * ks, idesc, 1u);
             } else {
-              const uint64_t a_hi = P.a_mn ? smem_desc_mn(st) : smem_desc(st);
-              const uint64_t a_lo = P.a_mn ? smem_desc_mn(st + C::A_LO_OFF) : smem_desc(st + C::A_LO_OFF);
+              const uint64_t a_hi = tmpl_a + st16;
+              const uint64_t a_lo = a_hi + (uint64_t)(C::A_LO_OFF >> 4);
+              if (three) {
 #pragma unroll
-              for (int ks = 0; ks < TC_BK / 8 && three; ++ks) {
-                const uint64_t oa = a_step * ks, ob = b_step * ks;
-                if (PAIR) {
-                  tc_mma_tf32_pair(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
-                  acc = 1;
-                  tc_mma_tf32_pair(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
-                } else {
-                  tc_mma_tf32(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
-                  acc = 1;
-                  tc_mma_tf32(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
+                for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                  const uint64_t oa = a_step * ks, ob = b_step * ks;
+                  if (PAIR) {
+                    tc_mma_tf32_pair(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
+                    acc = 1;
+                    tc_mma_tf32_pair(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
+                  } else {
+                    tc_mma_tf32(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
+                    acc = 1;
+                    tc_mma_tf32(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
+                  }
                 }
               }
 #pragma unroll
@@ -630,6 +640,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // pair mode: each CTA's 128 x 128 half of the tile is its own split-K unit (workspace slot, ticket)
       const int gt = (P.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
       const int n_sub = P.total_tiles * (PAIR ? 2 : 1);
+      // Who sums: with one unit per CTA (every split launch: units <= resident CTAs, so all slices of a tile run at the
+      // same time) the FIX-UP IS DISTRIBUTED: slice s sums and finishes the slabs sl with sl % S == s (at most four
+      // slices take part), after waiting for all S slices of the tile to have parked -- S x 16 KB per SM instead of
+      // S x 64 KB through the one SM of the last arriver (measured: the L2 -> SM port made that 7-16 us per tile).
+      // Otherwise (a CTA holds several units, a later slice may not be running yet) the last slice to arrive sums.
+      const bool dist = split && P.dist_fix != 0;
+      int fix_mod = 1, fix_me = 0;                               // this CTA finishes the slabs sl with sl % fix_mod == fix_me
       if (split) {
         float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
 #pragma unroll
@@ -637,18 +654,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           wp[(c4 >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (warp == TC_EPI_WARP0 && lane == 0) {
-          int* ticket = P.batch.sem + gt;
-          const int old = atomicAdd(ticket, 1);
-          const int last = (old == S - 1) ? 1 : 0;
-          if (last) *ticket = 0;                             // self-reset for the next launch (stream-ordered)
-          *flag_slot = (uint32_t)last;
+        int* const ticket = P.batch.sem + gt;
+        if (dist) {
+          if (warp == TC_EPI_WARP0 && lane == 0) {
+            atomicAdd(ticket, 1);
+            if (w.split < 4) {                                   // a fixer: wait until every slice has parked
+              while (ld_acquire(ticket) < S) __nanosleep(32);
+            }
+          }
+          if (w.split >= 4) continue;                            // nothing to sum for this slice
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          __threadfence();
+          fix_mod = S;
+          fix_me = w.split;
+        } else {
+          if (warp == TC_EPI_WARP0 && lane == 0) {
+            const int old = atomicAdd(ticket, 1);
+            const int last = (old == S - 1) ? 1 : 0;
+            if (last) *ticket = 0;                               // self-reset for the next launch (stream-ordered)
+            *flag_slot = (uint32_t)last;
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          const bool is_last = *reinterpret_cast<volatile uint32_t*>(flag_slot) != 0;
+          asm volatile("bar.sync 1, 128;" ::: "memory");        // flag consumed before the next unit rewrites it
+          if (!is_last) continue;
+          __threadfence();
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const bool is_last = *reinterpret_cast<volatile uint32_t*>(flag_slot) != 0;
-        asm volatile("bar.sync 1, 128;" ::: "memory");      // flag consumed before the next unit rewrites it
-        if (!is_last) continue;
-        __threadfence();
       }
       // ---- epilogue, one 128 x 32 slab at a time (thread = output row).  The slab comes from the register accumulator
       // or, for the last slice of a split tile, from the parked partials: all slices' loads of a slab are in flight
@@ -674,6 +705,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           if (w.n0 + 32 * sl >= gNs) break;
           float v[32];
           if constexpr (SPLIT) {
+            if (sl % fix_mod != fix_me) continue;                  // another slice finishes this slab
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = 0.f;
             const float4* rp = reinterpret_cast<const float4*>(P.ws) + (size_t)gt * (32 * 128) + r_in_tile + (8 * sl) * 128;
@@ -744,6 +776,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       };
       if (split) epilogue(std::true_type{});
       else epilogue(std::false_type{});
+      if (dist && warp == TC_EPI_WARP0 && lane == 0) {
+        // second round on the ticket: the last fixer to finish resets it for the next launch
+        const int nfix = S < 4 ? S : 4;
+        if (atomicAdd(P.batch.sem + gt, 1) == S + nfix - 1) P.batch.sem[gt] = 0;
+      }
       if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // bias slots free for the next tile
       if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
     }
@@ -967,6 +1004,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   P.dbg = ctx->tc_dbg;
   const long long units = (long long)tiles * splits;
   const int grid = (int)(units < sms ? units : sms);
+  P.dist_fix = (splits > 1 && units <= grid && !pair && getenv("PORL_TC_LAST_ARRIVER") == nullptr) ? 1 : 0;
 
   if (pair) {
     cudaLaunchConfig_t cfg = {};

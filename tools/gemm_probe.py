@@ -149,6 +149,44 @@ def epi():
         ctx.set_gemm_mode(0)
 
 
+def forms():
+    """python tools/gemm_probe.py forms: the four operand forms (K-major / MN-major A and B) on the weight-gradient and
+    forward shapes, with the per-role wait shares."""
+    for (M, N, K) in ((512, 512, 4096), (4096, 512, 512), (8192, 8192, 1024)):
+        g = torch.Generator().manual_seed(1)
+        Ak, Am = torch.randn(M, K, generator=g).to(dev), torch.randn(K, M, generator=g).to(dev)
+        Bk, Bm = torch.randn(N, K, generator=g).to(dev), torch.randn(K, N, generator=g).to(dev)
+        Cd = torch.zeros(M, N, device=dev)
+        stamps = torch.zeros(16 * 148, dtype=torch.int64, device=dev)
+        ctx.set_gemm_mode(1)
+        for a_k, b_k in ((1, 1), (1, 0), (0, 1), (0, 0)):
+            A, B = (Ak if a_k else Am), (Bk if b_k else Bm)
+            def go():
+                _C.check(_C.lib.porl_gemm(ctx.handle, a_k, b_k, M, N, K, A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0),
+                                          Cd.data_ptr(), N, None, 0, None, 0, N, None, None, 0, _C.stream_ptr()))
+            ctx.set_tc_debug(stamps.data_ptr())
+            for _ in range(3):
+                go()
+            torch.cuda.synchronize()
+            ctx.profile(True)
+            for _ in range(20):
+                go()
+            torch.cuda.synchronize()
+            c = ctx.profile_read()["contraction"]
+            ctx.profile(False)
+            us = c["ms"] / c["launches"] * 1e3
+            t = stamps.cpu().view(148, 16)
+            t = t[t[:, 15] > 0]
+            d = t[:, 15] - t[:, 0]
+            w = lambda i: int(t[0, i]) / max(int(t[0, 5]), 1)
+            print(f"forms M={M} N={N} K={K} a_kmajor={a_k} b_kmajor={b_k} {us:7.1f} us {2.0*M*N*K/us*1e-6:6.1f} TFLOP/s cta mean/max "
+                  f"{float(d.double().mean())/1e3:.1f}/{float(d.max())/1e3:.1f} drained {(int(t[0,8])-int(t[0,0]))/1e3:.1f} waits: prod/empty={w(11):.2f} "
+                  f"split/raw_full={w(12):.2f} mma/split_done={w(13):.2f} mma/tmem_empty={w(14):.2f} acc/tmem_full={w(4):.2f}", flush=True)
+            stamps.zero_()
+        ctx.set_tc_debug(None)
+        ctx.set_gemm_mode(0)
+
+
 def one():
     """python tools/gemm_probe.py one M N K [atm]: three launches of one shape in tensor-core mode (for ncu)."""
     M, N, K = (int(x) for x in sys.argv[2:5])
@@ -164,4 +202,4 @@ def one():
 
 
 if __name__ == "__main__" and len(sys.argv) > 1:
-    {"acc": acc, "time": time_shapes, "one": one, "epi": epi}[sys.argv[1]]()
+    {"acc": acc, "time": time_shapes, "one": one, "epi": epi, "forms": forms}[sys.argv[1]]()
