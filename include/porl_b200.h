@@ -180,10 +180,14 @@ typedef struct {
   float* saved;           /* porl_mlp_saved_floats(B) floats; a training forward keeps the activations
                              here for porl_mlp_backward, an inference forward uses it as scratch */
   float* out;             /* (n_nets, B, ld_out) */
-  int32_t inference;      /* 1: no backward follows (skip the transposed activation copies the tensor-core
-                             weight-gradient contractions read); 0: training forward */
-  int32_t pad_;
+  int32_t inference;      /* 1: no backward follows; 0: training forward (keeps the ReLU bits the backward reads) */
+  int32_t pad_;           /* flags: PORL_MLP_SKIP_HEAD | PORL_MLP_HEAD_DONE, else 0 */
 } porl_mlp_call_t;
+/* porl_mlp_forward stops before a scalar / narrow output layer (porl_value_head_step evaluates it) */
+#define PORL_MLP_SKIP_HEAD 1
+/* porl_mlp_backward: the output layer is already back-propagated (porl_value_head_step wrote its dW / db, the bias
+ * gradient of the layer below and, over the last hidden activation, dz); dout is ignored and may be NULL */
+#define PORL_MLP_HEAD_DONE 2
 
 /* Forward of up to PORL_MAX_CALLS MLPs on the same batch size; layer l of every call runs in one
  * grouped launch.  Replaces TwinV.both/forward, GaussianPolicy.net, QNetwork.forward. */
@@ -204,6 +208,17 @@ int porl_expectile_twin_loss(porl_ctx_t* ctx, const float* v1, const float* v2, 
                              const float* nv2, int64_t ldv, const float* rewards, const float* dones,
                              float gamma, float tau, int64_t B, int64_t B_norm, float* target_v,
                              float* dv1, float* dv2, float* loss_out, porl_stream_t stream);
+
+/* Fused head step of the twin value nets (agent/por.py:80-87, agent/sorl.py:85-92): the scalar heads of the target nets
+ * on next_obs and of the online nets on obs, the TD target, the twin expectile loss (as porl_expectile_twin_loss) and the
+ * heads' backward (dW, db, ReLU-masked dz in place, db of the layer below) in ONE pass over the last hidden activations.
+ * `target` / `online` are the calls a porl_mlp_forward with pad_ = PORL_MLP_SKIP_HEAD has just evaluated (same plan);
+ * follow with porl_mlp_backward(online with pad_ = PORL_MLP_HEAD_DONE, dout = NULL).  target_v (B) and loss_out[0] are
+ * overwritten.  porl_value_head_step_supported: twin nets, scalar head, last hidden width <= 1024, no LayerNorm. */
+int porl_value_head_step_supported(const porl_mlp_t* mlp);
+int porl_value_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* target, const porl_mlp_call_t* online, int64_t B,
+                         const float* rewards, const float* dones, float gamma, float tau, int64_t B_norm,
+                         float* target_v, float* grads, float* loss_out, porl_stream_t stream);
 
 /* ---- K5: advantage-weighted diagonal-Gaussian NLL (agent/por.py:97-106; agent/sorl.py:102-109;
  *          agent/policy.py:18-23,42-49) ------------------------------------------------------- */

@@ -245,4 +245,222 @@ int launch_head_backward(porl_ctx* ctx, const HeadBwdBatch& hb, cudaStream_t st)
   return PORL_OK;
 }
 
+
+// ---------------------------------------------------------------- fused scalar-V head step
+// grid (row chunks, 2 online nets), 8 warps; a warp takes one row at a time (lanes stride the columns in float4s,
+// NJ = ceil(H / 128) of them per lane): the two target rows and the online row are loaded together, three dot
+// products give v1', v2', v_k, the TD target / expectile weight / dL/dv follow in registers (the formulas of
+// expectile_kernel), and the same registers feed the head's backward: dz in place over h, dW and the bias gradient of
+// the layer below as per-lane accumulators.  Head weights sit in shared memory.  Reductions over the batch are
+// order-fixed: warps of a block in index order, row chunks in index order by the last block of the net (ticket), the
+// loss by the last block of the grid.  Replaces head_forward (4 nets) + expectile_kernel + head_backward (2 nets): three
+// launches and a second pass over the online activations.
+constexpr int kVhGroup = 16;   // fan-in of the reduction tree
+template <int NJ>
+__global__ void __launch_bounds__(256) vhead_fused_kernel(const __grid_constant__ VHeadArgs a, float* partials,
+                                                         uint32_t* tickets, uint32_t* status) {
+  pdl_entry();
+  extern __shared__ __align__(16) float vsm[];
+  constexpr int W128 = NJ * 128;
+  float* s_w = vsm;                       // [3][W128]: online w_k, target w_1, target w_2
+  float* s_acc = vsm + 3 * W128;          // [8 warps][2][W128]: dW and db_prev accumulators
+  __shared__ float s_scal[8][2];          // per warp: sum dv, loss
+  __shared__ int s_flag[1];
+  const int k = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = gridDim.x;
+  const int Hp = (a.H + 3) & ~3;
+  for (int i = threadIdx.x; i < 3 * W128; i += 256) {
+    const int v = i / W128, c = i % W128;
+    const float* src = v == 0 ? a.w[k] : a.wt[v - 1];
+    s_w[i] = c < a.H ? __ldg(src + c) : 0.f;
+  }
+  __syncthreads();
+  const float bk = a.b[k][0], bt1 = a.bt[0][0], bt2 = a.bt[1][0];
+  float* const hk = a.h[k];
+  const int64_t r0 = (int64_t)blockIdx.x * a.B / R, r1 = (int64_t)(blockIdx.x + 1) * a.B / R;
+  float4 dw[NJ], dbp[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) dw[j] = dbp[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float dbn = 0.f, loss = 0.f;
+  for (int64_t row = r0 + warp; row < r1; row += 8) {
+    float4 h4[NJ], t1[NJ], t2[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      const bool ok = c < Hp;
+      h4[j] = ok ? *reinterpret_cast<const float4*>(hk + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      t1[j] = ok ? *reinterpret_cast<const float4*>(a.ht[0] + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      t2[j] = ok ? *reinterpret_cast<const float4*>(a.ht[1] + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float s = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      const float4 w4 = *reinterpret_cast<const float4*>(s_w + c);
+      const float4 u4 = *reinterpret_cast<const float4*>(s_w + W128 + c);
+      const float4 x4 = *reinterpret_cast<const float4*>(s_w + 2 * W128 + c);
+      s = fmaf(h4[j].x, w4.x, s); s = fmaf(h4[j].y, w4.y, s); s = fmaf(h4[j].z, w4.z, s); s = fmaf(h4[j].w, w4.w, s);
+      s1 = fmaf(t1[j].x, u4.x, s1); s1 = fmaf(t1[j].y, u4.y, s1); s1 = fmaf(t1[j].z, u4.z, s1); s1 = fmaf(t1[j].w, u4.w, s1);
+      s2 = fmaf(t2[j].x, x4.x, s2); s2 = fmaf(t2[j].y, x4.y, s2); s2 = fmaf(t2[j].z, x4.z, s2); s2 = fmaf(t2[j].w, x4.w, s2);
+    }
+    const float v = warp_sum(s) + bk;
+    const float nv = fminf(warp_sum(s1) + bt1, warp_sum(s2) + bt2);
+    const float t = a.rewards[row] + ((1.f - a.dones[row]) * a.gamma) * nv;      // TD target (agent/por.py:85)
+    const float u = t - v;
+    const float wgt = fabsf(a.tau - (u < 0.f ? 1.f : 0.f));                        // asymmetric_l2_loss (por.py:15-17)
+    const float dv = -(wgt * u) * a.inv_bn;
+    if (lane == 0) {
+      loss += wgt * u * u;
+      if (k == 0) a.target_v[row] = t;
+    }
+    dbn += dv;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      if (c < Hp) {
+        const float4 w4 = *reinterpret_cast<const float4*>(s_w + c);
+        float4 g = make_float4(dv * w4.x, dv * w4.y, dv * w4.z, dv * w4.w);
+        if (!(h4[j].x > 0.f)) g.x = 0.f;
+        if (!(h4[j].y > 0.f)) g.y = 0.f;
+        if (!(h4[j].z > 0.f)) g.z = 0.f;
+        if (!(h4[j].w > 0.f)) g.w = 0.f;
+        *reinterpret_cast<float4*>(hk + row * a.ldh + c) = g;
+        dw[j].x = fmaf(dv, h4[j].x, dw[j].x); dw[j].y = fmaf(dv, h4[j].y, dw[j].y);
+        dw[j].z = fmaf(dv, h4[j].z, dw[j].z); dw[j].w = fmaf(dv, h4[j].w, dw[j].w);
+        dbp[j].x += g.x; dbp[j].y += g.y; dbp[j].z += g.z; dbp[j].w += g.w;
+      }
+    }
+  }
+  // block partial: the 8 warps in index order
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    const int c = 128 * j + 4 * lane;
+    *reinterpret_cast<float4*>(s_acc + ((size_t)warp * 2 + 0) * W128 + c) = dw[j];
+    *reinterpret_cast<float4*>(s_acc + ((size_t)warp * 2 + 1) * W128 + c) = dbp[j];
+  }
+  if (lane == 0) { s_scal[warp][0] = dbn; s_scal[warp][1] = loss; }
+  __syncthreads();
+  // partial layout per (net, row chunk): [2][W128] then [dv sum, loss]
+  const size_t per_chunk = (size_t)2 * W128 + 4;
+  float* part = partials + ((size_t)k * R + blockIdx.x) * per_chunk;
+  for (int i = threadIdx.x; i < 2 * W128; i += 256) {
+    float t = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) t += s_acc[(size_t)wq * 2 * W128 + i];
+    part[i] = t;
+  }
+  if (threadIdx.x < 2) {
+    float t = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+    part[2 * W128 + threadIdx.x] = t;
+  }
+  // Two-level, order-fixed reduction tree (fan-in kVhGroup): the last block of each group of kVhGroup consecutive row
+  // chunks sums the group's partials (chunk order) into a group partial, the last group of the net to finish sums the
+  // group partials (group order) into dW / db / db_prev, the last net adds the two loss sums.  One block summing all
+  // R partials would pull R x 4 KB through a single SM (measured: +30 us at R = 256).
+  const int G = (R + kVhGroup - 1) / kVhGroup, grp = blockIdx.x / kVhGroup;
+  const int g0 = grp * kVhGroup, g1 = min(g0 + kVhGroup, R);
+  float* const gpart = partials + (size_t)2 * R * per_chunk + ((size_t)k * G + grp) * per_chunk;
+  auto last_of = [&](uint32_t* tk, uint32_t n) {          // true in every thread of the n-th block to arrive
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t t = atomicAdd(tk, 1u);
+      const bool last = (t == n - 1);
+      if (last) *tk = 0;
+      s_flag[0] = last ? 1 : 0;
+    }
+    __syncthreads();
+    const bool last = s_flag[0] != 0;
+    __syncthreads();
+    if (last) __threadfence();
+    return last;
+  };
+  auto sum_partials = [&](const float* src, int n, float* dst, bool final_net) {
+    // element i of n consecutive partials, all n loads in flight, added in index order
+    for (int i = threadIdx.x; i < 2 * W128 + 2; i += 256) {
+      float vals[kVhGroup];
+#pragma unroll
+      for (int r = 0; r < kVhGroup; ++r) vals[r] = r < n ? __ldcg(src + (size_t)r * per_chunk + i) : 0.f;
+      float t = vals[0];
+#pragma unroll
+      for (int r = 1; r < kVhGroup; ++r)
+        if (r < n) t += vals[r];
+      if (!final_net) {
+        dst[i] = t;
+      } else if (i < W128) {
+        if (i < a.ldw) a.dW[k][i] = i < a.H ? t : 0.f;
+      } else if (i < 2 * W128) {
+        if (i - W128 < a.H) a.db_prev[k][i - W128] = t;
+      } else if (i == 2 * W128) {
+        a.db[k][0] = t;
+      } else {
+        dst[i] = t;                                            // the net's loss sum, for the last net to add
+      }
+    }
+  };
+  if (!last_of(tickets + 8 + k * 64 + grp, (uint32_t)(g1 - g0))) return;
+  sum_partials(partials + ((size_t)k * R + g0) * per_chunk, g1 - g0, gpart, false);
+  if (!last_of(tickets + k, (uint32_t)G)) return;
+  float* const npart = partials + (size_t)2 * R * per_chunk + (size_t)2 * G * per_chunk + (size_t)k * per_chunk;
+  for (int c0 = 0; c0 < G; c0 += kVhGroup) {                   // G <= kVhGroup here (R <= kVhGroup^2); kept general
+    sum_partials(partials + (size_t)2 * R * per_chunk + ((size_t)k * G + c0) * per_chunk, min(kVhGroup, G - c0), npart,
+                 true);
+  }
+  if (!last_of(tickets + 2, 2u)) return;
+  if (threadIdx.x == 0) {
+    const float* n0 = partials + (size_t)2 * R * per_chunk + (size_t)2 * G * per_chunk;
+    const float l = (__ldcg(n0 + 2 * W128 + 1) + __ldcg(n0 + per_chunk + 2 * W128 + 1)) * a.inv_bn * 0.5f;
+    a.loss_out[0] = l;
+    if (!isfinite(l)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
+  }
+}
+
+bool vhead_fused_supported(int H) { return H >= 4 && H <= 1024; }
+
+int launch_vhead_fused(porl_ctx* ctx, const VHeadArgs& a, cudaStream_t st) {
+  PORL_CHECK_ARG(vhead_fused_supported(a.H) && (a.ldh & 3) == 0 && a.ldh >= ((a.H + 3) & ~3) && a.ldw >= a.H && a.B > 0,
+                 "fused value head: bad geometry (H=%d ldh=%d ldw=%d)", a.H, a.ldh, a.ldw);
+  for (int k = 0; k < 2; ++k)
+    PORL_CHECK_ARG(a.ht[k] && a.wt[k] && a.bt[k] && a.h[k] && a.w[k] && a.b[k] && a.dW[k] && a.db[k] && a.db_prev[k] &&
+                       aligned16(a.ht[k]) && aligned16(a.h[k]),
+                   "fused value head: null or misaligned pointer (net %d)", k);
+  const int nj = a.H <= 128 ? 1 : a.H <= 256 ? 2 : a.H <= 512 ? 4 : 8;
+  const int w128 = nj * 128;
+  PORL_CHECK_ARG(a.ldw <= w128, "fused value head: ldw=%d exceeds %d", a.ldw, w128);
+  // row chunks: at least 16 rows per block (2 per warp); about two blocks per SM and net at most (the H = 1024
+  // instantiation holds one block per SM: 182 registers, 76 KB of shared memory)
+  int R = (int)((a.B + 15) / 16);
+  int cap = nj == 8 ? ctx->sm_count : 2 * ctx->sm_count;
+  if (cap > kVhGroup * kVhGroup) cap = kVhGroup * kVhGroup;        // two levels of the reduction tree
+  if (R > cap) R = cap;
+  if (R < 1) R = 1;
+  const size_t per_chunk = (size_t)2 * w128 + 4;
+  while (R > 1 && (2 * (size_t)R + 2 * ((R + kVhGroup - 1) / kVhGroup) + 2) * per_chunk > (size_t)kPartialFloats) R >>= 1;
+  const size_t smem = (size_t)(3 + 16) * w128 * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(vhead_fused_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 19 * 1024 * 4);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(vhead_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 19 * 512 * 4);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(fused value head) failed: %s", cudaGetErrorString(e));
+      return PORL_ERR_CUDA;
+    }
+    configured = true;
+  }
+  // bytes: three activations read, one written
+  ProfScope prof(ctx, PORL_CAT_HEAD, 4.0 * (double)a.B * a.H * (2 * 3 + 2), st);
+  uint32_t* tk = ctx->counters + kTicketBase;
+  const dim3 grid(R, 2);
+  switch (nj) {
+    case 1: launch_pdl(ctx, vhead_fused_kernel<1>, grid, 256, smem, st, a, ctx->partials, tk, ctx->counters); break;
+    case 2: launch_pdl(ctx, vhead_fused_kernel<2>, grid, 256, smem, st, a, ctx->partials, tk, ctx->counters); break;
+    case 4: launch_pdl(ctx, vhead_fused_kernel<4>, grid, 256, smem, st, a, ctx->partials, tk, ctx->counters); break;
+    default: launch_pdl(ctx, vhead_fused_kernel<8>, grid, 256, smem, st, a, ctx->partials, tk, ctx->counters); break;
+  }
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
 }  // namespace porl

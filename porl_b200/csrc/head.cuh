@@ -41,3 +41,28 @@ int launch_head_forward(porl_ctx* ctx, const HeadFwdBatch& hb, cudaStream_t st);
 int launch_head_backward(porl_ctx* ctx, const HeadBwdBatch& hb, cudaStream_t st);
 
 }  // namespace porl
+
+// ---- fused scalar-V head step (head.cu): forward of the target and online heads, TD target + twin expectile loss and
+// the head's backward in ONE pass over the last hidden activations (agent/por.py:80-87, agent/sorl.py:85-92).
+namespace porl {
+struct VHeadArgs {
+  const float* ht[2];   // target nets: last hidden activation of next_obs (B, ldh)
+  const float* wt[2];   // target head weight rows (H) and bias (1)
+  const float* bt[2];
+  float* h[2];          // online nets: in last hidden activation of obs, out dz (ReLU-masked input gradient), in place
+  const float* w[2];
+  const float* b[2];
+  float* dW[2];         // (ldw) head weight gradient, pad columns zero
+  float* db[2];         // (1)
+  float* db_prev[2];    // (H) bias gradient of the layer below (column sums of dz)
+  const float* rewards;
+  const float* dones;
+  float* target_v;      // (B) out
+  float* loss_out;      // scalar out
+  float gamma, tau, inv_bn;
+  int64_t B;
+  int H, ldh, ldw;
+};
+bool vhead_fused_supported(int H);
+int launch_vhead_fused(porl_ctx* ctx, const VHeadArgs& a, cudaStream_t st);
+}  // namespace porl

@@ -288,6 +288,7 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
       if (l >= m->d.n_layers) continue;
       const bool last = (l == m->d.n_layers - 1);
       const bool on_tc = tc_layer(ctx, m, l, B);
+      if (last && narrow_head(m) && (k.pad_ & PORL_MLP_SKIP_HEAD)) continue;   // the fused head step evaluates it
       if (last && narrow_head(m)) {
         for (int net = 0; net < m->d.n_nets; ++net) {
           const float* P = k.params + net * m->net_stride;
@@ -368,10 +369,11 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
 extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, int64_t B, float* dout,
                                  float* grads, porl_stream_t stream) {
   PORL_ON_DEVICE(ctx);
-  PORL_CHECK_ARG(ctx && call && call->mlp && dout && grads && call->params && call->x && call->saved,
+  PORL_CHECK_ARG(ctx && call && call->mlp && grads && call->params && call->x && call->saved &&
+                     (dout || (call->pad_ & PORL_MLP_HEAD_DONE)),
                  "porl_mlp_backward: null argument");
   PORL_CHECK_ARG(B > 0 && B < (1 << 24), "porl_mlp_backward: B=%lld", (long long)B);
-  PORL_CHECK_ARG(aligned16(dout) && aligned16(grads) && aligned16(call->x) && (call->ldx & 3) == 0,
+  PORL_CHECK_ARG((!dout || aligned16(dout)) && aligned16(grads) && aligned16(call->x) && (call->ldx & 3) == 0,
                  "porl_mlp_backward: buffers must be 16-byte aligned, ldx %% 4 == 0");
   PORL_CHECK_ARG(!call->inference, "porl_mlp_backward: the forward of this call ran with inference=1");
   const porl_mlp* m = call->mlp;
@@ -403,7 +405,13 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
   };
   int l_first = L - 1;
   bool bias_done[PORL_MAX_LAYERS] = {false, false, false, false, false, false};
-  if (narrow_head(m)) {
+  if (narrow_head(m) && (call->pad_ & PORL_MLP_HEAD_DONE)) {
+    // porl_value_head_step has run: dW / db of the head and db of the layer below are in `grads`, the last hidden
+    // activation holds dz
+    PORL_CHECK_ARG(L >= 2 && !m->d.layer_norm, "porl_mlp_backward: PORL_MLP_HEAD_DONE needs a hidden layer and no LayerNorm");
+    bias_done[L - 2] = true;
+    l_first = L - 2;
+  } else if (narrow_head(m)) {
     // output layer: weight / bias gradient, ReLU-masked input gradient and (without LayerNorm) the bias
     // gradient of the layer below in one pass over the last hidden activation
     const int l = L - 1;
@@ -509,4 +517,54 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     }
   }
   return PORL_OK;
+}
+
+// Fused head step of the twin value nets (head.cu: vhead_fused_kernel): forward of the target heads on next_obs and of
+// the online heads on obs, TD target, twin expectile loss and the heads' backward in one pass over the last hidden
+// activations.  `target` / `online`: the calls whose porl_mlp_forward ran with PORL_MLP_SKIP_HEAD.
+extern "C" int porl_value_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* target, const porl_mlp_call_t* online, int64_t B,
+                                    const float* rewards, const float* dones, float gamma, float tau, int64_t B_norm,
+                                    float* target_v, float* grads, float* loss_out, porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
+  PORL_CHECK_ARG(ctx && target && online && target->mlp && online->mlp == target->mlp && rewards && dones && target_v &&
+                     grads && loss_out && B > 0 && B_norm > 0,
+                 "porl_value_head_step: null argument");
+  PORL_CHECK_ARG(porl_value_head_step_supported(online->mlp), "porl_value_head_step: needs twin nets with a scalar head, "
+                 "at least one hidden layer of width <= 1024 and no LayerNorm");
+  const porl_mlp* m = online->mlp;
+  const int L = m->d.n_layers, l = L - 1;
+  VHeadArgs a;
+  for (int k = 0; k < 2; ++k) {
+    const float* Pt = target->params + k * m->net_stride;
+    const float* P = online->params + k * m->net_stride;
+    float* G = grads + k * m->net_stride;
+    a.ht[k] = saved_h(m, target->saved, k, l, B);
+    a.wt[k] = Pt + m->w_off[l];
+    a.bt[k] = Pt + m->b_off[l];
+    a.h[k] = saved_h(m, online->saved, k, l, B);
+    a.w[k] = P + m->w_off[l];
+    a.b[k] = P + m->b_off[l];
+    a.dW[k] = G + m->w_off[l];
+    a.db[k] = G + m->b_off[l];
+    a.db_prev[k] = G + m->b_off[l - 1];
+  }
+  a.rewards = rewards;
+  a.dones = dones;
+  a.target_v = target_v;
+  a.loss_out = loss_out;
+  a.gamma = gamma;
+  a.tau = tau;
+  a.inv_bn = 1.f / (float)B_norm;
+  a.B = B;
+  a.H = m->d.dims[l];
+  a.ldh = m->pad[l];
+  a.ldw = m->pad[l];
+  return launch_vhead_fused(ctx, a, as_stream(stream));
+}
+
+extern "C" int porl_value_head_step_supported(const porl_mlp_t* mlp) {
+  if (!mlp) return 0;
+  const int L = mlp->d.n_layers;
+  return (mlp->d.n_nets == 2 && L >= 2 && mlp->d.dims[L] == 1 && !mlp->d.layer_norm && mlp->d.out_act == 0 &&
+          vhead_fused_supported(mlp->d.dims[L - 1])) ? 1 : 0;
 }

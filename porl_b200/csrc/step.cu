@@ -70,16 +70,27 @@ int expectile_step(porl_ctx_t* ctx, const porl_agent_step_t* a, int64_t B, const
   int rc;
   // 1. target TwinV(next) + online TwinV(obs)   (por.py:80-84, sorl.py:85-89)
   porl_mlp_call_t calls[2];
-  calls[0] = porl_mlp_call_t{a->value_mlp, a->target_params, x_next, ld_x, w.saved_t, w.out_t, 1, 0};
-  calls[1] = porl_mlp_call_t{a->value_mlp, a->value.params, x_obs, ld_x, w.saved_v, w.out_v, 0, 0};
+  const bool fused_head = porl_value_head_step_supported(a->value_mlp) != 0;
+  calls[0] = porl_mlp_call_t{a->value_mlp, a->target_params, x_next, ld_x, w.saved_t, w.out_t, 1, fused_head ? PORL_MLP_SKIP_HEAD : 0};
+  calls[1] = porl_mlp_call_t{a->value_mlp, a->value.params, x_obs, ld_x, w.saved_v, w.out_v, 0, fused_head ? PORL_MLP_SKIP_HEAD : 0};
   if ((rc = porl_mlp_forward(ctx, 2, calls, B, st)) != PORL_OK) return rc;
-  // 2. TD target, twin expectile loss, dL/dv   (por.py:85-87)
-  if ((rc = porl_expectile_twin_loss(ctx, w.out_v, w.out_v + net, w.out_t, w.out_t + net, ldv, rewards, dones,
-                                     a->discount, a->tau, B, b_norm, w.target_v, w.dv, w.dv + net, a->value.loss, st)) !=
-      PORL_OK)
-    return rc;
-  // 3. backward of the online value nets into the group's bucket, 4. Adam + Polyak   (por.py:88-93)
-  if ((rc = porl_mlp_backward(ctx, &calls[1], B, w.dv, a->value.grads, st)) != PORL_OK) return rc;
+  if (fused_head) {
+    // 2+3a. heads, TD target, twin expectile loss and the heads' backward in one kernel   (por.py:85-87)
+    if ((rc = porl_value_head_step(ctx, &calls[0], &calls[1], B, rewards, dones, a->discount, a->tau, b_norm, w.target_v,
+                                   a->value.grads, a->value.loss, st)) != PORL_OK)
+      return rc;
+    calls[1].pad_ = PORL_MLP_HEAD_DONE;
+    if ((rc = porl_mlp_backward(ctx, &calls[1], B, nullptr, a->value.grads, st)) != PORL_OK) return rc;
+  } else {
+    // 2. TD target, twin expectile loss, dL/dv   (por.py:85-87)
+    if ((rc = porl_expectile_twin_loss(ctx, w.out_v, w.out_v + net, w.out_t, w.out_t + net, ldv, rewards, dones,
+                                       a->discount, a->tau, B, b_norm, w.target_v, w.dv, w.dv + net, a->value.loss,
+                                       st)) != PORL_OK)
+      return rc;
+    // 3. backward of the online value nets into the group's bucket   (por.py:88-90)
+    if ((rc = porl_mlp_backward(ctx, &calls[1], B, w.dv, a->value.grads, st)) != PORL_OK) return rc;
+  }
+  // 4. Adam + Polyak   (por.py:90-93)
   if ((rc = group_step(ctx, a->value, a->target_params, a->ema_beta, st)) != PORL_OK) return rc;
   if (value_only) return PORL_OK;
   // 5. online TwinV(obs) with the NEW weights + policy(obs)   (por.py:97-98,102)
