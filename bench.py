@@ -940,6 +940,9 @@ def run_b200(a):
 
 
 def main():
+    # the contract is ONE JSON line on stdout: NCCL's version banner (NCCL_DEBUG=VERSION) would precede it
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     a = parse()
     if a.impl == "reference":
         run_reference(a)
