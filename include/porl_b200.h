@@ -71,6 +71,11 @@ int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode);
 int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx);
 /* k-blocks (32 k each) accumulated inside the tensor core before the fp32 register add; default 1 */
 int porl_ctx_set_tc_chunk(porl_ctx_t* ctx, int k_blocks);
+/* 1 (default; env PORL_TC_PHASES): the tensor-core contractions of one MLP pass -- the hidden layers of a forward, or
+ * {dW_l, dx_l, dW_l-1, ...} of a backward -- run as phases of ONE persistent launch with grid-wide barriers where a phase
+ * reads what the previous one wrote, instead of one launch per contraction.  0: one launch each.  Results are bitwise
+ * identical either way (same tiles, same split-K cuts, same summation order). */
+int porl_ctx_set_tc_phases(porl_ctx_t* ctx, int enable);
 /* Measurement aid (bench.py's measured TF32 ceiling): 3 (default) = the 3xTF32 product mode; 1 = the same kernel
  * issuing only the hi*hi MMAs with the operand split skipped, i.e. a plain single-pass TF32 contraction whose
  * rate bounds what the 3-pass mode can reach (1/3 of it).  Results in mode 1 are TF32-accurate only (~1e-3). */

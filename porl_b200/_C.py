@@ -185,6 +185,7 @@ _SIGNATURES = {
     "porl_fasternet_forward": (C.c_int, [_p, C.POINTER(FasterNetParams), _p, _i64, _i64, _p, _i64, _p, _i64, _p]),
     "porl_ctx_set_tc_chunk": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_tc_terms": (C.c_int, [_p, C.c_int]),
+    "porl_ctx_set_tc_phases": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_tc_debug": (C.c_int, [_p, _p]),
     "porl_ctx_set_tc_variant": (C.c_int, [_p, C.c_int]),
     "porl_ctx_set_pdl": (C.c_int, [_p, C.c_int]),
@@ -265,6 +266,10 @@ class Context:
 
     def set_tc_chunk(self, k_blocks: int) -> None:
         check(lib.porl_ctx_set_tc_chunk(self.handle, k_blocks))
+        self.epoch += 1
+
+    def set_tc_phases(self, enable: bool) -> None:
+        check(lib.porl_ctx_set_tc_phases(self.handle, int(bool(enable))))
         self.epoch += 1
 
     def set_tc_terms(self, terms: int) -> None:

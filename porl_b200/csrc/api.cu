@@ -16,7 +16,7 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
+static int check_batch(bool a_kmajor, bool b_kmajor, const GemmBatch& batch) {
   PORL_CHECK_ARG(batch.n_groups >= 1 && batch.n_groups <= kMaxGroups, "contraction: %d groups", batch.n_groups);
   for (int i = 0; i < batch.n_groups; ++i) {
     const GemmGroup& g = batch.g[i];
@@ -35,18 +35,42 @@ int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, c
     PORL_CHECK_ARG((!g.A_lo || aligned16(g.A_lo)) && (!g.B_lo || aligned16(g.B_lo)) && (!g.C_lo || aligned16(g.C_lo)),
                    "contraction group %d: lo planes must be 16-byte aligned", i);
   }
+  return PORL_OK;
+}
+
+static double batch_flops(const GemmBatch& batch) {
   double flops = 0.0;
   for (int i = 0; i < batch.n_groups; ++i)
     flops += 2.0 * (double)batch.g[i].M * (double)batch.g[i].N * (double)batch.g[i].K;
-  ProfScope prof(ctx, PORL_CAT_CONTRACTION, flops, stream);
+  return flops;
+}
+
+int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
+  int rc = check_batch(a_kmajor, b_kmajor, batch);
+  if (rc != PORL_OK) return rc;
+  ProfScope prof(ctx, PORL_CAT_CONTRACTION, batch_flops(batch), stream);
   if (ctx->gemm_mode == 1) {
-    int rc = launch_gemm_tc(ctx, a_kmajor, b_kmajor, batch, stream);
+    rc = launch_gemm_tc(ctx, a_kmajor, b_kmajor, batch, stream);
     if (rc != PORL_ERR_UNSUPPORTED) return rc;
   }
   for (int i = 0; i < batch.n_groups; ++i)
     PORL_CHECK_ARG(!batch.g[i].Ct, "contraction group %d: a transposed output needs the tcgen05 path "
-                   "(gemm mode 1, K-major operands, M, N, K >= 32)", i);
+                   "(gemm mode 1, M, N, K >= 32)", i);
   return launch_gemm_simt(ctx, a_kmajor, b_kmajor, batch, stream);
+}
+
+int launch_gemm_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaStream_t stream) {
+  if (ctx->gemm_mode != 1 || ctx->tc_phases == 0) return PORL_ERR_UNSUPPORTED;
+  double flops = 0.0;
+  for (int p = 0; p < n_phases; ++p) {
+    int rc = check_batch(specs[p].a_kmajor, specs[p].b_kmajor, *specs[p].batch);
+    if (rc != PORL_OK) return rc;
+    for (int i = 0; i < specs[p].batch->n_groups; ++i)
+      if (!gemm_tc_eligible(specs[p].batch->g[i], specs[p].a_kmajor, specs[p].b_kmajor)) return PORL_ERR_UNSUPPORTED;
+    flops += batch_flops(*specs[p].batch);
+  }
+  ProfScope prof(ctx, PORL_CAT_CONTRACTION, flops, stream);
+  return launch_gemm_tc_phases(ctx, n_phases, specs, stream);
 }
 
 }  // namespace porl
@@ -93,6 +117,10 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->counters = nullptr;
   ctx->tc_chunk_kb = 1;
   ctx->tc_terms = 3;
+  {
+    const char* e = getenv("PORL_TC_PHASES");
+    ctx->tc_phases = e ? atoi(e) : 1;
+  }
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");
     ctx->tc_a_in_tmem = e ? atoi(e) : 0;
@@ -171,6 +199,12 @@ extern "C" int porl_ctx_set_gemm_mode(porl_ctx_t* ctx, int mode) {
 }
 
 extern "C" int porl_ctx_get_gemm_mode(const porl_ctx_t* ctx) { return ctx ? ctx->gemm_mode : -1; }
+
+extern "C" int porl_ctx_set_tc_phases(porl_ctx_t* ctx, int enable) {
+  PORL_CHECK_ARG(ctx, "porl_ctx_set_tc_phases: null context");
+  ctx->tc_phases = enable ? 1 : 0;
+  return PORL_OK;
+}
 
 extern "C" int porl_ctx_set_tc_terms(porl_ctx_t* ctx, int terms) {
   PORL_CHECK_ARG(ctx && (terms == 1 || terms == 3), "porl_ctx_set_tc_terms: terms=%d (1 or 3)", terms);

@@ -67,7 +67,19 @@ struct ColsumBatch { ColsumSeg seg[kMaxGroups]; int n_seg; int max_n; };
 int launch_transpose(porl_ctx* ctx, const TransposeBatch& tb, cudaStream_t st);
 int launch_colsum(porl_ctx* ctx, ColsumBatch& cb, cudaStream_t st);
 
-// tcgen05 3xTF32 path (K-major operands only); returns PORL_ERR_UNSUPPORTED when the shapes do not fit it.
+// Several grouped contractions in ONE persistent tcgen05 launch (gemm_tc.cu): phase p may read what phase p-1 wrote when
+// barrier_before is set (grid-wide barrier); phases without it share the CTAs freely.
+struct TcPhaseSpec {
+  GemmBatch* batch;
+  bool a_kmajor, b_kmajor;
+  bool barrier_before;
+};
+int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaStream_t stream);
+// the same with the argument checks and the profiling scope of launch_gemm (api.cu); PORL_ERR_UNSUPPORTED when some
+// problem needs the FFMA kernel or the context is in FFMA mode -- the caller then launches phase by phase
+int launch_gemm_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaStream_t stream);
+
+// tcgen05 3xTF32 path; returns PORL_ERR_UNSUPPORTED when the shapes do not fit it.
 bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor);
 int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream);
 

@@ -55,28 +55,42 @@ struct TcCfg {
   // those warps are busy with a tile's epilogue (short-K tiles: a whole next tile fits into four buffers)
   static constexpr int NBUF = ATM ? 2 : 4;
   static constexpr int ACC_COLS = NBUF * TC_BN;
-  static constexpr int NUM_BARS = 3 * STAGES + 2 * NBUF;
+  static constexpr int NUM_BARS = 3 * STAGES + 2 * NBUF + 1;   // + phase_go (grid barrier passed: producer may load)
   static constexpr int STAGING_BYTES = 2 * TC_TILE_BYTES;   // epilogue: two 128 x 32 fp32 slabs for the TMA stores of C
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + STAGING_BYTES + 256 /*barriers*/ + 512 /*bias*/;
   static constexpr int TMEM_COLS = 512;
 };
 constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 8;
 
-struct alignas(64) TcParams {
+// One launch runs up to kMaxPhases grouped contractions ("phases") back to back in the same persistent grid: the layers
+// of an MLP forward, or {weight gradient, input gradient, weight gradient of the layer below} of a backward.  A phase
+// whose inputs were produced by an earlier phase of the launch starts behind a grid-wide barrier (barrier_before);
+// phases that are independent of each other share the pool of CTAs without one.  This replaces a kernel boundary
+// (launch, TMEM allocation, barrier set-up, tensor-map fetch, pipeline fill and drain: ~9 us each at these sizes) by a
+// ~2 us barrier.
+constexpr int kMaxPhases = 3;
+struct alignas(64) TcPhase {
   CUtensorMap mapA[kMaxGroups];
   CUtensorMap mapB[kMaxGroups];
   CUtensorMap mapC[kMaxGroups];     // row-major C (n_store x M), box {32, 128}: the epilogue's TMA stores
-  CUtensorMap mapB2[kMaxGroups];    // pair mode: B with box {32, 64} (each CTA of a pair loads half of the B tile)
-  GemmBatch batch;
+  GemmBatch batch;                  // problems, split factor, ticket words of this phase
   int tile_begin[kMaxGroups + 1];   // prefix sum of tiles per group
   int tiles_n[kMaxGroups];          // n-tiles per group
   int total_tiles;
-  int chunk_kb;                     // k-blocks per TMEM accumulation chunk
-  int terms;                        // 3: 3xTF32; 1: hi*hi MMAs only, no operand split (ceiling probe)
   int dist_fix;                     // split-K: one unit per CTA, the slices of a tile share its final sum (see the epilogue)
   int a_mn, b_mn;                   // operand is MN-major in memory (A[k*lda + m] / B[k*ldb + n]): no transposed copy needed
+  int barrier_before;               // wait for every CTA to have finished the previous phases before loading operands
+  float* ws;                        // split-K partial tiles of this phase: [slice][tile][col/4][row] float4
+};
+struct alignas(64) TcParams {
+  TcPhase ph[kMaxPhases];
+  CUtensorMap mapB2[kMaxGroups];    // pair mode (one phase): B with box {32, 64} (each CTA of a pair loads half of the B tile)
+  int n_phases;
+  int chunk_kb;                     // k-blocks per TMEM accumulation chunk
+  int terms;                        // 3: 3xTF32; 1: hi*hi MMAs only, no operand split (ceiling probe)
   int tile_m;                       // rows per work unit: 128, or 256 in pair mode (two CTAs x 128)
-  float* ws;                        // split-K partial tiles: [slice][tile][col/4][row] float4
+  uint32_t* gbar;                   // grid barrier words: [2 * kMaxPhases] (arrived, departed per barrier), self-resetting
+  uint32_t* status;                 // device status word (PORL_FLAG_*)
   unsigned long long* dbg;          // optional per-CTA timestamps (tools/gemm_probe.py), or null
 };
 
@@ -237,21 +251,21 @@ struct TcUnit {
   int g, tile, m0, n0, kb0, kb1, split;
 };
 
-__device__ __forceinline__ bool tc_decode(const TcParams& P, int u, TcUnit& w) {
-  if (u >= P.total_tiles * P.batch.splits) return false;
-  w.split = u / P.total_tiles;
-  int t = u - w.split * P.total_tiles;
+__device__ __forceinline__ bool tc_decode(const TcPhase& F, int tile_m, int u, TcUnit& w) {
+  if (u >= F.total_tiles * F.batch.splits) return false;
+  w.split = u / F.total_tiles;
+  int t = u - w.split * F.total_tiles;
   int g = 0;
-  while (g + 1 < P.batch.n_groups && t >= P.tile_begin[g + 1]) ++g;
-  t -= P.tile_begin[g];
+  while (g + 1 < F.batch.n_groups && t >= F.tile_begin[g + 1]) ++g;
+  t -= F.tile_begin[g];
   w.g = g;
   w.tile = t;
-  const int nt = P.tiles_n[g];
-  w.m0 = (t / nt) * P.tile_m;
+  const int nt = F.tiles_n[g];
+  w.m0 = (t / nt) * tile_m;
   w.n0 = (t % nt) * TC_BN;
-  const int nkb = (P.batch.g[g].K + TC_BK - 1) / TC_BK;
-  w.kb0 = (int)((long long)w.split * nkb / P.batch.splits);
-  w.kb1 = (int)((long long)(w.split + 1) * nkb / P.batch.splits);
+  const int nkb = (F.batch.g[g].K + TC_BK - 1) / TC_BK;
+  w.kb0 = (int)((long long)w.split * nkb / F.batch.splits);
+  w.kb1 = (int)((long long)(w.split + 1) * nkb / F.batch.splits);
   return true;
 }
 
@@ -282,6 +296,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   auto empty_bar = [&](int s) { return bar0 + 8u * (2 * TC_STAGES + s); };
   auto tmem_full = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + b); };
   auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + TC_NBUF + b); };
+  const uint32_t phase_go = bar0 + 8u * (3 * TC_STAGES + 2 * TC_NBUF);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // CTA of the pair; rank 0 leads
@@ -299,11 +314,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   if (dbg && threadIdx.x == 0) dbg[0] = gtime();
 
   if (warp == 0 && lane == 0) {
-    for (int g = 0; g < P.batch.n_groups; ++g) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapA[g])) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapB[g])) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.mapC[g])) : "memory");
+    for (int p = 0; p < P.n_phases; ++p) {
+      for (int g = 0; g < P.ph[p].batch.n_groups; ++g) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.ph[p].mapA[g])) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.ph[p].mapB[g])) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&P.ph[p].mapC[g])) : "memory");
+      }
     }
+    mbar_init(phase_go, 1);
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(raw_full(s), 1);
       mbar_init(split_done(s), PAIR ? 2 * TC_SPLIT_THREADS : TC_SPLIT_THREADS);
@@ -345,7 +363,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       int it = 0;
       long long w_prod = 0;
       TcUnit w;
-      for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
+      uint32_t n_bar = 0;
+      for (int p = 0; p < P.n_phases; ++p) {
+      const TcPhase& F = P.ph[p];
+      if (F.barrier_before) {
+        // the accumulator warps of this CTA pass the grid barrier (every CTA's stores of the earlier phases are
+        // complete and visible) and release this thread; the operands are then read through the async proxy
+        mbar_wait(phase_go, n_bar & 1u);
+        ++n_bar;
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      for (int u = unit0; tc_decode(F, P.tile_m, u, w); u += unit_stride) {
         for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
           const int s = it % TC_STAGES;
           const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
@@ -354,23 +382,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           if (dbg) w_prod += clock64() - tw;
           mbar_expect_tx(raw_full(s), TC_TILE_BYTES + B_BYTES);
           const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-          if (P.a_mn) {         // MN-major: four {32 m, 32 k} boxes, 4096 bytes apart
+          if (F.a_mn) {         // MN-major: four {32 m, 32 k} boxes, 4096 bytes apart
 #pragma unroll
-            for (int i = 0; i < 4; ++i) tma_load_2d(st + 4096u * i, &P.mapA[w.g], raw_full(s), w.m0 + 32 * i, kb * TC_BK);
+            for (int i = 0; i < 4; ++i) tma_load_2d(st + 4096u * i, &F.mapA[w.g], raw_full(s), w.m0 + 32 * i, kb * TC_BK);
           } else {
-            tma_load_2d(st, &P.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
+            tma_load_2d(st, &F.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
           }
-          if (P.b_mn) {
+          if (F.b_mn) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              tma_load_2d(st + TC_TILE_BYTES + 4096u * i, &P.mapB[w.g], raw_full(s), w.n0 + 32 * i, kb * TC_BK);
+              tma_load_2d(st + TC_TILE_BYTES + 4096u * i, &F.mapB[w.g], raw_full(s), w.n0 + 32 * i, kb * TC_BK);
           } else if (PAIR) {
             tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
           } else {
-            tma_load_2d(st + TC_TILE_BYTES, &P.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+            tma_load_2d(st + TC_TILE_BYTES, &F.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
           }
           if (dbg && it == 0) dbg[2] = gtime();
         }
+      }
       }
       if (dbg) { dbg[3] = gtime(); dbg[11] = (unsigned long long)w_prod; }
     }
@@ -378,22 +407,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     // ===================== MMA issuer (pair mode: the leader CTA only) =====================
     if (lane == 0 && rank == 0) {
       // instruction descriptor: D fp32, A/B tf32, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
-      // bit 15 / 16: A / B is MN-major ("transposed") in shared memory
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
-                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24) | (P.a_mn ? (1u << 15) : 0u) |
-                             (P.b_mn ? (1u << 16) : 0u);
-      // 16-byte units the start address advances per 8-wide k-step: 32 bytes along a K-major row, one 1024-byte
-      // k-group of an MN-major tile
-      const uint64_t a_step = P.a_mn ? 64u : 2u, b_step = P.b_mn ? 64u : 2u;
-      // descriptor templates without the start address (this thread alone paces the tensor pipe: nothing that can be
-      // decided per launch is recomputed per k-block); stage addresses are 1024-byte aligned, so adding (bytes >> 4)
-      // to a descriptor moves its 14-bit start-address field only
-      const uint64_t tmpl_a = (P.a_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)(base >> 4);
-      const uint64_t tmpl_b = (P.b_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)((base + TC_TILE_BYTES) >> 4);
       int it = 0, chunk = 0;
       long long w_te = 0, w_sd = 0;
       TcUnit w;
-      for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
+      for (int p = 0; p < P.n_phases; ++p) {
+      const TcPhase& F = P.ph[p];
+      // bit 15 / 16: A / B is MN-major ("transposed") in shared memory
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
+                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24) | (F.a_mn ? (1u << 15) : 0u) |
+                             (F.b_mn ? (1u << 16) : 0u);
+      // 16-byte units the start address advances per 8-wide k-step: 32 bytes along a K-major row, one 1024-byte
+      // k-group of an MN-major tile
+      const uint64_t a_step = F.a_mn ? 64u : 2u, b_step = F.b_mn ? 64u : 2u;
+      // descriptor templates without the start address (this thread alone paces the tensor pipe: nothing that can be
+      // decided per phase is recomputed per k-block); stage addresses are 1024-byte aligned, so adding (bytes >> 4)
+      // to a descriptor moves its 14-bit start-address field only
+      const uint64_t tmpl_a = (F.a_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)(base >> 4);
+      const uint64_t tmpl_b = (F.b_mn ? smem_desc_mn(0u) : smem_desc(0u)) + (uint64_t)((base + TC_TILE_BYTES) >> 4);
+      for (int u = unit0; tc_decode(F, P.tile_m, u, w); u += unit_stride) {
         int kb = w.kb0;
         while (kb < w.kb1) {
           const int buf = chunk % TC_NBUF;
@@ -462,6 +493,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           kb += nk;
         }
       }
+      }
       if (dbg) { dbg[6] = gtime(); dbg[13] = (unsigned long long)w_sd; dbg[14] = (unsigned long long)w_te; }
     }
   } else if (warp < TC_EPI_WARP0) {
@@ -470,7 +502,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     int it = 0;
     long long w_rf = 0;
     TcUnit w;
-    for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
+    for (int p = 0; p < P.n_phases; ++p)
+    for (int u = unit0; tc_decode(P.ph[p], P.tile_m, u, w); u += unit_stride) {
       for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
         const int s = it % TC_STAGES;
         const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
@@ -542,11 +575,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     int chunk = 0, sbuf = 0;
     long long w_tf = 0;
     TcUnit w;
-    for (int u = unit0; tc_decode(P, u, w); u += unit_stride) {
+    for (int p = 0; p < P.n_phases; ++p) {
+    const TcPhase& F = P.ph[p];
+    if (F.barrier_before) {
+      // ---- grid barrier: every CTA's results of the earlier phases complete and visible before this phase loads them.
+      // This CTA's TMA stores have finished WRITING (wait_group 0, not .read), a device-scope fence orders them before
+      // the arrival; one thread arrives, waits for all CTAs of the (co-resident, persistent) grid, and releases the TMA
+      // producer of this CTA through phase_go.  The two words of barrier p reset themselves: the last CTA to leave
+      // zeroes them for the next launch.  A wait that exceeds 2 s raises PORL_FLAG_PEER_TIMEOUT and goes on (wrong
+      // results, flagged) rather than hang the device.
+      if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == TC_EPI_WARP0 * 32) {
+        int* const arrived = reinterpret_cast<int*>(P.gbar) + 2 * p;
+        int* const departed = arrived + 1;
+        const int n_cta = (int)gridDim.x;
+        __threadfence();
+        atomicAdd(arrived, 1);
+        const unsigned long long t0 = gtime();
+        while (ld_acquire(arrived) < n_cta) {
+          __nanosleep(64);
+          if (gtime() - t0 > 2000000000ull) {
+            atomicOr(P.status, (uint32_t)PORL_FLAG_PEER_TIMEOUT);
+            break;
+          }
+        }
+        if (atomicAdd(departed, 1) == n_cta - 1) {
+          *arrived = 0;
+          *departed = 0;
+        }
+        __threadfence();
+        mbar_arrive(phase_go);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    for (int u = unit0; tc_decode(F, P.tile_m, u, w); u += unit_stride) {
       w.m0 += (int)rank * TC_BM;                            // pair mode: this CTA's 128 rows of the 256-row tile
       // this tile's problem, by value: loads through a reference into the parameter block would be
       // re-issued after every global store of the epilogue
-      const GemmGroup& Gp = P.batch.g[w.g];
+      const GemmGroup& Gp = F.batch.g[w.g];
       float* const gCt = Gp.Ct;
       const float* const gBias = Gp.bias;
       const uint32_t* const gBitsIn = Gp.bits_in;
@@ -635,26 +703,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // ---- split-K: every slice parks its partial tile in the workspace; the LAST slice to arrive (ticket)
       // sums all partials in slice order -- a fixed order, so the result is bitwise reproducible whichever
       // CTA happens to be last -- and runs the epilogue.  No slice ever waits for another one.
-      const bool split = P.batch.splits > 1;
-      const int S = P.batch.splits;
+      const bool split = F.batch.splits > 1;
+      const int S = F.batch.splits;
       // pair mode: each CTA's 128 x 128 half of the tile is its own split-K unit (workspace slot, ticket)
-      const int gt = (P.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
-      const int n_sub = P.total_tiles * (PAIR ? 2 : 1);
+      const int gt = (F.tile_begin[w.g] + w.tile) * (PAIR ? 2 : 1) + (int)rank;
+      const int n_sub = F.total_tiles * (PAIR ? 2 : 1);
+      float* const ws_p = F.ws;
+      int* const sem_p = F.batch.sem;
+      const CUtensorMap* const map_c = &F.mapC[w.g];
       // Who sums: with one unit per CTA (every split launch: units <= resident CTAs, so all slices of a tile run at the
       // same time) the FIX-UP IS DISTRIBUTED: slice s sums and finishes the slabs sl with sl % S == s (at most four
       // slices take part), after waiting for all S slices of the tile to have parked -- S x 16 KB per SM instead of
       // S x 64 KB through the one SM of the last arriver (measured: the L2 -> SM port made that 7-16 us per tile).
       // Otherwise (a CTA holds several units, a later slice may not be running yet) the last slice to arrive sums.
-      const bool dist = split && P.dist_fix != 0;
+      const bool dist = split && F.dist_fix != 0;
       int fix_mod = 1, fix_me = 0;                               // this CTA finishes the slabs sl with sl % fix_mod == fix_me
       if (split) {
-        float4* wp = reinterpret_cast<float4*>(P.ws) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
+        float4* wp = reinterpret_cast<float4*>(ws_p) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
 #pragma unroll
         for (int c4 = 0; c4 < TC_BN; c4 += 4)
           wp[(c4 >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        int* const ticket = P.batch.sem + gt;
+        int* const ticket = sem_p + gt;
         if (dist) {
           if (warp == TC_EPI_WARP0 && lane == 0) {
             atomicAdd(ticket, 1);
@@ -708,7 +779,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             if (sl % fix_mod != fix_me) continue;                  // another slice finishes this slab
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = 0.f;
-            const float4* rp = reinterpret_cast<const float4*>(P.ws) + (size_t)gt * (32 * 128) + r_in_tile + (8 * sl) * 128;
+            const float4* rp = reinterpret_cast<const float4*>(ws_p) + (size_t)gt * (32 * 128) + r_in_tile + (8 * sl) * 128;
             const size_t sstride = (size_t)n_sub * (32 * 128);
             for (int s0 = 0; s0 < S; s0 += 4) {
               float4 o[4][8];
@@ -770,7 +841,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> copy-engine reads
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(&P.mapC[w.g], smem_u32(buf), w.n0 + 32 * sl, w.m0);
+          if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(map_c, smem_u32(buf), w.n0 + 32 * sl, w.m0);
           sbuf ^= 1;
         }
       };
@@ -779,10 +850,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       if (dist && warp == TC_EPI_WARP0 && lane == 0) {
         // second round on the ticket: the last fixer to finish resets it for the next launch
         const int nfix = S < 4 ? S : 4;
-        if (atomicAdd(P.batch.sem + gt, 1) == S + nfix - 1) P.batch.sem[gt] = 0;
+        if (atomicAdd(sem_p + gt, 1) == S + nfix - 1) sem_p[gt] = 0;
       }
       if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // bias slots free for the next tile
       if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
+    }
     }
     if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
@@ -914,46 +986,28 @@ static int max_pairs(int smem_bytes) {
   return cached;
 }
 
-int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
+// One persistent launch over up to kMaxPhases grouped contractions (see TcPhase).  Every phase decides its own split-K
+// factor; phases get disjoint slices of the split-K workspace and of the ticket words.  PORL_ERR_UNSUPPORTED when a
+// problem does not fit the kernel (the caller falls back to one launch per phase / the FFMA kernel).
+int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaStream_t stream) {
+  if (n_phases < 1 || n_phases > kMaxPhases) return PORL_ERR_UNSUPPORTED;
   // Split-K whenever the tiles alone would leave most SMs idle: weight gradients (K = batch) and, at small batches,
-  // the forward / input-gradient contractions too -- the last slice to arrive sums the partials in slice order and
-  // runs the whole epilogue (bias, ReLU, ReLU mask, transposed copy), so a batch-256 layer is 100+ short units instead
-  // of 32 tiles with a 16-k-block serial loop each.  The split factor is decided from the 128-row tile count and the
-  // SM count alone, so all kernel variants cut K at the same places (bitwise identical results).
-  const bool can_split = true;
-  int min_nkb = 1 << 30;
-  TcParams P;
-  int tiles = 0, tiles128 = 0;
-  // pair mode (variant 2): every problem at least one full 256-row tile high, otherwise the second CTA idles
-  const bool a_mn = !a_kmajor, b_mn = !b_kmajor;
-  // the A-in-TMEM variant un-swizzles K-major rows and the pair variant halves a K-major B tile: MN-major operands take
-  // the all-in-shared-memory variant
-  bool pair = ctx->tc_a_in_tmem == 2 && !a_mn && !b_mn;
-  for (int i = 0; i < batch.n_groups && pair; ++i)
-    if (batch.g[i].M < 2 * TC_BM) pair = false;
+  // the forward / input-gradient contractions too -- the slices of a tile share its final sum and run the whole
+  // epilogue (bias, ReLU, ReLU mask, transposed copy), so a batch-256 layer is 100+ short units instead of 32 tiles
+  // with a 16-k-block serial loop each.  The split factor is decided from the 128-row tile count and the SM count
+  // alone, so all kernel variants cut K at the same places (bitwise identical results).
+  static TcParams P;                 // 13 KB: filled per launch (the host side of the library is single-threaded per context)
+  bool any_mn = false;
+  for (int p = 0; p < n_phases; ++p) any_mn = any_mn || !specs[p].a_kmajor || !specs[p].b_kmajor;
+  // the A-in-TMEM variant un-swizzles K-major rows and the pair variant halves a K-major B tile: MN-major operands and
+  // multi-phase launches take the all-in-shared-memory variant.  Pair mode (variant 2): every problem at least one
+  // full 256-row tile high, otherwise the second CTA idles.
+  bool pair = ctx->tc_a_in_tmem == 2 && !any_mn && n_phases == 1;
+  for (int i = 0; i < specs[0].batch->n_groups && pair; ++i)
+    if (specs[0].batch->g[i].M < 2 * TC_BM) pair = false;
+  const bool atm = ctx->tc_a_in_tmem == 1 && !any_mn && n_phases == 1;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
-  for (int i = 0; i < batch.n_groups; ++i) {
-    const GemmGroup& g = batch.g[i];
-    if (!gemm_tc_eligible(g, a_kmajor, b_kmajor)) return PORL_ERR_UNSUPPORTED;
-    const int nkb = (g.K + TC_BK - 1) / TC_BK;
-    min_nkb = nkb < min_nkb ? nkb : min_nkb;
-    tiles128 += ((g.M + TC_BM - 1) / TC_BM) * ((g.n_store + TC_BN - 1) / TC_BN);
-    P.tile_begin[i] = tiles;
-    P.tiles_n[i] = (g.n_store + TC_BN - 1) / TC_BN;
-    tiles += ((g.M + P.tile_m - 1) / P.tile_m) * P.tiles_n[i];
-  }
-  for (int i = batch.n_groups; i <= kMaxGroups; ++i) P.tile_begin[i] = tiles;
-  for (int i = batch.n_groups; i < kMaxGroups; ++i) P.tiles_n[i] = 1;
-  P.total_tiles = tiles;
-  for (int i = 0; i < batch.n_groups; ++i) {
-    const GemmGroup& g = batch.g[i];
-    // K-major: (rows x K), box {32 k, 128 rows}; MN-major: (K x rows), box {32 rows, 32 k}
-    int rc = a_mn ? make_map(&P.mapA[i], g.A, g.M, g.K, g.lda, TC_BK, true) : make_map(&P.mapA[i], g.A, g.K, g.M, g.lda);
-    if (rc == PORL_OK) rc = b_mn ? make_map(&P.mapB[i], g.B, g.N, g.K, g.ldb, TC_BK, true) : make_map(&P.mapB[i], g.B, g.K, g.N, g.ldb);
-    if (rc == PORL_OK) rc = make_map(&P.mapC[i], g.C, g.n_store, g.M, g.ldc);
-    if (rc == PORL_OK && pair) rc = make_map(&P.mapB2[i], g.B, g.K, g.N, g.ldb, TC_BN / 2);
-    if (rc != PORL_OK) return rc;
-  }
+  P.n_phases = n_phases;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -981,31 +1035,70 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   // work slots: one per SM, or one per resident CTA pair; sub-tiles (128 x 128, one per CTA) for the split-K buffers
   const int sms = pair ? n_pairs : ctx->sm_count;
   const int sub = pair ? 2 : 1;
-  int splits = 1;
-  if (can_split && 2 * tiles128 <= ctx->sm_count) {
-    int want = ctx->sm_count / tiles128;
-    int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
-    splits = want < cap ? want : cap;
-    const long long ws_tiles = (long long)(kTcWsFloats / (TC_BM * TC_BN));
-    if ((long long)splits * tiles * sub > ws_tiles) splits = (int)(ws_tiles / ((long long)tiles * sub));
-    if (splits > 32) splits = 32;
-    if (splits < 1) splits = 1;
+  long long ws_used = 0, sem_used = 0, max_units = 0;
+  const long long ws_tiles = (long long)(kTcWsFloats / (TC_BM * TC_BN));
+  for (int p = 0; p < n_phases; ++p) {
+    TcPhase& F = P.ph[p];
+    GemmBatch& batch = *specs[p].batch;
+    const bool a_mn = !specs[p].a_kmajor, b_mn = !specs[p].b_kmajor;
+    int min_nkb = 1 << 30, tiles = 0, tiles128 = 0;
+    for (int i = 0; i < batch.n_groups; ++i) {
+      const GemmGroup& g = batch.g[i];
+      if (!gemm_tc_eligible(g, specs[p].a_kmajor, specs[p].b_kmajor)) return PORL_ERR_UNSUPPORTED;
+      const int nkb = (g.K + TC_BK - 1) / TC_BK;
+      min_nkb = nkb < min_nkb ? nkb : min_nkb;
+      tiles128 += ((g.M + TC_BM - 1) / TC_BM) * ((g.n_store + TC_BN - 1) / TC_BN);
+      F.tile_begin[i] = tiles;
+      F.tiles_n[i] = (g.n_store + TC_BN - 1) / TC_BN;
+      tiles += ((g.M + P.tile_m - 1) / P.tile_m) * F.tiles_n[i];
+    }
+    for (int i = batch.n_groups; i <= kMaxGroups; ++i) F.tile_begin[i] = tiles;
+    for (int i = batch.n_groups; i < kMaxGroups; ++i) F.tiles_n[i] = 1;
+    F.total_tiles = tiles;
+    for (int i = 0; i < batch.n_groups; ++i) {
+      const GemmGroup& g = batch.g[i];
+      // K-major: (rows x K), box {32 k, 128 rows}; MN-major: (K x rows), box {32 rows, 32 k}
+      int rc = a_mn ? make_map(&F.mapA[i], g.A, g.M, g.K, g.lda, TC_BK, true) : make_map(&F.mapA[i], g.A, g.K, g.M, g.lda);
+      if (rc == PORL_OK) rc = b_mn ? make_map(&F.mapB[i], g.B, g.N, g.K, g.ldb, TC_BK, true) : make_map(&F.mapB[i], g.B, g.K, g.N, g.ldb);
+      if (rc == PORL_OK) rc = make_map(&F.mapC[i], g.C, g.n_store, g.M, g.ldc);
+      if (rc == PORL_OK && pair) rc = make_map(&P.mapB2[i], g.B, g.K, g.N, g.ldb, TC_BN / 2);
+      if (rc != PORL_OK) return rc;
+    }
+    int splits = 1;
+    if (2 * tiles128 <= ctx->sm_count) {
+      int want = ctx->sm_count / tiles128;
+      int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
+      splits = want < cap ? want : cap;
+      const long long room = ws_tiles - ws_used;
+      if ((long long)splits * tiles * sub > room) splits = (int)(room / ((long long)tiles * sub));
+      if (splits > 32) splits = 32;
+      if (splits < 1) splits = 1;
+    }
+    if (sem_used + (long long)tiles * sub > kSemInts) splits = 1;
+    batch.splits = splits;
+    batch.sem = ctx->sem + sem_used;
+    batch.sem_stride = 0;
+    F.ws = ctx->tc_ws + ws_used * (TC_BM * TC_BN);
+    if (splits > 1) {
+      ws_used += (long long)splits * tiles * sub;
+      sem_used += (long long)tiles * sub;
+    }
+    F.batch = batch;
+    F.a_mn = a_mn ? 1 : 0;
+    F.b_mn = b_mn ? 1 : 0;
+    F.barrier_before = (p > 0 && specs[p].barrier_before) ? 1 : 0;
+    const long long units = (long long)tiles * splits;
+    max_units = units > max_units ? units : max_units;
+    // every slice of the phase on its own CTA of the persistent (co-resident) grid: a fixer waits for parks of its own
+    // phase only, and a CTA reaches a phase whatever happens in that phase elsewhere, so the waits cannot form a cycle
+    F.dist_fix = (splits > 1 && units <= sms && !pair && getenv("PORL_TC_LAST_ARRIVER") == nullptr) ? 1 : 0;
   }
-  if ((long long)tiles * sub > kSemInts) splits = 1;
-  batch.splits = splits;
-  batch.sem = ctx->sem;
-  batch.sem_stride = 0;
-  P.ws = ctx->tc_ws;
-  P.batch = batch;
   P.chunk_kb = ctx->tc_chunk_kb > 0 ? ctx->tc_chunk_kb : 1;
   P.terms = ctx->tc_terms == 1 ? 1 : 3;
-  P.a_mn = a_mn ? 1 : 0;
-  P.b_mn = b_mn ? 1 : 0;
   P.dbg = ctx->tc_dbg;
-  const long long units = (long long)tiles * splits;
-  const int grid = (int)(units < sms ? units : sms);
-  P.dist_fix = (splits > 1 && units <= grid && !pair && getenv("PORL_TC_LAST_ARRIVER") == nullptr) ? 1 : 0;
-
+  P.gbar = ctx->counters + kGridBarBase;
+  P.status = ctx->counters;
+  const int grid = (int)(max_units < sms ? max_units : sms);
   if (pair) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * grid, 1, 1);
@@ -1024,7 +1117,7 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
       set_error("cluster launch of the pair-mode contraction failed: %s", cudaGetErrorString(e));
       return PORL_ERR_CUDA;
     }
-  } else if (ctx->tc_a_in_tmem == 1 && !a_mn) {
+  } else if (atm) {
     launch_pdl(ctx, gemm_tc_kernel<true, false>, grid, TC_THREADS, TcCfg<true>::SMEM_BYTES, stream, P);
   } else {
     launch_pdl(ctx, gemm_tc_kernel<false, false>, grid, TC_THREADS, TcCfg<false>::SMEM_BYTES, stream, P);
@@ -1032,6 +1125,11 @@ int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch
   ctx->tc_launches++;
   PORL_LAUNCHED(ctx);
   return PORL_OK;
+}
+
+int launch_gemm_tc(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, cudaStream_t stream) {
+  TcPhaseSpec spec{&batch, a_kmajor, b_kmajor, false};
+  return launch_gemm_tc_phases(ctx, 1, &spec, stream);
 }
 
 }  // namespace porl

@@ -165,6 +165,8 @@ ln_param_grad_kernel(const float* __restrict__ dy, const float* __restrict__ xha
 
 using namespace porl;
 
+constexpr int kMaxTcPhases = 3;   // = kMaxPhases of gemm_tc.cu
+
 extern "C" int porl_mlp_create(porl_ctx_t* ctx, const porl_mlp_desc_t* desc, porl_mlp_t** out) {
   PORL_CHECK_ARG(ctx && desc && out, "porl_mlp_create: null argument");
   PORL_CHECK_ARG(desc->n_nets >= 1 && desc->n_nets <= kMaxGroups, "porl_mlp_create: n_nets=%d", desc->n_nets);
@@ -276,10 +278,9 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
   cudaStream_t st = as_stream(stream);
   int rc;
 
-  for (int l = 0; l < max_layers; ++l) {
-    GemmBatch tc, ff;           // tensor-core problems and FFMA problems of this layer
+  // tensor-core problems, FFMA problems and narrow output layers of layer l over all calls
+  auto build_layer = [&](int l, GemmBatch& tc, GemmBatch& ff, HeadFwdBatch& hf) {
     tc.n_groups = ff.n_groups = 0;
-    HeadFwdBatch hf;            // narrow output layers of this step
     hf.n_seg = 0;
     hf.B = B;
     for (int c = 0; c < n_calls; ++c) {
@@ -337,6 +338,51 @@ extern "C" int porl_mlp_forward(porl_ctx_t* ctx, int32_t n_calls, const porl_mlp
         }
       }
     }
+  };
+
+  // All hidden layers on the tensor cores: ONE persistent launch runs them back to back, a grid barrier between
+  // consecutive layers instead of a kernel boundary (gemm_tc.cu: TcPhase); the narrow heads follow.
+  bool any_ln = false;
+  for (int c = 0; c < n_calls; ++c) any_ln = any_ln || calls[c].mlp->d.layer_norm;
+  if (ctx->gemm_mode == 1 && ctx->tc_phases && !any_ln && max_layers >= 2) {
+    GemmBatch tcs[PORL_MAX_LAYERS], ff;
+    HeadFwdBatch hfs[PORL_MAX_LAYERS];
+    bool ok = true;
+    int n_tc = 0;
+    for (int l = 0; l < max_layers && ok; ++l) {
+      build_layer(l, tcs[l], ff, hfs[l]);
+      if (ff.n_groups) ok = false;
+      if (tcs[l].n_groups) {
+        if (n_tc != l) ok = false;          // tensor-core layers must be the leading ones
+        ++n_tc;
+      }
+    }
+    if (ok && n_tc >= 2) {
+      rc = PORL_OK;
+      for (int l0 = 0; l0 < n_tc && rc == PORL_OK; l0 += kMaxTcPhases) {
+        TcPhaseSpec specs[kMaxTcPhases];
+        const int n = n_tc - l0 < kMaxTcPhases ? n_tc - l0 : kMaxTcPhases;
+        for (int p = 0; p < n; ++p) specs[p] = TcPhaseSpec{&tcs[l0 + p], true, true, p > 0};
+        rc = launch_gemm_phases(ctx, n, specs, st);
+        if (rc == PORL_ERR_UNSUPPORTED && l0 > 0) {
+          for (int p = 0; p < n && (rc == PORL_OK || rc == PORL_ERR_UNSUPPORTED); ++p) rc = launch_gemm(ctx, true, true, tcs[l0 + p], st);
+        }
+      }
+      if (rc == PORL_OK) {
+        for (int l = 0; l < max_layers; ++l) {
+          rc = launch_head_forward(ctx, hfs[l], st);
+          if (rc != PORL_OK) return rc;
+        }
+        return PORL_OK;
+      }
+      if (rc != PORL_ERR_UNSUPPORTED) return rc;
+    }
+  }
+
+  for (int l = 0; l < max_layers; ++l) {
+    GemmBatch tc, ff;
+    HeadFwdBatch hf;
+    build_layer(l, tc, ff, hf);
     if (tc.n_groups) {
       rc = launch_gemm(ctx, true, true, tc, st);
       if (rc != PORL_OK) return rc;
@@ -445,30 +491,27 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
     l_first = L - 2;
   }
 
-  for (int l = l_first; l >= 0; --l) {
-    // gradient of this layer's pre-activation output: the head gradient, else the (in-place rewritten)
-    // hidden activation buffer of layer l+1 (and its transposed twin)
-    const bool head = (l == L - 1);
+  // gradient of layer l's pre-activation output: the head gradient, else the (in-place rewritten) hidden activation
+  // buffer of layer l+1
+  auto dz_of = [&](int l, int net) -> float* {
+    return (l == L - 1) ? dout + (int64_t)net * B * m->ld_out : saved_h(m, saved, net, l + 1, B);
+  };
+  // dW_l = dz^T a_l (contraction over the batch); db_l = sum_b dz
+  auto build_dw = [&](int l, GemmBatch& bw, ColsumBatch& cb) {
     const bool on_tc = tc_layer(ctx, m, l, B);
-    const int ld_dz = head ? m->ld_out : m->pad[l + 1];
-    auto dz = [&](int net) -> float* {
-      return head ? dout + (int64_t)net * B * m->ld_out : saved_h(m, saved, net, l + 1, B);
-    };
-    // dW_l = dz^T a_l (contraction over the batch); db_l = sum_b dz
-    GemmBatch bw;
+    const int ld_dz = (l == L - 1) ? m->ld_out : m->pad[l + 1];
     bw.n_groups = 0;
-    ColsumBatch cb;
     cb.n_seg = 0;
     for (int net = 0; net < nn; ++net) {
       GemmGroup& g = bw.g[bw.n_groups++];
       clear_group(g);
       float* G = grads + net * m->net_stride;
-      g.A = dz(net);                                               // (B x dims[l+1]): MN-major A, K = batch
+      g.A = dz_of(l, net);                                         // (B x dims[l+1]): MN-major A, K = batch
       g.lda = ld_dz;
       g.B = (l == 0) ? call->x : saved_h(m, saved, net, l, B);     // (B x dims[l]): MN-major B
       g.ldb = (l == 0) ? (int)call->ldx : m->pad[l];
       if (!bias_done[l]) {
-        if (on_tc) cb.seg[cb.n_seg++] = ColsumSeg{dz(net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
+        if (on_tc) cb.seg[cb.n_seg++] = ColsumSeg{dz_of(l, net), G + m->b_off[l], B, m->d.dims[l + 1], ld_dz};
         else g.colsum = G + m->b_off[l];
       }
       g.C = G + m->w_off[l];
@@ -478,21 +521,18 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       g.N = m->d.dims[l];
       g.K = (int)B;
     }
-    rc = launch_gemm(ctx, false, false, bw, st);
-    if (rc != PORL_OK) return rc;
-    rc = launch_colsum(ctx, cb, st);
-    if (rc != PORL_OK) return rc;
-    if (l == 0) break;
-    // da_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l (and over h_l^T)
-    const bool prev_tc = tc_layer(ctx, m, l - 1, B);
-    GemmBatch bx;
+  };
+  // da_l = dz W_l, masked by ReLU (h_l > 0), written in place over h_l
+  auto build_dx = [&](int l, GemmBatch& bx) {
+    const bool on_tc = tc_layer(ctx, m, l, B), prev_tc = tc_layer(ctx, m, l - 1, B);
+    const int ld_dz = (l == L - 1) ? m->ld_out : m->pad[l + 1];
     bx.n_groups = 0;
     for (int net = 0; net < nn; ++net) {
       GemmGroup& g = bx.g[bx.n_groups++];
       clear_group(g);
       const float* P = call->params + net * m->net_stride;
       float* h = saved_h(m, saved, net, l, B);
-      g.A = dz(net);
+      g.A = dz_of(l, net);
       g.lda = ld_dz;
       g.B = P + m->w_off[l];                                       // W_l (dims[l+1] x dims[l]) = (K x N): MN-major B
       g.ldb = m->pad[l];
@@ -509,6 +549,57 @@ extern "C" int porl_mlp_backward(porl_ctx_t* ctx, const porl_mlp_call_t* call, i
       g.N = m->d.dims[l];
       g.K = m->d.dims[l + 1];
     }
+  };
+
+  // Every remaining layer on the tensor cores (no LayerNorm): the contractions dW_l, dx_l, dW_{l-1}, ... run as phases
+  // of persistent launches (gemm_tc.cu: TcPhase).  dx_l overwrites h_l, which dW_l reads, and dW_{l-1} / dx_{l-1} read
+  // what dx_l wrote: a grid barrier in front of every phase but the first of a launch.  The bias-gradient column sums
+  // read buffers no later phase touches and follow the contractions.
+  bool all_tc = ctx->gemm_mode == 1 && ctx->tc_phases && !m->d.layer_norm && l_first >= 1;
+  for (int l = l_first; l >= 0 && all_tc; --l) all_tc = tc_layer(ctx, m, l, B);
+  if (all_tc) {
+    GemmBatch gb[2 * PORL_MAX_LAYERS];
+    ColsumBatch cbs[PORL_MAX_LAYERS];
+    TcPhaseSpec all[2 * PORL_MAX_LAYERS];
+    int n = 0;
+    for (int l = l_first; l >= 0; --l) {
+      build_dw(l, gb[n], cbs[l]);
+      all[n] = TcPhaseSpec{&gb[n], false, false, true};
+      ++n;
+      if (l > 0) {
+        build_dx(l, gb[n]);
+        all[n] = TcPhaseSpec{&gb[n], true, false, true};
+        ++n;
+      }
+    }
+    rc = PORL_OK;
+    for (int p0 = 0; p0 < n && rc == PORL_OK; p0 += kMaxTcPhases) {
+      const int k = n - p0 < kMaxTcPhases ? n - p0 : kMaxTcPhases;
+      rc = launch_gemm_phases(ctx, k, all + p0, st);
+      if (rc == PORL_ERR_UNSUPPORTED) {        // e.g. a problem too small for the tensor-core kernel: one launch each
+        rc = PORL_OK;
+        for (int p = p0; p < p0 + k && rc == PORL_OK; ++p) rc = launch_gemm(ctx, all[p].a_kmajor, all[p].b_kmajor, *all[p].batch, st);
+      }
+    }
+    if (rc != PORL_OK) return rc;
+    for (int l = l_first; l >= 0; --l) {
+      rc = launch_colsum(ctx, cbs[l], st);
+      if (rc != PORL_OK) return rc;
+    }
+    return PORL_OK;
+  }
+
+  for (int l = l_first; l >= 0; --l) {
+    GemmBatch bw;
+    ColsumBatch cb;
+    build_dw(l, bw, cb);
+    rc = launch_gemm(ctx, false, false, bw, st);
+    if (rc != PORL_OK) return rc;
+    rc = launch_colsum(ctx, cb, st);
+    if (rc != PORL_OK) return rc;
+    if (l == 0) break;
+    GemmBatch bx;
+    build_dx(l, bx);
     rc = launch_gemm(ctx, true, false, bx, st);
     if (rc != PORL_OK) return rc;
     if (m->d.layer_norm) {

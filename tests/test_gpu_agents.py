@@ -312,3 +312,28 @@ def test_update_graph_replay_is_bitwise_equal_to_eager_launches(kind, monkeypatc
     assert not eager._graphs
     for (k, a), (_, b) in zip(graphed.state_dict().items(), eager.state_dict().items()):
         assert torch.equal(a, b), k
+
+
+@pytest.mark.parametrize("kind,S,H,B", [("sorl", 362, 512, 256), ("por", 365, 256, 512), ("sorl", 362, 512, 4096)])
+def test_multi_phase_launches_are_bitwise_equal_to_one_launch_per_contraction(kind, S, H, B):
+    """gemm_tc.cu TcPhase: the hidden layers of a forward and {dW_l, dx_l, dW_l-1} of a backward as phases of one
+    persistent launch (grid barriers in between) must give the bits of one launch per contraction: same tiles, same
+    split-K cuts, same summation order -- over three free-running updates (any race across a barrier would show)."""
+    A = 2
+    rows = torch.from_numpy(synth.laser_rows(B * 3, S, 41, A)).to(DEV)
+    outs = []
+    for phases in (True, False):
+        agent, _ = make_agent(kind, S, H, A, 1000, 0.8, 3.0 if kind == "sorl" else 10.0, 5, gemm_mode=1)
+        agent.ctx.set_tc_phases(phases)
+        try:
+            before = agent.ctx.launches
+            losses = [step(agent, kind, slice_row(rows[i * B:(i + 1) * B], S, A)) for i in range(3)]
+            n_launch = agent.ctx.launches - before
+            outs.append((losses, {k: v.clone() for k, v in agent.state_dict().items()}, n_launch))
+        finally:
+            agent.ctx.set_tc_phases(True)
+            agent.ctx.set_gemm_mode(0)
+    assert outs[0][0] == outs[1][0]
+    for k, v in outs[0][1].items():
+        assert torch.equal(v, outs[1][1][k]), k
+    assert outs[0][2] < outs[1][2]          # fewer launches with phases
