@@ -119,7 +119,7 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->tc_terms = 3;
   {
     const char* e = getenv("PORL_TC_PHASES");
-    ctx->tc_phases = e ? atoi(e) : 1;
+    ctx->tc_phases = e ? atoi(e) : 0;
   }
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");

@@ -49,7 +49,7 @@ struct porl_ctx {
   float* tc_ws;             // split-K partial tiles of the tcgen05 kernel (kTcWsFloats)
   int tc_a_in_tmem;         // tcgen05 kernel variant: A operand staged in tensor memory (default) or in shared memory
   int tc_chunk_kb;          // k-blocks per TMEM accumulation chunk of the tcgen05 kernel (1 or 2)
-  int tc_phases;            // 1 (default): consecutive contractions of an MLP pass share one persistent launch; 0: one launch each
+  int tc_phases;            // 1: consecutive contractions of an MLP pass share one persistent launch; 0 (default): one launch each
   int tc_terms;             // 3 = 3xTF32 (fp32-grade, product default); 1 = hi*hi only (plain TF32: the measured ceiling probe)
   unsigned long long* tc_dbg;  // optional per-CTA timestamps of the tcgen05 kernel (device memory), or null
   int pdl;                  // launch the step's kernels with programmatic stream serialization (default 1)

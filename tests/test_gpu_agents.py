@@ -331,7 +331,7 @@ def test_multi_phase_launches_are_bitwise_equal_to_one_launch_per_contraction(ki
             n_launch = agent.ctx.launches - before
             outs.append((losses, {k: v.clone() for k, v in agent.state_dict().items()}, n_launch))
         finally:
-            agent.ctx.set_tc_phases(True)
+            agent.ctx.set_tc_phases(False)
             agent.ctx.set_gemm_mode(0)
     assert outs[0][0] == outs[1][0]
     for k, v in outs[0][1].items():
