@@ -217,6 +217,24 @@ int porl_expectile_twin_loss(porl_ctx_t* ctx, const float* v1, const float* v2, 
                              float gamma, float tau, int64_t B, int64_t B_norm, float* target_v,
                              float* dv1, float* dv2, float* loss_out, porl_stream_t stream);
 
+/* No-allocation variant of porl_expectile_twin_loss.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same arithmetic, same kernel and the same order-fixed reduction as porl_expectile_twin_loss (results
+ * are bitwise equal), but it takes no context and calls no cudaMalloc / cudaFree / allocating routine: the reduction
+ * scratch (one partial per 256 rows + ticket and status words, 16.25 KB) is a file-scope static __device__ array that
+ * every GPU loading the library holds until exit.  Limits: B <= PORL_NOALLOC_MAX_ROWS (larger B is rejected with
+ * PORL_ERR_INVALID and a message in porl_last_error).  All calls on a device share the array, which keeps the last
+ * call's contents (the ticket / status words are cleared by a cudaMemsetAsync on `stream` before each launch, the
+ * partials are rewritten): calls that OVERLAP on the GPU (different streams without ordering) race; calls on one
+ * stream are safe.  The array's device address is resolved with cudaGetSymbolAddress on the first call per device
+ * (make that call outside graph capture, with the device current).  A non-finite loss shows in loss_out[0] only (there
+ * is no context whose status flags could record it). */
+#define PORL_NOALLOC_MAX_ROWS (1 << 20)
+int porl_expectile_twin_loss_noalloc(const float* v1, const float* v2, const float* nv1, const float* nv2, int64_t ldv,
+                                     const float* rewards, const float* dones, float gamma, float tau, int64_t B,
+                                     int64_t B_norm, float* target_v, float* dv1, float* dv2, float* loss_out,
+                                     porl_stream_t stream);
+
 /* Fused head step of the twin value nets (agent/por.py:80-87, agent/sorl.py:85-92): the scalar heads of the target nets
  * on next_obs and of the online nets on obs, the TD target, the twin expectile loss (as porl_expectile_twin_loss) and the
  * heads' backward (dW, db, ReLU-masked dz in place, db of the layer below) in ONE pass over the last hidden activations.

@@ -5,6 +5,8 @@
 // losses and the log_std gradient are bitwise reproducible run to run.
 #include <math.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace porl {
@@ -296,5 +298,72 @@ extern "C" int porl_cql_head(porl_ctx_t* ctx, const float* q, const float* q_nex
       q, q_next_tgt, ldq, actions, rewards, dones, gamma, alpha, B, A, 1.0f / (float)B_norm, dq,
       losses_out, ctx->partials, ctx->counters + 3, ctx->counters);
   PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
+// ---------------------------------------------------------------- no-allocation variant of K4
+// Same kernel as porl_expectile_twin_loss, but the reduction scratch (ticket word, status word, block partials) lives
+// in a file-scope device array instead of the context's cudaMalloc'ed buffers, and no context is needed: the entry
+// point calls no cudaMalloc / cudaFree / allocating routine, so it can be used where allocation is forbidden (CUDA
+// graph capture, serving loops).  Every GPU that loads the library holds the array (kNoAllocScratchBytes) until exit.
+// All calls on a device SHARE the array: calls that overlap on the GPU (two streams) race.
+namespace {
+
+constexpr int kNoAllocMaxBlocks = PORL_NOALLOC_MAX_ROWS / 256;            // one partial per 256-row block
+constexpr int kNoAllocHeadWords = 64;                                     // [0] ticket, [1] status, rest padding
+constexpr size_t kNoAllocScratchBytes = (size_t)(kNoAllocHeadWords + kNoAllocMaxBlocks) * 4;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[kNoAllocHeadWords + kNoAllocMaxBlocks];
+
+// device address of the array per device ordinal, resolved once with that device current (the symbol's name is a
+// host-side stand-in in host code, never a device address)
+uint32_t* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch(uint32_t** out) {
+  int dev = -1;
+  PORL_CUDA(cudaGetDevice(&dev));
+  PORL_CHECK_ARG(dev >= 0 && dev < kNoAllocMaxDevices, "porl_expectile_twin_loss_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    uint32_t* p = nullptr;
+    PORL_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    PORL_CHECK_ARG(p != nullptr, "porl_expectile_twin_loss_noalloc: cudaGetSymbolAddress returned null");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return PORL_OK;
+}
+
+}  // namespace
+
+extern "C" int porl_expectile_twin_loss_noalloc(const float* v1, const float* v2, const float* nv1, const float* nv2,
+                                                int64_t ldv, const float* rewards, const float* dones, float gamma,
+                                                float tau, int64_t B, int64_t B_norm, float* target_v, float* dv1,
+                                                float* dv2, float* loss_out, porl_stream_t stream) {
+  PORL_CHECK_ARG(v1 && v2 && nv1 && nv2 && rewards && dones && target_v && dv1 && dv2 && loss_out,
+                 "porl_expectile_twin_loss_noalloc: null argument");
+  PORL_CHECK_ARG(B > 0 && B_norm >= B && ldv >= 1, "porl_expectile_twin_loss_noalloc: bad B=%lld B_norm=%lld",
+                 (long long)B, (long long)B_norm);
+  PORL_CHECK_ARG(B <= (int64_t)PORL_NOALLOC_MAX_ROWS,
+                 "porl_expectile_twin_loss_noalloc: B=%lld exceeds the static scratch's maximum of %d rows "
+                 "(PORL_NOALLOC_MAX_ROWS); use porl_expectile_twin_loss",
+                 (long long)B, (int)PORL_NOALLOC_MAX_ROWS);
+  uint32_t* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc != PORL_OK) return rc;
+  const int blocks = (int)((B + 255) / 256);
+  // the array keeps the last call's contents: the ticket and status words must start at zero (an aborted launch
+  // would leave the ticket mid-count); the partials are fully rewritten by the blocks of this launch
+  PORL_CUDA(cudaMemsetAsync(scratch, 0, kNoAllocHeadWords * sizeof(uint32_t), as_stream(stream)));
+  expectile_kernel<<<blocks, 256, 0, as_stream(stream)>>>(
+      v1, v2, nv1, nv2, ldv, rewards, dones, gamma, tau, B, 1.0f / (float)B_norm, target_v, dv1, dv2, loss_out,
+      reinterpret_cast<float*>(scratch + kNoAllocHeadWords), scratch, scratch + 1);
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    porl::set_error("porl_expectile_twin_loss_noalloc: kernel launch failed: %s", cudaGetErrorString(e));
+    return PORL_ERR_CUDA;
+  }
   return PORL_OK;
 }
