@@ -306,6 +306,19 @@ int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* m, float* v
                    porl_opt_state_t* state_dev, float beta1, float beta2, float eps, float* target,
                    float ema_beta, int32_t hard_every, porl_stream_t stream);
 
+/* The whole CQL / DQN gradient update in two launches (src/porl/train/cql_trainer.py:88-124: loss, backward,
+ * optimizer.step, and the hard target copy of dqn_trainer.py:196 every `hard_every` steps): porl_cql_fused_grad with
+ * the Adam step of porl_adam_step folded into the gradient reduction -- the thread that finishes a float4 of the gradient
+ * updates those four parameters, the last block advances the device-side optimizer clock.  Bitwise equal to
+ * porl_cql_fused_grad followed by porl_adam_step (same sums, same per-element update).  Single process only (B_norm = B):
+ * under data parallelism use porl_cql_fused_grad + porl_adam_step_peer.  grads still receives the gradient. */
+int porl_cql_fused_step(porl_ctx_t* ctx, const porl_mlp_t* mlp, float* params, float* target_params,
+                        const float* states, const float* next_states, int64_t ld_states, const int64_t* actions,
+                        const float* rewards, const float* dones, const int64_t* idx, int64_t n_rows, float gamma,
+                        float alpha, int64_t B, float* grads, float* losses_out, float* m, float* v,
+                        porl_opt_state_t* state_dev, float beta1, float beta2, float eps, int32_t hard_every,
+                        porl_stream_t stream);
+
 /* ---- data-parallel step: gradient sum over NVLink peer memory fused into the Adam kernel ----
  * (the reference has no distributed code.)  Every rank keeps its gradient bucket
  * (n gradients | tail_floats loss scalars) in memory the other ranks of the node have mapped (CUDA IPC,

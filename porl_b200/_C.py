@@ -161,6 +161,8 @@ _SIGNATURES = {
     "porl_cql_head": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _f, _f, _i64, _i32, _i64, _p, _p, _p]),
     "porl_cql_fused_supported": (C.c_int, [_p]),
     "porl_cql_fused_grad": (C.c_int, [_p, _p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _i64, _f, _f, _i64, _i64, _p, _p, _p]),
+    "porl_cql_fused_step": (C.c_int, [_p, _p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _i64, _f, _f, _i64, _p, _p, _p, _p, _p,
+                                      _f, _f, _f, _i32, _p]),
     "porl_mlp_desc": (C.c_int, [_p, _p]),
     "porl_adam_step": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _f, _f, _f, _p, _f, _i32, _p]),
     "porl_pointmlp_workspace_floats": (_i64, [C.POINTER(PointMlpParams), _i64]),

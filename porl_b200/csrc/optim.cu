@@ -8,36 +8,9 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "optim.cuh"
 
 namespace porl {
-
-struct AdamScalars {
-  float step_size;    // lr / (1 - beta1^t)
-  float inv_bc2_sqrt; // 1 / sqrt(1 - beta2^t)   (torch divides by bias_correction2_sqrt)
-  float bc2_sqrt;
-  int do_hard;        // copy p -> target this step
-};
-
-__device__ __forceinline__ AdamScalars adam_scalars(const porl_opt_state_t* st, float beta1, float beta2,
-                                                    int hard_every) {
-  const long long t = st->step + 1;
-  const double bc1 = 1.0 - pow((double)beta1, (double)t);
-  const double bc2 = 1.0 - pow((double)beta2, (double)t);
-  AdamScalars s;
-  s.step_size = (float)(st->lr / bc1);
-  s.bc2_sqrt = (float)sqrt(bc2);
-  s.inv_bc2_sqrt = 0.f;
-  s.do_hard = (hard_every > 0 && (t % hard_every) == 0) ? 1 : 0;
-  return s;
-}
-
-__device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, const AdamScalars& s,
-                                          float beta1, float beta2, float eps) {
-  m = m + (g - m) * (1.f - beta1);                    // exp_avg.lerp_(grad, 1 - beta1)
-  v = v * beta2 + (1.f - beta2) * g * g;              // mul_(beta2).addcmul_(g, g, 1 - beta2)
-  const float denom = sqrtf(v) / s.bc2_sqrt + eps;    // (exp_avg_sq.sqrt() / bc2_sqrt).add_(eps)
-  p = p - s.step_size * (m / denom);                  // addcdiv_(exp_avg, denom, value=-step_size)
-}
 
 // ---- peer-memory gradient sum (data parallel): signalling words live in every rank's pad ----
 struct PeerArgs {

@@ -70,6 +70,21 @@ class DQNTrainer:
                                       float(self.cql_alpha), B, B * pdist.world_size(), self.q_group.grads.data_ptr(),
                                       self.q_group.loss_ptr, _C.stream_ptr()))
 
+    def _two_launch(self) -> bool:
+        """Adam folded into the gradient reduction (porl_cql_fused_step): single process only -- under data
+        parallelism the optimizer kernel is the one that sums the ranks' buckets."""
+        return pdist.world_size() == 1 and self.q_group.peers is None and os.environ.get("PORL_CQL_FOLD_ADAM", "1") != "0"
+
+    def _fused_step(self, states, next_states, ld, actions, rewards, dones, idx, n_rows: int, B: int, hard_every: int) -> None:
+        g = self.q_group
+        check(lib.porl_cql_fused_step(self.ctx.handle, self.q_network.plan.handle, g.params.data_ptr(),
+                                      self.target_network.flat.data_ptr(), states.data_ptr(), next_states.data_ptr(),
+                                      ld, actions.data_ptr(), rewards.data_ptr(), dones.data_ptr(),
+                                      idx.data_ptr() if idx is not None else None, n_rows, self.gamma,
+                                      float(self.cql_alpha), B, g.grads.data_ptr(), g.loss_ptr, g.m.data_ptr(),
+                                      g.v.data_ptr(), g.state.data_ptr(), g.betas[0], g.betas[1], g.eps, int(hard_every),
+                                      _C.stream_ptr()))
+
     def learn_indices(self, idx: torch.Tensor, hard_every: int = 0) -> None:
         """TD (+ CQL) update on rows `idx` of the replay buffer; asynchronous.  With the fused kernel the rows go
         from the HBM-resident buffer straight into shared memory (no gathered copy of the minibatch exists)."""
@@ -79,6 +94,9 @@ class DQNTrainer:
             return self.learn_packed(self._pb, hard_every)
         if idx.device != self.device or idx.dtype != torch.int64 or not idx.is_contiguous():
             idx = idx.to(self.device, torch.int64).contiguous()
+        if self._two_launch():
+            return self._fused_step(rb._states, rb._next_states, rb.ld, rb.actions, rb.rewards, rb.dones, idx, rb.capacity,
+                                    int(idx.shape[0]), hard_every)
         self._fused_grad(rb._states, rb._next_states, rb.ld, rb.actions, rb.rewards, rb.dones, idx, rb.capacity,
                          int(idx.shape[0]))
         self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)
@@ -86,6 +104,8 @@ class DQNTrainer:
     def learn_packed(self, pb: PackedBatch, hard_every: int = 0) -> None:
         """TD (+ CQL) update on a packed minibatch; asynchronous.  losses land in q_group.tail[0:3]."""
         ctx, B, plan = self.ctx, pb.B, self.q_network.plan
+        if self.fused and self._two_launch():
+            return self._fused_step(pb.obs, pb.next_obs, pb.ld_obs, pb.actions, pb.rewards, pb.dones, None, B, B, hard_every)
         if self.fused:
             self._fused_grad(pb.obs, pb.next_obs, pb.ld_obs, pb.actions, pb.rewards, pb.dones, None, B, B)
             self.q_group.step(target=self.target_network.flat if hard_every > 0 else None, hard_every=hard_every)

@@ -41,7 +41,7 @@ def dry_porl(monkeypatch):
     calls = _Recorder()
     launching = ["porl_gather_rows_f32", "porl_gather_transitions", "porl_gather_soa", "porl_pack_rows",
                  "porl_mlp_forward", "porl_mlp_backward", "porl_expectile_twin_loss", "porl_awr_gauss_nll",
-                 "porl_cql_head", "porl_cql_fused_grad", "porl_adam_step", "porl_gemm", "porl_sorl_step", "porl_por_step"]
+                 "porl_cql_head", "porl_cql_fused_grad", "porl_cql_fused_step", "porl_adam_step", "porl_gemm", "porl_sorl_step", "porl_por_step"]
     for name in launching:
         monkeypatch.setattr(_C.lib, name, (lambda n: (lambda *a: calls.append((n, a)) or 0))(name))
 

@@ -214,3 +214,32 @@ def test_data_parallel_on_real_gpus(script, args):
     r = _torchrun(script, *args)
     assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
     assert "OK" in r.stdout
+
+
+def _final(stdout):
+    import ast
+    return [ast.literal_eval(l) for l in stdout.splitlines() if l.startswith("{'updates'")]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (one process per GPU over NVLink)")
+@pytest.mark.parametrize("backbone", ["none", "fasternet"])
+def test_sorl_train_cli_under_torchrun(backbone, tmp_path):
+    """The documented WORLD_SIZE > 1 mode of the trainer itself: `torchrun --nproc-per-node 2
+    sorl_train.py`.  Every rank must build its agent on its own GPU (process group and device first), finish, and report
+    the same losses; without a backbone the run must also reproduce the single-process run at the same global batch
+    (same permutation, each rank takes its slice of every minibatch, gradients summed in-kernel over NVLink)."""
+    flags = ["--backbone", backbone, "--batch_size", "256", "--dataset_rows", "8192", "--updates", "24", "--log_every", "8",
+             "--train_steps", "24", "--episodes", "1", "--weights_dir", str(tmp_path)]
+    r = _torchrun("sorl_train.py", *flags)
+    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
+    outs = _final(r.stdout)
+    assert len(outs) == 2 and all(o["updates"] == 24 for o in outs), r.stdout[-2000:]
+    assert all(np.isfinite([o["v_loss"], o["g_loss"]]).all() for o in outs)
+    assert outs[0]["v_loss"] == outs[1]["v_loss"] and outs[0]["g_loss"] == outs[1]["g_loss"]     # replicas agree
+    if backbone == "none":
+        one = subprocess.run([sys.executable, os.path.join(ROOT, "sorl_train.py"), *flags], cwd=ROOT, capture_output=True,
+                             text=True, timeout=600)
+        assert one.returncode == 0, (one.stdout[-3000:], one.stderr[-3000:])
+        single = _final(one.stdout)[0]
+        for k in ("v_loss", "g_loss"):
+            assert abs(outs[0][k] - single[k]) <= 1e-4 * abs(single[k]), (k, outs[0], single)

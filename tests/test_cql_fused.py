@@ -206,3 +206,35 @@ def test_fused_data_parallel_shards_sum_to_the_global_gradient(monkeypatch, mode
         tails.append(t.q_group._local_tail[0:3].clone())
     assert rel_l2(parts[0] + parts[1], g_all) <= 1e-6
     np.testing.assert_allclose((tails[0] + tails[1]).cpu().numpy(), l_all.cpu().numpy(), rtol=2e-6, atol=1e-8)
+
+
+def test_adam_folded_into_the_reduction_is_bitwise_equal_to_the_separate_optimizer_launch(monkeypatch, mode):
+    """porl_cql_fused_step (Adam + hard target copy + optimizer clock inside the gradient reduction: two launches per
+    update) against porl_cql_fused_grad + porl_adam_step (three launches), six updates with a hard copy every third:
+    parameters, target net, moments, optimizer clock and losses must be bitwise equal."""
+    S, A, n_rows, B = 362, 5, 4000, 512
+    runs = []
+    for fold in ("1", "0"):
+        monkeypatch.setenv("PORL_CQL_FOLD_ADAM", fold)
+        t, _, _, _ = make(S, A, n_rows, seed=9)
+        assert t.fused and t._two_launch() == (fold == "1")
+        g = torch.Generator().manual_seed(31)
+        launches0 = t.ctx.launches
+        losses = []
+        for _ in range(6):
+            t.learn_indices(torch.randint(0, n_rows, (B,), generator=g), hard_every=3)
+            losses.append(t.read_losses())
+        clock = t.q_group.read_clock()
+        runs.append((t.ctx.launches - launches0, losses, (int(clock.step), float(clock.lr)),
+                     {k: v.clone() for k, v in t.q_network.state_dict().items()},
+                     {k: v.clone() for k, v in t.target_network.state_dict().items()}, t.q_group.m.clone(),
+                     t.q_group.v.clone(), t.q_group.grads.clone()))
+    (n1, l1, c1, p1, t1, m1, v1, g1), (n0, l0, c0, p0, t0, m0, v0, g0) = runs
+    assert n1 == 12 and n0 == 18, (n1, n0)               # 2 vs 3 launches per update
+    assert l1 == l0 and c1 == c0 and c1[0] == 6
+    for k in p1:
+        assert torch.equal(p1[k], p0[k]), k
+        assert torch.equal(t1[k], t0[k]), k
+    assert torch.equal(m1, m0) and torch.equal(v1, v0) and torch.equal(g1, g0)
+    any_moved = any(not torch.equal(p1[k], t1[k]) for k in p1)
+    assert not any_moved                                  # update 6 ended with a hard copy: target == online

@@ -175,16 +175,23 @@ def test_cql_trainer_host_plumbing(dry_porl, tmp_path, monkeypatch):
     dry_porl.clear()
     assert t.fused                                      # 22 -> 64 -> 128 -> 64 -> 5 is served by the single-kernel update
     t.learn()
+    assert [c[0] for c in dry_porl] == ["porl_cql_fused_step"]       # single process: Adam rides in the gradient reduction
+    fused = dry_porl[0][1]
+    assert fused[6] == 32 and fused[11] == 100000 and fused[14] == 64 and fused[23] == 0     # ld, rows, B, hard_every
+    assert t.training_step == 1
+    monkeypatch.setenv("PORL_CQL_FOLD_ADAM", "0")        # the separate optimizer launch (what data parallelism uses)
+    dry_porl.clear()
+    t.learn()
     assert [c[0] for c in dry_porl] == ["porl_cql_fused_grad", "porl_adam_step"]
     fused = dry_porl[0][1]
     assert fused[6] == 32 and fused[11] == 100000 and fused[14] == 64 and fused[15] == 64   # ld, rows, B, B_norm
-    assert t.training_step == 1
+    assert t.training_step == 2
     monkeypatch.setenv("PORL_CQL_FUSED", "0")            # layer-by-layer path, kept for other network shapes
     dry_porl.clear()
     t.learn()
     assert [c[0] for c in dry_porl] == ["porl_gather_soa", "porl_mlp_forward", "porl_cql_head",
                                        "porl_mlp_backward", "porl_adam_step"]
-    assert t.training_step == 2
+    assert t.training_step == 3
 
 
 def test_epoch_sampler_reproduces_dataloader_stream():
