@@ -294,6 +294,9 @@ typedef struct {
   int64_t t_max;         /* > 0: torch CosineAnnealingLR(T_max=t_max, eta_min=0), recursive form */
   uint32_t blocks_done;  /* internal */
   uint32_t pad_;
+  uint32_t pad2_[2];
+  uint32_t rec_[2][4];   /* internal: two published 16-byte records of Adam scalars (parity of t); zero-initialise.
+                          * The buffer must be 16-byte aligned. */
 } porl_opt_state_t;
 
 /* torch.optim.Adam.step (beta1 .9, beta2 .999, eps 1e-8 defaults passed explicitly; single-tensor

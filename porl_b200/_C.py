@@ -41,7 +41,8 @@ class MlpCall(C.Structure):
 
 class OptState(C.Structure):
     _fields_ = [("step", C.c_int64), ("lr", C.c_double), ("base_lr", C.c_double), ("t_max", C.c_int64),
-                ("blocks_done", C.c_uint32), ("pad_", C.c_uint32)]
+                ("blocks_done", C.c_uint32), ("pad_", C.c_uint32), ("pad2_", C.c_uint32 * 2),
+                ("rec_", (C.c_uint32 * 4) * 2)]
 
 
 MAX_PEERS = 8

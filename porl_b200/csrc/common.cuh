@@ -23,10 +23,7 @@ constexpr int kTicketBase = 64;          // counters[0] status, [1..63] kernel t
 constexpr int kTickets = 4096;
 constexpr int kGridBarBase = kTicketBase + kTickets;   // grid-barrier words of the multi-phase contraction launch
 constexpr int kGridBarWords = 16;
-constexpr int kAdamCacheBase = kGridBarBase + kGridBarWords;   // two 16-byte records of published Adam scalars (cql_fused.cu)
-constexpr int kAdamCacheWords = 16;
-constexpr int kCounterWords = kAdamCacheBase + kAdamCacheWords;
-static_assert(kAdamCacheBase % 4 == 0, "the records are read with 16-byte accesses");
+constexpr int kCounterWords = kGridBarBase + kGridBarWords;
 
 void set_error(const char* fmt, ...);
 

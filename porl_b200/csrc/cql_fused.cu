@@ -656,32 +656,8 @@ constexpr int kRedCols = 8, kRedGroups = 32;
 // optimizer folded into the reduction (porl_cql_fused_step): the thread that finishes a float4 of the gradient also runs
 // Adam on those four parameters (+ the hard target copy), the last block of the launch advances the optimizer clock --
 // the whole CQL update is then two launches (fused forward/backward, reduce + Adam)
-// One published record of Adam scalars: 16 bytes, written and read with ONE vector access.  key = low 32 bits of t;
-// check mixes every input the scalars depend on (t, learning rate, betas, which optimizer state), so a record that is
-// stale, foreign or torn fails the check and the reader computes the scalars itself.
-struct AdamRecord {
-  float step_size, bc2_sqrt;
-  uint32_t t_lo, check;
-};
-static_assert(sizeof(AdamRecord) == 16, "one 16-byte access");
-
-__device__ __forceinline__ uint32_t adam_record_check(float step_size, float bc2_sqrt, long long t, double lr, float beta1,
-                                                      float beta2, const void* st) {
-  const unsigned long long lrb = (unsigned long long)__double_as_longlong(lr);
-  const unsigned long long sp = (unsigned long long)reinterpret_cast<uintptr_t>(st);
-  uint32_t h = __float_as_uint(step_size) * 0x9E3779B1u;
-  h = (h ^ __float_as_uint(bc2_sqrt)) * 0x85EBCA77u;
-  h = (h ^ (uint32_t)t ^ (uint32_t)((unsigned long long)t >> 32)) * 0xC2B2AE3Du;
-  h = (h ^ (uint32_t)lrb ^ (uint32_t)(lrb >> 32)) * 0x27D4EB2Fu;
-  h = (h ^ __float_as_uint(beta1)) * 0x165667B1u;
-  h = (h ^ __float_as_uint(beta2)) * 0x9E3779B1u;
-  h = (h ^ (uint32_t)sp ^ (uint32_t)(sp >> 32)) * 0x85EBCA77u;
-  return h ^ (h >> 15) ^ 0xA5A5A5A5u;
-}
-
 constexpr int kTicketGroup = 32;
 struct CqlOpt {
-  AdamRecord* cache;      // two records (ctx->counters + kAdamCacheBase), parity of t
   uint32_t* tickets;      // group ticket words, 32 words apart (ctx->counters + kTicketBase)
   float* p;
   float* m;
@@ -697,50 +673,25 @@ __global__ void __launch_bounds__(kRedCols * kRedGroups)
 cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_stride, int64_t n_floats,
                   float* __restrict__ grads, float* __restrict__ losses_out, float inv_bn, float alpha,
                   uint32_t* status, const CqlOpt o) {
-  // Programmatic dependent launch: blocks of this grid become resident while the fused kernel is still running and park
-  // at griddepcontrol.wait.  Adam's scalars (two double-precision pow, a division, a square root: ~4 us of dependent
-  // work and global round trips, which every one of the 1,300 blocks would otherwise have on its critical path --
-  // measured: 18 us for this kernel instead of 8) are computed ONCE, by block 0 BEFORE that wait, speculatively from the
-  // optimizer clock as it stands, and published as one 16-byte record.  After the wait a block needs one round trip
-  // (record, step count and learning rate loaded side by side); a record that does not verify is ignored and the block
-  // computes the scalars itself, so the result never depends on the speculation.  Two records (parity of t): the next
-  // launch's block 0 may already be publishing t + 1 while late blocks of this launch read t.
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // ADAM: launched with one block more than the columns need; that block has no column (j >= n_floats) and publishes
+  // the scalars of the next update on the side (optim.cuh: published scalars)
+  pdl_entry();
   const bool scalar_thread = ADAM && threadIdx.x == kRedCols * kRedGroups - 1;
-  if (scalar_thread && blockIdx.x == 0) {
-    const long long t_spec = *reinterpret_cast<volatile long long*>(&o.st->step) + 1;
-    __threadfence();              // adam_advance_clock publishes lr before step
-    const double lr = *reinterpret_cast<volatile double*>(&o.st->lr);
-    const double bc1 = 1.0 - pow((double)o.beta1, (double)t_spec);       // the expressions of adam_scalars()
-    const double bc2 = 1.0 - pow((double)o.beta2, (double)t_spec);
-    AdamRecord r;
-    r.step_size = (float)(lr / bc1);
-    r.bc2_sqrt = (float)sqrt(bc2);
-    r.t_lo = (uint32_t)t_spec;
-    r.check = adam_record_check(r.step_size, r.bc2_sqrt, t_spec, lr, o.beta1, o.beta2, o.st);
-    __stwt(reinterpret_cast<uint4*>(o.cache + (t_spec & 1)), *reinterpret_cast<const uint4*>(&r));   // one 16-byte store
-  }
-  asm volatile("griddepcontrol.wait;" ::: "memory");
   __shared__ float4 red[kRedGroups][kRedCols];
   __shared__ AdamScalars sh;
   const int col = threadIdx.x % kRedCols, grp = threadIdx.x / kRedCols;
   const int64_t j = ((int64_t)blockIdx.x * kRedCols + col) * 4;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   float4 pp = s, mm = s, vv = s;
-  uint4 rec0 = make_uint4(0u, 0u, 0u, 0u), rec1 = rec0;
-  long long step_now = 0;
-  double lr_now = 0.0;
+  __shared__ long long sh_t;
+  __shared__ double sh_lr;
   if (ADAM && grp == 0 && j < n_floats) {      // in flight during the partial sums
     pp = *reinterpret_cast<const float4*>(o.p + j);
     mm = *reinterpret_cast<const float4*>(o.m + j);
     vv = *reinterpret_cast<const float4*>(o.v + j);
   }
-  if (scalar_thread) {                         // four independent loads, one round trip
-    rec0 = __ldcv(reinterpret_cast<const uint4*>(o.cache));
-    rec1 = __ldcv(reinterpret_cast<const uint4*>(o.cache + 1));
-    step_now = *reinterpret_cast<const volatile long long*>(&o.st->step);
-    lr_now = *reinterpret_cast<const volatile double*>(&o.st->lr);
-  }
+  AdamClock clk = {};
+  if (scalar_thread) clk = adam_clock_load(o.st);      // in flight with the partial loads: one round trip
   if (j < n_floats) {
 #pragma unroll 4
     for (int c = grp; c < n_part; c += kRedGroups) {
@@ -750,22 +701,12 @@ cql_reduce_kernel(const float* __restrict__ partials, int n_part, int64_t part_s
   }
   red[grp][col] = s;
   if (scalar_thread) {
-    const long long t = step_now + 1;
-    const uint4 rr = (t & 1) ? rec1 : rec0;
-    AdamRecord r;
-    *reinterpret_cast<uint4*>(&r) = rr;
-    if (r.t_lo == (uint32_t)t && r.check == adam_record_check(r.step_size, r.bc2_sqrt, t, lr_now, o.beta1, o.beta2, o.st)) {
-      AdamScalars a;
-      a.step_size = r.step_size;
-      a.bc2_sqrt = r.bc2_sqrt;
-      a.inv_bc2_sqrt = 0.f;
-      a.do_hard = (o.hard_every > 0 && (t % o.hard_every) == 0) ? 1 : 0;
-      sh = a;
-    } else {
-      sh = adam_scalars(o.st, o.beta1, o.beta2, o.hard_every);
-    }
+    sh = adam_scalars_from(clk, o.st, o.beta1, o.beta2, o.hard_every);
+    sh_t = clk.t;
+    sh_lr = clk.lr;
   }
   __syncthreads();
+  if (ADAM && blockIdx.x == gridDim.x - 1 && threadIdx.x == 32) adam_publish_next(o.st, sh_t, sh_lr, o.beta1, o.beta2);
   if (grp == 0 && j < n_floats) {
 #pragma unroll
     for (int q = 1; q < kRedGroups; ++q) {
@@ -936,9 +877,9 @@ static int cql_fused_launch(porl_ctx_t* ctx, const porl_mlp_t* mlp, const float*
   {
     ProfScope prof(ctx, PORL_CAT_LOSS, (double)(grid + 1) * a.n_floats * 4.0, st);
     const int blocks = (int)((a.n_floats / 4 + kRedCols - 1) / kRedCols);
-    PORL_CHECK_ARG(!opt || (blocks + kTicketGroup - 1) / kTicketGroup * 32 <= kTickets, "porl_cql_fused_step: network too large");
+    PORL_CHECK_ARG(!opt || (blocks + kTicketGroup) / kTicketGroup * 32 <= kTickets, "porl_cql_fused_step: network too large");
     if (opt)
-      PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel<true>, blocks, kRedCols * kRedGroups, 0, st, (const float*)a.partials, grid,
+      PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel<true>, blocks + 1 /* publisher block */, kRedCols * kRedGroups, 0, st, (const float*)a.partials, grid,
                            a.part_stride, a.n_floats, grads, losses_out, a.inv_bn, alpha, ctx->counters, *opt));
     else
       PORL_CUDA(launch_pdl(ctx, cql_reduce_kernel<false>, blocks, kRedCols * kRedGroups, 0, st, (const float*)a.partials, grid,
@@ -968,7 +909,6 @@ extern "C" int porl_cql_fused_step(porl_ctx_t* ctx, const porl_mlp_t* mlp, float
   PORL_CHECK_ARG(aligned16(m) && aligned16(v), "porl_cql_fused_step: moment buffers must be 16-byte aligned");
   PORL_CHECK_ARG(hard_every >= 0, "porl_cql_fused_step: hard_every=%d", (int)hard_every);
   CqlOpt o;
-  o.cache = reinterpret_cast<AdamRecord*>(ctx->counters + kAdamCacheBase);
   o.tickets = ctx->counters + kTicketBase;
   o.p = params;
   o.m = m;

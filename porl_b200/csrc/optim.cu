@@ -65,9 +65,15 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   __shared__ AdamScalars sh;
   __shared__ uint32_t sh_epoch;
   __shared__ int sh_timeout;
+  __shared__ long long sh_t;
+  __shared__ double sh_lr;
+  // the LAST block of the grid owns no element: it publishes the scalars of the next update (optim.cuh) while the
+  // other blocks work, and takes its ticket like them
+  const int n_work = (int)gridDim.x - 1;
+  const bool publisher = (int)blockIdx.x == n_work;
   const bool ema = (target != nullptr) && ema_beta > 0.f;
   const int64_t n4 = n >> 2;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t stride = (int64_t)n_work * blockDim.x;
   float4* p4 = reinterpret_cast<float4*>(p);
   const float4* g4 = reinterpret_cast<const float4*>(g);
   float4* m4 = reinterpret_cast<float4*>(m);
@@ -77,17 +83,22 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   // block's HBM latency overlaps that scalar work instead of following it
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float4 pp0 = make_float4(0.f, 0.f, 0.f, 0.f), mm0 = pp0, vv0 = pp0, gg0 = pp0, tt0 = pp0;
-  if (i0 < n4) {
+  if (!publisher && i0 < n4) {
     pp0 = p4[i0]; mm0 = m4[i0]; vv0 = v4[i0];
     if (!PEER) gg0 = g4[i0];
     if (ema) tt0 = t4[i0];
   }
   if (threadIdx.x == 0) {
-    sh = adam_scalars(st, beta1, beta2, hard_every);
+    long long t_now;
+    double lr_now;
+    sh = adam_scalars_fast(st, beta1, beta2, hard_every, &t_now, &lr_now);
+    sh_t = t_now;
+    sh_lr = lr_now;
     if (PEER) sh_epoch = *reinterpret_cast<volatile uint32_t*>(peers.epoch) + 1u;
     sh_timeout = 0;
   }
   __syncthreads();
+  if (publisher && threadIdx.x == 32) adam_publish_next(st, sh_t, sh_lr, beta1, beta2);
   const AdamScalars s = sh;
   bool skip = false;
   if (PEER) {
@@ -115,7 +126,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   const bool hard = (target != nullptr) && s.do_hard;
   const float keep = 1.f - ema_beta;
 
-  for (int64_t i = i0; i < n4 && !skip; i += stride) {
+  for (int64_t i = i0; i < n4 && !skip && !publisher; i += stride) {
     float4 pp, mm, vv;
     if (i == i0) { pp = pp0; mm = mm0; vv = vv0; }
     else { pp = p4[i]; mm = m4[i]; vv = v4[i]; }
@@ -149,7 +160,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     }
   }
   // tail (n not a multiple of 4)
-  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n && !skip; i += stride) {
+  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n && !skip && !publisher; i += stride) {
     float pp = p[i], mm = m[i], vv = v[i];
     float gi;
     if (PEER) {
@@ -172,19 +183,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     if (ticket == gridDim.x - 1 && skip) st->blocks_done = 0;
     if (ticket == gridDim.x - 1 && !skip) {
       st->blocks_done = 0;
-      const long long e = st->step + 1;   // scheduler.last_epoch after its step()
-      if (st->t_max > 0) {
-        // torch CosineAnnealingLR.get_lr (recursive form, eta_min = 0)
-        const double T = (double)st->t_max;
-        double lr = st->lr;
-        if ((e - 1 - st->t_max) % (2 * st->t_max) == 0) {
-          lr = lr + st->base_lr * (1.0 - cos(M_PI / T)) / 2.0;
-        } else {
-          lr = (1.0 + cos(M_PI * (double)e / T)) / (1.0 + cos(M_PI * (double)(e - 1) / T)) * lr;
-        }
-        st->lr = lr;
-      }
-      st->step = e;
+      adam_advance_clock(st);
       if (PEER) *reinterpret_cast<volatile uint32_t*>(peers.epoch) = sh_epoch;
       __threadfence();
     }
@@ -228,6 +227,8 @@ adam_sharded_kernel(const __grid_constant__ ShardRank self, const ShardRank* __r
   // blockIdx.y selects the rank when several ranks are emulated inside one cooperative launch (single-GPU tests)
   __shared__ ShardRank a;
   __shared__ AdamScalars sh;
+  __shared__ long long sh_t;
+  __shared__ double sh_lr;
   __shared__ uint32_t sh_epoch;
   __shared__ int sh_flag;
   {
@@ -238,7 +239,11 @@ adam_sharded_kernel(const __grid_constant__ ShardRank self, const ShardRank* __r
   __syncthreads();
   const int world = a.peers.world, rank = a.peers.rank;
   if (threadIdx.x == 0) {
-    sh = adam_scalars(a.st, beta1, beta2, hard_every);
+    long long t_now;
+    double lr_now;
+    sh = adam_scalars_fast(a.st, beta1, beta2, hard_every, &t_now, &lr_now);
+    sh_t = t_now;
+    sh_lr = lr_now;
     sh_epoch = *reinterpret_cast<volatile uint32_t*>(a.peers.epoch) + 1u;
     sh_flag = 0;
   }
@@ -270,8 +275,12 @@ adam_sharded_kernel(const __grid_constant__ ShardRank self, const ShardRank* __r
   float4* v4 = reinterpret_cast<float4*>(a.v);
   const float4* p4 = reinterpret_cast<const float4*>(a.p);
   const float4* t4 = reinterpret_cast<const float4*>(a.target);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = s0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < s1 && !skip; i += stride) {
+  // the last block (in x) owns no element: it publishes the scalars of the next update while the others work (optim.cuh)
+  const int n_work = (int)gridDim.x - 1;
+  const bool publisher = (int)blockIdx.x == n_work;
+  if (publisher && threadIdx.x == 32) adam_publish_next(a.st, sh_t, sh_lr, beta1, beta2);
+  const int64_t stride = (int64_t)n_work * blockDim.x;
+  for (int64_t i = s0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < s1 && !skip && !publisher; i += stride) {
     float4 pp = p4[i], mm = m4[i], vv = v4[i];
     float4 gr[PORL_MAX_PEERS];
 #pragma unroll
@@ -353,7 +362,7 @@ extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* 
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * (target ? 36.0 : 28.0), as_stream(stream));
-  launch_pdl(ctx, adam_kernel<false>, (int)blocks, 256, 0, as_stream(stream), p, g, m, v, n, state_dev, beta1, beta2, eps,
+  launch_pdl(ctx, adam_kernel<false>, (int)blocks + 1 /* publisher block */, 256, 0, as_stream(stream), p, g, m, v, n, state_dev, beta1, beta2, eps,
                                                                  target, ema_beta, hard_every, PeerArgs{});
   PORL_LAUNCHED(ctx);
   return PORL_OK;
@@ -400,7 +409,7 @@ static int sharded_blocks(const porl_ctx_t* ctx, int64_t n, int world) {
   int64_t blocks = (chunk + 255) / 256;
   const int64_t cap = (int64_t)ctx->sm_count * 4;
   if (blocks > cap) blocks = cap;
-  return (int)(blocks < 1 ? 1 : blocks);
+  return (int)(blocks < 1 ? 1 : blocks) + 1;      // + the publisher block (owns no element)
 }
 
 // Single-GPU stand-in for `world` ranks (tests): ONE cooperative launch whose blockIdx.y is the rank, so the blocks that
@@ -480,7 +489,7 @@ extern "C" int porl_adam_step_peer(porl_ctx_t* ctx, float* p, const porl_peer_gr
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * ((target ? 32.0 : 24.0) + 4.0 * pg->world), as_stream(stream));
-  launch_pdl(ctx, adam_kernel<true>, (int)blocks, 256, 0, as_stream(stream), p, pg->bucket[pg->rank], m, v, n, state_dev, beta1,
+  launch_pdl(ctx, adam_kernel<true>, (int)blocks + 1 /* publisher block */, 256, 0, as_stream(stream), p, pg->bucket[pg->rank], m, v, n, state_dev, beta1,
                                                                 beta2, eps, target, ema_beta, hard_every, a);
   PORL_LAUNCHED(ctx);
   return PORL_OK;
