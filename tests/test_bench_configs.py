@@ -218,7 +218,8 @@ def test_data_parallel_on_real_gpus(script, args):
 
 def _final(stdout):
     import ast
-    return [ast.literal_eval(l) for l in stdout.splitlines() if l.startswith("{'updates'")]
+    import re
+    return [ast.literal_eval(m) for m in re.findall(r"\{'updates'[^}]*\}", stdout)]     # ranks may share a line
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (one process per GPU over NVLink)")
