@@ -203,10 +203,37 @@ def measure_ceilings(ctx, device):
         ctx.set_tc_terms(3)
         ctx.set_gemm_mode(mode)
     del x, w, out
-    return {"shape": "8192^3 fp32 operands, best of 5, CUDA events", "cublas_tf32_tflops": cublas_tf32,
+    form = mma_form_rates()
+    return {"mma_form": form, "shape": "8192^3 fp32 operands, best of 5, CUDA events", "cublas_tf32_tflops": cublas_tf32,
             "cublas_fp32_tflops": cublas_fp32, "own_kernel_1xtf32_tflops": own1, "own_kernel_3xtf32_tflops": own3,
             "ceiling_3xtf32_tflops": cublas_tf32 / 3.0,
             "note": "3xTF32 issues 3 MMAs per product: its ceiling is measured cuBLAS TF32 / 3"}
+
+
+def mma_form_rates():
+    """Issue rate of the contraction kernel's own MMA form, measured in this run by the stand-alone probe built beside the
+    library (tools/micro/umma_rate.cu --json: 12 tcgen05.mma.kind::tf32 M=128 K=8 + one commit per k-block, one issuing
+    warp per SM, 148 SMs).  form_ceiling_3xtf32_tflops = what a 128x128-tile SS kernel can reach with three MMAs per
+    product at the maximum SM clock; the cuBLAS-derived ceiling above it is that of N=256 / cta_group::2 tiles."""
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools", "micro", "umma_rate")
+    if not os.path.exists(exe):
+        return {"unavailable": "tools/micro/umma_rate not built"}
+    try:
+        r = subprocess.run([exe, "--json"], capture_output=True, text=True, timeout=60)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001 -- a probe failure must not lose the bench line
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+    try:
+        mhz = float(subprocess.run(["nvidia-smi", "--query-gpu=clocks.max.sm", "--format=csv,noheader,nounits", "-i", "0"],
+                                   capture_output=True, text=True, timeout=20).stdout.split()[0])
+    except Exception:  # noqa: BLE001
+        mhz = 1965.0
+    for k in ("ss_n128", "ss_n256", "ts_n128", "ts_n256"):
+        d[f"{k}_3xtf32_tflops"] = d[f"{k}_fma_per_clk_sm"] * 2.0 * 148 * mhz * 1e6 / 3.0 * 1e-12
+    d["sm_mhz"] = mhz
+    d["form_ceiling_3xtf32_tflops"] = d["ss_n128_3xtf32_tflops"]
+    d["how"] = "tools/micro/umma_rate --json; kernel form = ss_n128 (both operands in shared memory, N = 128)"
+    return d
 
 
 def traffic_record(gemm_mode):
@@ -794,6 +821,8 @@ def run_b200(a):
                             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
                             "frac_of_3xtf32_ceiling": achieved / ceiling3,
                             "ceiling_3xtf32_tflops": ceiling3,
+                            "frac_of_mma_form_rate": (achieved / ceil["mma_form"]["form_ceiling_3xtf32_tflops"]
+                                                      if ceil and "form_ceiling_3xtf32_tflops" in ceil.get("mma_form", {}) else None),
                             "ceiling_source": "measured in this run: cuBLAS TF32 8192^3 / 3" if ceil else "bf16 sustained / 6 (not measured)",
                             "measured_ceilings": ceil,
                             "kernel": "gemm_tc_kernel (tcgen05 3xTF32)" if a.gemm_mode == 1 else "gemm_simt_kernel (fp32 FFMA)",

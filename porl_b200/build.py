@@ -31,6 +31,11 @@ def _stale() -> bool:
         return True
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "porl_b200.h")]
+    probe = os.path.join(HERE, "..", "tools", "micro", "umma_rate.cu")
+    if os.path.exists(probe):
+        if not os.path.exists(probe[:-3]):
+            return True
+        deps.append(probe)
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -58,6 +63,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError(f"nvcc failed on {src}")
     link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
     subprocess.run(link, check=True)
+    # the tcgen05 instruction-rate probe bench.py runs beside the library (tools/micro/umma_rate.cu): a stand-alone binary
+    probe_src = os.path.join(HERE, "..", "tools", "micro", "umma_rate.cu")
+    if os.path.exists(probe_src):
+        subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", probe_src[:-3], probe_src], check=True)
     return LIB
 
 
