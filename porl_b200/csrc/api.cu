@@ -53,9 +53,12 @@ int launch_gemm(porl_ctx* ctx, bool a_kmajor, bool b_kmajor, GemmBatch& batch, c
     rc = launch_gemm_tc(ctx, a_kmajor, b_kmajor, batch, stream);
     if (rc != PORL_ERR_UNSUPPORTED) return rc;
   }
-  for (int i = 0; i < batch.n_groups; ++i)
+  for (int i = 0; i < batch.n_groups; ++i) {
     PORL_CHECK_ARG(!batch.g[i].Ct, "contraction group %d: a transposed output needs the tcgen05 path "
                    "(gemm mode 1, M, N, K >= 32)", i);
+    PORL_CHECK_ARG(!batch.g[i].a_affine, "contraction group %d: the operand affine needs the tcgen05 path (gemm mode 1, "
+                   "K-major A with K %% 32 == 0)", i);
+  }
   return launch_gemm_simt(ctx, a_kmajor, b_kmajor, batch, stream);
 }
 
@@ -250,6 +253,7 @@ extern "C" int porl_gemm(porl_ctx_t* ctx, int32_t a_kmajor, int32_t b_kmajor, in
   g.A = A; g.B = B; g.C = C; g.A_lo = nullptr; g.B_lo = nullptr; g.C_lo = nullptr; g.bias = bias; g.relu_src = relu_src; g.colsum = colsum;
   g.Ct = Ct; g.ldct = (int)ldct;
   g.bits_out = nullptr; g.bits_in = nullptr; g.ld_bits = 0;
+  g.a_affine = nullptr;
   g.M = (int)M; g.N = (int)N; g.K = (int)K;
   g.lda = (int)lda; g.ldb = (int)ldb; g.ldc = (int)ldc; g.ld_relu = (int)ld_relu;
   g.n_store = (int)(n_store > 0 ? n_store : N);

@@ -296,6 +296,7 @@ struct EncWs {
   double* totals;
   float* scale_shift;
   float *r0, *r1, *r2;
+  bool bn_on_operand;    // BatchNorm + ReLU between a block's two 1x1 convolutions applied on the second one's operand
   const porl_fasternet_t* net;
   porl_stream_t stream;
 };
@@ -317,7 +318,21 @@ int conv1x1(porl_ctx* ctx, const float* A, int64_t rows, int K, const float* W, 
   return launch_gemm(ctx, true, true, gb, st);
 }
 
-int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, const porl_bn_t& bn, int relu, cudaStream_t st) {
+// 1x1 convolution whose A operand is read through the BatchNorm + ReLU of the layer before: affine = scale | shift per
+// input channel (w.scale_shift as bn_finalize_kernel leaves it), applied by the contraction's operand splitters
+int conv1x1_affine(porl_ctx* ctx, const float* A, int64_t rows, int K, const float* W, int N, float* C, int64_t ldc,
+                   const float* affine, cudaStream_t st) {
+  GemmBatch gb;
+  gb.n_groups = 1;
+  gb.splits = 1;
+  conv1x1_group(gb.g[0], A, rows, K, W, N, C, ldc, nullptr, 0);
+  gb.g[0].a_affine = affine;
+  return launch_gemm(ctx, true, true, gb, st);
+}
+
+// apply == 0: only scale / shift are produced (w.scale_shift); the consumer applies them on the way in
+int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, const porl_bn_t& bn, int relu, cudaStream_t st,
+               int apply = 1) {
   PORL_CHECK_ARG(bn.weight && bn.bias && bn.running_mean && bn.running_var, "fasternet: null BatchNorm tensor");
   int64_t G = (rows + 255) / 256;
   if (G > kBnMaxBlocks) G = kBnMaxBlocks;
@@ -341,6 +356,7 @@ int batch_norm(porl_ctx* ctx, const EncWs& w, float* x, int64_t rows, int C, con
   bn_finalize_kernel<<<1, 128, 0, st>>>(w.totals, rows_global, C, bn.weight, bn.bias, bn.running_mean, bn.running_var,
                                         1e-5f, 0.1f, w.scale_shift);
   PORL_LAUNCHED(ctx);
+  if (!apply) return PORL_OK;
   const int64_t n4 = rows * C / 4;
   int64_t grid = (n4 + 255) / 256;
   if (grid > (int64_t)ctx->sm_count * 16) grid = (int64_t)ctx->sm_count * 16;
@@ -365,9 +381,13 @@ int mlp_block(porl_ctx* ctx, const EncWs& w, const porl_fn_block_t& blk, float* 
   }
   int rc = conv1x1(ctx, xm, rows, C, blk.w1, 2 * C, z, 2 * C, nullptr, 0, st);
   if (rc != PORL_OK) return rc;
-  rc = batch_norm(ctx, w, z, rows, 2 * C, blk.bn, 1, st);
+  // BatchNorm + ReLU between the two 1x1 convolutions: statistics of z in one pass; the normalised activation is never
+  // written -- the second contraction reads z through scale / shift / ReLU (same arithmetic as bn_apply_kernel, in its
+  // operand splitters), which saves a read and a write of the widest activation of the block
+  rc = batch_norm(ctx, w, z, rows, 2 * C, blk.bn, 1, st, w.bn_on_operand ? 0 : 1);
   if (rc != PORL_OK) return rc;
-  rc = conv1x1(ctx, z, rows, 2 * C, blk.w2, C, xm, C, nullptr, 0, st);      // branch output reuses xm
+  rc = w.bn_on_operand ? conv1x1_affine(ctx, z, rows, 2 * C, blk.w2, C, xm, C, w.scale_shift, st)
+                       : conv1x1(ctx, z, rows, 2 * C, blk.w2, C, xm, C, nullptr, 0, st);      // branch output reuses xm
   if (rc != PORL_OK) return rc;
   const int64_t n4 = rows * C / 4;
   int64_t grid = (n4 + 255) / 256;
@@ -427,6 +447,8 @@ extern "C" int porl_fasternet_forward(porl_ctx_t* ctx, const porl_fasternet_t* n
   w.r0 = workspace + kHdrFloats;
   w.r1 = w.r0 + rows0 * 96;
   w.r2 = w.r1 + rows0 * 96;
+  // PORL_ENC_FUSE_BN=0: BatchNorm apply as a pass of its own (the round-1 form, kept for comparison and the FFMA mode)
+  w.bn_on_operand = ctx->gemm_mode == 1 && !(getenv("PORL_ENC_FUSE_BN") && atoi(getenv("PORL_ENC_FUSE_BN")) == 0);
 
   // patch embedding straight from the scan (costmap never materialised) + BatchNorm
   {

@@ -28,6 +28,8 @@ struct GemmGroup {
   uint32_t* bits_out;     // tcgen05 path, epilogue 1: (M, ld_bits) words, bit j of word w = C[m, 32 w + j] > 0, or null
   const uint32_t* bits_in;  // tcgen05 path: ReLU mask as such bits (takes precedence over relu_src), or null
   int ld_bits;            // words per row, a multiple of 4 (rows are read with one 16-byte load per 128-column tile)
+  // tcgen05 path: BatchNorm + ReLU of the layer that produced A, applied on the way in (encoders)
+  const float* a_affine;  // (2, K): A is read as relu(A * a_affine[k] + a_affine[K + k]) (K-major A, K % 32 == 0), or null
   int M, N, K;
   int lda, ldb, ldc, ld_relu, ldct;
   int n_store;            // >= N; columns N..n_store-1 are written as zeros

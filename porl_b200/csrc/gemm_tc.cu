@@ -58,6 +58,7 @@ struct TcCfg {
   static constexpr int NUM_BARS = 3 * STAGES + 2 * NBUF + 1;   // + phase_go (grid barrier passed: producer may load)
   static constexpr int STAGING_BYTES = 2 * TC_TILE_BYTES;   // epilogue: two 128 x 32 fp32 slabs for the TMA stores of C
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + STAGING_BYTES + 256 /*barriers*/ + 512 /*bias*/;
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory per CTA");
   static constexpr int TMEM_COLS = 512;
 };
 constexpr int TC_SPLIT_WARP0 = 2, TC_EPI_WARP0 = 8;
@@ -545,15 +546,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             tc_fence_before();
           }
         } else {
-          const float4* src = reinterpret_cast<const float4*>(stage);
+          float4* src = reinterpret_cast<float4*>(stage);
           float4* dst = reinterpret_cast<float4*>(stage + C::A_LO_OFF);
           // raw A and raw B are adjacent (pair mode: only the first 64 rows of the B region are staged)
           constexpr int RAW16 = (int)(TC_TILE_BYTES + B_BYTES) / 16;
+          // BatchNorm + ReLU of the layer that produced A, applied on the way in (a_affine: scale | shift per k): the A
+          // tile is rewritten in place as relu(a * scale[k] + shift[k]) -- the arithmetic of bn_apply_kernel -- before
+          // its lo plane is taken.  K-major A only: 16-byte slot c of row r holds k = 4 * (c ^ (r & 7)) .. + 3.
+          // A thread's slots e = t + 192 i all hold the SAME four k (192 = 24 rows x 8 slots: slot index and row & 7 do
+          // not change with i), so one scale and one shift vector per k-block serve all of its elements.
+          const float* const aff = P.ph[p].batch.g[w.g].a_affine;
+          float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (aff != nullptr) {
+            static_assert(TC_SPLIT_THREADS % 64 == 0, "slot and row & 7 of a thread's elements must not depend on i");
+            const int k4 = kb * (TC_BK / 4) + ((t & 7) ^ ((t >> 3) & 7));
+            sc = __ldg(reinterpret_cast<const float4*>(aff) + k4);
+            sh = __ldg(reinterpret_cast<const float4*>(aff + P.ph[p].batch.g[w.g].K) + k4);
+          }
 #pragma unroll
           for (int i = 0; i < (RAW16 + TC_SPLIT_THREADS - 1) / TC_SPLIT_THREADS; ++i) {
             const int e = t + i * TC_SPLIT_THREADS;
             if (e < RAW16 && three) {
-              const float4 v = src[e];
+              float4 v = src[e];
+              if (aff != nullptr && e < TC_TILE_BYTES / 16) {
+                v.x = fmaxf(fmaf(v.x, sc.x, sh.x), 0.f); v.y = fmaxf(fmaf(v.y, sc.y, sh.y), 0.f);
+                v.z = fmaxf(fmaf(v.z, sc.z, sh.z), 0.f); v.w = fmaxf(fmaf(v.w, sc.w, sh.w), 0.f);
+                src[e] = v;
+              }
               dst[e] = make_float4(split_lo(v.x), split_lo(v.y), split_lo(v.z), split_lo(v.w));
             }
           }
@@ -949,7 +968,7 @@ static int make_map(CUtensorMap* out, const float* ptr, int k_extent, int rows, 
 }
 
 bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor) {
-  (void)a_kmajor; (void)b_kmajor;      // both operand forms are served: K-major and MN-major shared-memory descriptors
+  (void)b_kmajor;      // both operand forms are served: K-major and MN-major shared-memory descriptors
   if (g.A_lo || g.B_lo || g.C_lo || g.colsum) return false;
   if (g.N < 32 || g.K < 32 || g.M < 32) return false;
   if ((double)g.M * g.N * g.K < (double)(1 << 20)) return false;       // tiny problems: FFMA kernel
@@ -959,6 +978,7 @@ bool gemm_tc_eligible(const GemmGroup& g, bool a_kmajor, bool b_kmajor) {
   if (g.bias && !aligned16(g.bias)) return false;                        // read as float4 through pad4(N)
   if (g.relu_src && ((g.ld_relu & 3) || g.ld_relu < g.n_store || !aligned16(g.relu_src))) return false;
   if (g.Ct && g.ldct < g.M) return false;
+  if (g.a_affine && (!a_kmajor || (g.K % TC_BK) != 0 || !aligned16(g.a_affine))) return false;
   return true;
 }
 
@@ -1005,7 +1025,12 @@ int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaS
   bool pair = ctx->tc_a_in_tmem == 2 && !any_mn && n_phases == 1;
   for (int i = 0; i < specs[0].batch->n_groups && pair; ++i)
     if (specs[0].batch->g[i].M < 2 * TC_BM) pair = false;
-  const bool atm = ctx->tc_a_in_tmem == 1 && !any_mn && n_phases == 1;
+  bool bn_fused = false;             // operand affine: implemented in the all-in-shared-memory variant
+  for (int p = 0; p < n_phases; ++p)
+    for (int i = 0; i < specs[p].batch->n_groups; ++i)
+      bn_fused = bn_fused || specs[p].batch->g[i].a_affine;
+  if (bn_fused) pair = false;
+  const bool atm = ctx->tc_a_in_tmem == 1 && !any_mn && n_phases == 1 && !bn_fused;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
   P.n_phases = n_phases;
   static bool configured = false;

@@ -251,6 +251,7 @@ static void clear_group(GemmGroup& g) {
   g.bits_out = nullptr;
   g.bits_in = nullptr;
   g.ld_bits = 0;
+  g.a_affine = nullptr;
   g.M = g.N = g.K = 0;
   g.lda = g.ldb = g.ldc = g.ld_relu = g.ldct = 0;
   g.n_store = 0;

@@ -192,6 +192,44 @@ def test_cuda_fasternet_larger_batch_vs_oracle_and_determinism():
     assert rel(outs[0].cpu(), f64) < FEAT_TOL, rel(outs[0].cpu(), f64)
 
 
+@pytest.mark.gpu
+def test_cuda_fasternet_fused_batchnorm_matches_separate_passes(monkeypatch):
+    """BatchNorm scale / shift / ReLU applied on the consuming contraction's operand (the default in tensor-core mode)
+    against the same encoder with the apply as a pass of its own (PORL_ENC_FUSE_BN=0): the same arithmetic per element in
+    the same order, so features and running statistics must be BITWISE equal; both agree with the fp64 oracle."""
+    from porl_b200 import _C
+    from porl_b200.agent.fasternet import FasterNet
+    from oracle import synth
+    B = 40                                           # 40 * 5760 rows: whole 128-row tiles plus a ragged last one per layer
+    st = torch.from_numpy(synth.laser_rows(B, 362, 78)[:, :362].copy())
+    sd = encoder.det_encoder_state_dict(10)
+    ctx = _C.context(torch.device("cuda"))
+    ctx.set_gemm_mode(1)
+    try:
+        outs, stats, launches = [], [], []
+        for fuse in ("1", "0"):
+            monkeypatch.setenv("PORL_ENC_FUSE_BN", fuse)     # read by every porl_fasternet_forward call
+            net = FasterNet(3, 256)
+            net.load_state_dict(encoder.order_like({k: v.clone() for k, v in sd.items()}, net.state_dict().keys()))
+            net = net.cuda()
+            torch.manual_seed(3)
+            keeps = net._keep_scales(st.cuda(), B)
+            l0 = ctx.launches
+            outs.append(net(st.cuda(), keep_scales=keeps))
+            torch.cuda.synchronize()
+            launches.append(ctx.launches - l0)
+            stats.append({k: v.clone() for k, v in net.state_dict().items() if "running" in k})
+    finally:
+        ctx.set_gemm_mode(0)
+    assert launches[0] == launches[1] - 3, launches          # three bn_apply passes gone (one per block)
+    assert torch.equal(outs[0], outs[1]), rel(outs[0].cpu(), outs[1].cpu())
+    for k in stats[0]:
+        assert torch.equal(stats[0][k], stats[1][k]), k
+    sd64 = {k: (v.double() if v.is_floating_point() else v.clone()) for k, v in sd.items()}
+    f64 = encoder.fasternet_forward(sd64, st.clone(), [None if k is None else k.cpu() for k in keeps])
+    assert rel(outs[0].cpu(), f64) < FEAT_TOL, rel(outs[0].cpu(), f64)
+
+
 # ------------------------------------------------------------------------------------------ GPU: agents with a backbone
 class OracleBackbone:
     """The oracle's encoder as the callable the oracle agents expect (mutates its input, consumes one set of
