@@ -161,85 +161,125 @@ __global__ void __launch_bounds__(256) residual_kernel(float* __restrict__ x, co
 
 // ------------------------------------------------------------------------------------ partial 3x3 convolution
 // Partial_conv3.forward_split_cat (fasternet.py:131-138) on an NHWC matrix: channels [0, c) of the output are
-// the zero-padded 3x3 convolution of channels [0, c) of the input, channels [c, C) are copied.
-// grid (tiles_w, tiles_h, B), 128 threads; one block = 16 x 16 pixels, one thread = pixels (ty, tx) and
-// (ty + 8, tx) with all c output channels in registers.  Input channels go through shared memory 8 at a
-// time (18 x 18 halo tile, pixel stride 9 floats: conflict-free) together with the matching weight slab.
-// wk: (9, c, c) = [tap = kh * 3 + kw][ci][co].
-template <int CC>
+// the zero-padded 3x3 convolution of channels [0, c) of the input (this kernel), channels [c, C) are copied
+// (copy_channels_kernel).  FFMA-bound (2 * 9 * c^2 flop per pixel against 8 C bytes; a tensor-core form would waste 3/4 of an N = 128 MMA on
+// N = c <= 48 and costs the same).  grid (tiles_w, tiles_h, B), 128 threads = 16 x 8; one block = a 16-wide,
+// 8 * PIX-tall pixel tile, one thread = PIX pixels (rows ty + 8 j) with all c output channels in registers: per (tap,
+// input channel) PIX activation loads and c / 4 broadcast weight loads feed PIX * c FMAs (10 loads per 96 FMAs at c = 24,
+// PIX = 4; the round-1 kernel had 16).  Input channels go through shared memory CI at a time (halo tile, pixel stride
+// CI + 1 floats: conflict-free) together with the matching weight slab.  wk: (9, c, c) = [tap = kh * 3 + kw][ci][co].
+template <int CC, int PIX, int CI>
+struct PconvCfg {
+  static constexpr int TH = 8 * PIX, XS = CI + 1, HALO = (TH + 2) * 18;
+  static constexpr size_t SMEM = ((size_t)HALO * XS + 9 * CI * CC) * sizeof(float);
+};
+
+template <int CC, int PIX, int CI>
 __global__ void __launch_bounds__(128) pconv3_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                      const float* __restrict__ wk, int H, int W, int C) {
-  constexpr int CI = 8, XS = CI + 1;
-  __shared__ float xs[18 * 18 * XS];
-  __shared__ __align__(16) float ws[9 * CI * CC];
+  using Cfg = PconvCfg<CC, PIX, CI>;
+  constexpr int TH = Cfg::TH, XS = Cfg::XS, HALO = Cfg::HALO;
+  static_assert(CC % CI == 0 && CI % 4 == 0 && CC % 4 == 0, "channel blocking");
+  extern __shared__ __align__(16) float psm[];
+  float* const ws = psm;                          // [9][CI][CC], 16-byte aligned rows
+  float* const xs = psm + 9 * CI * CC;            // [HALO][XS]
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;       // ty 0..7
-  const int w0 = blockIdx.x * 16, h0 = blockIdx.y * 16, b = blockIdx.z;
+  const int w0 = blockIdx.x * 16, h0 = blockIdx.y * TH, b = blockIdx.z;
   const float* xb = x + (size_t)b * H * W * C;
   float* yb = y + (size_t)b * H * W * C;
-  float acc0[CC], acc1[CC];
+  float acc[PIX][CC];
 #pragma unroll
-  for (int j = 0; j < CC; ++j) acc0[j] = acc1[j] = 0.f;
+  for (int j = 0; j < PIX; ++j)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) acc[j][c] = 0.f;
 
   for (int ci0 = 0; ci0 < CC; ci0 += CI) {
     __syncthreads();
-    for (int i = threadIdx.x; i < 18 * 18 * 2; i += 128) {       // halo pixels x two float4 halves
-      const int pix = i >> 1, half = i & 1;
-      const int hh = h0 - 1 + pix / 18, ww = w0 - 1 + pix % 18;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (hh >= 0 && hh < H && ww >= 0 && ww < W)
-        v = *reinterpret_cast<const float4*>(xb + ((size_t)hh * W + ww) * C + ci0 + 4 * half);
-      float* d = xs + pix * XS + 4 * half;
-      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    // halo pixels x float4 groups of the channel slab, kLd global loads in flight per thread (one at a time left the
+    // block waiting ~30 round trips to L2 / HBM per stage: `long scoreboard` was 3 of every 4 stall cycles, ncu)
+    constexpr int kLd = 8, kHaloVec = HALO * (CI / 4);
+    for (int i0 = threadIdx.x; i0 < kHaloVec; i0 += 128 * kLd) {
+      float4 v[kLd];
+#pragma unroll
+      for (int u = 0; u < kLd; ++u) {
+        const int i = i0 + 128 * u;
+        const int pix = i / (CI / 4), q4 = i % (CI / 4);
+        const int hh = h0 - 1 + pix / 18, ww = w0 - 1 + pix % 18;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < kHaloVec && hh >= 0 && hh < H && ww >= 0 && ww < W)
+          v[u] = *reinterpret_cast<const float4*>(xb + ((size_t)hh * W + ww) * C + ci0 + 4 * q4);
+      }
+#pragma unroll
+      for (int u = 0; u < kLd; ++u) {
+        const int i = i0 + 128 * u;
+        if (i < kHaloVec) {
+          float* d = xs + (i / (CI / 4)) * XS + 4 * (i % (CI / 4));
+          d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+        }
+      }
     }
+#pragma unroll 4
     for (int i = threadIdx.x; i < 9 * CI * CC / 4; i += 128) {
       const int tap = i / (CI * CC / 4), rem = i % (CI * CC / 4);
-      reinterpret_cast<float4*>(ws)[i] =
-          *reinterpret_cast<const float4*>(wk + ((size_t)tap * CC + ci0) * CC + 4 * rem);
+      reinterpret_cast<float4*>(ws)[i] = __ldg(reinterpret_cast<const float4*>(wk + ((size_t)tap * CC + ci0) * CC + 4 * rem));
     }
     __syncthreads();
 #pragma unroll 1
     for (int tap = 0; tap < 9; ++tap) {
       const int dy = tap / 3, dx = tap % 3;
       const float* p0 = xs + ((ty + dy) * 18 + tx + dx) * XS;
-      const float* p1 = p0 + 8 * 18 * XS;
       const float* wt = ws + tap * CI * CC;
-#pragma unroll
+#pragma unroll 4
       for (int ci = 0; ci < CI; ++ci) {
-        const float a0 = p0[ci], a1 = p1[ci];
+        float a[PIX];
+#pragma unroll
+        for (int j = 0; j < PIX; ++j) a[j] = p0[j * 8 * 18 * XS + ci];
 #pragma unroll
         for (int co = 0; co < CC; co += 4) {
           const float4 wv = *reinterpret_cast<const float4*>(wt + ci * CC + co);
-          acc0[co] = fmaf(a0, wv.x, acc0[co]); acc0[co + 1] = fmaf(a0, wv.y, acc0[co + 1]);
-          acc0[co + 2] = fmaf(a0, wv.z, acc0[co + 2]); acc0[co + 3] = fmaf(a0, wv.w, acc0[co + 3]);
-          acc1[co] = fmaf(a1, wv.x, acc1[co]); acc1[co + 1] = fmaf(a1, wv.y, acc1[co + 1]);
-          acc1[co + 2] = fmaf(a1, wv.z, acc1[co + 2]); acc1[co + 3] = fmaf(a1, wv.w, acc1[co + 3]);
+#pragma unroll
+          for (int j = 0; j < PIX; ++j) {
+            acc[j][co] = fmaf(a[j], wv.x, acc[j][co]); acc[j][co + 1] = fmaf(a[j], wv.y, acc[j][co + 1]);
+            acc[j][co + 2] = fmaf(a[j], wv.z, acc[j][co + 2]); acc[j][co + 3] = fmaf(a[j], wv.w, acc[j][co + 3]);
+          }
         }
       }
     }
   }
   const int w = w0 + tx;
   if (w < W) {
-    const int ha = h0 + ty, hb = h0 + ty + 8;
-    if (ha < H) {
-      float4* o = reinterpret_cast<float4*>(yb + ((size_t)ha * W + w) * C);
 #pragma unroll
-      for (int co = 0; co < CC; co += 4) o[co >> 2] = make_float4(acc0[co], acc0[co + 1], acc0[co + 2], acc0[co + 3]);
-    }
-    if (hb < H) {
-      float4* o = reinterpret_cast<float4*>(yb + ((size_t)hb * W + w) * C);
+    for (int j = 0; j < PIX; ++j) {
+      const int hh = h0 + ty + 8 * j;
+      if (hh < H) {
+        float4* o = reinterpret_cast<float4*>(yb + ((size_t)hh * W + w) * C);
 #pragma unroll
-      for (int co = 0; co < CC; co += 4) o[co >> 2] = make_float4(acc1[co], acc1[co + 1], acc1[co + 2], acc1[co + 3]);
+        for (int co = 0; co < CC; co += 4) o[co >> 2] = make_float4(acc[j][co], acc[j][co + 1], acc[j][co + 2], acc[j][co + 3]);
+      }
     }
   }
-  // untouched channels [CC, C): straight copy of the tile
-  const int rest4 = (C - CC) >> 2;
-  for (int i = threadIdx.x; i < 256 * rest4; i += 128) {
-    const int pix = i / rest4, j = i % rest4;
-    const int hh = h0 + (pix >> 4), ww = w0 + (pix & 15);
-    if (hh < H && ww < W) {
-      const size_t off = ((size_t)hh * W + ww) * C + CC + 4 * j;
-      *reinterpret_cast<float4*>(yb + off) = *reinterpret_cast<const float4*>(xb + off);
+}
+
+// channels [c0, C) of every row of x copied to y (the untouched part of Partial_conv3's output): a grid-stride float4
+// copy with eight loads in flight per thread.  Its own launch on purpose: inside the convolution kernel (2-3 blocks of
+// 128 threads per SM, one tile at a time) the copy ran at a third of the HBM rate (`long scoreboard`, ncu).
+__global__ void __launch_bounds__(256) copy_channels_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t rows,
+                                                            int C, int c0) {
+  const int rest4 = (C - c0) >> 2;
+  const int64_t n = rows * rest4, stride = (int64_t)gridDim.x * 256;
+  constexpr int kCp = 8;
+  for (int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += stride * kCp) {
+    float4 v[kCp];
+    int64_t off[kCp];
+#pragma unroll
+    for (int u = 0; u < kCp; ++u) {
+      const int64_t i = i0 + stride * u;
+      off[u] = i < n ? (i / rest4) * C + c0 + 4 * (i % rest4) : -1;
+      if (off[u] >= 0) v[u] = __ldcs(reinterpret_cast<const float4*>(x + off[u]));      // read once here: streaming
     }
+#pragma unroll
+    for (int u = 0; u < kCp; ++u)
+      if (off[u] >= 0) *reinterpret_cast<float4*>(y + off[u]) = v[u];
   }
 }
 
@@ -374,9 +414,30 @@ int mlp_block(porl_ctx* ctx, const EncWs& w, const porl_fn_block_t& blk, float* 
   {
     const double cc = C / 4;
     ProfScope prof(ctx, PORL_CAT_PCONV, (double)rows * 18.0 * cc * cc, st);      // 2 * 9 * (C/4)^2 flop per pixel
-    const dim3 grid((W + 15) / 16, (H + 15) / 16, (unsigned)B);
-    if (C == 96) pconv3_kernel<24><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);
-    else pconv3_kernel<48><<<grid, 128, 0, st>>>(x, xm, blk.pconv_w, H, W, C);
+    // C = 96: 4 pixels x 24 channels per thread, all 24 input channels staged at once (16 x 32 tiles);
+    // C = 192: 2 pixels x 48 channels, input channels 24 at a time (16 x 16 tiles)
+    using K24 = PconvCfg<24, 4, 24>;
+    using K48 = PconvCfg<48, 2, 24>;
+    static bool configured = false;
+    if (!configured) {
+      PORL_CUDA(cudaFuncSetAttribute(pconv3_kernel<24, 4, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K24::SMEM));
+      PORL_CUDA(cudaFuncSetAttribute(pconv3_kernel<48, 2, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K48::SMEM));
+      configured = true;
+    }
+    {
+      const int64_t n4 = rows * (C - C / 4) / 4;
+      int64_t cg = (n4 + 256 * 8 - 1) / (256 * 8);
+      if (cg > (int64_t)ctx->sm_count * 8) cg = (int64_t)ctx->sm_count * 8;
+      copy_channels_kernel<<<(unsigned)cg, 256, 0, st>>>(x, xm, rows, C, C / 4);
+      PORL_LAUNCHED(ctx);
+    }
+    if (C == 96) {
+      const dim3 grid((W + 15) / 16, (H + K24::TH - 1) / K24::TH, (unsigned)B);
+      pconv3_kernel<24, 4, 24><<<grid, 128, K24::SMEM, st>>>(x, xm, blk.pconv_w, H, W, C);
+    } else {
+      const dim3 grid((W + 15) / 16, (H + K48::TH - 1) / K48::TH, (unsigned)B);
+      pconv3_kernel<48, 2, 24><<<grid, 128, K48::SMEM, st>>>(x, xm, blk.pconv_w, H, W, C);
+    }
     PORL_LAUNCHED(ctx);
   }
   int rc = conv1x1(ctx, xm, rows, C, blk.w1, 2 * C, z, 2 * C, nullptr, 0, st);
