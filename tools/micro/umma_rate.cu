@@ -259,23 +259,95 @@ __global__ void __launch_bounds__(384, 1) umma_kernel(Cfg c, long long* out) {
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
 }
 
+// The contraction kernel's issue pattern with nothing else in the loop: compile-time shape, 12 MMAs (lo*hi, hi*lo, hi*hi
+// over four 8-wide k-steps) + one commit per k-block, at most two k-blocks in flight, converged issuing warp.  This is
+// what --json reports: the rate of the MMA form itself.
+template <int N, bool TS>
+__global__ void __launch_bounds__(128, 1) umma_lean_kernel(int iters, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw), base = (raw + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(base_ptr + kStages * kStage);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  const uint32_t bar0 = smem_u32(bars);
+  for (int i = threadIdx.x; i < kStages * kStage / 4; i += blockDim.x) reinterpret_cast<float*>(base_ptr)[i] = 1.0f;
+  if (threadIdx.x == 0) {
+    for (int b = 0; b < 8; ++b) mbar_init(bar0 + 8u * b, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  if (warp_u == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (warp_u == 1) {
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(tmem_slot), 0);
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    constexpr uint32_t b_lo_off = (N == 256 ? 16384u : 32768u) >> 4;
+    const long long t0 = clock64();
+    for (int kb = 0; kb < iters; ++kb) {
+      if (kb >= 2) mbar_wait(bar0 + 8u * ((kb - 2) & 7), (uint32_t)(((kb - 2) >> 3) & 1));
+      const uint32_t st = base + (uint32_t)(kb % kStages) * kStage;
+      const uint64_t a_hi = smem_desc(st), b_hi = smem_desc(st + 16384u);
+      const uint32_t d = tmem_base + (uint32_t)((kb & 1) * (N == 256 ? 0 : 128));
+      const uint32_t at = tmem_base + 256u + (uint32_t)((kb & 3) * 64);
+      if (leader) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          if (TS) mma_ts(d, at + 32u + 8u * ks, b_hi + 2u * ks, idesc, ks ? 1u : 0u);
+          else mma_ss(d, a_hi + (32768u >> 4) + 2u * ks, b_hi + 2u * ks, idesc, ks ? 1u : 0u);
+          if (TS) mma_ts(d, at + 8u * ks, b_hi + b_lo_off + 2u * ks, idesc, 1u);
+          else mma_ss(d, a_hi + 2u * ks, b_hi + b_lo_off + 2u * ks, idesc, 1u);
+        }
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          if (TS) mma_ts(d, at + 8u * ks, b_hi + 2u * ks, idesc, 1u);
+          else mma_ss(d, a_hi + 2u * ks, b_hi + 2u * ks, idesc, 1u);
+        }
+        tc_commit(bar0 + 8u * (kb & 7));
+      }
+      __syncwarp();
+    }
+    for (int kb = (iters > 2 ? iters - 2 : 0); kb < iters; ++kb) mbar_wait(bar0 + 8u * (kb & 7), (uint32_t)((kb >> 3) & 1));
+    const long long t1 = clock64();
+    if (threadIdx.x == 32) out[blockIdx.x * 4] = t1 - t0;
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp_u == 1) {
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+template <int N, bool TS>
+static double lean_clk_per_mma(long long* out) {
+  const int iters = 1000;
+  cudaFuncSetAttribute(umma_lean_kernel<N, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+  for (int rep = 0; rep < 2; ++rep) umma_lean_kernel<N, TS><<<148, 128, kSmem>>>(iters, out);
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1.0;
+  long long h[148 * 4];
+  cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
+  double clk = 0;
+  for (int i = 0; i < 148; ++i) clk += (double)h[4 * i] / 148;
+  return clk / iters / 12.0;
+}
+
 // --json: the four forms the bench quotes (12 MMAs + one commit per k-block, converged issuer), as one JSON line
 static int quick_json(long long* out) {
-  const Cfg cfgs[] = {{128, 0, 1, 12, 0, 0, 2, 1000, 0, 0, 1, 1, 1}, {256, 0, 1, 12, 0, 0, 2, 1000, 0, 0, 1, 1, 1},
-                      {128, 1, 2, 12, 0, 0, 2, 1000, 0, 0, 1, 1, 1}, {256, 1, 1, 12, 0, 0, 2, 1000, 0, 0, 1, 1, 1}};
+  const double v[4] = {lean_clk_per_mma<128, false>(out), lean_clk_per_mma<256, false>(out), lean_clk_per_mma<128, true>(out),
+                       lean_clk_per_mma<256, true>(out)};
   const char* names[] = {"ss_n128", "ss_n256", "ts_n128", "ts_n256"};
+  const int n[4] = {128, 256, 128, 256};
   printf("{");
   for (int k = 0; k < 4; ++k) {
-    const Cfg& c = cfgs[k];
-    for (int rep = 0; rep < 2; ++rep) umma_kernel<<<148, 384, kSmem>>>(c, out);
-    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
-    long long h[148 * 4];
-    cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
-    double clk = 0;
-    for (int i = 0; i < 148; ++i) clk += (double)h[4 * i] / 148;
-    const double per_mma = clk / c.iters / c.mmas;
-    printf("%s\"%s_clk_per_mma\": %.1f, \"%s_fma_per_clk_sm\": %.0f", k ? ", " : "", names[k], per_mma, names[k],
-           128.0 * c.n * 8 / per_mma);
+    if (v[k] <= 0) return 1;
+    printf("%s\"%s_clk_per_mma\": %.1f, \"%s_fma_per_clk_sm\": %.0f", k ? ", " : "", names[k], v[k], names[k], 128.0 * n[k] * 8 / v[k]);
   }
   printf("}\n");
   return 0;
