@@ -118,7 +118,10 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   ctx->sem = nullptr;
   ctx->partials = nullptr;
   ctx->counters = nullptr;
-  ctx->tc_chunk_kb = 1;
+  {
+    const char* e = getenv("PORL_TC_CHUNK");            // k-blocks per TMEM accumulation chunk (porl_ctx_set_tc_chunk)
+    ctx->tc_chunk_kb = e && atoi(e) > 0 ? atoi(e) : 1;
+  }
   ctx->tc_terms = 3;
   {
     const char* e = getenv("PORL_TC_PHASES");
@@ -126,7 +129,7 @@ extern "C" int porl_ctx_create(porl_ctx_t** out, int device) {
   }
   {
     const char* e = getenv("PORL_TC_A_IN_TMEM");
-    ctx->tc_a_in_tmem = e ? atoi(e) : 0;
+    ctx->tc_a_in_tmem = e ? atoi(e) : 1;      // A operand through tensor memory wherever A is K-major (gemm_tc.cu)
     const char* pe = getenv("PORL_PDL");
     ctx->pdl = pe ? (atoi(pe) != 0) : 1;
   }

@@ -164,6 +164,13 @@ __device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, uint64_t a_des
       "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// one lane of a converged warp (elect.sync): the compiler knows the guarded block runs on exactly one thread and keeps
+// warp-uniform operands of the tcgen05 instructions inside it in uniform registers
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred px;\n\telect.sync _|px, 0xffffffff;\n\t@px mov.s32 %0, 1;\n\t}" : "+r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -299,7 +306,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   auto tmem_empty = [&](int b) { return bar0 + 8u * (3 * TC_STAGES + TC_NBUF + b); };
   const uint32_t phase_go = bar0 + 8u * (3 * TC_STAGES + 2 * TC_NBUF);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: provably warp-uniform for the compiler, so that the role branches below are uniform
+  // control flow and a role's warp-uniform values (descriptors, barrier addresses) can live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // CTA of the pair; rank 0 leads
   const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int unit_stride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
@@ -406,7 +415,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (pair mode: the leader CTA only) =====================
-    if (lane == 0 && rank == 0) {
+    // The WHOLE warp runs the loops below in lockstep (uniform control flow, every lane waits on the barriers) and one
+    // elected lane issues.  With a single-thread role (`if (lane == 0)`) the compiler treats every operand as
+    // divergent: each tcgen05.mma became an ELECT / 7 x R2UR / branch loop of ~28 instructions and the issue path, not
+    // the tensor pipe, set the pace -- 137 clk per MMA where the pipe needs 64 (tools/micro/umma_rate.cu measures
+    // 67.6 clk for this exact stream issued this way, 146-226 for the divergent form).
+    if (rank == 0) {
+      const bool leader = elect_one();
+      const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
       // instruction descriptor: D fp32, A/B tf32, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
       int it = 0, chunk = 0;
       long long w_te = 0, w_sd = 0;
@@ -433,9 +449,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           mbar_wait(tmem_empty(buf), ((uint32_t)(chunk / TC_NBUF) & 1u) ^ 1u);
           if (dbg) w_te += clock64() - tw0;
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + (uint32_t)(buf * TC_BN);
+          const uint32_t d_tmem = tmem_base_u + (uint32_t)(buf * TC_BN);
           const int nk = (w.kb1 - kb) < chunk_kb ? (w.kb1 - kb) : chunk_kb;
-          uint32_t acc = 0;
           for (int j = 0; j < nk; ++j, ++it) {
             const int s = it % TC_STAGES;
             const uint32_t ph = (uint32_t)(it / TC_STAGES) & 1u;
@@ -443,59 +458,62 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             mbar_wait(split_done(s), ph);
             if (dbg) w_sd += clock64() - tw1;
             tc_fence_after();
+            const uint32_t acc0 = j == 0 ? 0u : 1u;           // the chunk's first MMA starts a fresh accumulation
             const uint64_t st16 = (uint64_t)((uint32_t)s * (TC_STAGE_BYTES >> 4));
             const uint64_t b_hi = tmpl_b + st16;
             const uint64_t b_lo = b_hi + (uint64_t)((C::B_LO_OFF - TC_TILE_BYTES) >> 4);
-            // small terms first (they meet the smallest accumulator), then the hi*hi terms
-            if (ATM) {
-              const uint32_t a_hi = tmem_base + (uint32_t)(TC_ACC_COLS + s * 64), a_lo = a_hi + 32u;
+            if (leader) {
+              // small terms first (they meet the smallest accumulator), then the hi*hi terms
+              if (ATM) {
+                const uint32_t a_hi = tmem_base_u + (uint32_t)(TC_ACC_COLS + s * 64), a_lo = a_hi + 32u;
 #pragma unroll
-              for (int ks = 0; ks < TC_BK / 8; ++ks) {
-                const uint64_t o = b_step * ks;
-                tc_mma_tf32_ts(d_tmem, a_lo + 8u * ks, b_hi + o, idesc, acc);
-                acc = 1;
-                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_lo + o, idesc, 1u);
-              }
+                for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                  const uint64_t o = b_step * ks;
+                  tc_mma_tf32_ts(d_tmem, a_lo + 8u * ks, b_hi + o, idesc, ks == 0 ? acc0 : 1u);
+                  tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_lo + o, idesc, 1u);
+                }
 #pragma unroll
-              for (int ks = 0; ks < TC_BK / 8; ++ks)
-                tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + b_step * ks, idesc, 1u);
-            } else {
-              const uint64_t a_hi = tmpl_a + st16;
-              const uint64_t a_lo = a_hi + (uint64_t)(C::A_LO_OFF >> 4);
-              if (three) {
+                for (int ks = 0; ks < TC_BK / 8; ++ks)
+                  tc_mma_tf32_ts(d_tmem, a_hi + 8u * ks, b_hi + b_step * ks, idesc, 1u);
+              } else {
+                const uint64_t a_hi = tmpl_a + st16;
+                const uint64_t a_lo = a_hi + (uint64_t)(C::A_LO_OFF >> 4);
+                if (three) {
+#pragma unroll
+                  for (int ks = 0; ks < TC_BK / 8; ++ks) {
+                    const uint64_t oa = a_step * ks, ob = b_step * ks;
+                    if (PAIR) {
+                      tc_mma_tf32_pair(d_tmem, a_lo + oa, b_hi + ob, idesc, ks == 0 ? acc0 : 1u);
+                      tc_mma_tf32_pair(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
+                    } else {
+                      tc_mma_tf32(d_tmem, a_lo + oa, b_hi + ob, idesc, ks == 0 ? acc0 : 1u);
+                      tc_mma_tf32(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
+                    }
+                  }
+                }
 #pragma unroll
                 for (int ks = 0; ks < TC_BK / 8; ++ks) {
                   const uint64_t oa = a_step * ks, ob = b_step * ks;
-                  if (PAIR) {
-                    tc_mma_tf32_pair(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
-                    acc = 1;
-                    tc_mma_tf32_pair(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
-                  } else {
-                    tc_mma_tf32(d_tmem, a_lo + oa, b_hi + ob, idesc, acc);
-                    acc = 1;
-                    tc_mma_tf32(d_tmem, a_hi + oa, b_lo + ob, idesc, 1u);
-                  }
+                  const uint32_t acc = (three || ks != 0) ? 1u : acc0;
+                  if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
+                  else tc_mma_tf32(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
                 }
               }
-#pragma unroll
-              for (int ks = 0; ks < TC_BK / 8; ++ks) {
-                const uint64_t oa = a_step * ks, ob = b_step * ks;
-                if (PAIR) tc_mma_tf32_pair(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
-                else tc_mma_tf32(d_tmem, a_hi + oa, b_hi + ob, idesc, acc);
-                acc = 1;
+              if (PAIR) tc_commit_pair(empty_bar(s));   // frees the stage (in both CTAs) once these MMAs have read it
+              else tc_commit(empty_bar(s));
+              if (j == nk - 1) {                        // chunk accumulator complete (pair mode: both CTAs' halves)
+                if (PAIR) tc_commit_pair(tmem_full(buf));
+                else tc_commit(tmem_full(buf));
               }
             }
-            if (PAIR) tc_commit_pair(empty_bar(s));   // frees the stage (in both CTAs) once these MMAs have read it
-            else tc_commit(empty_bar(s));
+            __syncwarp();
           }
-          if (PAIR) tc_commit_pair(tmem_full(buf));   // chunk accumulator complete (both CTAs' halves)
-          else tc_commit(tmem_full(buf));
           ++chunk;
           kb += nk;
         }
       }
       }
-      if (dbg) { dbg[6] = gtime(); dbg[13] = (unsigned long long)w_sd; dbg[14] = (unsigned long long)w_te; }
+      if (dbg && leader) { dbg[6] = gtime(); dbg[13] = (unsigned long long)w_sd; dbg[14] = (unsigned long long)w_te; }
     }
   } else if (warp < TC_EPI_WARP0) {
     // ===================== splitters: lo = RN_tf32(x - trunc_tf32(x)) =====================
@@ -1030,7 +1048,11 @@ int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaS
     for (int i = 0; i < specs[p].batch->n_groups; ++i)
       bn_fused = bn_fused || specs[p].batch->g[i].a_affine;
   if (bn_fused) pair = false;
-  const bool atm = ctx->tc_a_in_tmem == 1 && !any_mn && n_phases == 1 && !bn_fused;
+  // A in tensor memory: the splitters un-swizzle K-major A rows, so every phase's A must be K-major; B may be either
+  // form (its split is a flat pass over the tile and the MMA's B descriptor carries the layout)
+  bool any_a_mn = false;
+  for (int p = 0; p < n_phases; ++p) any_a_mn = any_a_mn || !specs[p].a_kmajor;
+  const bool atm = ctx->tc_a_in_tmem == 1 && !any_a_mn && n_phases == 1 && !bn_fused;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
   P.n_phases = n_phases;
   static bool configured = false;

@@ -4,6 +4,8 @@ checked at the tolerance written next to each assert."""
 import ctypes as C
 import math
 
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -165,7 +167,7 @@ def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
             assert ctx.tc_launches == before + 1
         assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
     finally:
-        ctx.set_tc_variant(0)
+        ctx.set_tc_variant(int(os.environ.get("PORL_TC_A_IN_TMEM", "1")))      # the library's default
         ctx.set_gemm_mode(0)
 
 

@@ -40,7 +40,7 @@ def acc():
         Ad, Bd = A.to(dev), B.to(dev)
         scale = float(ref.abs().mean())
         rows = []
-        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 1, 1), (1, 1, 2), (1, 64, 0)):
+        for mode, chunk, atm in ((0, 1, 0), (1, 1, 0), (1, 1, 1), (1, 1, 2), (1, 2, 1), (1, 4, 1), (1, 64, 0)):
             ctx.set_gemm_mode(mode)
             ctx.set_tc_chunk(chunk)
             ctx.set_tc_variant(atm)
