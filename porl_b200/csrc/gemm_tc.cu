@@ -369,7 +369,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // like the MMA issuer: the whole warp runs the loops, one elected lane issues (uniform-register tensor-map
+    // addresses and coordinates instead of an R2UR loop per copy -- up to eight copies per k-block with MN-major operands)
+    {
+      const bool leader = elect_one();
       int it = 0;
       long long w_prod = 0;
       TcUnit w;
@@ -390,28 +393,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           const long long tw = dbg ? clock64() : 0;
           mbar_wait(empty_bar(s), ph ^ 1u);
           if (dbg) w_prod += clock64() - tw;
-          mbar_expect_tx(raw_full(s), TC_TILE_BYTES + B_BYTES);
           const uint32_t st = base + (uint32_t)s * TC_STAGE_BYTES;
-          if (F.a_mn) {         // MN-major: four {32 m, 32 k} boxes, 4096 bytes apart
+          if (leader) {
+            mbar_expect_tx(raw_full(s), TC_TILE_BYTES + B_BYTES);
+            if (F.a_mn) {         // MN-major: four {32 m, 32 k} boxes, 4096 bytes apart
 #pragma unroll
-            for (int i = 0; i < 4; ++i) tma_load_2d(st + 4096u * i, &F.mapA[w.g], raw_full(s), w.m0 + 32 * i, kb * TC_BK);
-          } else {
-            tma_load_2d(st, &F.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
-          }
-          if (F.b_mn) {
+              for (int i = 0; i < 4; ++i) tma_load_2d(st + 4096u * i, &F.mapA[w.g], raw_full(s), w.m0 + 32 * i, kb * TC_BK);
+            } else {
+              tma_load_2d(st, &F.mapA[w.g], raw_full(s), kb * TC_BK, w.m0 + (int)rank * TC_BM);
+            }
+            if (F.b_mn) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              tma_load_2d(st + TC_TILE_BYTES + 4096u * i, &F.mapB[w.g], raw_full(s), w.n0 + 32 * i, kb * TC_BK);
-          } else if (PAIR) {
-            tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
-          } else {
-            tma_load_2d(st + TC_TILE_BYTES, &F.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+              for (int i = 0; i < 4; ++i)
+                tma_load_2d(st + TC_TILE_BYTES + 4096u * i, &F.mapB[w.g], raw_full(s), w.n0 + 32 * i, kb * TC_BK);
+            } else if (PAIR) {
+              tma_load_2d(st + TC_TILE_BYTES, &P.mapB2[w.g], raw_full(s), kb * TC_BK, w.n0 + (int)rank * (TC_BN / 2));
+            } else {
+              tma_load_2d(st + TC_TILE_BYTES, &F.mapB[w.g], raw_full(s), kb * TC_BK, w.n0);
+            }
+            if (dbg && it == 0) dbg[2] = gtime();
           }
-          if (dbg && it == 0) dbg[2] = gtime();
+          __syncwarp();
         }
       }
       }
-      if (dbg) { dbg[3] = gtime(); dbg[11] = (unsigned long long)w_prod; }
+      if (dbg && leader) { dbg[3] = gtime(); dbg[11] = (unsigned long long)w_prod; }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (pair mode: the leader CTA only) =====================
