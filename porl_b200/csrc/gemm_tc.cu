@@ -437,8 +437,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       const TcPhase& F = P.ph[p];
       // bit 15 / 16: A / B is MN-major ("transposed") in shared memory
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
-                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24) | (F.a_mn ? (1u << 15) : 0u) |
-                             (F.b_mn ? (1u << 16) : 0u);
+                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24) | ((F.a_mn && !ATM) ? (1u << 15) : 0u) |
+                             (F.b_mn ? (1u << 16) : 0u);      // A from tensor memory has no shared-memory layout
       // 16-byte units the start address advances per 8-wide k-step: 32 bytes along a K-major row, one 1024-byte
       // k-group of an MN-major tile
       const uint64_t a_step = F.a_mn ? 64u : 2u, b_step = F.b_mn ? 64u : 2u;
@@ -550,18 +550,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
           }
           if (warp < TC_SPLIT_WARP0 + 4) {
             // A (first four splitter warps): this thread owns tile row r = its TMEM lane; un-swizzle the row
-            // (16-byte chunk j of row r sits at chunk j ^ (r & 7)) and store hi / lo as 32 + 32 TMEM columns
+            // (K-major: 16-byte chunk j of row r sits at chunk j ^ (r & 7)) and store hi / lo as 32 + 32 TMEM columns
             // (column = k index)
             const int r = 32 * (warp & 3) + lane;
-            const uint8_t* arow = stage + r * 128;
             uint32_t hi[32], lo[32];
+            if (P.ph[p].a_mn) {
+              // MN-major A tile (four boxes of {32 m, 32 k}): box warp & 3 holds this warp's 32 rows; its line k is the
+              // 128 bytes A[k][m0 .. m0 + 31] whose four 32-byte chunks are XOR-ed with (k & 3).  The warp reads one
+              // whole line per step (lane = row): conflict-free.
+              const uint8_t* abox = stage + (warp & 3) * 4096 + ((lane & 7) << 2);
+              const int c = lane >> 3;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
-              hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
-              hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
-              hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
-              hi[4 * j + 3] = __float_as_uint(v.w); lo[4 * j + 3] = __float_as_uint(split_lo(v.w));
+              for (int k = 0; k < 32; ++k) {
+                const float v = *reinterpret_cast<const float*>(abox + k * 128 + ((c ^ (k & 3)) << 5));
+                hi[k] = __float_as_uint(v);
+                lo[k] = __float_as_uint(split_lo(v));
+              }
+            } else {
+              const uint8_t* arow = stage + r * 128;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
+                hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
+                hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
+                hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
+                hi[4 * j + 3] = __float_as_uint(v.w); lo[4 * j + 3] = __float_as_uint(split_lo(v.w));
+              }
             }
             const uint32_t ta = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(TC_ACC_COLS + s * 64);
             tc_st32(ta, hi);
@@ -1054,11 +1068,9 @@ int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaS
     for (int i = 0; i < specs[p].batch->n_groups; ++i)
       bn_fused = bn_fused || specs[p].batch->g[i].a_affine;
   if (bn_fused) pair = false;
-  // A in tensor memory: the splitters un-swizzle K-major A rows, so every phase's A must be K-major; B may be either
-  // form (its split is a flat pass over the tile and the MMA's B descriptor carries the layout)
-  bool any_a_mn = false;
-  for (int p = 0; p < n_phases; ++p) any_a_mn = any_a_mn || !specs[p].a_kmajor;
-  const bool atm = ctx->tc_a_in_tmem == 1 && !any_a_mn && n_phases == 1 && !bn_fused;
+  // A in tensor memory: the splitters un-swizzle A rows of either form (K-major rows, or the lines of an MN-major tile);
+  // B's split is a flat pass over the tile and the MMA's B descriptor carries its layout
+  const bool atm = ctx->tc_a_in_tmem == 1 && n_phases == 1 && !bn_fused;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
   P.n_phases = n_phases;
   static bool configured = false;

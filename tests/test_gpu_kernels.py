@@ -155,7 +155,9 @@ def _gemm(env, a_k, b_k, M, N, K, epilogue=0, bias=False, relu=False, colsum=Fal
                                       (2048, 384, 512, dict(relu=True, transposed=True)), (300, 129, 640, dict(n_store=132))])
 def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
     """The three tcgen05 kernel variants (operands in shared memory / A in tensor memory / CTA pairs with
-    cta_group::2) issue the same MMAs on the same values in the same order: identical bits, incl. split-K."""
+    cta_group::2) issue the same MMAs on the same values in the same order: identical bits, incl. split-K.  The
+    A-in-tensor-memory variant also serves MN-major operands (the weight- and input-gradient forms): checked against the
+    shared-memory variant in all four operand forms."""
     ctx = env[1]
     ctx.set_gemm_mode(1)
     try:
@@ -166,6 +168,13 @@ def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
             outs.append(_gemm(env, 1, 1, M, N, K, seed=5, **kw))
             assert ctx.tc_launches == before + 1
         assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+        if not kw.get("transposed"):
+            for a_k, b_k in ((1, 0), (0, 0), (0, 1)):
+                forms = []
+                for variant in (0, 1):
+                    ctx.set_tc_variant(variant)
+                    forms.append(_gemm(env, a_k, b_k, M, N, K, seed=6, **kw))
+                assert torch.equal(forms[0], forms[1]), (a_k, b_k)
     finally:
         ctx.set_tc_variant(int(os.environ.get("PORL_TC_A_IN_TMEM", "1")))      # the library's default
         ctx.set_gemm_mode(0)
