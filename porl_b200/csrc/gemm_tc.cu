@@ -10,7 +10,7 @@
 //   warp 1      TMEM allocator + MMA issuer: per k-block 8 "small" MMAs (A_lo*B_hi, A_hi*B_lo for
 //               the four 8-wide k-steps) then 4 "big" ones (A_hi*B_hi), all into one fp32 TMEM
 //               accumulator that is RESTARTED every chunk (chunk_kb k-blocks, default 1).
-//   warps 8..11 accumulators + epilogue: drain each chunk's TMEM accumulator (tcgen05.ld) and add it
+//   warps 8..15 accumulators + epilogue (two sets of four, 64 columns each): drain each chunk's TMEM accumulator and add it
 //               to a register accumulator with round-to-nearest fp32 adds, in fixed order.  The
 //               tensor core truncates (RZ) on every accumulate; restarting the TMEM accumulator
 //               every 32..64 k keeps that error at the fp32 rounding level (measured: DESIGN.md).
@@ -35,7 +35,7 @@ namespace porl {
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;      // tile; BK floats = one 128-byte swizzle span
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;          // 16 KB
-constexpr int TC_THREADS = 384;                           // 12 warps: TMA, MMA, 6 splitters, 4 accumulators
+constexpr int TC_THREADS = 512;                           // 16 warps: TMA, MMA, 6 splitters, 8 accumulators (<= 128 registers each)
 constexpr int TC_SPLIT_THREADS = 192;
 // Two variants.  ATM = false: A_hi, A_lo, B_hi, B_lo all in shared memory (stage = 4 tiles, 3 stages).
 // ATM = true: the splitters put A_hi / A_lo into TENSOR MEMORY (tcgen05.st, 64 columns per stage) and the
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     }
     for (int b = 0; b < TC_NBUF; ++b) {
       mbar_init(tmem_full(b), 1);
-      mbar_init(tmem_empty(b), PAIR ? 256 : 128);
+      mbar_init(tmem_empty(b), PAIR ? 512 : 256);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -628,8 +628,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     if (dbg && t == 0) dbg[12] = (unsigned long long)w_rf;
   } else {
     // ===================== accumulators + epilogue =====================
+    // Eight warps in two sets: set `half` owns columns [64 half, 64 half + 64) of the tile, i.e. the slabs 2 half and
+    // 2 half + 1 -- half the TMEM drain per chunk and half the epilogue per warp of a four-warp design, and 64 instead of
+    // 128 accumulator registers per thread.  The sets run independently (named barrier 1 + half, own staging buffer,
+    // own TMA-store issuer); the few points that concern the whole tile (split-K parking, grid barrier) use barrier 3.
     const int q = warp & 3;                 // TMEM lane quarter this warp may read
-    int chunk = 0, sbuf = 0;
+    const int half = (warp - TC_EPI_WARP0) >> 2;
+    const int col0 = 64 * half;
+    const bool issuer = threadIdx.x == (TC_EPI_WARP0 + 4 * half) * 32;      // this set's TMA-store thread
+    const bool first = threadIdx.x == TC_EPI_WARP0 * 32;                    // one thread for tile-wide duties
+    auto set_sync = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory"); };
+    auto all_sync = [&]() { asm volatile("bar.sync 3, 256;" ::: "memory"); };
+    uint8_t* const sbuf_ptr = staging + (size_t)half * TC_TILE_BYTES;
+    int chunk = 0;
     long long w_tf = 0;
     TcUnit w;
     for (int p = 0; p < P.n_phases; ++p) {
@@ -641,10 +652,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // producer of this CTA through phase_go.  The two words of barrier p reset themselves: the last CTA to leave
       // zeroes them for the next launch.  A wait that exceeds 2 s raises PORL_FLAG_PEER_TIMEOUT and goes on (wrong
       // results, flagged) rather than hang the device.
-      if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
       __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == TC_EPI_WARP0 * 32) {
+      all_sync();
+      if (first) {
         int* const arrived = reinterpret_cast<int*>(P.gbar) + 2 * p;
         int* const departed = arrived + 1;
         const int n_cta = (int)gridDim.x;
@@ -665,7 +676,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         __threadfence();
         mbar_arrive(phase_go);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      all_sync();
     }
     for (int u = unit0; tc_decode(F, P.tile_m, u, w); u += unit_stride) {
       w.m0 += (int)rank * TC_BM;                            // pair mode: this CTA's 128 rows of the 256-row tile
@@ -689,9 +700,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       //     this tile's C is written by this CTA's (or, under split-K, the last-arriving slice's) epilogue only, after
       //     every slice has parked.
       const int r_in_tile = 32 * q + lane;
-      if (gBias) {
-        const int col = w.n0 + r_in_tile;
-        sbias[r_in_tile] = (col < ((gN + 3) & ~3)) ? __ldg(gBias + col) : 0.f;
+      if (gBias && r_in_tile < 64) {
+        const int col = w.n0 + col0 + r_in_tile;
+        sbias[col0 + r_in_tile] = (col < ((gN + 3) & ~3)) ? __ldg(gBias + col) : 0.f;
       }
       // ReLU mask of this thread's row.  Preferred form: one bit per element written by the forward epilogue that
       // produced the activation (bits_in): ONE 16-byte load per row, issued here and consumed only in the epilogue.
@@ -704,18 +715,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         const int col = w.n0 + 4 * lane;
         const float* mp = gRelu + (size_t)(w.m0 + 32 * q) * ldr + col;
         const bool col_ok = col < gNs;
-        float4 m4[32];
-#pragma unroll
-        for (int r = 0; r < 32; ++r) {
-          m4[r] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (col_ok && w.m0 + 32 * q + r < gM) m4[r] = *reinterpret_cast<const float4*>(mp + (size_t)r * ldr);
-        }
         uint32_t rb0 = 0u, rb1 = 0u, rb2 = 0u, rb3 = 0u;      // this thread's row: bit l of rb<k> = column 4 l + k
+#pragma unroll 1
+        for (int r0 = 0; r0 < 32; r0 += 8) {                  // eight rows' loads in flight at a time
+          float4 m4[8];
 #pragma unroll
-        for (int r = 0; r < 32; ++r) {
-          const uint32_t b0 = __ballot_sync(0xffffffffu, m4[r].x > 0.f), b1 = __ballot_sync(0xffffffffu, m4[r].y > 0.f);
-          const uint32_t b2 = __ballot_sync(0xffffffffu, m4[r].z > 0.f), b3 = __ballot_sync(0xffffffffu, m4[r].w > 0.f);
-          if (lane == r) { rb0 = b0; rb1 = b1; rb2 = b2; rb3 = b3; }
+          for (int r = 0; r < 8; ++r) {
+            m4[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (col_ok && w.m0 + 32 * q + r0 + r < gM) m4[r] = *reinterpret_cast<const float4*>(mp + (size_t)(r0 + r) * ldr);
+          }
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            const uint32_t b0 = __ballot_sync(0xffffffffu, m4[r].x > 0.f), b1 = __ballot_sync(0xffffffffu, m4[r].y > 0.f);
+            const uint32_t b2 = __ballot_sync(0xffffffffu, m4[r].z > 0.f), b3 = __ballot_sync(0xffffffffu, m4[r].w > 0.f);
+            if (lane == r0 + r) { rb0 = b0; rb1 = b1; rb2 = b2; rb3 = b3; }
+          }
         }
         // into column order: word wd covers lanes 8 wd .. 8 wd + 7; spread4 moves bit i of a byte to bit 4 i
         auto spread4 = [](uint32_t x) {
@@ -732,9 +746,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       }
       const bool masked = gBitsIn != nullptr || gRelu != nullptr;
 
-      float acc[TC_BN];
+      float acc[64];                                           // this set's 64 columns of this thread's row
 #pragma unroll
-      for (int j = 0; j < TC_BN; ++j) acc[j] = 0.f;
+      for (int j = 0; j < 64; ++j) acc[j] = 0.f;
       const int nchunks = (w.kb1 - w.kb0 + chunk_kb - 1) / chunk_kb;
       for (int c = 0; c < nchunks; ++c, ++chunk) {
         const int buf = chunk % TC_NBUF;
@@ -742,10 +756,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         mbar_wait(tmem_full(buf), (uint32_t)(chunk / TC_NBUF) & 1u);
         if (dbg) w_tf += clock64() - tw;
         tc_fence_after();
-        if (dbg && chunk == 0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[7] = gtime();
-        const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN);
+        if (dbg && chunk == 0 && first) dbg[7] = gtime();
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN + col0);
 #pragma unroll
-        for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+        for (int c0 = 0; c0 < 64; c0 += 32) {
           float v[32];
           tc_ld32(taddr + (uint32_t)c0, v);
 #pragma unroll
@@ -756,7 +770,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         else mbar_arrive(tmem_empty(buf));
       }
 
-      if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[8] = gtime();
+      if (dbg && u == unit0 && first) dbg[8] = gtime();
       // ---- split-K: every slice parks its partial tile in the workspace; the LAST slice to arrive (ticket)
       // sums all partials in slice order -- a fixed order, so the result is bitwise reproducible whichever
       // CTA happens to be last -- and runs the epilogue.  No slice ever waits for another one.
@@ -778,33 +792,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       if (split) {
         float4* wp = reinterpret_cast<float4*>(ws_p) + ((size_t)w.split * n_sub + gt) * (32 * 128) + r_in_tile;
 #pragma unroll
-        for (int c4 = 0; c4 < TC_BN; c4 += 4)
-          wp[(c4 >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
+        for (int c4 = 0; c4 < 64; c4 += 4)
+          wp[((col0 + c4) >> 2) * 128] = make_float4(acc[c4], acc[c4 + 1], acc[c4 + 2], acc[c4 + 3]);
         __threadfence();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        all_sync();                                              // both sets have parked their halves
         int* const ticket = sem_p + gt;
         if (dist) {
-          if (warp == TC_EPI_WARP0 && lane == 0) {
+          if (first) {
             atomicAdd(ticket, 1);
             if (w.split < 4) {                                   // a fixer: wait until every slice has parked
               while (ld_acquire(ticket) < S) __nanosleep(32);
             }
           }
           if (w.split >= 4) continue;                            // nothing to sum for this slice
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          all_sync();
           __threadfence();
           fix_mod = S;
           fix_me = w.split;
         } else {
-          if (warp == TC_EPI_WARP0 && lane == 0) {
+          if (first) {
             const int old = atomicAdd(ticket, 1);
             const int last = (old == S - 1) ? 1 : 0;
             if (last) *ticket = 0;                               // self-reset for the next launch (stream-ordered)
             *flag_slot = (uint32_t)last;
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          all_sync();
           const bool is_last = *reinterpret_cast<volatile uint32_t*>(flag_slot) != 0;
-          asm volatile("bar.sync 1, 128;" ::: "memory");        // flag consumed before the next unit rewrites it
+          all_sync();                                            // flag consumed before the next unit rewrites it
           if (!is_last) continue;
           __threadfence();
         }
@@ -817,19 +831,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       // stores (lanes = consecutive rows of one Ct row), and row-major C through TMA: the slab goes to shared memory
       // (eight 16-byte slots per row XOR-swizzled like every SWIZZLE_128B tile: conflict-free) and one thread hands it
       // to the copy engine, which writes full 128-byte row segments and clips rows >= M and columns >= n_store.  The
-      // stores are asynchronous: these warps return to the next tile's chunks at once.  Two slab buffers: before a
-      // buffer is rewritten, wait_group.read 1 guarantees every store but the latest one (which reads the other
-      // buffer) has finished reading.
+      // stores are asynchronous: these warps return to the next tile's chunks at once.  One slab buffer per warp set:
+      // before it is rewritten, wait_group.read 0 (on the set's issuing thread) guarantees the set's previous store has
+      // finished reading it.
       // Pad columns (N <= col < n_store) need no special case: their B rows are out of bounds for TMA, so their
       // accumulators are exact zeros, C owns those columns (ldc >= n_store), the staged bias is zero there and relu
       // maps 0 to 0; only the transposed store is guarded.
       const int row = w.m0 + r_in_tile;
       const bool row_ok = row < gM;
-      if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // staged bias visible to all four warps
+      if (gBias) set_sync();                                             // this set's 64 staged bias values visible to its four warps
       auto epilogue = [&](auto split_tag) {
         constexpr bool SPLIT = decltype(split_tag)::value;
 #pragma unroll
-        for (int sl = 0; sl < TC_BN / 32; ++sl) {
+        for (int s2 = 0; s2 < 2; ++s2) {
+          const int sl = 2 * half + s2;                            // slab of the tile: columns 32 sl .. 32 sl + 31
           if (w.n0 + 32 * sl >= gNs) break;
           float v[32];
           if constexpr (SPLIT) {
@@ -856,7 +871,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = acc[32 * sl + j];
+            for (int j = 0; j < 32; ++j) v[j] = acc[32 * s2 + j];
           }
           if (gBias) {
 #pragma unroll
@@ -889,32 +904,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
               ct += ldct;
             }
           }
-          uint8_t* const buf = staging + (size_t)sbuf * TC_TILE_BYTES;
-          if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint8_t* const buf = sbuf_ptr;                           // one staging slab per set: the previous store has read it
+          if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          set_sync();
           uint8_t* const srow = buf + r_in_tile * 128;
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes -> copy-engine reads
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (threadIdx.x == TC_EPI_WARP0 * 32) tma_store_2d(map_c, smem_u32(buf), w.n0 + 32 * sl, w.m0);
-          sbuf ^= 1;
+          set_sync();
+          if (issuer) tma_store_2d(map_c, smem_u32(buf), w.n0 + 32 * sl, w.m0);
         }
       };
       if (split) epilogue(std::true_type{});
       else epilogue(std::false_type{});
-      if (dist && warp == TC_EPI_WARP0 && lane == 0) {
+      if (dist) all_sync();                                       // both sets have finished this fixer's slabs
+      if (dist && first) {
         // second round on the ticket: the last fixer to finish resets it for the next launch
         const int nfix = S < 4 ? S : 4;
         if (atomicAdd(sem_p + gt, 1) == S + nfix - 1) sem_p[gt] = 0;
       }
-      if (gBias) asm volatile("bar.sync 1, 128;" ::: "memory");          // bias slots free for the next tile
-      if (dbg && u == unit0 && threadIdx.x == TC_EPI_WARP0 * 32) dbg[9] = gtime();
+      if (gBias) set_sync();                                             // bias slots free for the next tile
+      if (dbg && u == unit0 && first) dbg[9] = gtime();
     }
     }
-    if (threadIdx.x == TC_EPI_WARP0 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    if (dbg && threadIdx.x == TC_EPI_WARP0 * 32) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
+    if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (dbg && first) { dbg[10] = gtime(); dbg[4] = (unsigned long long)w_tf; }
   }
 
   tc_fence_before();
