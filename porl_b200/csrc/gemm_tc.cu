@@ -568,9 +568,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
               }
             } else {
               const uint8_t* arow = stage + r * 128;
+              // BatchNorm + ReLU of the layer that produced A, applied on the way in (a_affine: scale | shift per k, the
+              // arithmetic of bn_apply_kernel): every thread needs the k-block's 32 + 32 values -- broadcast loads
+              const float* const aff = P.ph[p].batch.g[w.g].a_affine;
+              const int affK = P.ph[p].batch.g[w.g].K;
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
+                float4 v = *reinterpret_cast<const float4*>(arow + ((j ^ (r & 7)) << 4));
+                if (aff != nullptr) {
+                  const float4 sc = __ldg(reinterpret_cast<const float4*>(aff) + kb * (TC_BK / 4) + j);
+                  const float4 sh = __ldg(reinterpret_cast<const float4*>(aff + affK) + kb * (TC_BK / 4) + j);
+                  v.x = fmaxf(fmaf(v.x, sc.x, sh.x), 0.f); v.y = fmaxf(fmaf(v.y, sc.y, sh.y), 0.f);
+                  v.z = fmaxf(fmaf(v.z, sc.z, sh.z), 0.f); v.w = fmaxf(fmaf(v.w, sc.w, sh.w), 0.f);
+                }
                 hi[4 * j + 0] = __float_as_uint(v.x); lo[4 * j + 0] = __float_as_uint(split_lo(v.x));
                 hi[4 * j + 1] = __float_as_uint(v.y); lo[4 * j + 1] = __float_as_uint(split_lo(v.y));
                 hi[4 * j + 2] = __float_as_uint(v.z); lo[4 * j + 2] = __float_as_uint(split_lo(v.z));
@@ -1078,14 +1088,14 @@ int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaS
   bool pair = ctx->tc_a_in_tmem == 2 && !any_mn && n_phases == 1;
   for (int i = 0; i < specs[0].batch->n_groups && pair; ++i)
     if (specs[0].batch->g[i].M < 2 * TC_BM) pair = false;
-  bool bn_fused = false;             // operand affine: implemented in the all-in-shared-memory variant
+  bool bn_fused = false;             // operand affine: in the shared-memory and the tensor-memory variant, not in pair mode
   for (int p = 0; p < n_phases; ++p)
     for (int i = 0; i < specs[p].batch->n_groups; ++i)
       bn_fused = bn_fused || specs[p].batch->g[i].a_affine;
   if (bn_fused) pair = false;
   // A in tensor memory: the splitters un-swizzle A rows of either form (K-major rows, or the lines of an MN-major tile);
   // B's split is a flat pass over the tile and the MMA's B descriptor carries its layout
-  const bool atm = ctx->tc_a_in_tmem == 1 && n_phases == 1 && !bn_fused;
+  const bool atm = ctx->tc_a_in_tmem == 1 && n_phases == 1;
   P.tile_m = pair ? 2 * TC_BM : TC_BM;
   P.n_phases = n_phases;
   static bool configured = false;
