@@ -246,6 +246,20 @@ int porl_value_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* target, const p
                          const float* rewards, const float* dones, float gamma, float tau, int64_t B_norm,
                          float* target_v, float* grads, float* loss_out, porl_stream_t stream);
 
+/* Fused policy head step (agent/sorl.py:96-111; agent/por.py:97-108 when the policy head is narrow): the scalar heads of
+ * the twin value nets on obs with the NEW value weights (forward only), the advantage weight, the weighted Gaussian
+ * NLL of the policy head's means (as porl_awr_gauss_nll, tanh folded when the policy net has a tanh output) and the
+ * head's backward (dW, db, ReLU-masked dz in place, db of the layer below, dlog_std) in ONE pass over the last hidden
+ * activations.  `value` / `policy` are the calls a porl_mlp_forward with pad_ = PORL_MLP_SKIP_HEAD has just evaluated;
+ * follow with porl_mlp_backward(policy with pad_ = PORL_MLP_HEAD_DONE, dout = NULL).  grads is the policy net's
+ * gradient buffer (flat layout), dlog_std (D) and loss_out[0] are overwritten.  Supported: twin scalar value nets and a
+ * one-net policy with at most 2 outputs, equal last hidden widths <= 1024, no LayerNorm. */
+int porl_policy_head_step_supported(const porl_mlp_t* value_mlp, const porl_mlp_t* policy_mlp);
+int porl_policy_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* value, const porl_mlp_call_t* policy, int64_t B,
+                          const float* log_std, const float* reg_target, int64_t ld_target, const float* target_v,
+                          float alpha, int32_t mode, int64_t B_norm, float* grads, float* dlog_std, float* loss_out,
+                          porl_stream_t stream);
+
 /* ---- K5: advantage-weighted diagonal-Gaussian NLL (agent/por.py:97-106; agent/sorl.py:102-109;
  *          agent/policy.py:18-23,42-49) ------------------------------------------------------- */
 enum { PORL_AWR_POR = 0 /* w = exp(adv/alpha) */, PORL_AWR_SORL = 1 /* w = exp(alpha*adv) */ };

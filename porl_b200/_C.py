@@ -155,6 +155,9 @@ _SIGNATURES = {
     "porl_mlp_backward": (C.c_int, [_p, C.POINTER(MlpCall), _i64, _p, _p, _p]),
     "porl_value_head_step_supported": (C.c_int, [_p]),
     "porl_value_head_step": (C.c_int, [_p, C.POINTER(MlpCall), C.POINTER(MlpCall), _i64, _p, _p, _f, _f, _i64, _p, _p, _p, _p]),
+    "porl_policy_head_step_supported": (C.c_int, [_p, _p]),
+    "porl_policy_head_step": (C.c_int, [_p, C.POINTER(MlpCall), C.POINTER(MlpCall), _i64, _p, _p, _i64, _p, _f, _i32, _i64,
+                                        _p, _p, _p, _p]),
     "porl_expectile_twin_loss": (C.c_int, [_p, _p, _p, _p, _p, _i64, _p, _p, _f, _f, _i64, _i64, _p, _p, _p, _p, _p]),
     "porl_expectile_twin_loss_noalloc": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _f, _f, _i64, _i64, _p, _p, _p, _p, _p]),
     "porl_awr_gauss_nll": (C.c_int, [_p, _p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _f, _i32, _i32, _i64, _i32, _i64,

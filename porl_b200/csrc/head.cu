@@ -417,6 +417,259 @@ __global__ void __launch_bounds__(256) vhead_fused_kernel(const __grid_constant_
   }
 }
 
+// ---------------------------------------------------------------- fused policy head step
+// The policy half of the update in one pass over the last hidden activations (agent/sorl.py:96-111, agent/por.py:97-108
+// for a narrow Gaussian head): the scalar heads of the two value nets (new weights, forward only) give the advantage
+// weight, the D <= 2 mean outputs of the policy head give the weighted Gaussian NLL (the formulas of awr_nll_kernel),
+// and the same registers feed the head's backward: dz in place over h, dW, db, the bias gradient of the layer below and
+// the log_std gradient.  grid (row chunks), 8 warps, a warp takes one row at a time.  Replaces head_forward (3 nets) +
+// awr_nll_kernel + head_backward: three launches and two more passes over the activations.  Reductions over the batch
+// are order-fixed like the value head's (warps in index order, then the two-level tree over the row chunks).
+constexpr float kPhLog2Pi = 1.8378770664093453f;
+constexpr float kPhWeightCap = 100.f;   // EXP_ADV_MAX, agent/por.py:12, agent/sorl.py:12
+template <int NJ, int D>
+__global__ void __launch_bounds__(256) phead_fused_kernel(const __grid_constant__ PHeadArgs a, float* partials,
+                                                         uint32_t* tickets, uint32_t* status) {
+  pdl_entry();
+  extern __shared__ __align__(16) float psm2[];
+  constexpr int W128 = NJ * 128;
+  constexpr int NV = D + 1;               // vectors reduced over the batch: dW rows, db_prev
+  constexpr int NS = 2 * D + 1;           // scalars: db[D], dlog_std[D], loss
+  float* s_w = psm2;                      // [2 + D][W128]: value w_1, value w_2, policy W rows
+  float* s_acc = psm2 + (2 + D) * W128;   // [8 warps][NV][W128]
+  __shared__ float s_scal[8][NS];
+  __shared__ int s_flag[1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = gridDim.x;
+  const int Hp = (a.H + 3) & ~3;
+  for (int i = threadIdx.x; i < (2 + D) * W128; i += 256) {
+    const int v = i / W128, c = i % W128;
+    const float* src = v < 2 ? a.wv[v] : a.w + (size_t)(v - 2) * a.ldw;
+    s_w[i] = c < a.H ? __ldg(src + c) : 0.f;
+  }
+  __syncthreads();
+  const float bv1 = a.bv[0][0], bv2 = a.bv[1][0];
+  float bp[D], ls[D], inv_std[D];
+  float nll_const = 0.5f * (float)D * kPhLog2Pi;
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    bp[d] = a.b[d];
+    ls[d] = fminf(fmaxf(a.log_std[d], -5.f), 2.f);
+    inv_std[d] = expf(-ls[d]);
+    nll_const += ls[d];
+  }
+  float* const hp = a.h;
+  const int64_t r0 = (int64_t)blockIdx.x * a.B / R, r1 = (int64_t)(blockIdx.x + 1) * a.B / R;
+  float4 dw[D][NJ], dbp[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    dbp[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int d = 0; d < D; ++d) dw[d][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float dbn[D], dls[D], loss = 0.f;
+#pragma unroll
+  for (int d = 0; d < D; ++d) dbn[d] = dls[d] = 0.f;
+  for (int64_t row = r0 + warp; row < r1; row += 8) {
+    float4 h4[NJ], t1[NJ], t2[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      const bool ok = c < Hp;
+      h4[j] = ok ? *reinterpret_cast<const float4*>(hp + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      t1[j] = ok ? *reinterpret_cast<const float4*>(a.hv[0] + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      t2[j] = ok ? *reinterpret_cast<const float4*>(a.hv[1] + row * a.ldh + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float s1 = 0.f, s2 = 0.f, sm[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) sm[d] = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      const float4 u4 = *reinterpret_cast<const float4*>(s_w + c);
+      const float4 x4 = *reinterpret_cast<const float4*>(s_w + W128 + c);
+      s1 = fmaf(t1[j].x, u4.x, s1); s1 = fmaf(t1[j].y, u4.y, s1); s1 = fmaf(t1[j].z, u4.z, s1); s1 = fmaf(t1[j].w, u4.w, s1);
+      s2 = fmaf(t2[j].x, x4.x, s2); s2 = fmaf(t2[j].y, x4.y, s2); s2 = fmaf(t2[j].z, x4.z, s2); s2 = fmaf(t2[j].w, x4.w, s2);
+#pragma unroll
+      for (int d = 0; d < D; ++d) {
+        const float4 w4 = *reinterpret_cast<const float4*>(s_w + (2 + d) * W128 + c);
+        sm[d] = fmaf(h4[j].x, w4.x, sm[d]); sm[d] = fmaf(h4[j].y, w4.y, sm[d]);
+        sm[d] = fmaf(h4[j].z, w4.z, sm[d]); sm[d] = fmaf(h4[j].w, w4.w, sm[d]);
+      }
+    }
+    const float v = fminf(warp_sum(s1) + bv1, warp_sum(s2) + bv2);
+    const float adv = a.target_v[row] - v;
+    const float e = (a.mode == PORL_AWR_POR) ? adv / a.alpha : a.alpha * adv;
+    const float w = fminf(expf(e), kPhWeightCap);
+    const float wn = w * a.inv_bn;
+    float dmu[D], sz2 = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      float mu = warp_sum(sm[d]) + bp[d];
+      if (a.tanh_out) mu = tanhf(mu);
+      const float z = (a.x[row * a.ld_x + d] - mu) * inv_std[d];
+      sz2 = fmaf(z, z, sz2);
+      dmu[d] = -wn * z * inv_std[d];
+      if (a.tanh_out) dmu[d] *= (1.f - mu * mu);
+      dbn[d] += dmu[d];
+      dls[d] += wn * (1.f - z * z);
+    }
+    const float nll = 0.5f * sz2 + nll_const;
+    if (lane == 0) {
+      if (!(nll > 0.f)) atomicOr(status, (uint32_t)PORL_FLAG_NONPOSITIVE_NLL);
+      loss += w * nll;
+    }
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int c = 128 * j + 4 * lane;
+      if (c < Hp) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+          const float4 w4 = *reinterpret_cast<const float4*>(s_w + (2 + d) * W128 + c);
+          g.x = fmaf(dmu[d], w4.x, g.x); g.y = fmaf(dmu[d], w4.y, g.y); g.z = fmaf(dmu[d], w4.z, g.z); g.w = fmaf(dmu[d], w4.w, g.w);
+          dw[d][j].x = fmaf(dmu[d], h4[j].x, dw[d][j].x); dw[d][j].y = fmaf(dmu[d], h4[j].y, dw[d][j].y);
+          dw[d][j].z = fmaf(dmu[d], h4[j].z, dw[d][j].z); dw[d][j].w = fmaf(dmu[d], h4[j].w, dw[d][j].w);
+        }
+        if (!(h4[j].x > 0.f)) g.x = 0.f;
+        if (!(h4[j].y > 0.f)) g.y = 0.f;
+        if (!(h4[j].z > 0.f)) g.z = 0.f;
+        if (!(h4[j].w > 0.f)) g.w = 0.f;
+        *reinterpret_cast<float4*>(hp + row * a.ldh + c) = g;
+        dbp[j].x += g.x; dbp[j].y += g.y; dbp[j].z += g.z; dbp[j].w += g.w;
+      }
+    }
+  }
+  // block partial: the 8 warps in index order
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    const int c = 128 * j + 4 * lane;
+#pragma unroll
+    for (int d = 0; d < D; ++d) *reinterpret_cast<float4*>(s_acc + ((size_t)warp * NV + d) * W128 + c) = dw[d][j];
+    *reinterpret_cast<float4*>(s_acc + ((size_t)warp * NV + D) * W128 + c) = dbp[j];
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int d = 0; d < D; ++d) { s_scal[warp][d] = dbn[d]; s_scal[warp][D + d] = dls[d]; }
+    s_scal[warp][2 * D] = loss;
+  }
+  __syncthreads();
+  // partial layout per row chunk: [NV][W128] then NS scalars (padded to 8)
+  constexpr size_t per_chunk = (size_t)NV * W128 + 8;
+  static_assert(NS <= 8, "scalar slots");
+  float* part = partials + (size_t)blockIdx.x * per_chunk;
+  for (int i = threadIdx.x; i < NV * W128; i += 256) {
+    float t = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) t += s_acc[(size_t)wq * NV * W128 + i];
+    part[i] = t;
+  }
+  if (threadIdx.x < NS) {
+    float t = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+    part[NV * W128 + threadIdx.x] = t;
+  }
+  // two-level, order-fixed reduction tree over the row chunks (fan-in kVhGroup), as in vhead_fused_kernel
+  const int G = (R + kVhGroup - 1) / kVhGroup, grp = blockIdx.x / kVhGroup;
+  const int g0 = grp * kVhGroup, g1 = min(g0 + kVhGroup, R);
+  float* const gpart = partials + (size_t)R * per_chunk + (size_t)grp * per_chunk;
+  auto last_of = [&](uint32_t* tk, uint32_t n) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t t = atomicAdd(tk, 1u);
+      const bool last = (t == n - 1);
+      if (last) *tk = 0;
+      s_flag[0] = last ? 1 : 0;
+    }
+    __syncthreads();
+    const bool last = s_flag[0] != 0;
+    __syncthreads();
+    if (last) __threadfence();
+    return last;
+  };
+  auto sum_partials = [&](const float* src, int n, float* dst, bool final) {
+    for (int i = threadIdx.x; i < NV * W128 + NS; i += 256) {
+      float vals[kVhGroup];
+#pragma unroll
+      for (int r = 0; r < kVhGroup; ++r) vals[r] = r < n ? __ldcg(src + (size_t)r * per_chunk + i) : 0.f;
+      float t = vals[0];
+#pragma unroll
+      for (int r = 1; r < kVhGroup; ++r)
+        if (r < n) t += vals[r];
+      if (!final) {
+        dst[i] = t;
+      } else if (i < D * W128) {
+        const int d = i / W128, c = i % W128;
+        if (c < a.ldw) a.dW[(size_t)d * a.ldw + c] = c < a.H ? t : 0.f;
+      } else if (i < NV * W128) {
+        if (i - D * W128 < a.H) a.db_prev[i - D * W128] = t;
+      } else {
+        const int sidx = i - NV * W128;
+        if (sidx < D) {
+          a.db[sidx] = t;
+        } else if (sidx < 2 * D) {
+          const float raw = a.log_std[sidx - D];
+          a.dlog_std[sidx - D] = (raw >= -5.f && raw <= 2.f) ? t : 0.f;
+        } else {
+          const float l = t * a.inv_bn;
+          a.loss_out[0] = l;
+          if (!isfinite(l)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
+        }
+      }
+    }
+  };
+  if (!last_of(tickets + 256 + grp, (uint32_t)(g1 - g0))) return;
+  sum_partials(partials + (size_t)g0 * per_chunk, g1 - g0, gpart, false);
+  if (!last_of(tickets + 4, (uint32_t)G)) return;
+  sum_partials(partials + (size_t)R * per_chunk, G, nullptr, true);            // G <= kVhGroup (R <= kVhGroup^2)
+}
+
+bool phead_fused_supported(int H, int D) { return H >= 4 && H <= 1024 && (D == 1 || D == 2); }
+
+int launch_phead_fused(porl_ctx* ctx, const PHeadArgs& a, cudaStream_t st) {
+  PORL_CHECK_ARG(phead_fused_supported(a.H, a.D) && (a.ldh & 3) == 0 && a.ldh >= ((a.H + 3) & ~3) && a.ldw >= a.H && a.B > 0,
+                 "fused policy head: bad geometry (H=%d D=%d ldh=%d ldw=%d)", a.H, a.D, a.ldh, a.ldw);
+  PORL_CHECK_ARG(a.hv[0] && a.hv[1] && a.wv[0] && a.wv[1] && a.bv[0] && a.bv[1] && a.h && a.w && a.b && a.log_std && a.x &&
+                     a.target_v && a.dW && a.db && a.db_prev && a.dlog_std && a.loss_out && aligned16(a.h) &&
+                     aligned16(a.hv[0]) && aligned16(a.hv[1]) && a.ld_x >= a.D && a.alpha != 0.f,
+                 "fused policy head: null or misaligned pointer");
+  const int nj = a.H <= 128 ? 1 : a.H <= 256 ? 2 : a.H <= 512 ? 4 : 8;
+  const int w128 = nj * 128;
+  PORL_CHECK_ARG(a.ldw <= w128, "fused policy head: ldw=%d exceeds %d", a.ldw, w128);
+  int R = (int)((a.B + 15) / 16);
+  int cap = nj == 8 ? ctx->sm_count : 2 * ctx->sm_count;
+  if (cap > kVhGroup * kVhGroup) cap = kVhGroup * kVhGroup;
+  if (R > cap) R = cap;
+  if (R < 1) R = 1;
+  const size_t per_chunk = (size_t)(a.D + 1) * w128 + 8;
+  while (R > 1 && ((size_t)R + (R + kVhGroup - 1) / kVhGroup + 1) * per_chunk > (size_t)kPartialFloats) R >>= 1;
+  const size_t smem = (size_t)((2 + a.D) + 8 * (a.D + 1)) * w128 * sizeof(float);
+  ProfScope prof(ctx, PORL_CAT_HEAD, 4.0 * (double)a.B * a.H * 4, st);
+  uint32_t* tk = ctx->counters + kTicketBase;
+  auto go = [&](auto kernel) -> int {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(fused policy head) failed: %s", cudaGetErrorString(e));
+      return PORL_ERR_CUDA;
+    }
+    launch_pdl(ctx, kernel, dim3(R), 256, smem, st, a, ctx->partials, tk, ctx->counters);
+    return PORL_OK;
+  };
+  int rc = PORL_ERR_UNSUPPORTED;
+  if (a.D == 1) {
+    rc = nj == 1 ? go(phead_fused_kernel<1, 1>) : nj == 2 ? go(phead_fused_kernel<2, 1>) : nj == 4 ? go(phead_fused_kernel<4, 1>)
+                                                                                                    : go(phead_fused_kernel<8, 1>);
+  } else {
+    rc = nj == 1 ? go(phead_fused_kernel<1, 2>) : nj == 2 ? go(phead_fused_kernel<2, 2>) : nj == 4 ? go(phead_fused_kernel<4, 2>)
+                                                                                                    : go(phead_fused_kernel<8, 2>);
+  }
+  if (rc != PORL_OK) return rc;
+  PORL_LAUNCHED(ctx);
+  return PORL_OK;
+}
+
 bool vhead_fused_supported(int H) { return H >= 4 && H <= 1024; }
 
 int launch_vhead_fused(porl_ctx* ctx, const VHeadArgs& a, cudaStream_t st) {

@@ -66,3 +66,31 @@ struct VHeadArgs {
 bool vhead_fused_supported(int H);
 int launch_vhead_fused(porl_ctx* ctx, const VHeadArgs& a, cudaStream_t st);
 }  // namespace porl
+
+// ---- fused policy head step (head.cu): value heads (new weights, forward only), advantage-weighted Gaussian NLL of a
+// narrow policy head (D <= 2 means) and that head's backward in ONE pass (agent/sorl.py:96-111).
+namespace porl {
+struct PHeadArgs {
+  const float* hv[2];   // value nets: last hidden activation of obs with the NEW value weights (B, ldh), read only
+  const float* wv[2];   // value head weight rows (H) and bias (1)
+  const float* bv[2];
+  float* h;             // policy net: in last hidden activation of obs, out dz (ReLU-masked input gradient), in place
+  const float* w;       // (D, ldw) policy head weight
+  const float* b;       // (D)
+  const float* log_std; // (D) raw parameter
+  const float* x;       // (B, ld_x) regression target (actions / next_obs)
+  const float* target_v;  // (B) TD target of the value step
+  float* dW;            // (D, ldw) overwritten, pad columns zero
+  float* db;            // (D)
+  float* db_prev;       // (H) bias gradient of the layer below
+  float* dlog_std;      // (D)
+  float* loss_out;      // scalar
+  float alpha, inv_bn;
+  int mode, tanh_out;   // PORL_AWR_*, tanh on the mean
+  int64_t B, ld_x;
+  int H, D, ldh, ldw;
+};
+bool phead_fused_supported(int H, int D);
+int launch_phead_fused(porl_ctx* ctx, const PHeadArgs& a, cudaStream_t st);
+}  // namespace porl
+

@@ -654,6 +654,68 @@ extern "C" int porl_value_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* targ
   return launch_vhead_fused(ctx, a, as_stream(stream));
 }
 
+// Fused policy head step (head.cu: phead_fused_kernel): the scalar heads of the twin value nets (new weights, forward only),
+// the advantage-weighted Gaussian NLL of a narrow policy head and that head's backward in one pass over the last hidden
+// activations.  `value` / `policy`: the calls whose porl_mlp_forward ran with PORL_MLP_SKIP_HEAD.
+extern "C" int porl_policy_head_step_supported(const porl_mlp_t* value_mlp, const porl_mlp_t* policy_mlp) {
+  if (!value_mlp || !policy_mlp) return 0;
+  const int Lv = value_mlp->d.n_layers, Lp = policy_mlp->d.n_layers;
+  if (!(value_mlp->d.n_nets == 2 && Lv >= 2 && value_mlp->d.dims[Lv] == 1 && !value_mlp->d.layer_norm &&
+        value_mlp->d.out_act == 0))
+    return 0;
+  if (!(policy_mlp->d.n_nets == 1 && Lp >= 2 && !policy_mlp->d.layer_norm)) return 0;
+  // one row loop over the three activations: same last hidden width and leading dimension
+  if (value_mlp->d.dims[Lv - 1] != policy_mlp->d.dims[Lp - 1] || value_mlp->pad[Lv - 1] != policy_mlp->pad[Lp - 1]) return 0;
+  return phead_fused_supported(policy_mlp->d.dims[Lp - 1], policy_mlp->d.dims[Lp]) ? 1 : 0;
+}
+
+extern "C" int porl_policy_head_step(porl_ctx_t* ctx, const porl_mlp_call_t* value, const porl_mlp_call_t* policy, int64_t B,
+                                     const float* log_std, const float* reg_target, int64_t ld_target, const float* target_v,
+                                     float alpha, int32_t mode, int64_t B_norm, float* grads, float* dlog_std, float* loss_out,
+                                     porl_stream_t stream) {
+  PORL_ON_DEVICE(ctx);
+  PORL_CHECK_ARG(ctx && value && policy && value->mlp && policy->mlp && log_std && reg_target && target_v && grads &&
+                     dlog_std && loss_out && B > 0 && B_norm >= B,
+                 "porl_policy_head_step: null argument");
+  PORL_CHECK_ARG(porl_policy_head_step_supported(value->mlp, policy->mlp),
+                 "porl_policy_head_step: needs twin scalar value nets and a policy net with a head of at most 2 outputs, "
+                 "equal last hidden widths <= 1024, no LayerNorm");
+  PORL_CHECK_ARG((mode == PORL_AWR_POR || mode == PORL_AWR_SORL) && alpha != 0.f, "porl_policy_head_step: mode=%d alpha=%g",
+                 mode, (double)alpha);
+  const porl_mlp* mv = value->mlp;
+  const porl_mlp* mp = policy->mlp;
+  const int lv = mv->d.n_layers - 1, lp = mp->d.n_layers - 1;
+  PHeadArgs a;
+  for (int k = 0; k < 2; ++k) {
+    const float* P = value->params + k * mv->net_stride;
+    a.hv[k] = saved_h(mv, value->saved, k, lv, B);
+    a.wv[k] = P + mv->w_off[lv];
+    a.bv[k] = P + mv->b_off[lv];
+  }
+  a.h = saved_h(mp, policy->saved, 0, lp, B);
+  a.w = policy->params + mp->w_off[lp];
+  a.b = policy->params + mp->b_off[lp];
+  a.log_std = log_std;
+  a.x = reg_target;
+  a.ld_x = ld_target;
+  a.target_v = target_v;
+  a.dW = grads + mp->w_off[lp];
+  a.db = grads + mp->b_off[lp];
+  a.db_prev = grads + mp->b_off[lp - 1];
+  a.dlog_std = dlog_std;
+  a.loss_out = loss_out;
+  a.alpha = alpha;
+  a.inv_bn = 1.f / (float)B_norm;
+  a.mode = mode;
+  a.tanh_out = mp->d.out_act == 1 ? 1 : 0;
+  a.B = B;
+  a.H = mp->d.dims[lp];
+  a.D = mp->d.dims[lp + 1];
+  a.ldh = mp->pad[lp];
+  a.ldw = mp->pad[lp];
+  return launch_phead_fused(ctx, a, as_stream(stream));
+}
+
 extern "C" int porl_value_head_step_supported(const porl_mlp_t* mlp) {
   if (!mlp) return 0;
   const int L = mlp->d.n_layers;

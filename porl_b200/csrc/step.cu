@@ -4,6 +4,8 @@
 // host in any language runs an update with one call (and captures it into one CUDA graph).  No kernel lives here: the
 // functions below only sequence porl_mlp_forward / porl_expectile_twin_loss / porl_mlp_backward / porl_adam_step[_peer]
 // / porl_awr_gauss_nll over one caller-owned workspace.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -94,9 +96,22 @@ int expectile_step(porl_ctx_t* ctx, const porl_agent_step_t* a, int64_t B, const
   if ((rc = group_step(ctx, a->value, a->target_params, a->ema_beta, st)) != PORL_OK) return rc;
   if (value_only) return PORL_OK;
   // 5. online TwinV(obs) with the NEW weights + policy(obs)   (por.py:97-98,102)
-  calls[0] = porl_mlp_call_t{a->value_mlp, a->value.params, x_obs, ld_x, w.saved_v2, w.out_v2, 1, 0};
-  calls[1] = porl_mlp_call_t{a->policy_mlp, a->policy.params, x_obs, ld_x, w.saved_p, w.out_p, 0, 0};
+  // PORL_FUSED_POLICY_HEAD=0: head forward, loss and head backward as three launches (kept for comparison)
+  const char* const fe = getenv("PORL_FUSED_POLICY_HEAD");
+  const bool fused_policy = porl_policy_head_step_supported(a->value_mlp, a->policy_mlp) != 0 && !(fe && atoi(fe) == 0);
+  calls[0] = porl_mlp_call_t{a->value_mlp, a->value.params, x_obs, ld_x, w.saved_v2, w.out_v2, 1, fused_policy ? PORL_MLP_SKIP_HEAD : 0};
+  calls[1] = porl_mlp_call_t{a->policy_mlp, a->policy.params, x_obs, ld_x, w.saved_p, w.out_p, 0, fused_policy ? PORL_MLP_SKIP_HEAD : 0};
   if ((rc = porl_mlp_forward(ctx, 2, calls, B, st)) != PORL_OK) return rc;
+  if (fused_policy) {
+    // 6+7a. value heads, advantage weight, Gaussian NLL and the policy head's backward in one kernel   (sorl.py:96-111)
+    if ((rc = porl_policy_head_step(ctx, &calls[0], &calls[1], B, a->policy.params + a->log_std_offset, reg_target, ld_target,
+                                    w.target_v, a->alpha, a->awr_mode, b_norm, a->policy.grads,
+                                    a->policy.grads + a->log_std_offset, a->policy.loss, st)) != PORL_OK)
+      return rc;
+    calls[1].pad_ = PORL_MLP_HEAD_DONE;
+    if ((rc = porl_mlp_backward(ctx, &calls[1], B, nullptr, a->policy.grads, st)) != PORL_OK) return rc;
+    return group_step(ctx, a->policy, nullptr, 0.f, st);
+  }
   // 6. advantage weight, Gaussian NLL, dL/dmean (tanh' folded), dL/dlog_std   (por.py:99-106, sorl.py:103-109)
   if ((rc = porl_awr_gauss_nll(ctx, w.out_p, ldp, a->policy.params + a->log_std_offset, reg_target, ld_target, w.target_v,
                                w.out_v2, w.out_v2 + net, ldv, a->alpha, a->awr_mode, a->tanh_out, B, a->policy_out, b_norm,

@@ -337,3 +337,33 @@ def test_multi_phase_launches_are_bitwise_equal_to_one_launch_per_contraction(ki
     for k, v in outs[0][1].items():
         assert torch.equal(v, outs[1][1][k]), k
     assert outs[0][2] < outs[1][2]          # fewer launches with phases
+
+
+@pytest.mark.parametrize("S,H,B,mode", [(362, 512, 256, 1), (362, 512, 4096, 1), (30, 64, 48, 0)])
+def test_fused_policy_head_step_matches_three_launches(S, H, B, mode, monkeypatch):
+    """porl_policy_head_step (value heads + advantage-weighted Gaussian NLL + policy head backward in one kernel) against
+    head forward, porl_awr_gauss_nll and head backward as three launches (PORL_FUSED_POLICY_HEAD=0): the same formulas,
+    the batch reductions in a different order -- losses to 2e-6, parameters after three free-running SORL updates to fp32
+    summation-order noise, and two launches fewer per update."""
+    A = 2
+    rows = torch.from_numpy(synth.laser_rows(B * 3, S, 43, A)).to(DEV)
+    outs = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("PORL_FUSED_POLICY_HEAD", fused)
+        monkeypatch.setenv("PORL_UPDATE_GRAPH", "0")
+        agent, _ = make_agent("sorl", S, H, A, 1000, 0.8, 3.0, 5, gemm_mode=mode)
+        try:
+            before = agent.ctx.launches
+            losses = [step(agent, "sorl", slice_row(rows[i * B:(i + 1) * B], S, A)) for i in range(3)]
+            outs.append((losses, {k: v.clone() for k, v in agent.state_dict().items()}, agent.ctx.launches - before))
+        finally:
+            agent.ctx.set_gemm_mode(0)
+    assert outs[0][2] == outs[1][2] - 6, (outs[0][2], outs[1][2])          # 2 launches fewer per update
+    for lf, ls in zip(outs[0][0], outs[1][0]):
+        np.testing.assert_allclose(lf, ls, rtol=2e-6)
+    for k, v in outs[0][1].items():
+        w = outs[1][1][k]
+        if v.is_floating_point():
+            assert float((v - w).abs().max()) <= 2e-6 * float(w.abs().max()) + 2e-7, k      # 3 Adam steps of 1e-4
+        else:
+            assert torch.equal(v, w), k
