@@ -358,7 +358,14 @@ extern "C" int porl_adam_step(porl_ctx_t* ctx, float* p, const float* g, float* 
                  "porl_adam_step: buffers must be 16-byte aligned");
   PORL_CHECK_ARG(!(ema_beta > 0.f && hard_every > 0), "porl_adam_step: choose Polyak or hard target update");
   int64_t blocks = ((n >> 2) + 255) / 256;
-  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  // one wave: every block pays the clock read, a fence and a ticket, so a second wave of blocks costs more than a second
+  // trip of the grid-stride loop (the kernel holds 3 blocks of 72 registers per SM; measured with ncu: 2.03 waves at 901
+  // blocks, `barrier` and `membar` the top stalls)
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_kernel<false>, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  }
+  const int64_t cap = (int64_t)ctx->sm_count * per_sm - 1;      // - the publisher block
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   ProfScope prof(ctx, PORL_CAT_OPTIMIZER, (double)n * (target ? 36.0 : 28.0), as_stream(stream));
