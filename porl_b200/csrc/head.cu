@@ -349,10 +349,12 @@ __global__ void __launch_bounds__(256) vhead_fused_kernel(const __grid_constant_
     for (int wq = 0; wq < 8; ++wq) t += s_acc[(size_t)wq * 2 * W128 + i];
     part[i] = t;
   }
-  if (threadIdx.x < 2) {
+  if (threadIdx.x < 4) {                                       // [dv sum, loss, 0, 0]: the tree reads whole float4s
     float t = 0.f;
+    if (threadIdx.x < 2) {
 #pragma unroll
-    for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+      for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+    }
     part[2 * W128 + threadIdx.x] = t;
   }
   // Two-level, order-fixed reduction tree (fan-in kVhGroup): the last block of each group of kVhGroup consecutive row
@@ -378,15 +380,9 @@ __global__ void __launch_bounds__(256) vhead_fused_kernel(const __grid_constant_
     return last;
   };
   auto sum_partials = [&](const float* src, int n, float* dst, bool final_net) {
-    // element i of n consecutive partials, all n loads in flight, added in index order
-    for (int i = threadIdx.x; i < 2 * W128 + 2; i += 256) {
-      float vals[kVhGroup];
-#pragma unroll
-      for (int r = 0; r < kVhGroup; ++r) vals[r] = r < n ? __ldcg(src + (size_t)r * per_chunk + i) : 0.f;
-      float t = vals[0];
-#pragma unroll
-      for (int r = 1; r < kVhGroup; ++r)
-        if (r < n) t += vals[r];
+    // four consecutive elements of n partials per thread: all n 16-byte loads in flight at once (one round trip for the
+    // whole 4 KB vector; element by element it was five), each element added over the partials in index order
+    auto emit = [&](int i, float t) {
       if (!final_net) {
         dst[i] = t;
       } else if (i < W128) {
@@ -395,9 +391,20 @@ __global__ void __launch_bounds__(256) vhead_fused_kernel(const __grid_constant_
         if (i - W128 < a.H) a.db_prev[k][i - W128] = t;
       } else if (i == 2 * W128) {
         a.db[k][0] = t;
-      } else {
+      } else if (i == 2 * W128 + 1) {
         dst[i] = t;                                            // the net's loss sum, for the last net to add
       }
+    };
+    for (int i4 = threadIdx.x; i4 < (2 * W128 + 4) / 4; i4 += 256) {
+      float4 vals[kVhGroup];
+#pragma unroll
+      for (int r = 0; r < kVhGroup; ++r)
+        vals[r] = r < n ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)r * per_chunk) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 t = vals[0];
+#pragma unroll
+      for (int r = 1; r < kVhGroup; ++r)
+        if (r < n) { t.x += vals[r].x; t.y += vals[r].y; t.z += vals[r].z; t.w += vals[r].w; }
+      emit(4 * i4, t.x); emit(4 * i4 + 1, t.y); emit(4 * i4 + 2, t.z); emit(4 * i4 + 3, t.w);
     }
   };
   if (!last_of(tickets + 8 + k * 64 + grp, (uint32_t)(g1 - g0))) return;
@@ -564,10 +571,12 @@ __global__ void __launch_bounds__(256) phead_fused_kernel(const __grid_constant_
     for (int wq = 0; wq < 8; ++wq) t += s_acc[(size_t)wq * NV * W128 + i];
     part[i] = t;
   }
-  if (threadIdx.x < NS) {
+  if (threadIdx.x < 8) {                                       // NS scalars, the rest of the 8 slots zero (read as float4s)
     float t = 0.f;
+    if (threadIdx.x < NS) {
 #pragma unroll
-    for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+      for (int wq = 0; wq < 8; ++wq) t += s_scal[wq][threadIdx.x];
+    }
     part[NV * W128 + threadIdx.x] = t;
   }
   // two-level, order-fixed reduction tree over the row chunks (fan-in kVhGroup), as in vhead_fused_kernel
@@ -590,14 +599,8 @@ __global__ void __launch_bounds__(256) phead_fused_kernel(const __grid_constant_
     return last;
   };
   auto sum_partials = [&](const float* src, int n, float* dst, bool final) {
-    for (int i = threadIdx.x; i < NV * W128 + NS; i += 256) {
-      float vals[kVhGroup];
-#pragma unroll
-      for (int r = 0; r < kVhGroup; ++r) vals[r] = r < n ? __ldcg(src + (size_t)r * per_chunk + i) : 0.f;
-      float t = vals[0];
-#pragma unroll
-      for (int r = 1; r < kVhGroup; ++r)
-        if (r < n) t += vals[r];
+    auto emit = [&](int i, float t) {
+      if (i >= NV * W128 + NS) return;
       if (!final) {
         dst[i] = t;
       } else if (i < D * W128) {
@@ -618,6 +621,18 @@ __global__ void __launch_bounds__(256) phead_fused_kernel(const __grid_constant_
           if (!isfinite(l)) atomicOr(status, (uint32_t)PORL_FLAG_NONFINITE_LOSS);
         }
       }
+    };
+    // four consecutive elements of n partials per thread, all n 16-byte loads in flight (see vhead_fused_kernel)
+    for (int i4 = threadIdx.x; i4 < (int)(per_chunk / 4); i4 += 256) {
+      float4 vals[kVhGroup];
+#pragma unroll
+      for (int r = 0; r < kVhGroup; ++r)
+        vals[r] = r < n ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)r * per_chunk) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 t = vals[0];
+#pragma unroll
+      for (int r = 1; r < kVhGroup; ++r)
+        if (r < n) { t.x += vals[r].x; t.y += vals[r].y; t.z += vals[r].z; t.w += vals[r].w; }
+      emit(4 * i4, t.x); emit(4 * i4 + 1, t.y); emit(4 * i4 + 2, t.z); emit(4 * i4 + 3, t.w);
     }
   };
   if (!last_of(tickets + 256 + grp, (uint32_t)(g1 - g0))) return;
@@ -639,7 +654,7 @@ int launch_phead_fused(porl_ctx* ctx, const PHeadArgs& a, cudaStream_t st) {
   const int w128 = nj * 128;
   PORL_CHECK_ARG(a.ldw <= w128, "fused policy head: ldw=%d exceeds %d", a.ldw, w128);
   int R = (int)((a.B + 15) / 16);
-  int cap = nj == 8 ? ctx->sm_count : 2 * ctx->sm_count;
+  int cap = ctx->sm_count;                 // one block per SM is resident (156 registers): one wave
   if (cap > kVhGroup * kVhGroup) cap = kVhGroup * kVhGroup;
   if (R > cap) R = cap;
   if (R < 1) R = 1;
@@ -682,10 +697,11 @@ int launch_vhead_fused(porl_ctx* ctx, const VHeadArgs& a, cudaStream_t st) {
   const int nj = a.H <= 128 ? 1 : a.H <= 256 ? 2 : a.H <= 512 ? 4 : 8;
   const int w128 = nj * 128;
   PORL_CHECK_ARG(a.ldw <= w128, "fused value head: ldw=%d exceeds %d", a.ldw, w128);
-  // row chunks: at least 16 rows per block (2 per warp); about two blocks per SM and net at most (the H = 1024
-  // instantiation holds one block per SM: 182 registers, 76 KB of shared memory)
+  // row chunks: at least 16 rows per block, and ONE wave of blocks -- grid (R, 2 nets) against the kernel's residency
+  // (2 blocks per SM at H <= 512 by registers, 1 at H = 1024): a second wave repeats the weight staging and the rows'
+  // load latency (ncu: 1.73 waves, `long scoreboard` the top stall)
   int R = (int)((a.B + 15) / 16);
-  int cap = nj == 8 ? ctx->sm_count : 2 * ctx->sm_count;
+  int cap = nj == 8 ? ctx->sm_count / 2 : ctx->sm_count;
   if (cap > kVhGroup * kVhGroup) cap = kVhGroup * kVhGroup;        // two levels of the reduction tree
   if (R > cap) R = cap;
   if (R < 1) R = 1;

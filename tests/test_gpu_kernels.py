@@ -168,6 +168,14 @@ def test_gemm_tc_variants_bitwise_identical(env, M, N, K, kw):
             outs.append(_gemm(env, 1, 1, M, N, K, seed=5, **kw))
             assert ctx.tc_launches == before + 1
         assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+        # split-K: the last-arriver fix-up (PORL_TC_LAST_ARRIVER: one slice sums all partials) against the distributed one
+        os.environ["PORL_TC_LAST_ARRIVER"] = "1"
+        try:
+            for variant in (0, 1):
+                ctx.set_tc_variant(variant)
+                assert torch.equal(_gemm(env, 1, 1, M, N, K, seed=5, **kw), outs[0]), ("last arriver", variant)
+        finally:
+            del os.environ["PORL_TC_LAST_ARRIVER"]
         if not kw.get("transposed"):
             for a_k, b_k in ((1, 0), (0, 0), (0, 1)):
                 forms = []
