@@ -95,9 +95,14 @@ __global__ void __launch_bounds__(256) colsum_kernel(const __grid_constant__ Col
   __syncthreads();
   if (last_flag && warp == 0 && col < s.n) {
     __threadfence();
+    // all R <= 32 partials in flight at once (one round trip), added in row-chunk order
+    float vals[32];
+#pragma unroll
+    for (int r = 0; r < 32; ++r) vals[r] = r < R ? __ldcg(partials + ((size_t)blockIdx.z * R + r) * cb.max_n + col) : 0.f;
     float t = 0.f;
-#pragma unroll 8
-    for (int r = 0; r < R; ++r) t += __ldcg(partials + ((size_t)blockIdx.z * R + r) * cb.max_n + col);
+#pragma unroll
+    for (int r = 0; r < 32; ++r)
+      if (r < R) t += vals[r];
     s.out[col] = t;
   }
 }
