@@ -925,17 +925,26 @@ def run_b200(a):
             line["also"] = {"workload": workload_name(a.also_batch), "value": K * 4 / (ms2 * 1e-3), "unit": UNIT,
                             "ms_per_step": ms2 / (K * 4)}
 
-        # the literal sorl_train.py agent: FasterNet scan encoder in front of the heads (config 2b); eager launches
-        # (DropPath draws from torch's device generator every forward)
+        # the literal sorl_train.py agent: FasterNet scan encoder in front of the heads (config 2b).  Single process: the
+        # whole step (gather, two encoder forwards with their DropPath draws from torch's device generator, heads) is
+        # replayed as one CUDA graph; data parallel: eager (the encoder's BatchNorm sums go through a torch.distributed
+        # callback)
         if a.encoder_batch:
             Be = a.encoder_batch
             r3 = Runner(a, Be, device, rank, world, table, backbone=True)
+            enc_graph = use_graph and not dist_on
+            if enc_graph:
+                r3.run(r3.indices(2, 2008))           # eager calls allocate the workspaces
+                r3.capture()
             ms3, l3 = timed(r3, r3.indices(3, 2005), r3.indices(10, 2006), False)
             r3.agent.read_losses()                    # raises on device flags (scan range, NaN)
             flop = 3.449e9 * Be                       # 2 encoder forwards + heads, algorithmic
             line["also_encoder"] = {"workload": f"sorl_fasternet_S{S}_F256_H{H}_rows1M_b{Be}", "value": 10 / (ms3 * 1e-3),
                                     "unit": UNIT, "ms_per_step": ms3 / 10, "gpu_launches": l3,
-                                    "achieved_tflops": flop / (ms3 / 10 * 1e-3) * 1e-12, "graph": False}
+                                    "achieved_tflops": flop / (ms3 / 10 * 1e-3) * 1e-12, "graph": bool(enc_graph)}
+            if enc_graph:
+                line["also_encoder"]["gpu_launches"] = r3.launches_per_step * 10
+                r3.graph = None                       # the per-kernel table below needs eager launches
             ctx.profile(True)
             r3.run(r3.indices(2, 2007))
             torch.cuda.synchronize()

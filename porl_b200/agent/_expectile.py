@@ -238,9 +238,16 @@ class ExpectileAgent(nn.Module):
         self._value_step(pb, *self._head_inputs(pb))
 
     def _graphable(self) -> bool:
-        """The update may be replayed from a CUDA graph: MLP-only heads (the encoder's DropPath draws from torch's device
-        generator), no profiling, and no NCCL call inside the step (single process, or the peer-memory gradient sum)."""
-        if self.device.type != "cuda" or self.backbone is not None or os.environ.get("PORL_UPDATE_GRAPH", "1") == "0":
+        """The update may be replayed from a CUDA graph: no profiling, and no host-driven collective inside the step
+        (single process, or the peer-memory gradient sum).  With a scan encoder in front of the heads the step is
+        capturable in a single process: its DropPath factors come from torch's device generator, whose Philox offsets
+        torch.cuda.graph advances per replay; under data parallelism the encoder's BatchNorm sums go through a
+        torch.distributed callback, and a test that feeds recorded DropPath factors (`keep_queue`) consumes them on the
+        host -- both stay eager."""
+        if self.device.type != "cuda" or os.environ.get("PORL_UPDATE_GRAPH", "1") == "0":
+            return False
+        if self.backbone is not None and (pdist.is_dp() or self.backbone._cache.get("keep_queue") or
+                                          os.environ.get("PORL_ENCODER_GRAPH", "1") == "0"):
             return False
         if getattr(self.ctx, "profiling", False) or torch.cuda.is_current_stream_capturing():
             return False
