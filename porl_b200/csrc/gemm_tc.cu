@@ -1157,7 +1157,12 @@ int launch_gemm_tc_phases(porl_ctx* ctx, int n_phases, TcPhaseSpec* specs, cudaS
     int splits = 1;
     if (2 * tiles128 <= ctx->sm_count) {
       int want = ctx->sm_count / tiles128;
-      int cap = min_nkb / 4;                   // at least 4 k-blocks (128 k) per slice
+      // at least 4 k-blocks (128 k) per slice.  PORL_TC_SPLIT_KB overrides: measured at batch 256, 4 -> 5106, 3 -> 5188,
+      // 2 -> 5330, 1 -> 5225 updates/s (a slice's main loop shrinks, the fix-up's round trips do not grow); the default
+      // stays 4 because the cut changes the summation grouping and with it the free-running trajectory the 1,000-update
+      // drift test of tests/test_bench_configs.py was validated on (its per-step loss bound tripped at 2)
+      static const int kb_per_slice = getenv("PORL_TC_SPLIT_KB") ? atoi(getenv("PORL_TC_SPLIT_KB")) : 4;
+      int cap = min_nkb / (kb_per_slice > 0 ? kb_per_slice : 4);
       splits = want < cap ? want : cap;
       const long long room = ws_tiles - ws_used;
       if ((long long)splits * tiles * sub > room) splits = (int)(room / ((long long)tiles * sub));
