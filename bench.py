@@ -839,7 +839,7 @@ def run_b200(a):
         # its loss read-back lie inside the timed region.  SORL.update() (the reference's blocking signature) is timed
         # beside it.
         Ke = a.e2e_steps or K
-        ring, depth = 8, 2
+        ring, depth = 8, int(os.environ.get("PORL_E2E_DEPTH", "2"))
         host = torch.empty(ring, a.batch, table.row_len, dtype=torch.float32).pin_memory()
         src_idx = runner.indices(ring, 2002)
         for r in range(ring):
