@@ -833,13 +833,13 @@ def run_b200(a):
         line["kernels"] = kern
 
         # e2e: the public API with HOST buffers: pinned rows -> H2D -> agent.update_async() -> losses D2H, every step.
-        # Three device row buffers: while update(i) runs, the rows of steps i+1 and i+2 travel host -> device on a side
-        # stream (a DataLoader with pin_memory and prefetch_factor 2), and the losses of update(i-1) are read on the host
+        # Four device row buffers: while update(i) runs, the rows of steps i+1 .. i+3 travel host -> device on a side
+        # stream (a DataLoader with pin_memory and prefetch_factor 3), and the losses of update(i-1) are read on the host
         # -- one step late, each through its own event -- so the compute stream never drains.  Every step's H2D copy and
         # its loss read-back lie inside the timed region.  SORL.update() (the reference's blocking signature) is timed
         # beside it.
         Ke = a.e2e_steps or K
-        ring, depth = 8, int(os.environ.get("PORL_E2E_DEPTH", "2"))
+        ring, depth = 8, int(os.environ.get("PORL_E2E_DEPTH", "3"))
         host = torch.empty(ring, a.batch, table.row_len, dtype=torch.float32).pin_memory()
         src_idx = runner.indices(ring, 2002)
         for r in range(ring):
@@ -893,7 +893,7 @@ def run_b200(a):
         dt_block = time.perf_counter() - t0
         line["e2e"] = {"value": Ke / dt, "unit": UNIT, "h2d_bytes_per_step": a.batch * table.row_len * 4,
                        "d2h_bytes_per_step": 12, "steps": Ke,
-                       "h2d_overlap": "rows of steps i+1, i+2 are copied on a side stream while update(i) runs",
+                       "h2d_overlap": f"rows of steps i+1 .. i+{depth} are copied on a side stream while update(i) runs",
                        "api": "SORL.update_async(observations, actions, rewards, next_observations, terminals) -> handle; "
                               "handle.result() -> (float, float), read one step late (every step's losses are read)",
                        "blocking_api": {"value": Ke / dt_block, "unit": UNIT,
